@@ -1,0 +1,188 @@
+/*
+ * radiomedium_b200.h -- C-ABI of the B200-native radio medium (librmb200.so).
+ *
+ * This is the drop-in boundary for radio-sim's radio-medium hot path.  Every entry point
+ * names the reference interface it replaces (paths relative to the reference tree,
+ * radio-medium/java/se/sics/emul8/radiomedium/ unless a directory is given).
+ * Plain C: opaque handle, plain pointers and sizes, no exceptions, no torch types.
+ * The Java side binds these with Panama FFM (INTEGRATION.md shows the stub).
+ *
+ * Threading: a handle is serialised internally by one mutex (RadioMedium.transmit is called
+ * from any client reader thread: net/SimulatorJSONHandler.java:93).
+ * Ownership: inputs are caller-owned and copied before return.  Result pointers are
+ * handle-owned pinned host memory, valid until the next rmb_tick* / rmb_fetch / rmb_destroy.
+ * Errors: 0 or a negative rmb_status; text via rmb_last_error().  There is no CPU fallback:
+ * without a CUDA device rmb_create fails with RMB_ERR_NO_DEVICE.
+ */
+#ifndef RADIOMEDIUM_B200_H
+#define RADIOMEDIUM_B200_H
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RMB_ABI_VERSION 1
+
+typedef struct rmb_handle rmb_handle;
+
+enum rmb_status {
+    RMB_OK            =  0,
+    RMB_ERR_INVALID   = -1,   /* bad argument / bad index                               */
+    RMB_ERR_NO_DEVICE = -2,   /* no CUDA device (no CPU fallback exists)                */
+    RMB_ERR_CUDA      = -3,   /* CUDA runtime error, see rmb_last_error                 */
+    RMB_ERR_CAPACITY  = -4,   /* more heard pairs than max_pairs                        */
+    RMB_ERR_UNIFORMS  = -5,   /* uniform stream too short (missing draws read as 0.0)   */
+    RMB_ERR_STATE     = -6,   /* call order (e.g. tick before set_nodes)                */
+    RMB_ERR_UNSUPPORTED = -7
+};
+
+/* which RadioMedium implementation the handle behaves as */
+enum rmb_model {
+    RMB_MODEL_NULL          = 0,  /* NullRadioMedium.java:48-77                         */
+    RMB_MODEL_UDGM          = 1,  /* UDGMRadioMedium.java:63-116                        */
+    RMB_MODEL_UDGM_CONSTANT = 2,  /* UDGMConstantLossRadioMedium.java:16-36             */
+    RMB_MODEL_N2N           = 3,  /* N2NRadioMedium.java:24-72                          */
+    RMB_MODEL_SINR          = 4   /* new: log-distance + co-channel interference + SINR */
+};
+
+/* per (tx,rx) outcome == what the Java medium does with the pair:
+ * no call / generateReceptionEvents(..,false) / generateReceptionEvents(..,true)
+ * (Simulator.java:321-335, events/ReceptionEvent.java:12-16) */
+enum rmb_outcome { RMB_NOT_HEARD = 0, RMB_INTERFERED = 1, RMB_DELIVERED = 2 };
+
+enum rmb_flags {
+    RMB_FLAG_F64_VALUES = 1   /* also return rssi/sinr as double (exact-path values)    */
+};
+
+/* Replaces the fields/setters of the media (UDGMRadioMedium.java:17-61,
+ * UDGMConstantLossRadioMedium.java:8, AbstractRadioMedium.java:38) and the
+ * "configuration-set" parameters (net/SimulatorJSONHandler.java:170-216). */
+typedef struct rmb_config {
+    int32_t struct_size;          /* = sizeof(rmb_config), ABI check                     */
+    int32_t model;                /* rmb_model                                           */
+    int32_t device;               /* CUDA device ordinal                                 */
+    int32_t flags;                /* rmb_flags                                           */
+    double  success_ratio_tx;     /* 1.0  (never read by transmit(): reference quirk)    */
+    double  success_ratio_rx;     /* 1.0                                                 */
+    double  transmission_range;   /* 50.0                                                */
+    double  constant_range;       /* 100.0                                               */
+    double  pl0_db;               /* 40.05  path loss at d0                              */
+    double  pl_exponent;          /* 3.0                                                 */
+    double  d0_m;                 /* 1.0                                                 */
+    double  sensitivity_dbm;      /* -95.0                                               */
+    double  sinr_threshold_db;    /* 4.0                                                 */
+    double  noise_floor_dbm;      /* -100.0 == AbstractRadioMedium.baseRSSI              */
+    int64_t max_pairs;            /* cap on heard pairs per tick, 0 = default (64 Mi)    */
+    int32_t rx_base;              /* multi-GPU: global index of this shard's first node  */
+    int32_t n_shards;             /* multi-GPU: number of receiver shards (0/1 = unsharded) */
+} rmb_config;
+
+/* One active transmission as the device sees it (RadioPacket.java:46-52 plus the
+ * source's Position.java:37-39 and Transciever.txProbability).  48 bytes; this is the
+ * record that is all-gathered between GPUs. */
+typedef struct rmb_tx_record {
+    double  x, y, z;
+    double  power_dbm;
+    double  txprob;
+    int32_t channel;
+    int32_t src;                  /* global node index, -1 = padding (ignored)           */
+} rmb_tx_record;
+
+/* Result of one tick: the heard (tx,rx) pairs in the Java call order of
+ * generateReceptionEvents -- packets in arrival order, receivers in node-array order
+ * (UDGMRadioMedium.java:99-114). */
+typedef struct rmb_result {
+    int64_t  n_pairs;             /* heard pairs                                         */
+    int64_t  n_delivered;
+    int64_t  n_interfered;
+    uint64_t n_decisions;         /* filter-passing (tx,rx) pairs evaluated              */
+    int64_t  n_uniforms_used;
+    int64_t  n_recheck;           /* receivers that took the exact double path           */
+    int32_t  n_tx;
+    int32_t  near_slots;          /* internal per-receiver candidate capacity used       */
+    const int32_t *tx;            /* [n_pairs] index into this tick's packet list        */
+    const int32_t *rx;            /* [n_pairs] global node index ("neighbour index")     */
+    const float   *rssi_dbm;      /* [n_pairs] value for generateReceptionEvents         */
+    const float   *sinr_db;       /* [n_pairs] NaN for the reference media               */
+    const uint8_t *outcome;       /* [n_pairs] RMB_INTERFERED / RMB_DELIVERED            */
+    const double  *rssi_dbm_f64;  /* NULL unless RMB_FLAG_F64_VALUES                     */
+    const double  *sinr_db_f64;
+    const uint8_t *tx_failed;     /* [n_tx] UDGMRadioMedium.java:88-92 "interference"    */
+} rmb_result;
+
+/* device-side durations of the last tick, CUDA events on the handle's stream */
+typedef struct rmb_timing {
+    float ms_total;               /* first kernel .. last kernel (no host copies)        */
+    float ms_prepare;             /* tx record gather + channel bucketing                */
+    float ms_sweep;               /* the link-budget / decision sweep (dominant kernel)  */
+    float ms_resolve;             /* exact near-pair evaluation + guard-band recheck     */
+    float ms_emit;                /* compaction, ordering, stochastic rule, outputs      */
+    int32_t sweep_launches;
+    int32_t kernel_launches;      /* all kernels launched by the last tick               */
+} rmb_timing;
+
+int         rmb_version(void);
+void        rmb_config_default(rmb_config *cfg, int32_t model);
+/* Replaces `new XxxRadioMedium()` + Simulator.setRadioMedium (Simulator.java:234-239). */
+int         rmb_create(const rmb_config *cfg, rmb_handle **out);
+int         rmb_destroy(rmb_handle *h);
+const char *rmb_last_error(const rmb_handle *h);   /* h may be NULL: last create error  */
+
+/* Replaces Simulator.addNode + the node-config-set fields (Simulator.java:249-277,
+ * net/SimulatorJSONHandler.java:105-143): the whole node array, registration order.
+ * NULL arrays take the reference defaults: z=0, txpower=0, channel=26, enabled=1,
+ * rxprob=txprob=1 (Transciever.java:11-18), id_int = index+1 (Node.java:52-58). */
+int rmb_set_nodes(rmb_handle *h, int32_t n, const double *x, const double *y, const double *z,
+                  const double *txpower_dbm, const int32_t *channel, const uint8_t *enabled,
+                  const double *rxprob, const double *txprob, const int32_t *id_int);
+/* N2NRadioMedium.setN2NMatrix / matrix-data (N2NRadioMedium.java:20-22,
+ * net/SimulatorJSONHandler.java:183-206): flat row-major n x n. */
+int rmb_set_matrix(rmb_handle *h, int32_t n, const double *matrix);
+/* node-config-set "position" (net/SimulatorJSONHandler.java:111-122; Position.java:44-52):
+ * idx==NULL => dense replace of all `count`==n nodes; z==NULL => z=0 (Position.set(x,y)). */
+int rmb_update_positions(rmb_handle *h, int32_t count, const int32_t *idx,
+                         const double *x, const double *y, const double *z);
+/* node-config-set rf-power / wireless-channel / rx-loss / tx-loss / radio-state
+ * (net/SimulatorJSONHandler.java:123-143).  NULL field arrays are left unchanged. */
+int rmb_update_radio(rmb_handle *h, int32_t count, const int32_t *idx, const double *txpower_dbm,
+                     const int32_t *channel, const uint8_t *enabled,
+                     const double *rxprob, const double *txprob);
+
+/* Replaces the tick's RadioMedium.transmit(RadioPacket) calls (RadioMedium.java:41),
+ * batched: packet t = {source node index, power, channel} in arrival order.
+ * power_dbm / channel NULL => snapshot from the source radio (RadioPacket.java:49-50).
+ * uniforms stands in for simulator.getRandom().nextDouble() (Simulator.java:94), consumed
+ * in the Java draw order.  All sources must be local to this handle. */
+int rmb_tick(rmb_handle *h, int32_t n_tx, const int32_t *src, const double *power_dbm,
+             const int32_t *channel, const double *uniforms, size_t n_uniforms, rmb_result *out);
+
+/* Multi-GPU form of the same step (receivers sharded, tx records all-gathered):
+ * rmb_build_tx_records writes n_tx records to DEVICE memory d_records (src indices are
+ * global; entries whose source is not local get src=-1 unless take_all!=0);
+ * rmb_tick_records evaluates n_tx records (DEVICE pointer, src=-1 entries ignored but they
+ * keep their arrival index). */
+int rmb_build_tx_records(rmb_handle *h, int32_t n_tx, const int32_t *src, const double *power_dbm,
+                         const int32_t *channel, void *d_records);
+int rmb_tick_records(rmb_handle *h, int32_t n_tx, const void *d_records,
+                     const double *uniforms, size_t n_uniforms, rmb_result *out);
+/* Same computation on records already resident in HBM; results stay on the device
+ * (out gets counts only, pointers NULL).  rmb_fetch downloads the lists afterwards. */
+int rmb_tick_resident(rmb_handle *h, int32_t n_tx, const void *d_records, rmb_result *out);
+int rmb_fetch(rmb_handle *h, rmb_result *out);
+
+/* Replaces Transciever.getRSSI / RadioMedium.getBaseRSSI for the per-tick node-info
+ * (Transciever.java:52-61, net/JSONClientConnection.java:331-341): total in-band power
+ * of the last tick per local node [dBm] (noise floor when idle), and 1 if the node heard
+ * at least one frame. NULL outputs are skipped. */
+int rmb_node_info(rmb_handle *h, float *rssi_dbm, uint8_t *receiving);
+
+int rmb_last_timing(const rmb_handle *h, rmb_timing *out);
+/* tuning knob for benchmarks/tests: sweep variant (0 = auto) and near-slot capacity */
+int rmb_set_tuning(rmb_handle *h, int32_t sweep_variant, int32_t near_slots);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,749 @@
+// api.cu -- the C-ABI of include/radiomedium_b200.h: handle, HBM buffers, per-tick pipeline.
+//
+// No CPU fallback lives here: every evaluation is a CUDA kernel launch; without a device
+// rmb_create fails.  One mutex per handle; one stream per handle; the host blocks only where
+// it needs a count (list capacity) or the results.
+#include "common.cuh"
+#include "kernels.h"
+#include <algorithm>
+#include <cmath>
+#include <climits>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+using namespace rmb;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+template <class T> struct DevBuf {
+    T *p = nullptr; size_t cap = 0;
+    cudaError_t ensure(size_t need, bool zero = false) {
+        if (need <= cap) return cudaSuccess;
+        size_t ncap = std::max(need, cap + cap / 2);
+        if (p) { cudaFree(p); p = nullptr; cap = 0; }
+        cudaError_t e = cudaMalloc((void **)&p, std::max<size_t>(ncap, 1) * sizeof(T));
+        if (e != cudaSuccess) return e;
+        cap = ncap;
+        if (zero) return cudaMemset(p, 0, ncap * sizeof(T));
+        return cudaSuccess;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+template <class T> struct PinBuf {
+    T *p = nullptr; size_t cap = 0;
+    cudaError_t ensure(size_t need) {
+        if (need <= cap) return cudaSuccess;
+        size_t ncap = std::max(need, cap + cap / 2);
+        if (p) { cudaFreeHost(p); p = nullptr; cap = 0; }
+        cudaError_t e = cudaMallocHost((void **)&p, std::max<size_t>(ncap, 1) * sizeof(T));
+        if (e != cudaSuccess) return e;
+        cap = ncap;
+        return cudaSuccess;
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+};
+
+}  // namespace
+
+struct rmb_handle {
+    rmb_config cfg{};
+    std::mutex mu;
+    std::string err;
+    cudaStream_t st = nullptr;
+    cudaEvent_t ev[6] = {};
+    rmb_timing timing{};
+
+    // host mirrors of the radio state (work order + stochastic detection are host-built)
+    int n = 0;
+    std::vector<int> h_channel; std::vector<uint8_t> h_enabled;
+    std::vector<double> h_txpower, h_rxprob, h_txprob;
+    bool maybe_draws = false;
+    bool planar = true;
+
+    // device state
+    DevBuf<double> x, y, z, txpower, rxprob, txprob, matrix;
+    DevBuf<int> channel, id_int;
+    DevBuf<uint8_t> enabled;
+    int matrix_n = 0;
+    DevBuf<int> perm; DevBuf<float> fx, fy, fz;
+    int n_work = 0;
+    Groups groups{};
+    DevBuf<DevParams> dp; DevBuf<Geom> geom; DevBuf<unsigned long long> geom_scratch;
+    DevBuf<Counters> ctr; PinBuf<Counters> h_ctr;
+    DevBuf<float> node_rssi; DevBuf<uint8_t> node_recv;
+
+    // per tick: tx side
+    DevBuf<int> pk_src, pk_channel; DevBuf<double> pk_power; PinBuf<char> pk_stage;
+    DevBuf<rmb_tx_record> rec;
+    DevBuf<float4> txf; DevBuf<float> theta, theta_min_g; DevBuf<int> arrival, goff, gcount;
+    DevBuf<double> uniforms;
+
+    // slots
+    int K = 8;
+    DevBuf<int> slots, cnt, hcnt, hoff, recheck; DevBuf<float> far_sum;
+    DevBuf<double> sl_prx, sl_lin, sl_sinr, itot; DevBuf<uint8_t> sl_flags;
+
+    // pairs
+    DevBuf<unsigned long long> key, key_alt; DevBuf<unsigned> val, val_alt;
+    DevBuf<double> pr_p, pr_rssi, pr_sinr; DevBuf<uint8_t> pr_cand;
+    DevBuf<int> draw_scan, seg, scan_tmp, blkcnt; DevBuf<long long> tx_base; DevBuf<uint8_t> tx_failed;
+    DevBuf<char> cub_tmp;
+    DevBuf<int> o_tx, o_rx; DevBuf<float> o_rssi, o_sinr; DevBuf<uint8_t> o_outcome; DevBuf<double> o_rssi64, o_sinr64;
+    PinBuf<int> ho_tx, ho_rx; PinBuf<float> ho_rssi, ho_sinr; PinBuf<uint8_t> ho_outcome, ho_failed;
+    PinBuf<double> ho_rssi64, ho_sinr64;
+
+    // last tick
+    long long last_pairs = 0; int last_ntx = 0;
+    rmb_result last{};
+    int sweep_variant = 0;
+    bool have_nodes = false;
+
+    int fail(int code, const std::string &m) { err = m; return code; }
+    int cuda_fail(cudaError_t e, const char *where) {
+        err = std::string(where) + ": " + cudaGetErrorString(e);
+        cudaGetLastError();
+        return RMB_ERR_CUDA;
+    }
+};
+
+#define RMB_CK(h, expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) return (h)->cuda_fail(e__, #expr); } while (0)
+
+namespace {
+
+NodeArrays node_arrays(rmb_handle *h)
+{
+    NodeArrays a;
+    a.n = h->n; a.x = h->x.p; a.y = h->y.p; a.z = h->z.p; a.txpower = h->txpower.p; a.rxprob = h->rxprob.p;
+    a.txprob = h->txprob.p; a.channel = h->channel.p; a.enabled = h->enabled.p; a.id_int = h->id_int.p;
+    return a;
+}
+WorkArrays work_arrays(rmb_handle *h)
+{
+    WorkArrays w; w.n_work = h->n_work; w.perm = h->perm.p; w.fx = h->fx.p; w.fy = h->fy.p; w.fz = h->fz.p;
+    return w;
+}
+TxTiles tx_tiles(rmb_handle *h)
+{
+    TxTiles t; t.f = h->txf.p; t.arrival = h->arrival.p; t.goff = h->goff.p; t.gcount = h->gcount.p;
+    return t;
+}
+SlotArrays slot_arrays(rmb_handle *h)
+{
+    SlotArrays s; s.K = h->K; s.slots = h->slots.p; s.cnt = h->cnt.p; s.far_sum = h->far_sum.p; s.prx = h->sl_prx.p;
+    s.lin = h->sl_lin.p; s.sinr = h->sl_sinr.p; s.flags = h->sl_flags.p; s.hcnt = h->hcnt.p; s.itot = h->itot.p;
+    s.recheck = h->recheck.p;
+    return s;
+}
+PairArrays pair_arrays(rmb_handle *h)
+{
+    PairArrays p{};
+    p.cap = (long long)h->key.cap; p.key = h->key.p; p.key_alt = h->key_alt.p; p.val = h->val.p; p.val_alt = h->val_alt.p;
+    p.p = h->pr_p.p; p.rssi = h->pr_rssi.p; p.sinr = h->pr_sinr.p; p.cand = h->pr_cand.p; p.draw_scan = h->draw_scan.p;
+    p.seg = h->seg.p; p.tx_base = h->tx_base.p; p.tx_failed = h->tx_failed.p; p.scan_tmp = h->scan_tmp.p;
+    p.cub_tmp = h->cub_tmp.p; p.cub_tmp_bytes = h->cub_tmp.cap;
+    p.o_tx = h->o_tx.p; p.o_rx = h->o_rx.p; p.o_rssi = h->o_rssi.p; p.o_sinr = h->o_sinr.p; p.o_outcome = h->o_outcome.p;
+    p.o_rssi64 = (h->cfg.flags & RMB_FLAG_F64_VALUES) ? h->o_rssi64.p : nullptr;
+    p.o_sinr64 = (h->cfg.flags & RMB_FLAG_F64_VALUES) ? h->o_sinr64.p : nullptr;
+    int bits = 1;
+    while (bits < 31 && (1ll << bits) < (long long)h->cfg.rx_base + h->n + 1) ++bits;
+    p.key_shift = bits;
+    return p;
+}
+
+int bits_for(long long v) { int b = 1; while (b < 62 && (1ll << b) < v + 1) ++b; return b; }
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------
+// work order: enabled receivers grouped by channel (ascending), node order inside a group,
+// every group padded to 1024 so that a sweep block never straddles two channels
+// ------------------------------------------------------------------------------------------
+static int ensure_slots(rmb_handle *h)
+{
+    const size_t nw = (size_t)h->n_work, nk = nw * (size_t)h->K;
+    RMB_CK(h, h->slots.ensure(nk)); RMB_CK(h, h->sl_prx.ensure(nk)); RMB_CK(h, h->sl_lin.ensure(nk));
+    RMB_CK(h, h->sl_sinr.ensure(nk)); RMB_CK(h, h->sl_flags.ensure(nk));
+    RMB_CK(h, h->cnt.ensure(nw)); RMB_CK(h, h->hcnt.ensure(nw)); RMB_CK(h, h->hoff.ensure(nw + 2));
+    RMB_CK(h, h->recheck.ensure(nw)); RMB_CK(h, h->far_sum.ensure(nw)); RMB_CK(h, h->itot.ensure(nw));
+    RMB_CK(h, h->scan_tmp.ensure(nw / 1024 + 8));
+    return RMB_OK;
+}
+
+static int build_work_order(rmb_handle *h)
+{
+    const int n = h->n;
+    std::vector<int> chans;
+    for (int i = 0; i < n; ++i) if (h->h_enabled[i]) chans.push_back(h->h_channel[i]);
+    std::sort(chans.begin(), chans.end());
+    chans.erase(std::unique(chans.begin(), chans.end()), chans.end());
+    if ((int)chans.size() > kMaxGroups)
+        return h->fail(RMB_ERR_UNSUPPORTED, "more than 64 distinct receiver channels");
+    Groups g{};
+    g.ngroups = (int)chans.size();
+    std::vector<int> count(g.ngroups, 0);
+    std::vector<int> gid(n, -1);
+    for (int i = 0; i < n; ++i) if (h->h_enabled[i]) {
+        int k = (int)(std::lower_bound(chans.begin(), chans.end(), h->h_channel[i]) - chans.begin());
+        gid[i] = k; ++count[k];
+    }
+    int w = 0;
+    for (int k = 0; k < g.ngroups; ++k) {
+        g.channel[k] = chans[k]; g.n_rx[k] = count[k]; g.w_begin[k] = w;
+        w += (count[k] + 1023) / 1024 * 1024;
+    }
+    g.w_begin[g.ngroups] = w;
+    for (int k = g.ngroups + 1; k <= kMaxGroups; ++k) g.w_begin[k] = w;
+    std::vector<int> perm((size_t)std::max(w, 1), -1), cur(g.w_begin, g.w_begin + g.ngroups);
+    for (int i = 0; i < n; ++i) if (gid[i] >= 0) perm[cur[gid[i]]++] = i;
+    h->groups = g;
+    h->n_work = w;
+    RMB_CK(h, h->perm.ensure(std::max(w, 1))); RMB_CK(h, h->fx.ensure(w)); RMB_CK(h, h->fy.ensure(w)); RMB_CK(h, h->fz.ensure(w));
+    RMB_CK(h, cudaMemcpyAsync(h->perm.p, perm.data(), perm.size() * sizeof(int), cudaMemcpyHostToDevice, h->st));
+    RMB_CK(h, cudaStreamSynchronize(h->st));      // perm is a stack-lifetime vector
+    int rc = ensure_slots(h);
+    if (rc) return rc;
+    // idle nodes report the noise floor (AbstractRadioMedium.java:38,45-52)
+    std::vector<float> idle((size_t)std::max(n, 1), (float)h->cfg.noise_floor_dbm);
+    RMB_CK(h, h->node_rssi.ensure(std::max(n, 1))); RMB_CK(h, h->node_recv.ensure(std::max(n, 1)));
+    RMB_CK(h, cudaMemcpy(h->node_rssi.p, idle.data(), idle.size() * sizeof(float), cudaMemcpyHostToDevice));
+    RMB_CK(h, cudaMemset(h->node_recv.p, 0, std::max(n, 1)));
+    return RMB_OK;
+}
+
+static void update_draw_flag(rmb_handle *h)
+{
+    bool d = false;
+    const int m = h->cfg.model;
+    if (m == RMB_MODEL_N2N) d = true;
+    if (m == RMB_MODEL_UDGM && h->cfg.success_ratio_rx < 1.0) d = true;
+    if (m == RMB_MODEL_UDGM || m == RMB_MODEL_SINR || m == RMB_MODEL_N2N)
+        for (int i = 0; i < h->n && !d; ++i) if (h->h_rxprob[i] < 1.0 || h->h_txprob[i] < 1.0) d = true;
+    h->maybe_draws = d;
+}
+
+// bounding box -> centre / planarity, then the fp32 work-order copy
+static int refresh_geometry(rmb_handle *h)
+{
+    NodeArrays nd = node_arrays(h);
+    RMB_CK(h, launch_geom(nd, h->geom_scratch.p, h->geom.p, h->st));
+    Geom g;
+    RMB_CK(h, cudaMemcpyAsync(&g, h->geom.p, sizeof(Geom), cudaMemcpyDeviceToHost, h->st));
+    RMB_CK(h, launch_regather(nd, work_arrays(h), h->geom.p, h->st));
+    RMB_CK(h, cudaStreamSynchronize(h->st));
+    h->planar = g.planar != 0;
+    return RMB_OK;
+}
+
+template <class T>
+static cudaError_t upload(DevBuf<T> &dst, const T *src, T dflt, int n, std::vector<T> *mirror)
+{
+    cudaError_t e = dst.ensure(std::max(n, 1));
+    if (e != cudaSuccess) return e;
+    std::vector<T> tmp;
+    const T *from = src;
+    if (!src) { tmp.assign((size_t)n, dflt); from = tmp.data(); }
+    if (mirror) mirror->assign(from, from + n);
+    if (n > 0) return cudaMemcpy(dst.p, from, (size_t)n * sizeof(T), cudaMemcpyHostToDevice);
+    return cudaSuccess;
+}
+
+extern "C" {
+
+int rmb_version(void) { return RMB_ABI_VERSION; }
+
+void rmb_config_default(rmb_config *cfg, int32_t model)
+{
+    if (!cfg) return;
+    memset(cfg, 0, sizeof(*cfg));
+    cfg->struct_size = (int32_t)sizeof(rmb_config);
+    cfg->model = model;
+    cfg->success_ratio_tx = 1.0;      // UDGMRadioMedium.java:17
+    cfg->success_ratio_rx = 1.0;      // UDGMRadioMedium.java:18
+    cfg->transmission_range = 50.0;   // UDGMRadioMedium.java:23
+    cfg->constant_range = 100.0;      // UDGMConstantLossRadioMedium.java:8
+    cfg->pl0_db = 40.05; cfg->pl_exponent = 3.0; cfg->d0_m = 1.0;
+    cfg->sensitivity_dbm = -95.0; cfg->sinr_threshold_db = 4.0;
+    cfg->noise_floor_dbm = -100.0;    // AbstractRadioMedium.java:38
+}
+
+const char *rmb_last_error(const rmb_handle *h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+
+int rmb_create(const rmb_config *cfg, rmb_handle **out)
+{
+    if (!cfg || !out) { g_create_error = "null argument"; return RMB_ERR_INVALID; }
+    *out = nullptr;
+    if (cfg->struct_size != (int32_t)sizeof(rmb_config)) { g_create_error = "rmb_config.struct_size mismatch"; return RMB_ERR_INVALID; }
+    if (cfg->model < RMB_MODEL_NULL || cfg->model > RMB_MODEL_SINR) { g_create_error = "unknown model"; return RMB_ERR_INVALID; }
+    if (cfg->model == RMB_MODEL_SINR && !(cfg->pl_exponent > 0.0 && cfg->d0_m > 0.0)) { g_create_error = "pl_exponent and d0_m must be > 0"; return RMB_ERR_INVALID; }
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev <= 0) {
+        cudaGetLastError();
+        g_create_error = "no CUDA device available (this medium has no CPU fallback)";
+        return RMB_ERR_NO_DEVICE;
+    }
+    if (cfg->device < 0 || cfg->device >= ndev) { g_create_error = "device ordinal out of range"; return RMB_ERR_INVALID; }
+    rmb_handle *h = new rmb_handle();
+    h->cfg = *cfg;
+    if (h->cfg.max_pairs <= 0) h->cfg.max_pairs = 64ll << 20;
+    auto bail = [&](cudaError_t ce, const char *w) { g_create_error = std::string(w) + ": " + cudaGetErrorString(ce); delete h; return RMB_ERR_CUDA; };
+    if ((e = cudaSetDevice(cfg->device)) != cudaSuccess) return bail(e, "cudaSetDevice");
+    if ((e = cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+    for (auto &ev : h->ev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) return bail(e, "cudaEventCreate");
+    if ((e = h->dp.ensure(1)) != cudaSuccess || (e = h->geom.ensure(1)) != cudaSuccess ||
+        (e = h->geom_scratch.ensure(8)) != cudaSuccess || (e = h->ctr.ensure(1)) != cudaSuccess ||
+        (e = h->h_ctr.ensure(1)) != cudaSuccess || (e = h->theta_min_g.ensure(kMaxGroups)) != cudaSuccess ||
+        (e = h->goff.ensure(kMaxGroups + 1)) != cudaSuccess || (e = h->gcount.ensure(kMaxGroups)) != cudaSuccess)
+        return bail(e, "cudaMalloc");
+    DevParams dp{};
+    dp.model = cfg->model; dp.success_ratio_rx = cfg->success_ratio_rx; dp.transmission_range = cfg->transmission_range;
+    dp.constant_range = cfg->constant_range; dp.pl0_db = cfg->pl0_db; dp.pl_exponent = cfg->pl_exponent; dp.d0_m = cfg->d0_m;
+    dp.sensitivity_dbm = cfg->sensitivity_dbm; dp.sinr_threshold_db = cfg->sinr_threshold_db;
+    dp.noise_floor_dbm = cfg->noise_floor_dbm; dp.rx_base = cfg->rx_base;
+    if ((e = cudaMemcpy(h->dp.p, &dp, sizeof(dp), cudaMemcpyHostToDevice)) != cudaSuccess) return bail(e, "cudaMemcpy");
+    if ((e = launch_init_params(h->dp.p, h->st)) != cudaSuccess) return bail(e, "init_params");
+    if ((e = cudaStreamSynchronize(h->st)) != cudaSuccess) return bail(e, "init_params sync");
+    *out = h;
+    return RMB_OK;
+}
+
+int rmb_destroy(rmb_handle *h)
+{
+    if (!h) return RMB_ERR_INVALID;
+    cudaSetDevice(h->cfg.device);
+    cudaStreamSynchronize(h->st);
+    // DevBuf/PinBuf have no destructors on purpose (explicit lifetime): free through cudaDeviceReset-safe calls
+    h->x.release(); h->y.release(); h->z.release(); h->txpower.release(); h->rxprob.release(); h->txprob.release();
+    h->matrix.release(); h->channel.release(); h->id_int.release(); h->enabled.release(); h->perm.release();
+    h->fx.release(); h->fy.release(); h->fz.release(); h->dp.release(); h->geom.release(); h->geom_scratch.release();
+    h->ctr.release(); h->h_ctr.release(); h->node_rssi.release(); h->node_recv.release(); h->pk_src.release();
+    h->pk_channel.release(); h->pk_power.release(); h->pk_stage.release(); h->rec.release(); h->txf.release();
+    h->theta.release(); h->theta_min_g.release(); h->arrival.release(); h->goff.release(); h->gcount.release();
+    h->uniforms.release(); h->slots.release(); h->cnt.release(); h->hcnt.release(); h->hoff.release();
+    h->recheck.release(); h->far_sum.release(); h->sl_prx.release(); h->sl_lin.release(); h->sl_sinr.release();
+    h->itot.release(); h->sl_flags.release(); h->key.release(); h->key_alt.release(); h->val.release();
+    h->val_alt.release(); h->pr_p.release(); h->pr_rssi.release(); h->pr_sinr.release(); h->pr_cand.release();
+    h->draw_scan.release(); h->seg.release(); h->scan_tmp.release(); h->blkcnt.release(); h->tx_base.release();
+    h->tx_failed.release(); h->cub_tmp.release(); h->o_tx.release(); h->o_rx.release(); h->o_rssi.release();
+    h->o_sinr.release(); h->o_outcome.release(); h->o_rssi64.release(); h->o_sinr64.release(); h->ho_tx.release();
+    h->ho_rx.release(); h->ho_rssi.release(); h->ho_sinr.release(); h->ho_outcome.release(); h->ho_failed.release();
+    h->ho_rssi64.release(); h->ho_sinr64.release();
+    for (auto &ev : h->ev) if (ev) cudaEventDestroy(ev);
+    if (h->st) cudaStreamDestroy(h->st);
+    delete h;
+    return RMB_OK;
+}
+
+int rmb_set_nodes(rmb_handle *h, int32_t n, const double *x, const double *y, const double *z,
+                  const double *txpower_dbm, const int32_t *channel, const uint8_t *enabled,
+                  const double *rxprob, const double *txprob, const int32_t *id_int)
+{
+    if (!h) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (n < 0 || (n > 0 && (!x || !y))) return h->fail(RMB_ERR_INVALID, "rmb_set_nodes: n < 0 or missing x/y");
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    h->n = n;
+    RMB_CK(h, upload<double>(h->x, x, 0.0, n, nullptr));
+    RMB_CK(h, upload<double>(h->y, y, 0.0, n, nullptr));
+    RMB_CK(h, upload<double>(h->z, z, 0.0, n, nullptr));
+    RMB_CK(h, upload<double>(h->txpower, txpower_dbm, 0.0, n, &h->h_txpower));
+    RMB_CK(h, upload<int>(h->channel, channel, 26, n, &h->h_channel));          // Transciever.java:12
+    RMB_CK(h, upload<uint8_t>(h->enabled, enabled, (uint8_t)1, n, &h->h_enabled));
+    RMB_CK(h, upload<double>(h->rxprob, rxprob, 1.0, n, &h->h_rxprob));         // Transciever.java:17-18
+    RMB_CK(h, upload<double>(h->txprob, txprob, 1.0, n, &h->h_txprob));
+    std::vector<int> ids;
+    if (!id_int) { ids.resize(n); for (int i = 0; i < n; ++i) ids[i] = h->cfg.rx_base + i + 1; }
+    RMB_CK(h, upload<int>(h->id_int, id_int ? id_int : ids.data(), 0, n, nullptr));
+    for (auto &e : h->h_enabled) e = e ? 1 : 0;
+    int rc = build_work_order(h);
+    if (rc) return rc;
+    update_draw_flag(h);
+    rc = refresh_geometry(h);
+    if (rc) return rc;
+    h->have_nodes = true;
+    return RMB_OK;
+}
+
+int rmb_set_matrix(rmb_handle *h, int32_t n, const double *matrix)
+{
+    if (!h) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (n < 0 || (n > 0 && !matrix)) return h->fail(RMB_ERR_INVALID, "rmb_set_matrix: bad arguments");
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    RMB_CK(h, h->matrix.ensure(std::max<size_t>((size_t)n * n, 1)));
+    if (n > 0) RMB_CK(h, cudaMemcpy(h->matrix.p, matrix, (size_t)n * n * sizeof(double), cudaMemcpyHostToDevice));
+    h->matrix_n = n;
+    return RMB_OK;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------
+// K4 entry points
+// ------------------------------------------------------------------------------------------
+extern "C" int rmb_update_positions(rmb_handle *h, int32_t count, const int32_t *idx,
+                                    const double *x, const double *y, const double *z)
+{
+    if (!h) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (!h->have_nodes) return h->fail(RMB_ERR_STATE, "rmb_update_positions before rmb_set_nodes");
+    if (count < 0 || (count > 0 && (!x || !y))) return h->fail(RMB_ERR_INVALID, "rmb_update_positions: bad arguments");
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    if (count == 0) return RMB_OK;
+    if (!idx) {
+        if (count != h->n) return h->fail(RMB_ERR_INVALID, "dense position update needs count == n");
+        const size_t b = (size_t)count * sizeof(double);
+        RMB_CK(h, cudaMemcpyAsync(h->x.p, x, b, cudaMemcpyHostToDevice, h->st));
+        RMB_CK(h, cudaMemcpyAsync(h->y.p, y, b, cudaMemcpyHostToDevice, h->st));
+        if (z) RMB_CK(h, cudaMemcpyAsync(h->z.p, z, b, cudaMemcpyHostToDevice, h->st));
+        else   RMB_CK(h, cudaMemsetAsync(h->z.p, 0, b, h->st));       // Position.set(x, y) zeroes z (Position.java:44-46)
+    } else {
+        for (int i = 0; i < count; ++i)
+            if (idx[i] < 0 || idx[i] >= h->n) return h->fail(RMB_ERR_INVALID, "rmb_update_positions: node index out of range");
+        // staging: idx | x | y | z in the packet staging buffers (reused; ticks are serialised by the mutex)
+        RMB_CK(h, h->pk_src.ensure(count)); RMB_CK(h, h->uniforms.ensure((size_t)count * 3));
+        RMB_CK(h, cudaMemcpyAsync(h->pk_src.p, idx, (size_t)count * sizeof(int), cudaMemcpyHostToDevice, h->st));
+        const size_t b = (size_t)count * sizeof(double);
+        double *dx = h->uniforms.p, *dy = dx + count, *dz = dy + count;
+        RMB_CK(h, cudaMemcpyAsync(dx, x, b, cudaMemcpyHostToDevice, h->st));
+        RMB_CK(h, cudaMemcpyAsync(dy, y, b, cudaMemcpyHostToDevice, h->st));
+        if (z) RMB_CK(h, cudaMemcpyAsync(dz, z, b, cudaMemcpyHostToDevice, h->st));
+        RMB_CK(h, launch_scatter_positions(node_arrays(h), count, h->pk_src.p, dx, dy, z ? dz : nullptr, h->st));
+    }
+    return refresh_geometry(h);
+}
+
+extern "C" int rmb_update_radio(rmb_handle *h, int32_t count, const int32_t *idx, const double *txpower_dbm,
+                                const int32_t *channel, const uint8_t *enabled, const double *rxprob, const double *txprob)
+{
+    if (!h) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (!h->have_nodes) return h->fail(RMB_ERR_STATE, "rmb_update_radio before rmb_set_nodes");
+    if (count < 0) return h->fail(RMB_ERR_INVALID, "rmb_update_radio: count < 0");
+    if (!idx && count != h->n && count != 0) return h->fail(RMB_ERR_INVALID, "dense radio update needs count == n");
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    for (int i = 0; i < count; ++i) {
+        const int p = idx ? idx[i] : i;
+        if (p < 0 || p >= h->n) return h->fail(RMB_ERR_INVALID, "rmb_update_radio: node index out of range");
+    }
+    bool regroup = false;
+    for (int i = 0; i < count; ++i) {
+        const int p = idx ? idx[i] : i;
+        if (txpower_dbm) h->h_txpower[p] = txpower_dbm[i];
+        if (rxprob) h->h_rxprob[p] = rxprob[i];
+        if (txprob) h->h_txprob[p] = txprob[i];
+        if (channel && h->h_channel[p] != channel[i]) { h->h_channel[p] = channel[i]; regroup = true; }
+        if (enabled && h->h_enabled[p] != (enabled[i] ? 1 : 0)) { h->h_enabled[p] = enabled[i] ? 1 : 0; regroup = true; }
+    }
+    const size_t n = (size_t)h->n;
+    if (txpower_dbm) RMB_CK(h, cudaMemcpy(h->txpower.p, h->h_txpower.data(), n * sizeof(double), cudaMemcpyHostToDevice));
+    if (rxprob) RMB_CK(h, cudaMemcpy(h->rxprob.p, h->h_rxprob.data(), n * sizeof(double), cudaMemcpyHostToDevice));
+    if (txprob) RMB_CK(h, cudaMemcpy(h->txprob.p, h->h_txprob.data(), n * sizeof(double), cudaMemcpyHostToDevice));
+    if (channel) RMB_CK(h, cudaMemcpy(h->channel.p, h->h_channel.data(), n * sizeof(int), cudaMemcpyHostToDevice));
+    if (enabled) RMB_CK(h, cudaMemcpy(h->enabled.p, h->h_enabled.data(), n, cudaMemcpyHostToDevice));
+    update_draw_flag(h);
+    if (regroup) {
+        int rc = build_work_order(h);
+        if (rc) return rc;
+        return refresh_geometry(h);
+    }
+    return RMB_OK;
+}
+
+extern "C" int rmb_set_tuning(rmb_handle *h, int32_t sweep_variant, int32_t near_slots)
+{
+    if (!h) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    h->sweep_variant = sweep_variant;
+    if (near_slots > 0 && near_slots != h->K) { h->K = near_slots; return ensure_slots(h); }
+    return RMB_OK;
+}
+
+extern "C" int rmb_node_info(rmb_handle *h, float *rssi_dbm, uint8_t *receiving)
+{
+    if (!h) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (!h->have_nodes) return h->fail(RMB_ERR_STATE, "rmb_node_info before rmb_set_nodes");
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    RMB_CK(h, cudaStreamSynchronize(h->st));
+    if (rssi_dbm && h->n) RMB_CK(h, cudaMemcpy(rssi_dbm, h->node_rssi.p, (size_t)h->n * sizeof(float), cudaMemcpyDeviceToHost));
+    if (receiving && h->n) RMB_CK(h, cudaMemcpy(receiving, h->node_recv.p, (size_t)h->n, cudaMemcpyDeviceToHost));
+    return RMB_OK;
+}
+
+extern "C" int rmb_last_timing(const rmb_handle *h, rmb_timing *out)
+{
+    if (!h || !out) return RMB_ERR_INVALID;
+    *out = h->timing;
+    return RMB_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// the tick
+// ------------------------------------------------------------------------------------------
+static int ensure_pairs(rmb_handle *h, long long m)
+{
+    if (m > h->cfg.max_pairs) {
+        char b[160]; snprintf(b, sizeof b, "tick produced %lld heard pairs, max_pairs is %lld", m, (long long)h->cfg.max_pairs);
+        return h->fail(RMB_ERR_CAPACITY, b);
+    }
+    const size_t c = (size_t)std::max<long long>(m, 1);
+    RMB_CK(h, h->key.ensure(c));
+    const size_t cap = h->key.cap;       // grow all pair arrays to the same capacity
+    RMB_CK(h, h->pr_p.ensure(cap)); RMB_CK(h, h->pr_rssi.ensure(cap)); RMB_CK(h, h->pr_sinr.ensure(cap));
+    RMB_CK(h, h->pr_cand.ensure(cap)); RMB_CK(h, h->draw_scan.ensure(cap + 2));
+    RMB_CK(h, h->o_tx.ensure(cap)); RMB_CK(h, h->o_rx.ensure(cap)); RMB_CK(h, h->o_rssi.ensure(cap));
+    RMB_CK(h, h->o_sinr.ensure(cap)); RMB_CK(h, h->o_outcome.ensure(cap));
+    if (h->cfg.flags & RMB_FLAG_F64_VALUES) { RMB_CK(h, h->o_rssi64.ensure(cap)); RMB_CK(h, h->o_sinr64.ensure(cap)); }
+    RMB_CK(h, h->scan_tmp.ensure(cap / 1024 + 8));
+    if (h->cfg.model == RMB_MODEL_SINR) {
+        RMB_CK(h, h->key_alt.ensure(cap)); RMB_CK(h, h->val.ensure(cap)); RMB_CK(h, h->val_alt.ensure(cap));
+        RMB_CK(h, h->cub_tmp.ensure(sort_pairs_tmp_bytes((long long)cap)));
+    }
+    return RMB_OK;
+}
+
+static int read_counters(rmb_handle *h)
+{
+    RMB_CK(h, cudaMemcpyAsync(h->h_ctr.p, h->ctr.p, sizeof(Counters), cudaMemcpyDeviceToHost, h->st));
+    RMB_CK(h, cudaStreamSynchronize(h->st));
+    return RMB_OK;
+}
+
+// d_rec: n_tx records in device memory.  Leaves the result lists on the device.
+static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const double *uniforms, size_t n_uniforms)
+{
+    int rc;
+    int launches = 0, sweeps = 0;
+    const NodeArrays nd = node_arrays(h);
+    const WorkArrays wk = work_arrays(h);
+    const bool draws = h->maybe_draws;
+    if (draws && h->cfg.n_shards > 1)
+        return h->fail(RMB_ERR_UNSUPPORTED, "stochastic reception (rx/tx probability < 1) is not supported on a sharded handle");
+    RMB_CK(h, h->seg.ensure((size_t)n_tx + 2)); RMB_CK(h, h->tx_base.ensure((size_t)n_tx + 1));
+    RMB_CK(h, h->tx_failed.ensure((size_t)n_tx + 1));
+    long long nu = 0;
+    if (draws && uniforms && n_uniforms) {
+        RMB_CK(h, h->uniforms.ensure(n_uniforms));
+        RMB_CK(h, cudaMemcpyAsync(h->uniforms.p, uniforms, n_uniforms * sizeof(double), cudaMemcpyHostToDevice, h->st));
+        nu = (long long)n_uniforms;
+    } else {
+        RMB_CK(h, h->uniforms.ensure(1));
+    }
+    RMB_CK(h, cudaMemsetAsync(h->ctr.p, 0, sizeof(Counters), h->st));
+    RMB_CK(h, cudaEventRecord(h->ev[0], h->st));
+    long long m = 0;
+    if (h->cfg.model == RMB_MODEL_SINR) {
+        const size_t tcap = (size_t)n_tx + (size_t)(h->groups.ngroups + 1) * kTile;
+        RMB_CK(h, h->txf.ensure(tcap)); RMB_CK(h, h->theta.ensure(tcap)); RMB_CK(h, h->arrival.ensure(tcap));
+        TxTiles tx = tx_tiles(h);
+        RMB_CK(h, launch_prepare(nd, h->dp.p, h->geom.p, h->groups, n_tx, d_rec, tx, h->theta.p, h->theta_min_g.p, h->ctr.p, h->st));
+        ++launches;
+        RMB_CK(h, cudaEventRecord(h->ev[1], h->st));
+        for (int attempt = 0;; ++attempt) {
+            SweepArgs a;
+            a.fx = h->fx.p; a.fy = h->fy.p; a.fz = h->fz.p; a.groups = h->groups; a.tx = tx; a.theta = h->theta.p;
+            a.theta_min_g = h->theta_min_g.p; a.neg_h = (float)(-0.5 * h->cfg.pl_exponent);
+            a.far_out = h->far_sum.p; a.cnt_out = h->cnt.p; a.slots = h->slots.p; a.K = h->K; a.ctr = h->ctr.p;
+            if (attempt) RMB_CK(h, cudaEventRecord(h->ev[1], h->st));
+            RMB_CK(h, launch_sweep(sweep_mode_for_exponent(h->cfg.pl_exponent), h->planar, h->sweep_variant, h->n_work, a, h->st));
+            ++launches; ++sweeps;
+            RMB_CK(h, cudaEventRecord(h->ev[2], h->st));
+            RMB_CK(h, launch_resolve(nd, wk, h->dp.p, tx, d_rec, slot_arrays(h), h->node_rssi.p, h->node_recv.p, h->ctr.p, h->st));
+            ++launches;
+            if ((rc = read_counters(h))) return rc;
+            if (h->h_ctr.p->max_near <= h->K) break;
+            // a receiver had more near candidates than slots: grow and redo the sweep (deterministic)
+            int k = h->K;
+            while (k < h->h_ctr.p->max_near) k *= 2;
+            if ((double)k * h->n_work > 3.0e9 || attempt > 4)
+                return h->fail(RMB_ERR_CAPACITY, "too many near candidates per receiver (dense all-hear-all tick)");
+            h->K = k;
+            if ((rc = ensure_slots(h))) return rc;
+            Counters keep = *h->h_ctr.p;
+            keep.heard = 0; keep.max_near = 0; keep.n_recheck = 0;
+            RMB_CK(h, cudaMemcpyAsync(h->ctr.p, &keep, sizeof(keep), cudaMemcpyHostToDevice, h->st));
+            RMB_CK(h, cudaStreamSynchronize(h->st));
+        }
+        m = (long long)h->h_ctr.p->heard;
+        if ((rc = ensure_pairs(h, m))) return rc;
+        SlotArrays sl = slot_arrays(h);
+        const int nre = h->h_ctr.p->n_recheck;
+        if (nre > 0) { RMB_CK(h, launch_recheck(nd, wk, h->dp.p, h->groups, tx, d_rec, sl, nre, h->node_rssi.p, h->st)); ++launches; }
+        RMB_CK(h, cudaEventRecord(h->ev[3], h->st));
+        if (m > 0) {
+            PairArrays pa = pair_arrays(h);
+            RMB_CK(h, launch_exclusive_scan(h->hcnt.p, h->hoff.p, h->n_work, h->scan_tmp.p, nullptr, h->st)); launches += 3;
+            RMB_CK(h, launch_scatter_pairs(wk, h->dp.p, tx, sl, h->hoff.p, pa, h->st)); ++launches;
+            RMB_CK(h, launch_sort_pairs(pa, m, pa.key_shift + bits_for(n_tx), h->st)); launches += 6;
+            // the sort may have swapped the double buffers
+            if (pa.key != h->key.p) std::swap(h->key, h->key_alt);
+            if (pa.val != h->val.p) std::swap(h->val, h->val_alt);
+            pa = pair_arrays(h);
+            RMB_CK(h, launch_gather_sorted(nd, h->dp.p, sl, pa, m, h->st)); ++launches;
+        }
+    } else {
+        const int nblk = refmedia_blocks_per_tx(h->n);
+        const size_t nb = (size_t)nblk * (size_t)n_tx;
+        if (nb > 0x7fffffffull) return h->fail(RMB_ERR_CAPACITY, "n_tx * n too large for the reference-media path");
+        RMB_CK(h, h->blkcnt.ensure(nb + 2)); RMB_CK(h, h->scan_tmp.ensure(nb / 1024 + 8));
+        RMB_CK(h, cudaMemsetAsync(h->node_recv.p, 0, std::max(h->n, 1), h->st));
+        RMB_CK(h, cudaEventRecord(h->ev[1], h->st));
+        RMB_CK(h, launch_refmedia_count(nd, h->dp.p, h->matrix.p, h->matrix_n, n_tx, d_rec, h->blkcnt.p, h->ctr.p, h->st));
+        ++launches; ++sweeps;
+        RMB_CK(h, cudaEventRecord(h->ev[2], h->st));
+        if ((rc = read_counters(h))) return rc;
+        m = (long long)h->h_ctr.p->heard;
+        if ((rc = ensure_pairs(h, m))) return rc;
+        RMB_CK(h, cudaEventRecord(h->ev[3], h->st));
+        if (m > 0) {
+            RMB_CK(h, launch_exclusive_scan(h->blkcnt.p, h->blkcnt.p, (int)nb, h->scan_tmp.p, nullptr, h->st)); launches += 3;
+            RMB_CK(h, launch_refmedia_scatter(nd, h->dp.p, h->matrix.p, h->matrix_n, n_tx, d_rec, h->blkcnt.p, pair_arrays(h),
+                                              h->node_recv.p, h->st));
+            ++launches;
+        }
+    }
+    RMB_CK(h, launch_emit(h->dp.p, d_rec, n_tx, pair_arrays(h), m, draws, h->uniforms.p, nu, h->ctr.p, h->st));
+    launches += draws ? 7 : 2;
+    RMB_CK(h, cudaEventRecord(h->ev[4], h->st));
+    if ((rc = read_counters(h))) return rc;
+    const Counters &c = *h->h_ctr.p;
+    rmb_timing &t = h->timing;
+    cudaEventElapsedTime(&t.ms_total, h->ev[0], h->ev[4]);
+    cudaEventElapsedTime(&t.ms_prepare, h->ev[0], h->ev[1]);
+    cudaEventElapsedTime(&t.ms_sweep, h->ev[1], h->ev[2]);
+    cudaEventElapsedTime(&t.ms_resolve, h->ev[2], h->ev[3]);
+    cudaEventElapsedTime(&t.ms_emit, h->ev[3], h->ev[4]);
+    t.sweep_launches = sweeps; t.kernel_launches = launches;
+    rmb_result &r = h->last;
+    memset(&r, 0, sizeof(r));
+    r.n_pairs = m; r.n_delivered = c.n_delivered; r.n_interfered = c.n_interfered; r.n_decisions = c.decisions;
+    r.n_uniforms_used = draws ? c.uniforms_used : 0; r.n_recheck = c.n_recheck; r.n_tx = n_tx; r.near_slots = h->K;
+    h->last_pairs = m; h->last_ntx = n_tx;
+    if (draws && c.uniforms_short) { h->err = "uniform stream exhausted; missing draws were read as 0.0"; return RMB_ERR_UNIFORMS; }
+    return RMB_OK;
+}
+
+static int download(rmb_handle *h, rmb_result *out)
+{
+    const long long m = h->last_pairs;
+    const int nt = h->last_ntx;
+    const size_t c = (size_t)std::max<long long>(m, 1);
+    RMB_CK(h, h->ho_tx.ensure(c)); RMB_CK(h, h->ho_rx.ensure(c)); RMB_CK(h, h->ho_rssi.ensure(c));
+    RMB_CK(h, h->ho_sinr.ensure(c)); RMB_CK(h, h->ho_outcome.ensure(c)); RMB_CK(h, h->ho_failed.ensure((size_t)nt + 1));
+    const bool f64 = (h->cfg.flags & RMB_FLAG_F64_VALUES) != 0;
+    if (f64) { RMB_CK(h, h->ho_rssi64.ensure(c)); RMB_CK(h, h->ho_sinr64.ensure(c)); }
+    if (m > 0) {
+        RMB_CK(h, cudaMemcpyAsync(h->ho_tx.p, h->o_tx.p, m * sizeof(int), cudaMemcpyDeviceToHost, h->st));
+        RMB_CK(h, cudaMemcpyAsync(h->ho_rx.p, h->o_rx.p, m * sizeof(int), cudaMemcpyDeviceToHost, h->st));
+        RMB_CK(h, cudaMemcpyAsync(h->ho_rssi.p, h->o_rssi.p, m * sizeof(float), cudaMemcpyDeviceToHost, h->st));
+        RMB_CK(h, cudaMemcpyAsync(h->ho_sinr.p, h->o_sinr.p, m * sizeof(float), cudaMemcpyDeviceToHost, h->st));
+        RMB_CK(h, cudaMemcpyAsync(h->ho_outcome.p, h->o_outcome.p, m, cudaMemcpyDeviceToHost, h->st));
+        if (f64) {
+            RMB_CK(h, cudaMemcpyAsync(h->ho_rssi64.p, h->o_rssi64.p, m * sizeof(double), cudaMemcpyDeviceToHost, h->st));
+            RMB_CK(h, cudaMemcpyAsync(h->ho_sinr64.p, h->o_sinr64.p, m * sizeof(double), cudaMemcpyDeviceToHost, h->st));
+        }
+    }
+    if (nt > 0) RMB_CK(h, cudaMemcpyAsync(h->ho_failed.p, h->tx_failed.p, nt, cudaMemcpyDeviceToHost, h->st));
+    RMB_CK(h, cudaStreamSynchronize(h->st));
+    rmb_result &r = h->last;
+    r.tx = h->ho_tx.p; r.rx = h->ho_rx.p; r.rssi_dbm = h->ho_rssi.p; r.sinr_db = h->ho_sinr.p; r.outcome = h->ho_outcome.p;
+    r.rssi_dbm_f64 = f64 ? h->ho_rssi64.p : nullptr; r.sinr_db_f64 = f64 ? h->ho_sinr64.p : nullptr;
+    r.tx_failed = h->ho_failed.p;
+    if (out) *out = r;
+    return RMB_OK;
+}
+
+// packets (host) -> tx records (device)
+static int stage_records(rmb_handle *h, int n_tx, const int32_t *src, const double *power, const int32_t *channel,
+                         rmb_tx_record *d_out, bool require_local)
+{
+    if (n_tx == 0) return RMB_OK;
+    if (require_local)
+        for (int t = 0; t < n_tx; ++t)
+            if (src[t] < h->cfg.rx_base || src[t] >= h->cfg.rx_base + h->n)
+                return h->fail(RMB_ERR_INVALID, "rmb_tick: source node index out of range");
+    RMB_CK(h, h->pk_src.ensure(n_tx)); RMB_CK(h, h->pk_power.ensure(n_tx)); RMB_CK(h, h->pk_channel.ensure(n_tx));
+    RMB_CK(h, cudaMemcpyAsync(h->pk_src.p, src, (size_t)n_tx * sizeof(int), cudaMemcpyHostToDevice, h->st));
+    if (power) RMB_CK(h, cudaMemcpyAsync(h->pk_power.p, power, (size_t)n_tx * sizeof(double), cudaMemcpyHostToDevice, h->st));
+    if (channel) RMB_CK(h, cudaMemcpyAsync(h->pk_channel.p, channel, (size_t)n_tx * sizeof(int), cudaMemcpyHostToDevice, h->st));
+    RMB_CK(h, launch_gather_records(node_arrays(h), h->cfg.rx_base, n_tx, h->pk_src.p, power ? h->pk_power.p : nullptr,
+                                    channel ? h->pk_channel.p : nullptr, d_out, h->st));
+    return RMB_OK;
+}
+
+extern "C" {
+
+int rmb_tick(rmb_handle *h, int32_t n_tx, const int32_t *src, const double *power_dbm, const int32_t *channel,
+             const double *uniforms, size_t n_uniforms, rmb_result *out)
+{
+    if (!h) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (!h->have_nodes) return h->fail(RMB_ERR_STATE, "rmb_tick before rmb_set_nodes");
+    if (n_tx < 0 || (n_tx > 0 && !src) || !out) return h->fail(RMB_ERR_INVALID, "rmb_tick: bad arguments");
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    RMB_CK(h, h->rec.ensure(std::max(n_tx, 1)));
+    int rc = stage_records(h, n_tx, src, power_dbm, channel, h->rec.p, true);
+    if (rc) return rc;
+    rc = compute(h, n_tx, h->rec.p, uniforms, n_uniforms);
+    if (rc && rc != RMB_ERR_UNIFORMS) return rc;
+    int rc2 = download(h, out);
+    return rc2 ? rc2 : rc;
+}
+
+int rmb_build_tx_records(rmb_handle *h, int32_t n_tx, const int32_t *src, const double *power_dbm,
+                         const int32_t *channel, void *d_records)
+{
+    if (!h) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (!h->have_nodes) return h->fail(RMB_ERR_STATE, "rmb_build_tx_records before rmb_set_nodes");
+    if (n_tx < 0 || (n_tx > 0 && (!src || !d_records))) return h->fail(RMB_ERR_INVALID, "rmb_build_tx_records: bad arguments");
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    int rc = stage_records(h, n_tx, src, power_dbm, channel, (rmb_tx_record *)d_records, false);
+    if (rc) return rc;
+    RMB_CK(h, cudaStreamSynchronize(h->st));      // the caller hands d_records to another stream (NCCL)
+    return RMB_OK;
+}
+
+int rmb_tick_records(rmb_handle *h, int32_t n_tx, const void *d_records, const double *uniforms, size_t n_uniforms,
+                     rmb_result *out)
+{
+    if (!h) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (!h->have_nodes) return h->fail(RMB_ERR_STATE, "rmb_tick_records before rmb_set_nodes");
+    if (n_tx < 0 || (n_tx > 0 && !d_records) || !out) return h->fail(RMB_ERR_INVALID, "rmb_tick_records: bad arguments");
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    int rc = compute(h, n_tx, (const rmb_tx_record *)d_records, uniforms, n_uniforms);
+    if (rc && rc != RMB_ERR_UNIFORMS) return rc;
+    int rc2 = download(h, out);
+    return rc2 ? rc2 : rc;
+}
+
+int rmb_tick_resident(rmb_handle *h, int32_t n_tx, const void *d_records, rmb_result *out)
+{
+    if (!h) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (!h->have_nodes) return h->fail(RMB_ERR_STATE, "rmb_tick_resident before rmb_set_nodes");
+    if (n_tx < 0 || (n_tx > 0 && !d_records)) return h->fail(RMB_ERR_INVALID, "rmb_tick_resident: bad arguments");
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    int rc = compute(h, n_tx, (const rmb_tx_record *)d_records, nullptr, 0);
+    if (out) *out = h->last;
+    return rc;
+}
+
+int rmb_fetch(rmb_handle *h, rmb_result *out)
+{
+    if (!h || !out) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    return download(h, out);
+}
+
+}  // extern "C"

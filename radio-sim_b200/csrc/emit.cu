@@ -1,0 +1,296 @@
+// emit.cu -- K3: order-preserving compaction of the heard pairs, (tx arrival, rx index)
+// ordering, the reference's stochastic reception rule with host-supplied uniforms, outputs.
+//
+// The result list reproduces the Java call order of Simulator.generateReceptionEvents
+// (UDGMRadioMedium.java:99-114, Simulator.java:321-335): packets in arrival order, receivers
+// in node-array order.  Compaction is warp ballot / shuffle prefix sums (no atomic appends).
+// The uniforms stand in for simulator.getRandom().nextDouble() and are consumed in the
+// reference's draw order (UDGMRadioMedium.java:88-92,104-111): per packet first the tx draw
+// (only if 0 < p_tx < 1), then one draw per receiver that needs it, in node order.
+#include "common.cuh"
+#include "kernels.h"
+#include <cub/device/device_radix_sort.cuh>
+
+namespace rmb {
+
+// ---- device-wide exclusive scan of int32 (1024 elements per block) ------------------------
+__device__ __forceinline__ int block_exclusive_scan_1024(int v, int *s_warp, int &block_total)
+{
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    int incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
+    if (lane == 31) s_warp[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+        int x = s_warp[lane], xi = x;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, xi, o); if (lane >= o) xi += y; }
+        s_warp[lane] = xi - x;
+        if (lane == 31) s_warp[32] = xi;
+    }
+    __syncthreads();
+    block_total = s_warp[32];
+    return incl - v + s_warp[wid];
+}
+
+__global__ void __launch_bounds__(1024) scan_sums_kernel(const int *in, int n, int *sums)
+{
+    __shared__ int s_warp[33];
+    int i = blockIdx.x * 1024 + threadIdx.x;
+    int total;
+    block_exclusive_scan_1024(i < n ? in[i] : 0, s_warp, total);
+    if (threadIdx.x == 0) sums[blockIdx.x] = total;
+}
+
+// single block: exclusive scan of the block sums in place, grand total to sums[nb]
+__global__ void __launch_bounds__(1024) scan_top_kernel(int *sums, int nb, int *total_out)
+{
+    __shared__ int s_warp[33];
+    __shared__ int s_carry;
+    if (threadIdx.x == 0) s_carry = 0;
+    __syncthreads();
+    for (int c0 = 0; c0 < nb; c0 += 1024) {
+        int i = c0 + threadIdx.x, total;
+        int v = i < nb ? sums[i] : 0;
+        int ex = block_exclusive_scan_1024(v, s_warp, total);
+        int carry = s_carry;
+        if (i < nb) sums[i] = carry + ex;
+        __syncthreads();
+        if (threadIdx.x == 0) s_carry = carry + total;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { sums[nb] = s_carry; if (total_out) *total_out = s_carry; }
+}
+
+__global__ void __launch_bounds__(1024) scan_final_kernel(const int *in, int *out, int n, const int *sums, int nb)
+{
+    __shared__ int s_warp[33];
+    int i = blockIdx.x * 1024 + threadIdx.x, total;
+    int ex = block_exclusive_scan_1024(i < n ? in[i] : 0, s_warp, total);
+    if (i < n) out[i] = sums[blockIdx.x] + ex;
+    if (i == n) out[n] = sums[nb];           // out has n+1 entries: out[n] = grand total
+}
+
+cudaError_t launch_exclusive_scan(const int *in, int *out, int n, int *tmp, int *total_out, cudaStream_t st)
+{
+    int nb = n / 1024 + 1;                    // covers index n as well (out[n] = total)
+    scan_sums_kernel<<<nb, 1024, 0, st>>>(in, n, tmp);
+    scan_top_kernel<<<1, 1024, 0, st>>>(tmp, nb, total_out);
+    scan_final_kernel<<<nb, 1024, 0, st>>>(in, out, n, tmp, nb);
+    return cudaGetLastError();
+}
+
+// ---- heard slots -> dense (key, slot reference) list ----------------------------------------
+__global__ void scatter_pairs_kernel(WorkArrays wk, const DevParams *dp, TxTiles tx, SlotArrays sl, const int *hoff,
+                                     PairArrays pa)
+{
+    const int w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= wk.n_work) return;
+    const int p = wk.perm[w];
+    if (p < 0 || sl.hcnt[w] == 0) return;
+    const int c = min(sl.cnt[w], sl.K);
+    const size_t base = (size_t)w * sl.K;
+    int o = hoff[w];
+    const unsigned rxg = (unsigned)(dp->rx_base + p);
+    for (int s = 0; s < c; ++s) {
+        if (!(sl.flags[base + s] & kHeard)) continue;
+        const unsigned t = (unsigned)tx.arrival[sl.slots[base + s]];
+        pa.key[o] = ((unsigned long long)t << pa.key_shift) | rxg;
+        pa.val[o] = (unsigned)(base + s);
+        ++o;
+    }
+}
+
+cudaError_t launch_scatter_pairs(const WorkArrays &wk, const DevParams *dp, TxTiles tx, SlotArrays sl, const int *hoff,
+                                 PairArrays pa, cudaStream_t st)
+{
+    if (wk.n_work <= 0) return cudaSuccess;
+    scatter_pairs_kernel<<<(wk.n_work + 127) / 128, 128, 0, st>>>(wk, dp, tx, sl, hoff, pa);
+    return cudaGetLastError();
+}
+
+// ---- (tx, rx) ordering: LSD radix sort of the 64-bit keys (CUB, not on the hot path) --------
+size_t sort_pairs_tmp_bytes(long long n)
+{
+    size_t bytes = 0;
+    cub::DoubleBuffer<unsigned long long> k(nullptr, nullptr);
+    cub::DoubleBuffer<unsigned> v(nullptr, nullptr);
+    cub::DeviceRadixSort::SortPairs(nullptr, bytes, k, v, (int)n, 0, 64, 0);
+    return bytes;
+}
+
+cudaError_t launch_sort_pairs(PairArrays &pa, long long n, int key_bits, cudaStream_t st)
+{
+    if (n <= 1) return cudaSuccess;
+    cub::DoubleBuffer<unsigned long long> k(pa.key, pa.key_alt);
+    cub::DoubleBuffer<unsigned> v(pa.val, pa.val_alt);
+    size_t bytes = pa.cub_tmp_bytes;
+    cudaError_t e = cub::DeviceRadixSort::SortPairs(pa.cub_tmp, bytes, k, v, (int)n, 0, key_bits, st);
+    if (e != cudaSuccess) return e;
+    if (k.Current() != pa.key) { unsigned long long *t = pa.key; pa.key = pa.key_alt; pa.key_alt = t; }
+    if (v.Current() != pa.val) { unsigned *t = pa.val; pa.val = pa.val_alt; pa.val_alt = t; }
+    return cudaSuccess;
+}
+
+__global__ void gather_sorted_kernel(NodeArrays nd, const DevParams *dp, SlotArrays sl, PairArrays pa, long long n)
+{
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const unsigned v = pa.val[i];
+    const int p = (int)(pa.key[i] & ((1ull << pa.key_shift) - 1)) - dp->rx_base;
+    pa.p[i] = nd.rxprob[p];
+    pa.rssi[i] = sl.prx[v];
+    pa.sinr[i] = sl.sinr[v];
+    pa.cand[i] = (sl.flags[v] & kDecodable) ? 1 : 0;
+}
+
+cudaError_t launch_gather_sorted(const NodeArrays &nd, const DevParams *dp, SlotArrays sl, PairArrays pa, long long n,
+                                 cudaStream_t st)
+{
+    if (n <= 0) return cudaSuccess;
+    gather_sorted_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(nd, dp, sl, pa, n);
+    return cudaGetLastError();
+}
+
+// ---- stochastic rule + outputs ---------------------------------------------------------------
+// first sorted pair of every packet (lower bound of t << key_shift)
+__global__ void seg_kernel(const unsigned long long *key, long long n, int n_tx, int shift, int *seg)
+{
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t > n_tx) return;
+    const unsigned long long target = (unsigned long long)t << shift;
+    long long lo = 0, hi = n;
+    while (lo < hi) { long long mid = (lo + hi) >> 1; if (key[mid] < target) lo = mid + 1; else hi = mid; }
+    seg[t] = (int)lo;
+}
+
+// 1 where the pair would consume a uniform if its packet did not fail
+__global__ void drawflag_kernel(const uint8_t *cand, const double *p, long long n, int *flag)
+{
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) flag[i] = (cand[i] && p[i] < 1.0) ? 1 : 0;
+}
+
+__device__ __forceinline__ double tx_success(const DevParams *dp, const rmb_tx_record &r)
+{
+    if (dp->model == RMB_MODEL_UDGM) return dp->success_ratio_rx * r.txprob;   // UDGMRadioMedium.java:63-65 (sic: Rx)
+    if (dp->model == RMB_MODEL_N2N || dp->model == RMB_MODEL_SINR) return r.txprob;   // N2NRadioMedium.java:24-26
+    return 1.0;                                                                 // Null / ConstantLoss: no loss model
+}
+
+// no draws possible: the tx rule degenerates to p_tx <= 0
+__global__ void txfail_det_kernel(const DevParams *dp, const rmb_tx_record *rec, int n_tx, uint8_t *failed, long long *base)
+{
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_tx) return;
+    const rmb_tx_record r = rec[t];
+    failed[t] = (r.src >= 0 && tx_success(dp, r) <= 0.0) ? 1 : 0;
+    base[t] = 0;
+}
+
+// The draw order is inherently sequential over packets (whether packet t consumes its
+// receivers' uniforms depends on its own tx draw).  One block: all threads stage a chunk of
+// per-packet (p_tx, draws) into shared memory, thread 0 walks it.
+__global__ void __launch_bounds__(1024)
+txloop_kernel(const DevParams *dp, const rmb_tx_record *rec, int n_tx, const int *seg, const int *draw_scan,
+              const double *uniforms, long long n_uniforms, uint8_t *failed, long long *base, Counters *ctr)
+{
+    __shared__ double s_ptx[1024];
+    __shared__ int s_draws[1024];
+    __shared__ long long s_u;
+    __shared__ int s_short;
+    if (threadIdx.x == 0) { s_u = 0; s_short = 0; }
+    for (int c0 = 0; c0 < n_tx; c0 += 1024) {
+        const int t = c0 + threadIdx.x;
+        if (t < n_tx) {
+            const rmb_tx_record r = rec[t];
+            s_ptx[threadIdx.x] = r.src >= 0 ? tx_success(dp, r) : 1.0;
+            s_draws[threadIdx.x] = draw_scan[seg[t + 1]] - draw_scan[seg[t]];
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            long long u = s_u;
+            int sh = s_short;
+            const int nc = min(1024, n_tx - c0);
+            for (int i = 0; i < nc; ++i) {
+                const double ptx = s_ptx[i];
+                int f = 0;
+                if (ptx <= 0.0) f = 1;
+                else if (ptx < 1.0) {
+                    double uu = 0.0;
+                    if (u < n_uniforms) uu = uniforms[u]; else sh = 1;
+                    ++u;
+                    if (uu > ptx) f = 1;
+                }
+                failed[c0 + i] = (uint8_t)f;
+                base[c0 + i] = u;
+                if (!f) u += s_draws[i];
+            }
+            s_u = u; s_short = sh;
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        ctr->uniforms_used = s_u;
+        if (s_u > n_uniforms) s_short = 1;
+        ctr->uniforms_short = s_short;
+    }
+}
+
+__global__ void finalize_kernel(PairArrays pa, long long n, bool stochastic, const double *uniforms, long long n_uniforms,
+                                Counters *ctr)
+{
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    int delivered = 0, interfered = 0;
+    if (i < n) {
+        const unsigned long long k = pa.key[i];
+        const int t = (int)(k >> pa.key_shift);
+        const double p = pa.p[i];
+        int outcome;
+        if (pa.tx_failed[t] || !pa.cand[i]) outcome = RMB_INTERFERED;
+        else if (p < 1.0 && stochastic) {
+            const long long idx = pa.tx_base[t] + (long long)(pa.draw_scan[i] - pa.draw_scan[pa.seg[t]]);
+            const double uu = idx < n_uniforms ? uniforms[idx] : 0.0;
+            outcome = uu > p ? RMB_INTERFERED : RMB_DELIVERED;
+        } else outcome = RMB_DELIVERED;
+        pa.o_tx[i] = t;
+        pa.o_rx[i] = (int)(k & ((1ull << pa.key_shift) - 1));
+        const double rssi = pa.rssi[i], sinr = pa.sinr[i];
+        pa.o_rssi[i] = (float)rssi;
+        pa.o_sinr[i] = (float)sinr;
+        if (pa.o_rssi64) { pa.o_rssi64[i] = rssi; pa.o_sinr64[i] = sinr; }
+        pa.o_outcome[i] = (uint8_t)outcome;
+        delivered = outcome == RMB_DELIVERED; interfered = !delivered;
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        delivered += __shfl_xor_sync(0xffffffffu, delivered, o);
+        interfered += __shfl_xor_sync(0xffffffffu, interfered, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (delivered) atomicAdd(&ctr->n_delivered, delivered);
+        if (interfered) atomicAdd(&ctr->n_interfered, interfered);
+    }
+}
+
+cudaError_t launch_emit(const DevParams *dp, const rmb_tx_record *rec, int n_tx, PairArrays pa, long long n,
+                        bool stochastic, const double *uniforms, long long n_uniforms, Counters *ctr, cudaStream_t st)
+{
+    if (n_tx <= 0) return cudaSuccess;
+    if (stochastic) {
+        seg_kernel<<<(n_tx + 1 + 255) / 256, 256, 0, st>>>(pa.key, n, n_tx, pa.key_shift, pa.seg);
+        if (n > 0) drawflag_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(pa.cand, pa.p, n, pa.draw_scan);
+        // in-place exclusive scan (n+1 entries)
+        cudaError_t e = launch_exclusive_scan(pa.draw_scan, pa.draw_scan, (int)n, pa.scan_tmp, nullptr, st);
+        if (e != cudaSuccess) return e;
+        txloop_kernel<<<1, 1024, 0, st>>>(dp, rec, n_tx, pa.seg, pa.draw_scan, uniforms, n_uniforms, pa.tx_failed,
+                                          pa.tx_base, ctr);
+    } else {
+        txfail_det_kernel<<<(n_tx + 255) / 256, 256, 0, st>>>(dp, rec, n_tx, pa.tx_failed, pa.tx_base);
+    }
+    if (n > 0)
+        finalize_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(pa, n, stochastic, uniforms, n_uniforms, ctr);
+    return cudaGetLastError();
+}
+
+}  // namespace rmb

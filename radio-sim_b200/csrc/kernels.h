@@ -1,0 +1,111 @@
+// kernels.h -- host-callable launchers of the CUDA kernels (one .cu per pipeline stage).
+#pragma once
+#include "common.cuh"
+
+namespace rmb {
+
+// ---- node state in HBM (SoA, node-array order == Simulator.getNodes() order) -------------
+struct NodeArrays {
+    int n;
+    double *x, *y, *z;                // Position.java:37-39 (exact master copy)
+    double *txpower, *rxprob, *txprob;
+    int    *channel;
+    uint8_t *enabled;
+    int    *id_int;                   // Node.getIdAsInteger (N2N)
+};
+
+// ---- receivers in work order (grouped by channel, padded) --------------------------------
+struct WorkArrays {
+    int n_work;                       // multiple of 1024
+    int *perm;                        // work slot -> local node index, -1 = padding
+    float *fx, *fy, *fz;              // centred fp32 copy used by the sweep
+};
+
+// ---- K4: state maintenance ----------------------------------------------------------------
+cudaError_t launch_geom(const NodeArrays &nd, unsigned long long *scratch6, Geom *geom, cudaStream_t st);
+cudaError_t launch_regather(const NodeArrays &nd, const WorkArrays &wk, const Geom *geom, cudaStream_t st);
+cudaError_t launch_scatter_positions(const NodeArrays &nd, int count, const int *idx,
+                                     const double *x, const double *y, const double *z, cudaStream_t st);
+cudaError_t launch_init_params(DevParams *dp, cudaStream_t st);
+
+// ---- per tick: tx records and channel bucketing ---------------------------------------------
+// packets: src (global index), power (NaN => node's), channel (INT32_MIN => node's)
+cudaError_t launch_gather_records(const NodeArrays &nd, int rx_base, int n_tx, const int *src, const double *power,
+                                  const int *channel, rmb_tx_record *rec, cudaStream_t st);
+cudaError_t launch_prepare(const NodeArrays &nd, const DevParams *dp, const Geom *geom, Groups groups, int n_tx,
+                           const rmb_tx_record *rec, TxTiles tx, float *theta, float *theta_min_g,
+                           Counters *ctr, cudaStream_t st);
+
+// ---- K1 ---------------------------------------------------------------------------------------
+struct SweepArgs {
+    const float *fx, *fy, *fz;
+    Groups groups;
+    TxTiles tx;
+    const float *theta, *theta_min_g;
+    float neg_h;                      // -n/2 (general-exponent mode)
+    float *far_out;
+    int *cnt_out, *slots;
+    int K;
+    Counters *ctr;
+};
+int sweep_mode_for_exponent(double n);
+cudaError_t launch_sweep(int mode, bool planar, int variant, int n_work, const SweepArgs &a, cudaStream_t st);
+
+// ---- exact resolve of the near candidates + guard-band recheck --------------------------------
+struct SlotArrays {
+    int K;
+    int *slots;                       // [n_work*K] bucket position j of the candidate
+    int *cnt;                         // [n_work] candidates found (may exceed K => retry)
+    float *far_sum;                   // [n_work] fp32 far-field interference sum [mW]
+    double *prx, *lin, *sinr;         // [n_work*K] exact values per candidate
+    uint8_t *flags;                   // [n_work*K] kHeard | kDecodable
+    int *hcnt;                        // [n_work] heard pairs of the receiver
+    double *itot;                     // [n_work] total in-band power [mW]
+    int *recheck;                     // receivers inside the SINR guard band
+};
+cudaError_t launch_resolve(const NodeArrays &nd, const WorkArrays &wk, const DevParams *dp, TxTiles tx,
+                           const rmb_tx_record *rec, SlotArrays sl, float *node_rssi, uint8_t *node_recv,
+                           Counters *ctr, cudaStream_t st);
+cudaError_t launch_recheck(const NodeArrays &nd, const WorkArrays &wk, const DevParams *dp, Groups groups, TxTiles tx,
+                           const rmb_tx_record *rec, SlotArrays sl, int n_recheck, float *node_rssi,
+                           cudaStream_t st);
+
+// ---- emission: compaction, (tx,rx) ordering, stochastic rule, outputs -------------------------
+struct PairArrays {
+    long long cap;
+    int key_shift;                       // key = (t << key_shift) | global rx
+    unsigned long long *key, *key_alt;   // (t << key_shift) | global rx
+    unsigned *val, *val_alt;             // slot reference (SINR) / unused
+    double *p;                           // reception probability of the pair
+    double *rssi, *sinr;                 // exact values (sorted order)
+    uint8_t *cand;                       // pair may be delivered (decodable / in range)
+    int *draw_scan;                      // exclusive scan of "needs a draw" flags
+    int *seg;                            // [n_tx+1] first sorted pair of packet t
+    long long *tx_base;                  // [n_tx] uniform index of the packet's first receiver draw
+    uint8_t *tx_failed;                  // [n_tx]
+    int *scan_tmp;                       // block sums for the scans
+    void *cub_tmp; size_t cub_tmp_bytes;
+    // outputs
+    int *o_tx, *o_rx; float *o_rssi, *o_sinr; uint8_t *o_outcome; double *o_rssi64, *o_sinr64;
+};
+// exclusive scan of int32 (n elements) using tmp (>= n/1024+2 ints); total written to *total_out (device)
+cudaError_t launch_exclusive_scan(const int *in, int *out, int n, int *tmp, int *total_out, cudaStream_t st);
+cudaError_t launch_scatter_pairs(const WorkArrays &wk, const DevParams *dp, TxTiles tx, SlotArrays sl, const int *hoff,
+                                 PairArrays pa, cudaStream_t st);
+size_t      sort_pairs_tmp_bytes(long long n);
+cudaError_t launch_sort_pairs(PairArrays &pa, long long n, int key_bits, cudaStream_t st);   // result in key/val
+cudaError_t launch_gather_sorted(const NodeArrays &nd, const DevParams *dp, SlotArrays sl, PairArrays pa, long long n,
+                                 cudaStream_t st);
+cudaError_t launch_emit(const DevParams *dp, const rmb_tx_record *rec, int n_tx, PairArrays pa, long long n,
+                        bool stochastic, const double *uniforms, long long n_uniforms, Counters *ctr,
+                        cudaStream_t st);
+
+// ---- K2: the reference media (Null / UDGM / UDGMConstantLoss / N2N), exact double --------------
+cudaError_t launch_refmedia_count(const NodeArrays &nd, const DevParams *dp, const double *matrix, int matrix_n,
+                                  int n_tx, const rmb_tx_record *rec, int *blkcnt, Counters *ctr, cudaStream_t st);
+cudaError_t launch_refmedia_scatter(const NodeArrays &nd, const DevParams *dp, const double *matrix, int matrix_n,
+                                    int n_tx, const rmb_tx_record *rec, const int *blkoff, PairArrays pa,
+                                    uint8_t *node_recv, cudaStream_t st);
+int refmedia_blocks_per_tx(int n);
+
+}  // namespace rmb

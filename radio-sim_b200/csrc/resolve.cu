@@ -1,0 +1,154 @@
+// resolve.cu -- exact (double, strict IEEE) evaluation of the near candidates and the
+// guard-band recheck.  This is where every heard / decodable DECISION of the SINR medium is
+// taken; the fp32 sweep only supplies the weak far-field interference sum.
+//
+// Specification implemented here (the CPU oracle states the same):
+//   d    = Position.getDistance(src, rx)              (Position.java:56-64, unfused)
+//   Prx  = Ptx - (PL0 + (10 n) log10(max(d,d0)/d0))   [dBm]
+//   lin  = exp(Prx * ln10/10)                         [mW]
+//   Itot = N0 + sum of lin over co-channel packets (arrival order, source != rx)
+//   heard iff Prx >= sensitivity && rxProbability > 0
+//   SINR = Prx - 10 log10(Itot - lin);  decodable iff SINR >= threshold
+#include "common.cuh"
+#include "kernels.h"
+#include "exact_math.cuh"
+
+namespace rmb {
+
+__device__ __forceinline__ double rx_power_dbm(const DevParams *dp, double power_dbm, double d)
+{
+    double dd = d < dp->d0_m ? dp->d0_m : d;
+    double pl = xm::add(dp->pl0_db, xm::mul(xm::mul(10.0, dp->pl_exponent), xm::log10_strict(xm::dvd(dd, dp->d0_m))));
+    return xm::sub(power_dbm, pl);
+}
+
+__device__ __forceinline__ double sinr_db(double prx, double itot, double lin)
+{
+    double ioth = xm::sub(itot, lin);
+    return ioth > 0.0 ? xm::sub(prx, xm::mw_to_dbm(ioth)) : __longlong_as_double(0x7ff0000000000000ll);
+}
+
+// one thread per receiver (work order)
+__global__ void __launch_bounds__(128)
+resolve_kernel(NodeArrays nd, WorkArrays wk, const DevParams *dp, TxTiles tx, const rmb_tx_record *rec,
+               SlotArrays sl, float *node_rssi, uint8_t *node_recv, Counters *ctr)
+{
+    const int w = blockIdx.x * blockDim.x + threadIdx.x;
+    int nh = 0;
+    if (w < wk.n_work) {
+        const int p = wk.perm[w];
+        if (p >= 0) {
+            const int K = sl.K;
+            const int c = min(sl.cnt[w], K);
+            const double X = nd.x[p], Y = nd.y[p], Z = nd.z[p];
+            const double rxp = nd.rxprob[p];
+            const int self = dp->rx_base + p;
+            double itot = xm::add(dp->n0_mw, (double)sl.far_sum[w]);
+            const size_t base = (size_t)w * K;
+            for (int s = 0; s < c; ++s) {
+                const int t = tx.arrival[sl.slots[base + s]];
+                const rmb_tx_record r = rec[t];
+                uint8_t f = 0;
+                double prx = 0.0, lin = 0.0;
+                if (r.src != self) {
+                    const double d = xm::distance(r.x, r.y, r.z, X, Y, Z);
+                    prx = rx_power_dbm(dp, r.power_dbm, d);
+                    lin = xm::dbm_to_mw(prx);
+                    itot = xm::add(itot, lin);
+                    if (prx >= dp->sensitivity_dbm && rxp > 0.0) { f = kHeard; ++nh; }
+                }
+                sl.prx[base + s] = prx; sl.lin[base + s] = lin; sl.flags[base + s] = f;
+            }
+            bool guard = false;
+            for (int s = 0; s < c; ++s) {
+                uint8_t f = sl.flags[base + s];
+                if (!(f & kHeard)) continue;
+                const double sinr = sinr_db(sl.prx[base + s], itot, sl.lin[base + s]);
+                if (sinr >= dp->sinr_threshold_db) f |= kDecodable;
+                if (fabs(sinr - dp->sinr_threshold_db) < dp->sinr_guard_db) guard = true;
+                sl.sinr[base + s] = sinr; sl.flags[base + s] = f;
+            }
+            sl.hcnt[w] = nh;
+            sl.itot[w] = itot;
+            node_rssi[p] = (float)xm::mw_to_dbm(itot);
+            node_recv[p] = nh > 0;
+            if (guard && sl.cnt[w] <= K) sl.recheck[atomicAdd(&ctr->n_recheck, 1)] = w;
+        } else {
+            sl.hcnt[w] = 0;
+        }
+    }
+    // total heard pairs (capacity check on the host)
+    unsigned long long v = (unsigned long long)nh;
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0 && v) atomicAdd(&ctr->heard, v);
+}
+
+cudaError_t launch_resolve(const NodeArrays &nd, const WorkArrays &wk, const DevParams *dp, TxTiles tx,
+                           const rmb_tx_record *rec, SlotArrays sl, float *node_rssi, uint8_t *node_recv,
+                           Counters *ctr, cudaStream_t st)
+{
+    if (wk.n_work <= 0) return cudaSuccess;
+    resolve_kernel<<<(wk.n_work + 127) / 128, 128, 0, st>>>(nd, wk, dp, tx, rec, sl, node_rssi, node_recv, ctr);
+    return cudaGetLastError();
+}
+
+// Guard-band recheck: one block per flagged receiver.  The full co-channel sum is redone in
+// double, the per-packet terms in parallel, the ADDITION strictly sequential in arrival order
+// (thread 0), so the total is bit-identical to a sequential Java/C loop.
+constexpr int kRecheckChunk = 2048;
+
+__global__ void __launch_bounds__(256)
+recheck_kernel(NodeArrays nd, WorkArrays wk, const DevParams *dp, Groups groups, TxTiles tx, const rmb_tx_record *rec,
+               SlotArrays sl, float *node_rssi)
+{
+    __shared__ double s_lin[kRecheckChunk];
+    __shared__ double s_itot;
+    const int w = sl.recheck[blockIdx.x];
+    const int p = wk.perm[w];
+    int g = 0;
+    while (g + 1 < groups.ngroups && w >= groups.w_begin[g + 1]) ++g;
+    const int j0 = tx.goff[g], nj = tx.gcount[g];
+    const double X = nd.x[p], Y = nd.y[p], Z = nd.z[p];
+    const int self = dp->rx_base + p;
+    double itot = dp->n0_mw;
+    for (int c0 = 0; c0 < nj; c0 += kRecheckChunk) {
+        const int nc = min(kRecheckChunk, nj - c0);
+        for (int i = threadIdx.x; i < nc; i += blockDim.x) {
+            const rmb_tx_record r = rec[tx.arrival[j0 + c0 + i]];
+            double lin = 0.0;     // itot + 0.0 == itot: skipping the source is the same as adding zero
+            if (r.src != self) lin = xm::dbm_to_mw(rx_power_dbm(dp, r.power_dbm, xm::distance(r.x, r.y, r.z, X, Y, Z)));
+            s_lin[i] = lin;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0)
+            for (int i = 0; i < nc; ++i) itot = xm::add(itot, s_lin[i]);
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        s_itot = itot;
+        sl.itot[w] = itot;
+        node_rssi[p] = (float)xm::mw_to_dbm(itot);
+    }
+    __syncthreads();
+    itot = s_itot;
+    const int c = min(sl.cnt[w], sl.K);
+    const size_t base = (size_t)w * sl.K;
+    for (int s = threadIdx.x; s < c; s += blockDim.x) {
+        uint8_t f = sl.flags[base + s];
+        if (!(f & kHeard)) continue;
+        const double sinr = sinr_db(sl.prx[base + s], itot, sl.lin[base + s]);
+        f = kHeard | (sinr >= dp->sinr_threshold_db ? kDecodable : 0);
+        sl.sinr[base + s] = sinr; sl.flags[base + s] = f;
+    }
+}
+
+cudaError_t launch_recheck(const NodeArrays &nd, const WorkArrays &wk, const DevParams *dp, Groups groups, TxTiles tx,
+                           const rmb_tx_record *rec, SlotArrays sl, int n_recheck, float *node_rssi,
+                           cudaStream_t st)
+{
+    if (n_recheck <= 0) return cudaSuccess;
+    recheck_kernel<<<n_recheck, 256, 0, st>>>(nd, wk, dp, groups, tx, rec, sl, node_rssi);
+    return cudaGetLastError();
+}
+
+}  // namespace rmb

@@ -1,0 +1,257 @@
+// state.cu -- K4 (per-tick node/transmission state in HBM) and the tx-side preparation.
+//
+// Replaces the AoS objects Node/Position/Transciever/RadioPacket (Node.java:39-59,
+// Position.java:37-52, Transciever.java:5-113, RadioPacket.java:46-52) by SoA device
+// buffers: an exact double master copy in node-array order plus a centred fp32 copy in
+// "work order" (receivers grouped by channel) for the sweep.
+#include "common.cuh"
+#include "kernels.h"
+#include "exact_math.cuh"
+#include <cfloat>
+#include <climits>
+
+namespace rmb {
+
+// ---- bounding box ------------------------------------------------------------------------
+__device__ __forceinline__ unsigned long long enc(double d)
+{
+    unsigned long long u = (unsigned long long)__double_as_longlong(d);
+    return (u >> 63) ? ~u : (u | 0x8000000000000000ull);
+}
+__device__ __forceinline__ double dec(unsigned long long u)
+{
+    u = (u >> 63) ? (u & 0x7fffffffffffffffull) : ~u;
+    return __longlong_as_double((long long)u);
+}
+
+__global__ void geom_init_kernel(unsigned long long *s)
+{
+    if (threadIdx.x < 3) s[threadIdx.x] = ~0ull;          // minima
+    else if (threadIdx.x < 6) s[threadIdx.x] = 0ull;      // maxima
+}
+
+__global__ void geom_reduce_kernel(NodeArrays nd, unsigned long long *s)
+{
+    double mn[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, mx[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX};
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nd.n; i += gridDim.x * blockDim.x) {
+        double v[3] = {nd.x[i], nd.y[i], nd.z[i]};
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { mn[k] = fmin(mn[k], v[k]); mx[k] = fmax(mx[k], v[k]); }
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+        for (int o = 16; o > 0; o >>= 1) {
+            mn[k] = fmin(mn[k], __shfl_xor_sync(0xffffffffu, mn[k], o));
+            mx[k] = fmax(mx[k], __shfl_xor_sync(0xffffffffu, mx[k], o));
+        }
+    if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { atomicMin(&s[k], enc(mn[k])); atomicMax(&s[3 + k], enc(mx[k])); }
+    }
+}
+
+__global__ void geom_final_kernel(int n, const unsigned long long *s, Geom *g)
+{
+    if (n <= 0) { *g = Geom{0, 0, 0, 0, 0, 0, 1, 0}; return; }
+    double mn[3], mx[3];
+    for (int k = 0; k < 3; ++k) { mn[k] = dec(s[k]); mx[k] = dec(s[3 + k]); }
+    g->cx = 0.5 * (mn[0] + mx[0]); g->cy = 0.5 * (mn[1] + mx[1]); g->cz = 0.5 * (mn[2] + mx[2]);
+    double m = fmax(fmax(mx[0] - g->cx, mx[1] - g->cy), mx[2] - g->cz);
+    g->maxabs = m;
+    g->zmin = mn[2]; g->zmax = mx[2];
+    g->planar = (mn[2] == mx[2]) ? 1 : 0;
+}
+
+cudaError_t launch_geom(const NodeArrays &nd, unsigned long long *scratch6, Geom *geom, cudaStream_t st)
+{
+    geom_init_kernel<<<1, 32, 0, st>>>(scratch6);
+    if (nd.n > 0) {
+        int blocks = min(148 * 4, (nd.n + 255) / 256);
+        geom_reduce_kernel<<<blocks, 256, 0, st>>>(nd, scratch6);
+    }
+    geom_final_kernel<<<1, 1, 0, st>>>(nd.n, scratch6, geom);
+    return cudaGetLastError();
+}
+
+// ---- fp32 work-order copy ----------------------------------------------------------------
+__global__ void regather_kernel(NodeArrays nd, WorkArrays wk, const Geom *geom)
+{
+    int w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= wk.n_work) return;
+    int p = wk.perm[w];
+    if (p < 0) { wk.fx[w] = 1e18f; wk.fy[w] = 1e18f; wk.fz[w] = 1e18f; return; }   // padding: infinitely far
+    wk.fx[w] = (float)(nd.x[p] - geom->cx);
+    wk.fy[w] = (float)(nd.y[p] - geom->cy);
+    wk.fz[w] = (float)(nd.z[p] - geom->cz);
+}
+
+cudaError_t launch_regather(const NodeArrays &nd, const WorkArrays &wk, const Geom *geom, cudaStream_t st)
+{
+    if (wk.n_work <= 0) return cudaSuccess;
+    regather_kernel<<<(wk.n_work + 255) / 256, 256, 0, st>>>(nd, wk, geom);
+    return cudaGetLastError();
+}
+
+// node-config-set "position" for a sparse set of nodes (net/SimulatorJSONHandler.java:111-122)
+__global__ void scatter_positions_kernel(NodeArrays nd, int count, const int *idx, const double *x, const double *y,
+                                         const double *z)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    int p = idx[i];
+    if (p < 0 || p >= nd.n) return;
+    nd.x[p] = x[i]; nd.y[p] = y[i]; nd.z[p] = z ? z[i] : 0.0;
+}
+
+cudaError_t launch_scatter_positions(const NodeArrays &nd, int count, const int *idx, const double *x, const double *y,
+                                     const double *z, cudaStream_t st)
+{
+    if (count <= 0) return cudaSuccess;
+    scatter_positions_kernel<<<(count + 255) / 256, 256, 0, st>>>(nd, count, idx, x, y, z);
+    return cudaGetLastError();
+}
+
+__global__ void init_params_kernel(DevParams *dp)
+{
+    dp->n0_mw = xm::dbm_to_mw(dp->noise_floor_dbm);
+    dp->sinr_guard_db = 1.5e-3;
+}
+
+cudaError_t launch_init_params(DevParams *dp, cudaStream_t st)
+{
+    init_params_kernel<<<1, 1, 0, st>>>(dp);
+    return cudaGetLastError();
+}
+
+// ---- RadioPacket snapshot (RadioPacket.java:46-52): source position, power, channel ------
+__global__ void gather_records_kernel(NodeArrays nd, int rx_base, int n_tx, const int *src, const double *power,
+                                      const int *channel, rmb_tx_record *rec)
+{
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_tx) return;
+    int s = src[t] - rx_base;
+    rmb_tx_record r;
+    if (s < 0 || s >= nd.n) {
+        r.x = r.y = r.z = 0.0; r.power_dbm = 0.0; r.txprob = 1.0; r.channel = 0; r.src = -1;
+    } else {
+        r.x = nd.x[s]; r.y = nd.y[s]; r.z = nd.z[s];
+        double pw = power ? power[t] : nan("");
+        r.power_dbm = isnan(pw) ? nd.txpower[s] : pw;
+        int ch = channel ? channel[t] : INT_MIN;
+        r.channel = (ch == INT_MIN) ? nd.channel[s] : ch;
+        r.txprob = nd.txprob[s];
+        r.src = src[t];
+    }
+    rec[t] = r;
+}
+
+cudaError_t launch_gather_records(const NodeArrays &nd, int rx_base, int n_tx, const int *src, const double *power,
+                                  const int *channel, rmb_tx_record *rec, cudaStream_t st)
+{
+    if (n_tx <= 0) return cudaSuccess;
+    gather_records_kernel<<<(n_tx + 255) / 256, 256, 0, st>>>(nd, rx_base, n_tx, src, power, channel, rec);
+    return cudaGetLastError();
+}
+
+// ---- channel bucketing + fast-path constants ----------------------------------------------
+// One block.  For every receiver channel group g (in work order) the tick's records on that
+// channel are compacted, ARRIVAL ORDER PRESERVED (warp ballot + prefix sums), into bucket g of
+// the sweep's tx tiles; buckets are padded to kTile with infinitely weak dummies.
+//   c_t     = P_t^(-1/n),  P_t = 10^((Ptx - PL0)/10) * d0^n        (power folded into geometry)
+//   theta_t = min(sensitivity (minus 0.05 dB), P_t * Dnear^-n)     (near threshold, mW)
+//   Dnear   = max(d0, n * delta_d / 1e-4), delta_d = fp32 geometry error of the centred copy
+__global__ void __launch_bounds__(1024)
+prepare_kernel(NodeArrays nd, const DevParams *dp, const Geom *geom, Groups groups, int n_tx,
+               const rmb_tx_record *rec, TxTiles tx, float *theta, float *theta_min_g, Counters *ctr)
+{
+    __shared__ int s_warp[32];
+    __shared__ int s_total;
+    __shared__ float s_min[32];
+    __shared__ unsigned long long s_dec[32];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const double n = dp->pl_exponent, d0 = dp->d0_m;
+    const double d0n = pow(d0, n);
+    const double delta_d = geom->maxabs * (geom->planar ? 1.7e-7 : 2.1e-7);
+    const double dnear = fmax(d0, n * delta_d / 1e-4);
+    const double dnear_n = pow(dnear, -n);
+    const double theta_s = pow(10.0, (dp->sensitivity_dbm - 0.05) / 10.0);
+    int cursor = 0;
+    unsigned long long decisions = 0;
+    for (int g = 0; g < groups.ngroups; ++g) {
+        const int ch = groups.channel[g];
+        int count_g = 0;
+        float tmin = FLT_MAX;
+        for (int c0 = 0; c0 < n_tx; c0 += 1024) {
+            const int t = c0 + tid;
+            rmb_tx_record r;
+            bool match = false;
+            if (t < n_tx) { r = rec[t]; match = r.src >= 0 && r.channel == ch; }
+            unsigned b = __ballot_sync(0xffffffffu, match);
+            int rank = __popc(b & ((1u << lane) - 1));
+            if (lane == 0) s_warp[wid] = __popc(b);
+            __syncthreads();
+            if (wid == 0) {
+                int v = s_warp[lane], incl = v;
+                for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
+                s_warp[lane] = incl - v;
+                if (lane == 31) s_total = incl;
+            }
+            __syncthreads();
+            if (match) {
+                const int j = cursor + count_g + s_warp[wid] + rank;
+                const double P = pow(10.0, (r.power_dbm - dp->pl0_db) / 10.0) * d0n;
+                const float cf = (float)pow(P, -1.0 / n);
+                const double c = (double)cf;
+                tx.f[j] = make_float4((float)((r.x - geom->cx) * c), (float)((r.y - geom->cy) * c),
+                                      (float)((r.z - geom->cz) * c), cf);
+                const float th = (float)(fmin(theta_s, P * dnear_n) * (1.0 - 1e-6));
+                theta[j] = th;
+                tx.arrival[j] = t;
+                tmin = fminf(tmin, th);
+                // decisions of this packet: every enabled co-channel receiver except its own source
+                int s = r.src - dp->rx_base;
+                int self = (s >= 0 && s < nd.n && nd.enabled[s] && nd.channel[s] == ch) ? 1 : 0;
+                decisions += (unsigned long long)(groups.n_rx[g] - self);
+            }
+            count_g += s_total;
+            __syncthreads();
+        }
+        const int padded = (count_g + kTile - 1) / kTile * kTile;
+        for (int j = cursor + count_g + tid; j < cursor + padded; j += 1024) {
+            tx.f[j] = make_float4(1e18f, 1e18f, 1e18f, 0.f);      // d2' ~ 1e36 -> lin underflows to 0
+            theta[j] = FLT_MAX;
+            tx.arrival[j] = -1;
+        }
+        for (int o = 16; o > 0; o >>= 1) tmin = fminf(tmin, __shfl_xor_sync(0xffffffffu, tmin, o));
+        if (lane == 0) s_min[wid] = tmin;
+        __syncthreads();
+        if (tid == 0) {
+            float m = FLT_MAX;
+            for (int i = 0; i < 32; ++i) m = fminf(m, s_min[i]);
+            theta_min_g[g] = m;
+            tx.goff[g] = cursor;
+            tx.gcount[g] = count_g;
+        }
+        __syncthreads();
+        cursor += padded;
+    }
+    for (int o = 16; o > 0; o >>= 1) decisions += __shfl_xor_sync(0xffffffffu, decisions, o);
+    if (lane == 0) s_dec[wid] = decisions;
+    __syncthreads();
+    if (tid == 0) {
+        unsigned long long d = 0;
+        for (int i = 0; i < 32; ++i) d += s_dec[i];
+        tx.goff[groups.ngroups] = cursor;
+        ctr->decisions = d;
+    }
+}
+
+cudaError_t launch_prepare(const NodeArrays &nd, const DevParams *dp, const Geom *geom, Groups groups, int n_tx,
+                           const rmb_tx_record *rec, TxTiles tx, float *theta, float *theta_min_g,
+                           Counters *ctr, cudaStream_t st)
+{
+    prepare_kernel<<<1, 1024, 0, st>>>(nd, dp, geom, groups, n_tx, rec, tx, theta, theta_min_g, ctr);
+    return cudaGetLastError();
+}
+
+}  // namespace rmb

@@ -1,0 +1,197 @@
+"""Host-side handle over the C-ABI: one `Medium` == one `rmb_handle` == one RadioMedium instance.
+
+Mirrors what the reference's media expose (radio-medium/java/se/sics/emul8/radiomedium/
+RadioMedium.java:35-45 and the setters of UDGMRadioMedium.java:26-61), batched per tick.
+All evaluation happens in librmb200.so on the GPU; this module only marshals numpy arrays.
+"""
+import ctypes as C
+import numpy as np
+from . import _abi as A
+
+
+class MediumError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"rmb error {code}: {msg}")
+        self.code = code
+
+
+def _ptr(a, ct):
+    return None if a is None else a.ctypes.data_as(C.POINTER(ct))
+
+
+def _arr(a, dt, n=None):
+    if a is None:
+        return None
+    a = np.ascontiguousarray(a, dtype=dt)
+    if n is not None and a.shape != (n,):
+        raise ValueError(f"expected shape ({n},), got {a.shape}")
+    return a
+
+
+class TickResult:
+    """Heard (tx, rx) pairs of one tick in generateReceptionEvents call order
+    (packets in arrival order, receivers in node-array order; Simulator.java:321-335)."""
+
+    def __init__(self, r, f64, copy=True):
+        n = int(r.n_pairs)
+        self.n_pairs, self.n_delivered, self.n_interfered = n, int(r.n_delivered), int(r.n_interfered)
+        self.n_decisions, self.n_uniforms_used = int(r.n_decisions), int(r.n_uniforms_used)
+        self.n_recheck, self.n_tx, self.near_slots = int(r.n_recheck), int(r.n_tx), int(r.near_slots)
+
+        def view(p, dt, m):
+            if not p or m == 0:
+                return np.zeros(0, dtype=dt)
+            v = np.ctypeslib.as_array(p, shape=(m,))
+            return v.copy() if copy else v
+        self.tx = view(r.tx, np.int32, n)
+        self.rx = view(r.rx, np.int32, n)
+        self.rssi_dbm = view(r.rssi_dbm, np.float32, n)
+        self.sinr_db = view(r.sinr_db, np.float32, n)
+        self.outcome = view(r.outcome, np.uint8, n)
+        self.rssi_dbm_f64 = view(r.rssi_dbm_f64, np.float64, n) if f64 else None
+        self.sinr_db_f64 = view(r.sinr_db_f64, np.float64, n) if f64 else None
+        self.tx_failed = view(r.tx_failed, np.uint8, self.n_tx)
+
+
+class Medium:
+    """A radio medium living on one B200.  model: 'null' | 'udgm' | 'udgm-constant' | 'n2n' | 'sinr'."""
+
+    MODELS = {"null": A.MODEL_NULL, "nullrm": A.MODEL_NULL, "udgm": A.MODEL_UDGM,
+              "udgm-constant": A.MODEL_UDGM_CONSTANT, "n2n": A.MODEL_N2N, "n2n-link": A.MODEL_N2N,
+              "sinr": A.MODEL_SINR, "sinr-b200": A.MODEL_SINR}
+
+    def __init__(self, model="sinr", device=0, f64_values=False, rx_base=0, n_shards=1, max_pairs=0, **params):
+        self._lib = A.load()
+        cfg = A.Config()
+        self._lib.rmb_config_default(C.byref(cfg), self.MODELS[model] if isinstance(model, str) else int(model))
+        cfg.device, cfg.rx_base, cfg.n_shards, cfg.max_pairs = device, rx_base, n_shards, max_pairs
+        if f64_values:
+            cfg.flags |= A.FLAG_F64_VALUES
+        for k, v in params.items():
+            if not hasattr(cfg, k):
+                raise AttributeError(f"unknown medium parameter {k}")
+            setattr(cfg, k, v)
+        self.cfg = cfg
+        self._f64 = bool(f64_values)
+        self._h = C.c_void_p()
+        rc = self._lib.rmb_create(C.byref(cfg), C.byref(self._h))
+        if rc != A.OK:
+            msg = self._lib.rmb_last_error(None).decode()
+            self._h = None
+            raise MediumError(rc, msg)
+        self.n = 0
+
+    # -- lifetime ---------------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.rmb_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _ck(self, rc, allow=()):
+        if rc != A.OK and rc not in allow:
+            raise MediumError(rc, self._lib.rmb_last_error(self._h).decode())
+        return rc
+
+    # -- node state (Simulator.addNode + node-config-set) ----------------------------------------
+    def set_nodes(self, x, y, z=None, txpower_dbm=None, channel=None, enabled=None, rxprob=None, txprob=None,
+                  id_int=None):
+        x = _arr(x, np.float64)
+        n = x.shape[0]
+        y, z = _arr(y, np.float64, n), _arr(z, np.float64, n)
+        txpower_dbm, rxprob, txprob = _arr(txpower_dbm, np.float64, n), _arr(rxprob, np.float64, n), _arr(txprob, np.float64, n)
+        channel, id_int, enabled = _arr(channel, np.int32, n), _arr(id_int, np.int32, n), _arr(enabled, np.uint8, n)
+        self._ck(self._lib.rmb_set_nodes(self._h, n, _ptr(x, C.c_double), _ptr(y, C.c_double), _ptr(z, C.c_double),
+                                         _ptr(txpower_dbm, C.c_double), _ptr(channel, C.c_int32),
+                                         _ptr(enabled, C.c_uint8), _ptr(rxprob, C.c_double), _ptr(txprob, C.c_double),
+                                         _ptr(id_int, C.c_int32)))
+        self.n = n
+
+    def set_matrix(self, matrix):
+        m = np.ascontiguousarray(matrix, dtype=np.float64)
+        n = int(round(m.size ** 0.5))
+        if n * n != m.size:
+            raise ValueError("matrix must be square (flat row-major n*n)")
+        self._ck(self._lib.rmb_set_matrix(self._h, n, _ptr(m.reshape(-1), C.c_double)))
+
+    def update_positions(self, x, y, z=None, idx=None):
+        x = _arr(x, np.float64)
+        c = x.shape[0]
+        y, z, idx = _arr(y, np.float64, c), _arr(z, np.float64, c), _arr(idx, np.int32, c)
+        self._ck(self._lib.rmb_update_positions(self._h, c, _ptr(idx, C.c_int32), _ptr(x, C.c_double),
+                                                _ptr(y, C.c_double), _ptr(z, C.c_double)))
+
+    def update_radio(self, idx=None, txpower_dbm=None, channel=None, enabled=None, rxprob=None, txprob=None):
+        fields = [f for f in (txpower_dbm, channel, enabled, rxprob, txprob) if f is not None]
+        c = len(idx) if idx is not None else (len(fields[0]) if fields else 0)
+        idx = _arr(idx, np.int32, c)
+        txpower_dbm, rxprob, txprob = _arr(txpower_dbm, np.float64, c), _arr(rxprob, np.float64, c), _arr(txprob, np.float64, c)
+        channel, enabled = _arr(channel, np.int32, c), _arr(enabled, np.uint8, c)
+        self._ck(self._lib.rmb_update_radio(self._h, c, _ptr(idx, C.c_int32), _ptr(txpower_dbm, C.c_double),
+                                            _ptr(channel, C.c_int32), _ptr(enabled, C.c_uint8),
+                                            _ptr(rxprob, C.c_double), _ptr(txprob, C.c_double)))
+
+    # -- the tick (batched RadioMedium.transmit) ----------------------------------------------------
+    def tick(self, src, power_dbm=None, channel=None, uniforms=None, copy=True, allow_short_uniforms=False):
+        src = _arr(src, np.int32)
+        t = src.shape[0]
+        power_dbm, channel = _arr(power_dbm, np.float64, t), _arr(channel, np.int32, t)
+        uniforms = _arr(uniforms, np.float64)
+        r = A.Result()
+        rc = self._lib.rmb_tick(self._h, t, _ptr(src, C.c_int32), _ptr(power_dbm, C.c_double), _ptr(channel, C.c_int32),
+                                _ptr(uniforms, C.c_double), 0 if uniforms is None else uniforms.shape[0], C.byref(r))
+        self._ck(rc, allow=(A.ERR_UNIFORMS,) if allow_short_uniforms else ())
+        res = TickResult(r, self._f64, copy)
+        res.status = rc
+        return res
+
+    def build_tx_records(self, src, d_records, power_dbm=None, channel=None):
+        """Write this tick's records for locally owned sources to DEVICE memory (int address)."""
+        src = _arr(src, np.int32)
+        t = src.shape[0]
+        power_dbm, channel = _arr(power_dbm, np.float64, t), _arr(channel, np.int32, t)
+        self._ck(self._lib.rmb_build_tx_records(self._h, t, _ptr(src, C.c_int32), _ptr(power_dbm, C.c_double),
+                                                _ptr(channel, C.c_int32), C.c_void_p(d_records)))
+
+    def tick_records(self, n_tx, d_records, uniforms=None, copy=True):
+        uniforms = _arr(uniforms, np.float64)
+        r = A.Result()
+        self._ck(self._lib.rmb_tick_records(self._h, n_tx, C.c_void_p(d_records), _ptr(uniforms, C.c_double),
+                                            0 if uniforms is None else uniforms.shape[0], C.byref(r)))
+        return TickResult(r, self._f64, copy)
+
+    def tick_resident(self, n_tx, d_records):
+        r = A.Result()
+        self._ck(self._lib.rmb_tick_resident(self._h, n_tx, C.c_void_p(d_records), C.byref(r)))
+        return TickResult(r, False, True)
+
+    def fetch(self, copy=True):
+        r = A.Result()
+        self._ck(self._lib.rmb_fetch(self._h, C.byref(r)))
+        return TickResult(r, self._f64, copy)
+
+    # -- node-info (Transciever.getRSSI / getBaseRSSI) ---------------------------------------------
+    def node_info(self):
+        rssi = np.zeros(max(self.n, 1), dtype=np.float32)
+        recv = np.zeros(max(self.n, 1), dtype=np.uint8)
+        self._ck(self._lib.rmb_node_info(self._h, _ptr(rssi, C.c_float), _ptr(recv, C.c_uint8)))
+        return rssi[:self.n], recv[:self.n]
+
+    def timing(self):
+        t = A.Timing()
+        self._ck(self._lib.rmb_last_timing(self._h, C.byref(t)))
+        return {k: getattr(t, k) for k, _ in A.Timing._fields_}
+
+    def set_tuning(self, sweep_variant=0, near_slots=0):
+        self._ck(self._lib.rmb_set_tuning(self._h, sweep_variant, near_slots))
