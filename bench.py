@@ -1,0 +1,295 @@
+#!/usr/bin/env python
+"""bench.py -- (tx,rx) SINR link decisions per second per tick (BASELINE.json metric).
+
+Workload (config.workload): BASELINE.json configs[3], the tick the metric and north_star are quoted
+on -- 1 000 000 nodes uniform in a 10 km square, 10 000 concurrent transmitters, one channel,
+log-distance path loss + co-channel interference + SINR decisions.  It fits one B200, so the same
+tick is used at every N; at N > 1 the receivers are block-partitioned over the ranks (strong
+scaling, as north_star asks) and the tick's tx records are all-gathered with NCCL.
+
+A "step" is one tick.  `value` = decisions / time with the tick's tx records resident in HBM and the
+result lists left in HBM; `e2e` = the same tick through the public C-ABI call (rmb_tick /
+rmb_build_tx_records + all-gather + rmb_tick_records) with HOST packet lists in and HOST result lists
+out.  Timing: every step is bracketed by barrier + device synchronise; the L2 is flushed (256 MiB
+write) before each timed step; the per-step times are summed and the max over ranks is used.
+
+`--impl reference`: the reference is Java and cannot be built here (no JVM), so this arm times the
+oracle port of the medium's loop (oracle/, plain C, all host threads) on a bounded sample of the
+same workload; rank 0 only.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np
+
+N_NODES, N_TX, SIDE = 1_000_000, 10_000, 10_000.0
+METRIC = "tx_rx_sinr_link_decisions_per_sec"
+UNIT = "decisions/s"
+WORKLOAD = "1M-node random deployment (10 km square), 10k concurrent transmitters, single channel, SINR (BASELINE configs[3])"
+# Algorithmic work per decision on the dominant kernel (DESIGN.md "K1"): ONE MUFU (rsqrt) op.
+# The XU (MUFU) pipe issues 16 lanes/SM/clk -> peak = 148 SMs * 16 * f_SM pairs/s.
+SMS, XU_LANES = 148, 16
+CPU_SAMPLE_NODES = 50_000
+
+
+def deployment(grid=False):
+    rng = np.random.default_rng(3)
+    if grid:
+        g = np.arange(1000, dtype=np.float64) * 10.0
+        x, y = np.meshgrid(g, g)
+        x, y = x.reshape(-1).copy(), y.reshape(-1).copy()
+        rng.uniform(size=2 * N_NODES)
+    else:
+        x, y = rng.uniform(0, SIDE, N_NODES), rng.uniform(0, SIDE, N_NODES)
+    src = rng.permutation(N_NODES)[:N_TX].astype(np.int32)
+    return x, y, src
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.stop_flag, self.max_mhz = index, [], set(), False, None
+        self.active = False
+
+    def run(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            names = {"hw_slowdown": nv.nvmlClocksThrottleReasonHwSlowdown,
+                     "hw_thermal_slowdown": nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+                     "sw_thermal_slowdown": nv.nvmlClocksThrottleReasonSwThermalSlowdown,
+                     "sw_power_cap": nv.nvmlClocksThrottleReasonSwPowerCap}
+            while not self.stop_flag:
+                if self.active:
+                    self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                    for k, bit in names.items():
+                        if r & bit:
+                            self.reasons.add(k)
+                time.sleep(0.005)
+        except Exception as e:          # NVML missing: report that rather than invent clocks
+            self.reasons.add(f"nvml_unavailable:{type(e).__name__}")
+
+    def summary(self):
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+def cpu_reference_sample(threads, steps=1, warmup=0):
+    """The oracle port of the medium loop on a bounded sample: the 10k transmitters plus the first
+    nodes of the deployment up to CPU_SAMPLE_NODES receivers, all 10k packets."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle_py as orc
+    x, y, src = deployment()
+    keep = np.zeros(N_NODES, dtype=bool)
+    keep[src] = True
+    extra = np.flatnonzero(~keep)[:CPU_SAMPLE_NODES - N_TX]
+    keep[extra] = True
+    idx = np.flatnonzero(keep)
+    remap = -np.ones(N_NODES, dtype=np.int64)
+    remap[idx] = np.arange(idx.size)
+    nodes = orc.NodeSet(x[idx], y[idx])
+    pk = orc.make_packets(remap[src].astype(np.int32), 0.0, 26)
+    p = orc.params(orc.MODEL_SINR)
+    times, dec = [], 0
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        r = orc.tick(p, nodes, pk, threads=threads, want_pairs=True, cap=4_000_000)
+        dt = time.perf_counter() - t0
+        dec = r["n_decisions"]
+        if i >= warmup:
+            times.append(dt)
+    return dec, times, f"{idx.size} receivers (the 10k sources + first {idx.size - N_TX} other nodes) x {N_TX} packets of the same tick"
+
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def run_reference(args):
+    """--impl reference: rank 0 times the CPU port of the reference loop; other ranks exit 0."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    cores = host_threads()
+    dec, times, sample = cpu_reference_sample(cores, steps=args.steps, warmup=args.warmup)
+    total = sum(times)
+    value = dec * len(times) / total
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times), "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "sample": sample},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import radio_sim_b200 as rsb
+
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the medium has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    G = world
+
+    x, y, src = deployment(args.grid)
+    lo, hi = rank * N_NODES // G, (rank + 1) * N_NODES // G
+    med = rsb.Medium("sinr", device=local, rx_base=lo, n_shards=G)
+    med.set_nodes(x[lo:hi], y[lo:hi])
+    if args.variant:
+        med.set_tuning(args.variant, 0)
+
+    # tx records: every rank contributes the packets whose source it owns, padded to a common length
+    counts = [int(((src >= r * N_NODES // G) & (src < (r + 1) * N_NODES // G)).sum()) for r in range(G)]
+    tpad = max(counts)
+    mine = src[(src >= lo) & (src < hi)]
+    mine_padded = np.full(tpad, -1, dtype=np.int32)
+    mine_padded[:mine.size] = mine
+    rec_local = torch.zeros(tpad * 48, dtype=torch.uint8, device=dev)
+    rec_all = torch.zeros(G * tpad * 48, dtype=torch.uint8, device=dev) if G > 1 else rec_local
+    n_rec = G * tpad
+    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def exchange():
+        if G > 1:
+            dist.all_gather_into_tensor(rec_all, rec_local)
+            torch.cuda.current_stream().synchronize()
+
+    def step_resident():
+        exchange()
+        return med.tick_resident(n_rec, rec_all.data_ptr())
+
+    def step_e2e():
+        if G == 1:
+            return med.tick(src, copy=False)
+        med.build_tx_records(mine_padded, rec_local.data_ptr())
+        exchange()
+        return med.tick_records(n_rec, rec_all.data_ptr(), copy=False)
+
+    def timed(fn, steps, sampler=None):
+        times, res, sweep_ms, launches = [], None, [], 0
+        for _ in range(steps):
+            flush_buf.fill_(1)                      # evict L2 between timed iterations
+            torch.cuda.synchronize()
+            if G > 1:
+                dist.barrier()
+            if sampler:
+                sampler.active = True
+            t0 = time.perf_counter()
+            res = fn()
+            torch.cuda.synchronize()
+            times.append(time.perf_counter() - t0)
+            if sampler:
+                sampler.active = False
+            tm = med.timing()
+            sweep_ms.append(tm["ms_sweep"]); launches += tm["kernel_launches"]
+        return times, res, sweep_ms, launches
+
+    med.build_tx_records(mine_padded, rec_local.data_ptr())
+    sampler = ClockSampler(local)
+    sampler.start()
+    timed(step_resident, args.warmup)
+    times, res, sweep_ms, launches = timed(step_resident, args.steps, sampler)
+    local_dec = res.n_decisions
+    timed(step_e2e, args.warmup)
+    e_times, e_res, _, _ = timed(step_e2e, args.steps)
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+
+    tot = torch.tensor([sum(times), sum(e_times)], dtype=torch.float64, device=dev)
+    cnt = torch.tensor([float(local_dec), float(e_res.n_pairs)], dtype=torch.float64, device=dev)
+    if G > 1:
+        dist.all_reduce(tot, op=dist.ReduceOp.MAX)
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+    t_res, t_e2e = float(tot[0]), float(tot[1])
+    decisions, pairs = float(cnt[0]), float(cnt[1])
+    if rank == 0:
+        clocks = sampler.summary()
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        f_max = (clocks["sm_max_mhz"] or peaks.get("sm_max_mhz") or 1965.0) * 1e6
+        f_run = (clocks["sm_mhz"] or 0) * 1e6
+        ms_sweep = float(np.mean(sweep_ms))
+        achieved = local_dec / (ms_sweep * 1e-3)                       # MUFU ops (== decisions) per second, this GPU
+        peak = SMS * XU_LANES * f_max
+        hbm_bytes = 32.0 * (hi - lo) + 32.0 * N_TX                     # algorithmic bytes of one sweep launch
+        traffic = None
+        try:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "sweep_traffic.json")))["dram_bytes_per_launch"]
+        except Exception:
+            pass
+        line = {"metric": METRIC, "value": decisions * args.steps / t_res, "unit": UNIT, "n_gpus": G,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_res / args.steps,
+                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32+f64",
+                "data": "synthetic",
+                "config": {"workload": WORKLOAD, "deployment": "grid" if args.grid else "random", "nodes": N_NODES,
+                           "transmitters": N_TX, "parallelism": f"receivers sharded x{G}",
+                           "l2": "flushed (256 MiB write) before every timed step",
+                           "timing": "host clock between device synchronisations, per step, max over ranks"},
+                "clocks": clocks,
+                "e2e": {"value": decisions * args.steps / t_e2e, "unit": UNIT, "ms_per_step": 1e3 * t_e2e / args.steps,
+                        "h2d_bytes_per_step": int(4 * (src.size if G == 1 else tpad)),
+                        "d2h_bytes_per_step": int(17 * pairs / G + n_rec + 96), "heard_pairs": int(pairs)},
+                "gpu_launches": int(launches),
+                "roofline": {"bound": "sfu", "kernel": "sweep_kernel", "achieved": achieved / 1e9, "peak": peak / 1e9,
+                             "unit": "G MUFU-op/s (1 rsqrt per decision; peak = 148 SM x 16 lanes x sm_max_mhz)",
+                             "frac": achieved / peak,
+                             "frac_at_sampled_clock": (achieved / (SMS * XU_LANES * f_run)) if f_run else None,
+                             "ms_per_launch": ms_sweep, "traffic": traffic,
+                             "hbm": {"achieved_gbs": hbm_bytes / (ms_sweep * 1e-3) / 1e9, "peak_gbs": peaks.get("hbm_gbs"),
+                                     "note": "algorithmic bytes (32 B/receiver + 32 B/tx) / sweep time: HBM is not the binding roofline"}}}
+        if G == 1 and not args.no_cpu:
+            cores = host_threads()
+            dec_c, t_c, sample = cpu_reference_sample(cores)
+            line["cpu_baseline"] = {"value": dec_c / t_c[0], "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
+        print(json.dumps(line), flush=True)
+    med.close()
+    if G > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--grid", action="store_true", help="1000x1000 grid deployment (10 m pitch) instead of random")
+    ap.add_argument("--variant", type=int, default=0, help="sweep kernel variant (tuning)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

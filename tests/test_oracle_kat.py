@@ -1,0 +1,87 @@
+"""CPU: the oracle against hand-derived known-answer cases (tests/golden/kat_reference_media.json).
+The reference holds no golden vectors for this path; these follow from its source."""
+import json
+import os
+import numpy as np
+import pytest
+
+KAT = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "kat_reference_media.json")))
+MODEL = {"null": 0, "udgm": 1, "udgm-constant": 2, "n2n": 3, "sinr": 4}
+
+
+def oracle_case(orc, c):
+    n = len(c["x"])
+    nodes = orc.NodeSet(np.array(c["x"], float), np.array(c["y"], float), channel=c.get("channel"),
+                        enabled=c.get("enabled"), rxprob=c.get("rxprob"), txprob=c.get("txprob"))
+    src = np.array(c["src"], dtype=np.int32)
+    txp = np.array(c.get("txpower", [0.0] * n))
+    ch = np.array(c.get("pkt_channel", nodes.channel[src]))
+    kw = dict(c.get("params", {}))
+    if "matrix" in c:
+        kw["matrix"] = np.array(c["matrix"], float)
+    return orc.tick(orc.params(MODEL[c["model"]], **kw), nodes, orc.make_packets(src, txp[src], ch))
+
+
+def test_java_util_random(orc):
+    assert orc.jrandom_doubles(KAT["jrandom"]["seed"], 3).tolist() == KAT["jrandom"]["next_double"]
+
+
+@pytest.mark.parametrize("c", KAT["cases"], ids=[c["name"] for c in KAT["cases"]])
+def test_known_answers(orc, c):
+    r = oracle_case(orc, c)
+    got = [[int(p["tx"]), int(p["rx"]), int(p["outcome"])] for p in r["pairs"]]
+    assert got == c["expect"], c["why"]
+    if "tx_failed" in c:
+        assert r["tx_failed"].tolist() == c["tx_failed"]
+    if "rssi" in c:
+        assert r["pairs"]["rssi_dbm"].tolist() == c["rssi"]
+
+
+def test_distance_is_unfused(orc):
+    L = orc.lib()
+    assert L.orc_distance(0, 0, 0, 30, 40, 0) == 50.0
+    assert L.orc_distance(1, 2, 3, 1, 2, 3) == 0.0
+
+
+def test_strict_math_matches_libm_within_1ulp(orc):
+    L = orc.lib()
+    rng = np.random.default_rng(0)
+    for v in np.concatenate([rng.uniform(1e-12, 1e6, 2000), [1.0, 10.0, 0.1, 2.0 ** -1022]]):
+        for f, g in ((L.orc_log, np.log), (L.orc_log10, np.log10)):
+            a, b = f(float(v)), float(g(v))
+            assert abs(a - b) <= 2 * np.spacing(abs(b)) + 1e-300
+    for v in rng.uniform(-60, 5, 2000):
+        a, b = L.orc_exp(float(v)), float(np.exp(v))
+        assert abs(a - b) <= 2 * np.spacing(b)
+
+
+def test_sinr_spec_values(orc):
+    p = orc.params(orc.MODEL_SINR)
+    L = orc.lib()
+    import ctypes as C
+    assert L.orc_sinr_rx_power_dbm(C.byref(p), 0.0, 10.0) == pytest.approx(-70.05, abs=1e-12)
+    assert L.orc_sinr_rx_power_dbm(C.byref(p), 0.0, 0.5) == -40.05          # clamped to d0
+    # a lone transmitter: SINR = Prx - noise floor
+    r = orc.tick(p, orc.NodeSet(np.array([0.0, 10.0]), np.zeros(2)), orc.make_packets([0], 0.0, 26), want_total=True)
+    assert r["pairs"]["sinr_db"][0] == pytest.approx(-70.05 + 100.0, abs=1e-9)
+    assert r["pairs"]["outcome"][0] == orc.DELIVERED
+    assert r["total_dbm"][0] == pytest.approx(-100.0, abs=1e-9)          # the source itself hears only noise
+
+
+def test_sinr_collision_two_equal_transmitters(orc):
+    # receiver midway between two equal-power transmitters: SINR ~ 0 dB < 4 dB -> both interfered
+    x = np.array([0.0, 20.0, 40.0])
+    r = orc.tick(orc.params(orc.MODEL_SINR), orc.NodeSet(x, np.zeros(3)), orc.make_packets([0, 2], 0.0, 26))
+    mid = r["pairs"][r["pairs"]["rx"] == 1]
+    assert len(mid) == 2 and (mid["outcome"] == orc.INTERFERED).all()
+    assert np.all(np.abs(mid["sinr_db"]) < 0.1)
+
+
+def test_draw_order_and_exhaustion(orc):
+    x = np.arange(6, dtype=float)
+    nodes = orc.NodeSet(x, np.zeros(6), rxprob=np.array([1, .5, .5, 1, .5, 1.0]), txprob=np.array([.5, 1, 1, 1, 1, 1.0]))
+    u = np.array([0.4, 0.6, 0.4, 0.9])       # tx draw 0.4 <= .5 ok; rx1 0.6 > .5 interfered; rx2 0.4 delivered; rx4 0.9 interfered
+    r = orc.tick(orc.params(orc.MODEL_UDGM), nodes, orc.make_packets([0], 0.0, 26), uniforms=u)
+    assert r["pairs"]["outcome"].tolist() == [1, 2, 2, 1, 2] and r["n_uniforms_used"] == 4 and r["status"] == 0
+    r = orc.tick(orc.params(orc.MODEL_UDGM), nodes, orc.make_packets([0], 0.0, 26), uniforms=u[:2])
+    assert r["status"] == -2
