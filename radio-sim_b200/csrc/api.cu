@@ -86,7 +86,7 @@ struct rmb_handle {
 
     // slots
     int K = 8;
-    DevBuf<int> slots, cnt, hcnt, hoff, recheck; DevBuf<float> far_sum;
+    DevBuf<int> slots, cnt, hcnt, hoff, recheck; DevBuf<float> far_part; int splits = 1, forced_splits = 0;
     DevBuf<double> sl_prx, sl_lin, sl_sinr, itot; DevBuf<uint8_t> sl_flags;
 
     // pairs
@@ -135,7 +135,7 @@ TxTiles tx_tiles(rmb_handle *h)
 }
 SlotArrays slot_arrays(rmb_handle *h)
 {
-    SlotArrays s; s.K = h->K; s.slots = h->slots.p; s.cnt = h->cnt.p; s.far_sum = h->far_sum.p; s.prx = h->sl_prx.p;
+    SlotArrays s; s.K = h->K; s.slots = h->slots.p; s.cnt = h->cnt.p; s.far_part = h->far_part.p; s.splits = h->splits; s.prx = h->sl_prx.p;
     s.lin = h->sl_lin.p; s.sinr = h->sl_sinr.p; s.flags = h->sl_flags.p; s.hcnt = h->hcnt.p; s.itot = h->itot.p;
     s.recheck = h->recheck.p;
     return s;
@@ -170,7 +170,7 @@ static int ensure_slots(rmb_handle *h)
     RMB_CK(h, h->slots.ensure(nk)); RMB_CK(h, h->sl_prx.ensure(nk)); RMB_CK(h, h->sl_lin.ensure(nk));
     RMB_CK(h, h->sl_sinr.ensure(nk)); RMB_CK(h, h->sl_flags.ensure(nk));
     RMB_CK(h, h->cnt.ensure(nw)); RMB_CK(h, h->hcnt.ensure(nw)); RMB_CK(h, h->hoff.ensure(nw + 2));
-    RMB_CK(h, h->recheck.ensure(nw)); RMB_CK(h, h->far_sum.ensure(nw)); RMB_CK(h, h->itot.ensure(nw));
+    RMB_CK(h, h->recheck.ensure(nw)); RMB_CK(h, h->far_part.ensure(nw)); RMB_CK(h, h->itot.ensure(nw));
     RMB_CK(h, h->scan_tmp.ensure(nw / 1024 + 8));
     return RMB_OK;
 }
@@ -326,7 +326,7 @@ int rmb_destroy(rmb_handle *h)
     h->pk_channel.release(); h->pk_power.release(); h->pk_stage.release(); h->rec.release(); h->txf.release();
     h->theta.release(); h->theta_min_g.release(); h->arrival.release(); h->goff.release(); h->gcount.release();
     h->uniforms.release(); h->slots.release(); h->cnt.release(); h->hcnt.release(); h->hoff.release();
-    h->recheck.release(); h->far_sum.release(); h->sl_prx.release(); h->sl_lin.release(); h->sl_sinr.release();
+    h->recheck.release(); h->far_part.release(); h->sl_prx.release(); h->sl_lin.release(); h->sl_sinr.release();
     h->itot.release(); h->sl_flags.release(); h->key.release(); h->key_alt.release(); h->val.release();
     h->val_alt.release(); h->pr_p.release(); h->pr_rssi.release(); h->pr_sinr.release(); h->pr_cand.release();
     h->draw_scan.release(); h->seg.release(); h->scan_tmp.release(); h->blkcnt.release(); h->tx_base.release();
@@ -461,7 +461,9 @@ extern "C" int rmb_set_tuning(rmb_handle *h, int32_t sweep_variant, int32_t near
     if (!h) return RMB_ERR_INVALID;
     std::lock_guard<std::mutex> lk(h->mu);
     RMB_CK(h, cudaSetDevice(h->cfg.device));
-    h->sweep_variant = sweep_variant;
+    // low byte: kernel variant; bits 8..15: forced number of tx splits (0 = planned per tick)
+    h->sweep_variant = sweep_variant & 0xff;
+    h->forced_splits = (sweep_variant >> 8) & 0xff;
     if (near_slots > 0 && near_slots != h->K) { h->K = near_slots; return ensure_slots(h); }
     return RMB_OK;
 }
@@ -544,6 +546,9 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
         const size_t tcap = (size_t)n_tx + (size_t)(h->groups.ngroups + 1) * kTile;
         RMB_CK(h, h->txf.ensure(tcap)); RMB_CK(h, h->theta.ensure(tcap)); RMB_CK(h, h->arrival.ensure(tcap));
         TxTiles tx = tx_tiles(h);
+        const int mode = sweep_mode_for_exponent(h->cfg.pl_exponent);
+        h->splits = sweep_plan(mode, h->planar, h->sweep_variant, h->n_work, n_tx / std::max(1, h->groups.ngroups), h->forced_splits);
+        RMB_CK(h, h->far_part.ensure((size_t)h->splits * (size_t)std::max(h->n_work, 1)));
         RMB_CK(h, launch_prepare(nd, h->dp.p, h->geom.p, h->groups, n_tx, d_rec, tx, h->theta.p, h->theta_min_g.p, h->ctr.p, h->st));
         ++launches;
         RMB_CK(h, cudaEventRecord(h->ev[1], h->st));
@@ -551,9 +556,10 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
             SweepArgs a;
             a.fx = h->fx.p; a.fy = h->fy.p; a.fz = h->fz.p; a.groups = h->groups; a.tx = tx; a.theta = h->theta.p;
             a.theta_min_g = h->theta_min_g.p; a.neg_h = (float)(-0.5 * h->cfg.pl_exponent);
-            a.far_out = h->far_sum.p; a.cnt_out = h->cnt.p; a.slots = h->slots.p; a.K = h->K; a.ctr = h->ctr.p;
+            a.far_part = h->far_part.p; a.cnt = h->cnt.p; a.slots = h->slots.p; a.K = h->K;
+            RMB_CK(h, cudaMemsetAsync(h->cnt.p, 0, (size_t)h->n_work * sizeof(int), h->st));
             if (attempt) RMB_CK(h, cudaEventRecord(h->ev[1], h->st));
-            RMB_CK(h, launch_sweep(sweep_mode_for_exponent(h->cfg.pl_exponent), h->planar, h->sweep_variant, h->n_work, a, h->st));
+            RMB_CK(h, launch_sweep(mode, h->planar, h->sweep_variant, h->n_work, h->splits, a, h->st));
             ++launches; ++sweeps;
             RMB_CK(h, cudaEventRecord(h->ev[2], h->st));
             RMB_CK(h, launch_resolve(nd, wk, h->dp.p, tx, d_rec, slot_arrays(h), h->node_rssi.p, h->node_recv.p, h->ctr.p, h->st));

@@ -7,8 +7,7 @@
 namespace rmb {
 
 constexpr int kMaxGroups = 64;        // distinct receiver channels handled per tick
-constexpr int kTile = 8;              // tx per unrolled tile in the sweep (near test granularity)
-constexpr int kStageTx = 2048;        // tx records per shared-memory stage (32 KB of float4)
+constexpr int kTile = 16;             // tx per unrolled tile in the sweep (near test granularity)
 
 // model parameters as the kernels see them
 struct DevParams {

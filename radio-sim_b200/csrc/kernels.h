@@ -43,20 +43,22 @@ struct SweepArgs {
     TxTiles tx;
     const float *theta, *theta_min_g;
     float neg_h;                      // -n/2 (general-exponent mode)
-    float *far_out;
-    int *cnt_out, *slots;
+    float *far_part;                  // [splits][n_work] partial far-field sums
+    int *cnt, *slots;                 // cnt must be zero on entry (atomic append of near candidates)
     int K;
-    Counters *ctr;
 };
 int sweep_mode_for_exponent(double n);
-cudaError_t launch_sweep(int mode, bool planar, int variant, int n_work, const SweepArgs &a, cudaStream_t st);
+// number of tx splits (grid.y) for a bucket of about n_tx_bucket transmissions; forced_splits > 0 overrides
+int sweep_plan(int mode, bool planar, int variant, int n_work, int n_tx_bucket, int forced_splits);
+cudaError_t launch_sweep(int mode, bool planar, int variant, int n_work, int splits, const SweepArgs &a, cudaStream_t st);
 
 // ---- exact resolve of the near candidates + guard-band recheck --------------------------------
 struct SlotArrays {
     int K;
-    int *slots;                       // [n_work*K] bucket position j of the candidate
+    int *slots;                       // [n_work*K] bucket position j of the candidate (resolve sorts them ascending)
     int *cnt;                         // [n_work] candidates found (may exceed K => retry)
-    float *far_sum;                   // [n_work] fp32 far-field interference sum [mW]
+    float *far_part;                  // [splits][n_work] fp32 partial far-field interference sums [mW]
+    int splits;
     double *prx, *lin, *sinr;         // [n_work*K] exact values per candidate
     uint8_t *flags;                   // [n_work*K] kHeard | kDecodable
     int *hcnt;                        // [n_work] heard pairs of the receiver

@@ -39,12 +39,24 @@ resolve_kernel(NodeArrays nd, WorkArrays wk, const DevParams *dp, TxTiles tx, co
         const int p = wk.perm[w];
         if (p >= 0) {
             const int K = sl.K;
-            const int c = min(sl.cnt[w], K);
+            const int found = sl.cnt[w];
+            if (found > K) atomicMax(&ctr->max_near, found);      // slot overflow: the host grows K and redoes the sweep
+            const int c = min(found, K);
             const double X = nd.x[p], Y = nd.y[p], Z = nd.z[p];
             const double rxp = nd.rxprob[p];
             const int self = dp->rx_base + p;
-            double itot = xm::add(dp->n0_mw, (double)sl.far_sum[w]);
+            // far field: the sweep's per-split partial sums, added in split order (deterministic)
+            double far = 0.0;
+            for (int s = 0; s < sl.splits; ++s) far = xm::add(far, (double)sl.far_part[(size_t)s * wk.n_work + w]);
+            double itot = xm::add(dp->n0_mw, far);
             const size_t base = (size_t)w * K;
+            // the sweep appends near candidates in arbitrary order: sort by bucket position (= arrival order)
+            for (int a = 1; a < c; ++a) {
+                const int v = sl.slots[base + a];
+                int b = a - 1;
+                while (b >= 0 && sl.slots[base + b] > v) { sl.slots[base + b + 1] = sl.slots[base + b]; --b; }
+                sl.slots[base + b + 1] = v;
+            }
             for (int s = 0; s < c; ++s) {
                 const int t = tx.arrival[sl.slots[base + s]];
                 const rmb_tx_record r = rec[t];

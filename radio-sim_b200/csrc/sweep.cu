@@ -1,7 +1,7 @@
 // sweep.cu -- K1, the link-budget / interference sweep (the hot kernel).
 //
-// For every enabled receiver (work order: grouped by channel) and every co-channel
-// transmission of the tick it evaluates the log-distance link budget
+// For every enabled receiver (work order: grouped by channel, spatially sorted inside a group)
+// and every co-channel transmission of the tick it evaluates the log-distance link budget
 //     lin(t,r) = P_t * d(t,r)^-n   [mW]              
 // and accumulates the co-channel interference sum in the linear domain (N2).  Replaces the
 // O(N) receiver loop of RadioMedium.transmit (UDGMRadioMedium.java:99-114) for all the
@@ -10,9 +10,17 @@
 // Formulation (DESIGN.md "K1"): the tx power is folded into the geometry.  With
 // c_t = P_t^(-1/n) the kernel works on scaled coordinates x' = c_t*x, so that
 //     d2' = c_t^2 * d^2   and   lin = (d2')^(-n/2)
-// i.e. per pair 2 FFMA (scaled differences) + FMUL + FFMA (d2') + ONE MUFU (rsqrt / rcp;
-// lg2+ex2 for a general exponent) + 1-2 FP32 ops to accumulate.  The MUFU (XU) pipe,
-// 16 lanes/SM/clk, is the binding unit.
+// Blackwell packed fp32 (FFMA2 / FMUL2, `fma.rn.f32x2`): one instruction handles the SAME
+// receiver against TWO transmissions (the shared-memory tx stage is SoA, so a 64-bit LDS
+// yields {c_j, c_j+1} directly; the receiver coordinate is duplicated once in registers).
+// Per pair: 2.5 FMA-pipe issue slots + ONE MUFU (rsqrt / rcp; lg2+ex2 for a general
+// exponent).  The MUFU (XU) pipe, 16 lanes/SM/clk, is the binding unit.
+//
+// Decomposition: grid = (receiver blocks) x (tx splits).  A block owns THREADS*R receivers
+// and 1/S of its channel bucket; it writes one fp32 partial far-field sum per receiver
+// (far_part[split][w], summed in fixed order by the resolve kernel -> deterministic).  S is
+// chosen on the host so that the grid is many waves deep (tail < 5 %) even when the
+// receivers are sharded over 8 GPUs.
 //
 // "Near" pairs -- those that might be heard (lin >= theta_t) or whose fp32 geometry is
 // not accurate enough (d <= D_near) -- are NOT summed here: they are detected per tile of
@@ -26,44 +34,51 @@ namespace rmb {
 
 enum { MODE_N2 = 0, MODE_N3 = 1, MODE_N4 = 2, MODE_GEN = 3 };
 
+typedef unsigned long long f32x2;     // two fp32 lanes in one 64-bit register pair
+
 __device__ __forceinline__ float mufu_rsq(float x) { float y; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ float mufu_rcp(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ float mufu_lg2(float x) { float y; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ float mufu_ex2(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 
-// scaled squared distance; t = {x', y', z', c}
-template <bool PLANAR>
-__device__ __forceinline__ float scaled_d2(float rx, float ry, float rz, const float4 &t)
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void unpack2(f32x2 v, float &lo, float &hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) { f32x2 d; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) { f32x2 d; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+
+// (d2)^(-n/2), one pair, scalar (rescan path)
+template <int MODE>
+__device__ __forceinline__ float lin_of(float d2, float neg_h)
 {
-    float dx = __fmaf_rn(rx, t.w, -t.x);
-    float dy = __fmaf_rn(ry, t.w, -t.y);
-    float d2 = __fmaf_rn(dy, dy, __fmul_rn(dx, dx));
-    if (!PLANAR) {
-        float dz = __fmaf_rn(rz, t.w, -t.z);
-        d2 = __fmaf_rn(dz, dz, d2);
-    }
-    return d2;
+    if (MODE == MODE_N3) { float q = mufu_rsq(d2); return __fmul_rn(__fmul_rn(q, q), q); }
+    if (MODE == MODE_N2) return mufu_rcp(d2);
+    if (MODE == MODE_N4) { float q = mufu_rcp(d2); return __fmul_rn(q, q); }
+    return mufu_ex2(__fmul_rn(neg_h, mufu_lg2(d2)));
 }
 
-// acc + (d2)^(-n/2)
+// acc + (d2)^(-n/2) on both lanes
 template <int MODE>
-__device__ __forceinline__ float accumulate(float d2, float acc, float neg_h)
+__device__ __forceinline__ f32x2 accumulate2(f32x2 d2, f32x2 acc, float neg_h)
 {
-    if (MODE == MODE_N3) { float q = mufu_rsq(d2); return __fmaf_rn(__fmul_rn(q, q), q, acc); }
-    if (MODE == MODE_N2) { return __fadd_rn(acc, mufu_rcp(d2)); }
-    if (MODE == MODE_N4) { float q = mufu_rcp(d2); return __fmaf_rn(q, q, acc); }
-    return __fadd_rn(acc, mufu_ex2(__fmul_rn(neg_h, mufu_lg2(d2))));
+    float a, b;
+    unpack2(d2, a, b);
+    if (MODE == MODE_N3) { f32x2 q = pack2(mufu_rsq(a), mufu_rsq(b)); return fma2(mul2(q, q), q, acc); }
+    if (MODE == MODE_N2) return add2(acc, pack2(mufu_rcp(a), mufu_rcp(b)));
+    if (MODE == MODE_N4) { f32x2 q = pack2(mufu_rcp(a), mufu_rcp(b)); return fma2(q, q, acc); }
+    return add2(acc, pack2(mufu_ex2(__fmul_rn(neg_h, mufu_lg2(a))), mufu_ex2(__fmul_rn(neg_h, mufu_lg2(b)))));
 }
+
+constexpr int kStage = 1024;          // tx per shared-memory stage (SoA: c, -x', -y', -z', theta)
 
 template <int MODE, bool PLANAR, int R, int THREADS>
 __global__ void __launch_bounds__(THREADS)
 sweep_kernel(const float *__restrict__ fx, const float *__restrict__ fy, const float *__restrict__ fz,
              Groups groups, TxTiles tx, const float *__restrict__ theta, const float *__restrict__ theta_min_g,
-             float neg_h, float *__restrict__ far_out, int *__restrict__ cnt_out, int *__restrict__ slots,
-             int K, Counters *ctr)
+             float neg_h, float *__restrict__ far_part, int *__restrict__ cnt, int *__restrict__ slots,
+             int K, int n_work)
 {
-    __shared__ float4 s_tx[kStageTx];
-    __shared__ float  s_theta[kStageTx];
+    __shared__ __align__(16) float s_c[kStage], s_nx[kStage], s_ny[kStage], s_nz[PLANAR ? 4 : kStage], s_theta[kStage];
 
     const int w0 = (blockIdx.x * THREADS + threadIdx.x) * R;
     // the block's receivers all belong to one channel group (groups are padded to 1024)
@@ -71,85 +86,122 @@ sweep_kernel(const float *__restrict__ fx, const float *__restrict__ fy, const f
     int g = 0;
     while (g + 1 < groups.ngroups && wb >= groups.w_begin[g + 1]) ++g;
 
-    float rx[R], ry[R], rz[R], sum[R], ps[R];
-    int cnt[R];
+    // this block's share of the bucket: split blockIdx.y of gridDim.y, a multiple of kTile
+    const int b0 = tx.goff[g], b1 = tx.goff[g + 1];
+    const int per = ((b1 - b0 + (int)gridDim.y - 1) / (int)gridDim.y + kTile - 1) / kTile * kTile;
+    const int j_begin = min(b1, b0 + (int)blockIdx.y * per), j_end = min(b1, j_begin + per);
+
+    float rx[R], ry[R], rz[R], sum[R];
+    f32x2 X[R], Y[R], Z[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
         rx[r] = fx[w0 + r]; ry[r] = fy[w0 + r]; rz[r] = PLANAR ? 0.f : fz[w0 + r];
-        sum[r] = 0.f; ps[r] = 0.f; cnt[r] = 0;
+        X[r] = pack2(rx[r], rx[r]); Y[r] = pack2(ry[r], ry[r]); Z[r] = pack2(rz[r], rz[r]);
+        sum[r] = 0.f;
     }
-    const int j_begin = tx.goff[g], j_end = tx.goff[g + 1];
     const float th_min = theta_min_g[g];
 
-    for (int s0 = j_begin; s0 < j_end; s0 += kStageTx) {
-        const int ns = min(kStageTx, j_end - s0);
+    for (int s0 = j_begin; s0 < j_end; s0 += kStage) {
+        const int ns = min(kStage, j_end - s0);
         __syncthreads();
-        for (int i = threadIdx.x; i < ns; i += THREADS) { s_tx[i] = tx.f[s0 + i]; s_theta[i] = theta[s0 + i]; }
+        for (int i = threadIdx.x; i < ns; i += THREADS) {
+            const float4 t = tx.f[s0 + i];
+            s_c[i] = t.w; s_nx[i] = -t.x; s_ny[i] = -t.y;
+            if (!PLANAR) s_nz[i] = -t.z;
+            s_theta[i] = theta[s0 + i];
+        }
         __syncthreads();
         for (int j = 0; j < ns; j += kTile) {
+            f32x2 ps[R];
 #pragma unroll
-            for (int u = 0; u < kTile; ++u) {
-                const float4 t = s_tx[j + u];
+            for (int r = 0; r < R; ++r) ps[r] = 0ull;
 #pragma unroll
-                for (int r = 0; r < R; ++r)
-                    ps[r] = accumulate<MODE>(scaled_d2<PLANAR>(rx[r], ry[r], rz[r], t), ps[r], neg_h);
+            for (int u = 0; u < kTile; u += 4) {
+                // four transmissions = two packed operands per coordinate (LDS.128, warp-uniform address)
+                const ulonglong2 c2 = *reinterpret_cast<const ulonglong2 *>(&s_c[j + u]);
+                const ulonglong2 x2 = *reinterpret_cast<const ulonglong2 *>(&s_nx[j + u]);
+                const ulonglong2 y2 = *reinterpret_cast<const ulonglong2 *>(&s_ny[j + u]);
+                ulonglong2 z2 = make_ulonglong2(0ull, 0ull);
+                if (!PLANAR) z2 = *reinterpret_cast<const ulonglong2 *>(&s_nz[j + u]);
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    f32x2 dx = fma2(X[r], c2.x, x2.x), dy = fma2(Y[r], c2.x, y2.x);
+                    f32x2 d2 = fma2(dy, dy, mul2(dx, dx));
+                    if (!PLANAR) { f32x2 dz = fma2(Z[r], c2.x, z2.x); d2 = fma2(dz, dz, d2); }
+                    ps[r] = accumulate2<MODE>(d2, ps[r], neg_h);
+                    dx = fma2(X[r], c2.y, x2.y); dy = fma2(Y[r], c2.y, y2.y);
+                    d2 = fma2(dy, dy, mul2(dx, dx));
+                    if (!PLANAR) { f32x2 dz = fma2(Z[r], c2.y, z2.y); d2 = fma2(dz, dz, d2); }
+                    ps[r] = accumulate2<MODE>(d2, ps[r], neg_h);
+                }
             }
-            float m = ps[0];
+            float s[R];
 #pragma unroll
-            for (int r = 1; r < R; ++r) m = fmaxf(m, ps[r]);
+            for (int r = 0; r < R; ++r) { float a, b; unpack2(ps[r], a, b); s[r] = __fadd_rn(a, b); }
+            float m = s[0];
+#pragma unroll
+            for (int r = 1; r < R; ++r) m = fmaxf(m, s[r]);
             if (!(m < th_min)) {
                 // rare: some pair of this tile may be near -- re-scan the affected receivers
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
-                    if (!(ps[r] < th_min)) {
+                    if (!(s[r] < th_min)) {
                         float far = 0.f;
                         for (int u = 0; u < kTile; ++u) {
-                            const float4 t = s_tx[j + u];
-                            const float lin = accumulate<MODE>(scaled_d2<PLANAR>(rx[r], ry[r], rz[r], t), 0.f, neg_h);
+                            const float c = s_c[j + u];
+                            const float dx = __fmaf_rn(rx[r], c, s_nx[j + u]), dy = __fmaf_rn(ry[r], c, s_ny[j + u]);
+                            float d2 = __fmaf_rn(dy, dy, __fmul_rn(dx, dx));
+                            if (!PLANAR) { const float dz = __fmaf_rn(rz[r], c, s_nz[j + u]); d2 = __fmaf_rn(dz, dz, d2); }
+                            const float lin = lin_of<MODE>(d2, neg_h);
                             if (!(lin < s_theta[j + u])) {
-                                if (cnt[r] < K) slots[(size_t)(w0 + r) * K + cnt[r]] = s0 + j + u;
-                                ++cnt[r];
+                                // order of arrival in the slots is arbitrary; resolve sorts them
+                                const int pos = atomicAdd(&cnt[w0 + r], 1);
+                                if (pos < K) slots[(size_t)(w0 + r) * K + pos] = s0 + j + u;
                             } else {
                                 far = __fadd_rn(far, lin);
                             }
                         }
-                        ps[r] = far;
+                        s[r] = far;
                     }
                 }
             }
 #pragma unroll
-            for (int r = 0; r < R; ++r) { sum[r] = __fadd_rn(sum[r], ps[r]); ps[r] = 0.f; }
+            for (int r = 0; r < R; ++r) sum[r] = __fadd_rn(sum[r], s[r]);
         }
     }
-    int over = 0;
+    float *out = far_part + (size_t)blockIdx.y * n_work + w0;
 #pragma unroll
-    for (int r = 0; r < R; ++r) {
-        far_out[w0 + r] = sum[r];
-        cnt_out[w0 + r] = cnt[r];
-        over = max(over, cnt[r]);
-    }
-    if (over > K) atomicMax(&ctr->max_near, over);
+    for (int r = 0; r < R; ++r) out[r] = sum[r];
 }
 
+// ---- host side: variant table, split planning, launch ---------------------------------------
+struct SweepVariant { const void *fn; int R, threads; };
+
 template <int MODE, bool PLANAR>
-static cudaError_t launch_variant(int variant, int n_work, const SweepArgs &a, cudaStream_t st)
+static SweepVariant variant_of(int variant)
 {
-#define RMB_LAUNCH(RR, TT)                                                                              \
-    do {                                                                                                \
-        int blocks = n_work / ((RR) * (TT));                                                            \
-        sweep_kernel<MODE, PLANAR, RR, TT><<<blocks, TT, 0, st>>>(a.fx, a.fy, a.fz, a.groups, a.tx,     \
-            a.theta, a.theta_min_g, a.neg_h, a.far_out, a.cnt_out, a.slots, a.K, a.ctr);                \
-    } while (0)
+#define RMB_V(RR, TT) SweepVariant{(const void *)&sweep_kernel<MODE, PLANAR, RR, TT>, RR, TT}
     switch (variant) {
-    case 2:  RMB_LAUNCH(8, 128); break;
-    case 3:  RMB_LAUNCH(2, 64);  break;
-    case 4:  RMB_LAUNCH(4, 64);  break;
-    case 5:  RMB_LAUNCH(8, 64);  break;
-    case 6:  RMB_LAUNCH(1, 32);  break;
-    default: RMB_LAUNCH(4, 128); break;
+    case 2:  return RMB_V(8, 128);
+    case 3:  return RMB_V(2, 64);
+    case 4:  return RMB_V(4, 64);
+    case 5:  return RMB_V(8, 64);
+    case 6:  return RMB_V(1, 32);
+    case 7:  return RMB_V(2, 128);
+    case 8:  return RMB_V(4, 256);
+    default: return RMB_V(4, 128);
     }
-#undef RMB_LAUNCH
-    return cudaGetLastError();
+#undef RMB_V
+}
+
+static SweepVariant pick(int mode, bool planar, int variant)
+{
+    switch (mode) {
+    case MODE_N2:  return planar ? variant_of<MODE_N2, true>(variant)  : variant_of<MODE_N2, false>(variant);
+    case MODE_N3:  return planar ? variant_of<MODE_N3, true>(variant)  : variant_of<MODE_N3, false>(variant);
+    case MODE_N4:  return planar ? variant_of<MODE_N4, true>(variant)  : variant_of<MODE_N4, false>(variant);
+    default:       return planar ? variant_of<MODE_GEN, true>(variant) : variant_of<MODE_GEN, false>(variant);
+    }
 }
 
 int sweep_mode_for_exponent(double n)
@@ -160,15 +212,42 @@ int sweep_mode_for_exponent(double n)
     return MODE_GEN;
 }
 
-cudaError_t launch_sweep(int mode, bool planar, int variant, int n_work, const SweepArgs &a, cudaStream_t st)
+// Number of tx splits S: the smallest S whose grid (rx blocks x S) fills the resident block
+// slots of the GPU to >= 95 % over its waves (quantisation tail), each split keeping at least
+// kMinSplitTx transmissions; if none reaches 95 % the best one.
+int sweep_plan(int mode, bool planar, int variant, int n_work, int n_tx_bucket, int forced_splits)
+{
+    constexpr int kMinSplitTx = 256, kMaxSplits = 64;
+    const SweepVariant v = pick(mode, planar, variant);
+    const int max_s = max(1, min(kMaxSplits, n_tx_bucket / kMinSplitTx));
+    if (forced_splits > 0) return min(forced_splits, kMaxSplits);
+    int dev = 0, sms = 148, occ = 1;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, v.fn, v.threads, 0) != cudaSuccess || occ < 1) { occ = 1; cudaGetLastError(); }
+    const double slots = (double)sms * occ;
+    const int rx_blocks = max(1, n_work / (v.R * v.threads));
+    int best = 1; double best_eff = 0.0;
+    for (int s = 1; s <= max_s; ++s) {
+        const double waves = rx_blocks * (double)s / slots;
+        const double eff = waves / ceil(waves);
+        if (eff > best_eff + 1e-9) { best_eff = eff; best = s; }
+        if (eff >= 0.95) { best = s; break; }
+    }
+    return best;
+}
+
+cudaError_t launch_sweep(int mode, bool planar, int variant, int n_work, int splits, const SweepArgs &a, cudaStream_t st)
 {
     if (n_work <= 0) return cudaSuccess;
-    switch (mode) {
-    case MODE_N2:  return planar ? launch_variant<MODE_N2, true>(variant, n_work, a, st)  : launch_variant<MODE_N2, false>(variant, n_work, a, st);
-    case MODE_N3:  return planar ? launch_variant<MODE_N3, true>(variant, n_work, a, st)  : launch_variant<MODE_N3, false>(variant, n_work, a, st);
-    case MODE_N4:  return planar ? launch_variant<MODE_N4, true>(variant, n_work, a, st)  : launch_variant<MODE_N4, false>(variant, n_work, a, st);
-    default:       return planar ? launch_variant<MODE_GEN, true>(variant, n_work, a, st) : launch_variant<MODE_GEN, false>(variant, n_work, a, st);
-    }
+    const SweepVariant v = pick(mode, planar, variant);
+    SweepArgs b = a;
+    int nw = n_work;
+    void *args[] = {(void *)&b.fx, (void *)&b.fy, (void *)&b.fz, (void *)&b.groups, (void *)&b.tx, (void *)&b.theta,
+                    (void *)&b.theta_min_g, (void *)&b.neg_h, (void *)&b.far_part, (void *)&b.cnt, (void *)&b.slots,
+                    (void *)&b.K, (void *)&nw};
+    dim3 grid((unsigned)(n_work / (v.R * v.threads)), (unsigned)max(1, splits));
+    return cudaLaunchKernel(v.fn, grid, dim3((unsigned)v.threads), args, 0, st);
 }
 
 }  // namespace rmb
