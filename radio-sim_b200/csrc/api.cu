@@ -71,7 +71,8 @@ struct rmb_handle {
     DevBuf<int> channel, id_int;
     DevBuf<uint8_t> enabled;
     int matrix_n = 0;
-    DevBuf<int> perm; DevBuf<float> fx, fy, fz;
+    DevBuf<int> perm, gid; DevBuf<float> fx, fy, fz;
+    DevBuf<unsigned long long> ro_key, ro_key_alt; DevBuf<int> ro_val, ro_val_alt; DevBuf<char> ro_tmp;
     int n_work = 0;
     Groups groups{};
     DevBuf<DevParams> dp; DevBuf<Geom> geom; DevBuf<unsigned long long> geom_scratch;
@@ -199,13 +200,16 @@ static int build_work_order(rmb_handle *h)
     }
     g.w_begin[g.ngroups] = w;
     for (int k = g.ngroups + 1; k <= kMaxGroups; ++k) g.w_begin[k] = w;
-    std::vector<int> perm((size_t)std::max(w, 1), -1), cur(g.w_begin, g.w_begin + g.ngroups);
-    for (int i = 0; i < n; ++i) if (gid[i] >= 0) perm[cur[gid[i]]++] = i;
+    int dense = 0;
+    for (int k = 0; k <= kMaxGroups; ++k) { g.dense_begin[k] = dense; if (k < g.ngroups) dense += count[k]; }
     h->groups = g;
     h->n_work = w;
+    // perm itself is built on the device (Morton order inside a group): refresh_geometry(h, true)
+    const int nn = std::max(n, 1);
     RMB_CK(h, h->perm.ensure(std::max(w, 1))); RMB_CK(h, h->fx.ensure(w)); RMB_CK(h, h->fy.ensure(w)); RMB_CK(h, h->fz.ensure(w));
-    RMB_CK(h, cudaMemcpyAsync(h->perm.p, perm.data(), perm.size() * sizeof(int), cudaMemcpyHostToDevice, h->st));
-    RMB_CK(h, cudaStreamSynchronize(h->st));      // perm is a stack-lifetime vector
+    RMB_CK(h, h->gid.ensure(nn)); RMB_CK(h, h->ro_key.ensure(nn)); RMB_CK(h, h->ro_key_alt.ensure(nn));
+    RMB_CK(h, h->ro_val.ensure(nn)); RMB_CK(h, h->ro_val_alt.ensure(nn)); RMB_CK(h, h->ro_tmp.ensure(reorder_tmp_bytes(nn)));
+    if (n > 0) RMB_CK(h, cudaMemcpy(h->gid.p, gid.data(), (size_t)n * sizeof(int), cudaMemcpyHostToDevice));
     int rc = ensure_slots(h);
     if (rc) return rc;
     // idle nodes report the noise floor (AbstractRadioMedium.java:38,45-52)
@@ -228,12 +232,16 @@ static void update_draw_flag(rmb_handle *h)
 }
 
 // bounding box -> centre / planarity, then the fp32 work-order copy
-static int refresh_geometry(rmb_handle *h)
+static int refresh_geometry(rmb_handle *h, bool reorder)
 {
     NodeArrays nd = node_arrays(h);
     RMB_CK(h, launch_geom(nd, h->geom_scratch.p, h->geom.p, h->st));
     Geom g;
     RMB_CK(h, cudaMemcpyAsync(&g, h->geom.p, sizeof(Geom), cudaMemcpyDeviceToHost, h->st));
+    if (reorder) {
+        ReorderScratch sc{h->ro_key.p, h->ro_key_alt.p, h->ro_val.p, h->ro_val_alt.p, h->ro_tmp.p, h->ro_tmp.cap};
+        RMB_CK(h, launch_reorder(nd, h->gid.p, h->geom.p, h->groups, h->n_work, sc, h->perm.p, h->st));
+    }
     RMB_CK(h, launch_regather(nd, work_arrays(h), h->geom.p, h->st));
     RMB_CK(h, cudaStreamSynchronize(h->st));
     h->planar = g.planar != 0;
@@ -320,7 +328,7 @@ int rmb_destroy(rmb_handle *h)
     cudaStreamSynchronize(h->st);
     // DevBuf/PinBuf have no destructors on purpose (explicit lifetime): free through cudaDeviceReset-safe calls
     h->x.release(); h->y.release(); h->z.release(); h->txpower.release(); h->rxprob.release(); h->txprob.release();
-    h->matrix.release(); h->channel.release(); h->id_int.release(); h->enabled.release(); h->perm.release();
+    h->matrix.release(); h->channel.release(); h->id_int.release(); h->enabled.release(); h->perm.release(); h->gid.release(); h->ro_key.release(); h->ro_key_alt.release(); h->ro_val.release(); h->ro_val_alt.release(); h->ro_tmp.release();
     h->fx.release(); h->fy.release(); h->fz.release(); h->dp.release(); h->geom.release(); h->geom_scratch.release();
     h->ctr.release(); h->h_ctr.release(); h->node_rssi.release(); h->node_recv.release(); h->pk_src.release();
     h->pk_channel.release(); h->pk_power.release(); h->pk_stage.release(); h->rec.release(); h->txf.release();
@@ -364,7 +372,7 @@ int rmb_set_nodes(rmb_handle *h, int32_t n, const double *x, const double *y, co
     int rc = build_work_order(h);
     if (rc) return rc;
     update_draw_flag(h);
-    rc = refresh_geometry(h);
+    rc = refresh_geometry(h, true);
     if (rc) return rc;
     h->have_nodes = true;
     return RMB_OK;
@@ -416,7 +424,8 @@ extern "C" int rmb_update_positions(rmb_handle *h, int32_t count, const int32_t 
         if (z) RMB_CK(h, cudaMemcpyAsync(dz, z, b, cudaMemcpyHostToDevice, h->st));
         RMB_CK(h, launch_scatter_positions(node_arrays(h), count, h->pk_src.p, dx, dy, z ? dz : nullptr, h->st));
     }
-    return refresh_geometry(h);
+    // a dense update re-sorts the work order; a sparse one keeps it (the order only affects speed)
+    return refresh_geometry(h, idx == nullptr);
 }
 
 extern "C" int rmb_update_radio(rmb_handle *h, int32_t count, const int32_t *idx, const double *txpower_dbm,
@@ -451,7 +460,7 @@ extern "C" int rmb_update_radio(rmb_handle *h, int32_t count, const int32_t *idx
     if (regroup) {
         int rc = build_work_order(h);
         if (rc) return rc;
-        return refresh_geometry(h);
+        return refresh_geometry(h, true);
     }
     return RMB_OK;
 }

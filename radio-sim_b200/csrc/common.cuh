@@ -42,7 +42,7 @@ struct Groups {
     int channel[kMaxGroups];
     int w_begin[kMaxGroups + 1];      // work-order range of group g, padded to the block size
     int n_rx[kMaxGroups];             // enabled receivers in the group
-    int blk_begin[kMaxGroups + 1];    // first sweep block of group g
+    int dense_begin[kMaxGroups + 1];  // first enabled receiver of group g in the unpadded (sorted) list
 };
 
 // counters the host reads back once per tick

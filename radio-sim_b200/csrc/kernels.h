@@ -23,6 +23,12 @@ struct WorkArrays {
 
 // ---- K4: state maintenance ----------------------------------------------------------------
 cudaError_t launch_geom(const NodeArrays &nd, unsigned long long *scratch6, Geom *geom, cudaStream_t st);
+// work order = enabled receivers grouped by channel group (gid, -1 = disabled), Morton-sorted by (x, y)
+// inside a group (stable: ties keep node order), every group padded to 1024 (perm = -1).
+struct ReorderScratch { unsigned long long *key, *key_alt; int *val, *val_alt; void *tmp; size_t tmp_bytes; };
+size_t      reorder_tmp_bytes(int n);
+cudaError_t launch_reorder(const NodeArrays &nd, const int *gid, const Geom *geom, const Groups &groups, int n_work,
+                           ReorderScratch sc, int *perm, cudaStream_t st);
 cudaError_t launch_regather(const NodeArrays &nd, const WorkArrays &wk, const Geom *geom, cudaStream_t st);
 cudaError_t launch_scatter_positions(const NodeArrays &nd, int count, const int *idx,
                                      const double *x, const double *y, const double *z, cudaStream_t st);

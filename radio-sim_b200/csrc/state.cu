@@ -9,6 +9,7 @@
 #include "exact_math.cuh"
 #include <cfloat>
 #include <climits>
+#include <cub/cub.cuh>
 
 namespace rmb {
 
@@ -70,6 +71,66 @@ cudaError_t launch_geom(const NodeArrays &nd, unsigned long long *scratch6, Geom
         geom_reduce_kernel<<<blocks, 256, 0, st>>>(nd, scratch6);
     }
     geom_final_kernel<<<1, 1, 0, st>>>(nd.n, scratch6, geom);
+    return cudaGetLastError();
+}
+
+// ---- work order: channel group, then Morton (Z-curve) order of (x, y) ----------------------
+// Spatially close receivers share a warp, so the rare "near" re-scans of the sweep hit the same
+// tx tile for all lanes of a warp instead of 32 different ones.  The order only affects speed:
+// every result list is re-ordered to (packet, node index) by the emit stage.
+__device__ __forceinline__ unsigned spread16(unsigned v)
+{
+    v &= 0xffffu;
+    v = (v | (v << 8)) & 0x00ff00ffu; v = (v | (v << 4)) & 0x0f0f0f0fu;
+    v = (v | (v << 2)) & 0x33333333u; v = (v | (v << 1)) & 0x55555555u;
+    return v;
+}
+
+__global__ void morton_keys_kernel(NodeArrays nd, const int *gid, const Geom *geom, unsigned long long *key, int *val)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nd.n) return;
+    const int g = gid[i];
+    unsigned long long k = ~0ull;                       // disabled nodes sort to the end
+    if (g >= 0) {
+        const double ext = geom->maxabs > 0.0 ? 2.0 * geom->maxabs : 1.0;
+        const double ux = (nd.x[i] - (geom->cx - geom->maxabs)) / ext, uy = (nd.y[i] - (geom->cy - geom->maxabs)) / ext;
+        const unsigned qx = (unsigned)fmin(fmax(ux * 65535.0, 0.0), 65535.0), qy = (unsigned)fmin(fmax(uy * 65535.0, 0.0), 65535.0);
+        k = ((unsigned long long)g << 32) | (spread16(qx) | (spread16(qy) << 1));
+    }
+    key[i] = k; val[i] = i;
+}
+
+__global__ void place_perm_kernel(int n_enabled, const unsigned long long *key, const int *val, Groups groups, int *perm)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_enabled) return;
+    const int g = (int)(key[i] >> 32);
+    perm[groups.w_begin[g] + (i - groups.dense_begin[g])] = val[i];
+}
+
+size_t reorder_tmp_bytes(int n)
+{
+    size_t bytes = 0;
+    cub::DoubleBuffer<unsigned long long> k(nullptr, nullptr);
+    cub::DoubleBuffer<int> v(nullptr, nullptr);
+    cub::DeviceRadixSort::SortPairs(nullptr, bytes, k, v, n, 0, 40, 0);
+    return bytes;
+}
+
+cudaError_t launch_reorder(const NodeArrays &nd, const int *gid, const Geom *geom, const Groups &groups, int n_work,
+                           ReorderScratch sc, int *perm, cudaStream_t st)
+{
+    RMB_CUDA_OK(cudaMemsetAsync(perm, 0xff, (size_t)(n_work > 0 ? n_work : 1) * sizeof(int), st));    // -1 = padding
+    if (nd.n <= 0) return cudaSuccess;
+    morton_keys_kernel<<<(nd.n + 255) / 256, 256, 0, st>>>(nd, gid, geom, sc.key, sc.val);
+    cub::DoubleBuffer<unsigned long long> k(sc.key, sc.key_alt);
+    cub::DoubleBuffer<int> v(sc.val, sc.val_alt);
+    size_t bytes = sc.tmp_bytes;
+    RMB_CUDA_OK(cub::DeviceRadixSort::SortPairs(sc.tmp, bytes, k, v, nd.n, 0, 40, st));     // 6 bits group + 32 Morton; all-ones = disabled
+    const int n_enabled = groups.dense_begin[groups.ngroups];
+    if (n_enabled > 0)
+        place_perm_kernel<<<(n_enabled + 255) / 256, 256, 0, st>>>(n_enabled, k.Current(), v.Current(), groups, perm);
     return cudaGetLastError();
 }
 
