@@ -82,7 +82,7 @@ struct rmb_handle {
     // per tick: tx side
     DevBuf<int> pk_src, pk_channel; DevBuf<double> pk_power; PinBuf<char> pk_stage;
     DevBuf<rmb_tx_record> rec;
-    DevBuf<float4> txf; DevBuf<float> theta, theta_min_g; DevBuf<int> arrival, goff, gcount;
+    DevBuf<float4> txf, stg_f; DevBuf<float> theta, theta_min_g, stg_theta; DevBuf<int> stg_gid; DevBuf<int> arrival, goff, gcount;
     DevBuf<double> uniforms;
 
     // slots
@@ -331,7 +331,7 @@ int rmb_destroy(rmb_handle *h)
     h->matrix.release(); h->channel.release(); h->id_int.release(); h->enabled.release(); h->perm.release(); h->gid.release(); h->ro_key.release(); h->ro_key_alt.release(); h->ro_val.release(); h->ro_val_alt.release(); h->ro_tmp.release();
     h->fx.release(); h->fy.release(); h->fz.release(); h->dp.release(); h->geom.release(); h->geom_scratch.release();
     h->ctr.release(); h->h_ctr.release(); h->node_rssi.release(); h->node_recv.release(); h->pk_src.release();
-    h->pk_channel.release(); h->pk_power.release(); h->pk_stage.release(); h->rec.release(); h->txf.release();
+    h->pk_channel.release(); h->pk_power.release(); h->pk_stage.release(); h->rec.release(); h->txf.release(); h->stg_f.release(); h->stg_theta.release(); h->stg_gid.release();
     h->theta.release(); h->theta_min_g.release(); h->arrival.release(); h->goff.release(); h->gcount.release();
     h->uniforms.release(); h->slots.release(); h->cnt.release(); h->hcnt.release(); h->hoff.release();
     h->recheck.release(); h->far_part.release(); h->sl_prx.release(); h->sl_lin.release(); h->sl_sinr.release();
@@ -558,8 +558,10 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
         const int mode = sweep_mode_for_exponent(h->cfg.pl_exponent);
         h->splits = sweep_plan(mode, h->planar, h->sweep_variant, h->n_work, n_tx / std::max(1, h->groups.ngroups), h->forced_splits);
         RMB_CK(h, h->far_part.ensure((size_t)h->splits * (size_t)std::max(h->n_work, 1)));
-        RMB_CK(h, launch_prepare(nd, h->dp.p, h->geom.p, h->groups, n_tx, d_rec, tx, h->theta.p, h->theta_min_g.p, h->ctr.p, h->st));
-        ++launches;
+        RMB_CK(h, h->stg_f.ensure(std::max(n_tx, 1))); RMB_CK(h, h->stg_theta.ensure(std::max(n_tx, 1))); RMB_CK(h, h->stg_gid.ensure(std::max(n_tx, 1)));
+        TxStage stg{h->stg_f.p, h->stg_theta.p, h->stg_gid.p};
+        RMB_CK(h, launch_prepare(nd, h->dp.p, h->geom.p, h->groups, n_tx, d_rec, stg, tx, h->theta.p, h->theta_min_g.p, h->ctr.p, h->st));
+        launches += 3;
         RMB_CK(h, cudaEventRecord(h->ev[1], h->st));
         for (int attempt = 0;; ++attempt) {
             SweepArgs a;

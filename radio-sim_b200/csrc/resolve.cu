@@ -28,71 +28,122 @@ __device__ __forceinline__ double sinr_db(double prx, double itot, double lin)
     return ioth > 0.0 ? xm::sub(prx, xm::mw_to_dbm(ioth)) : __longlong_as_double(0x7ff0000000000000ll);
 }
 
-// one thread per receiver (work order)
+// One warp per 32 receivers (work order).  The exact evaluation of the near candidates is the
+// expensive part (fdlibm log10 + exp in strict double) and the candidate counts differ between
+// receivers, so the warp pools its candidates: candidate i of the warp (prefix sum of the
+// per-lane counts) is evaluated by lane i % 32, whoever owns it.  The per-receiver parts (far
+// sum, the ordered addition of the near terms, flags) stay on the owning lane.
+constexpr uint8_t kGuard = 4;         // slot flag, resolve-internal: SINR within the guard band
+
+__device__ __forceinline__ int owner_of(int i, int P)
+{
+    // largest lane o with P_o <= i (P = exclusive prefix of the per-lane candidate counts)
+    int lo = 0, hi = 31;
+#pragma unroll
+    for (int step = 0; step < 5; ++step) {
+        const int mid = (lo + hi + 1) >> 1;
+        const int pm = __shfl_sync(0xffffffffu, P, mid);
+        if (pm <= i) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+}
+
 __global__ void __launch_bounds__(128)
 resolve_kernel(NodeArrays nd, WorkArrays wk, const DevParams *dp, TxTiles tx, const rmb_tx_record *rec,
                SlotArrays sl, float *node_rssi, uint8_t *node_recv, Counters *ctr)
 {
-    const int w = blockIdx.x * blockDim.x + threadIdx.x;
-    int nh = 0;
-    if (w < wk.n_work) {
-        const int p = wk.perm[w];
-        if (p >= 0) {
-            const int K = sl.K;
-            const int found = sl.cnt[w];
-            if (found > K) atomicMax(&ctr->max_near, found);      // slot overflow: the host grows K and redoes the sweep
-            const int c = min(found, K);
-            const double X = nd.x[p], Y = nd.y[p], Z = nd.z[p];
-            const double rxp = nd.rxprob[p];
-            const int self = dp->rx_base + p;
-            // far field: the sweep's per-split partial sums, added in split order (deterministic)
-            double far = 0.0;
-            for (int s = 0; s < sl.splits; ++s) far = xm::add(far, (double)sl.far_part[(size_t)s * wk.n_work + w]);
-            double itot = xm::add(dp->n0_mw, far);
-            const size_t base = (size_t)w * K;
-            // the sweep appends near candidates in arbitrary order: sort by bucket position (= arrival order)
-            for (int a = 1; a < c; ++a) {
-                const int v = sl.slots[base + a];
-                int b = a - 1;
-                while (b >= 0 && sl.slots[base + b] > v) { sl.slots[base + b + 1] = sl.slots[base + b]; --b; }
-                sl.slots[base + b + 1] = v;
-            }
-            for (int s = 0; s < c; ++s) {
-                const int t = tx.arrival[sl.slots[base + s]];
-                const rmb_tx_record r = rec[t];
-                uint8_t f = 0;
-                double prx = 0.0, lin = 0.0;
-                if (r.src != self) {
-                    const double d = xm::distance(r.x, r.y, r.z, X, Y, Z);
-                    prx = rx_power_dbm(dp, r.power_dbm, d);
-                    lin = xm::dbm_to_mw(prx);
-                    itot = xm::add(itot, lin);
-                    if (prx >= dp->sensitivity_dbm && rxp > 0.0) { f = kHeard; ++nh; }
-                }
-                sl.prx[base + s] = prx; sl.lin[base + s] = lin; sl.flags[base + s] = f;
-            }
-            bool guard = false;
-            for (int s = 0; s < c; ++s) {
-                uint8_t f = sl.flags[base + s];
-                if (!(f & kHeard)) continue;
-                const double sinr = sinr_db(sl.prx[base + s], itot, sl.lin[base + s]);
-                if (sinr >= dp->sinr_threshold_db) f |= kDecodable;
-                if (fabs(sinr - dp->sinr_threshold_db) < dp->sinr_guard_db) guard = true;
-                sl.sinr[base + s] = sinr; sl.flags[base + s] = f;
-            }
-            sl.hcnt[w] = nh;
-            sl.itot[w] = itot;
-            node_rssi[p] = (float)xm::mw_to_dbm(itot);
-            node_recv[p] = nh > 0;
-            if (guard && sl.cnt[w] <= K) sl.recheck[atomicAdd(&ctr->n_recheck, 1)] = w;
-        } else {
-            sl.hcnt[w] = 0;
+    const int w = blockIdx.x * blockDim.x + threadIdx.x;       // n_work is a multiple of 1024: no partial warps
+    const int lane = threadIdx.x & 31;
+    const int K = sl.K;
+    const int p = wk.perm[w];
+    const size_t base = (size_t)w * K;
+    int c = 0;
+    double itot = dp->n0_mw;
+    if (p >= 0) {
+        const int found = sl.cnt[w];
+        if (found > K) atomicMax(&ctr->max_near, found);      // slot overflow: the host grows K and redoes the sweep
+        c = min(found, K);
+        // far field: the sweep's per-split partial sums, added in split order (deterministic)
+        double far = 0.0;
+        for (int s = 0; s < sl.splits; ++s) far = xm::add(far, (double)sl.far_part[(size_t)s * wk.n_work + w]);
+        itot = xm::add(itot, far);
+        // the sweep appends near candidates in arbitrary order: sort by bucket position (= arrival order)
+        for (int a = 1; a < c; ++a) {
+            const int v = sl.slots[base + a];
+            int b = a - 1;
+            while (b >= 0 && sl.slots[base + b] > v) { sl.slots[base + b + 1] = sl.slots[base + b]; --b; }
+            sl.slots[base + b + 1] = v;
         }
     }
+    int incl = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
+    const int P = incl - c;
+    const int total = __shfl_sync(0xffffffffu, incl, 31);
+    const size_t wbase = (size_t)(w - lane) * K;
+    __syncwarp();
+
+    // pass 1 (pooled): link budget of every candidate
+    for (int i0 = 0; i0 < total; i0 += 32) {
+        const int i = i0 + lane;
+        const int o = owner_of(i, P);
+        const int po = __shfl_sync(0xffffffffu, p, o);
+        const int so = i - __shfl_sync(0xffffffffu, P, o);
+        if (i < total) {
+            const size_t q = wbase + (size_t)o * K + so;
+            const rmb_tx_record r = rec[tx.arrival[sl.slots[q]]];
+            uint8_t f = 0;
+            double prx = 0.0, lin = 0.0;
+            if (r.src != dp->rx_base + po) {
+                const double d = xm::distance(r.x, r.y, r.z, nd.x[po], nd.y[po], nd.z[po]);
+                prx = rx_power_dbm(dp, r.power_dbm, d);
+                lin = xm::dbm_to_mw(prx);
+                if (prx >= dp->sensitivity_dbm && nd.rxprob[po] > 0.0) f = kHeard;
+            }
+            sl.prx[q] = prx; sl.lin[q] = lin; sl.flags[q] = f;
+        }
+    }
+    __syncwarp();
+
+    // per receiver: total in-band power, near terms added in arrival order
+    int nh = 0;
+    for (int s = 0; s < c; ++s) {
+        itot = xm::add(itot, sl.lin[base + s]);       // the source's own packet contributes lin = 0
+        nh += sl.flags[base + s] & kHeard;
+    }
+
+    // pass 2 (pooled): SINR of every heard candidate
+    for (int i0 = 0; i0 < total; i0 += 32) {
+        const int i = i0 + lane;
+        const int o = owner_of(i, P);
+        const int so = i - __shfl_sync(0xffffffffu, P, o);
+        const double it = __shfl_sync(0xffffffffu, itot, o);
+        if (i < total) {
+            const size_t q = wbase + (size_t)o * K + so;
+            uint8_t f = sl.flags[q];
+            if (f & kHeard) {
+                const double sinr = sinr_db(sl.prx[q], it, sl.lin[q]);
+                if (sinr >= dp->sinr_threshold_db) f |= kDecodable;
+                if (fabs(sinr - dp->sinr_threshold_db) < dp->sinr_guard_db) f |= kGuard;
+                sl.sinr[q] = sinr; sl.flags[q] = f;
+            }
+        }
+    }
+    __syncwarp();
+
+    if (p >= 0) {
+        bool guard = false;
+        for (int s = 0; s < c; ++s) guard |= (sl.flags[base + s] & kGuard) != 0;
+        sl.itot[w] = itot;
+        node_rssi[p] = (float)xm::mw_to_dbm(itot);
+        node_recv[p] = nh > 0;
+        if (guard && sl.cnt[w] <= K) sl.recheck[atomicAdd(&ctr->n_recheck, 1)] = w;
+    }
+    sl.hcnt[w] = nh;
     // total heard pairs (capacity check on the host)
     unsigned long long v = (unsigned long long)nh;
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if ((threadIdx.x & 31) == 0 && v) atomicAdd(&ctr->heard, v);
+    if (lane == 0 && v) atomicAdd(&ctr->heard, v);
 }
 
 cudaError_t launch_resolve(const NodeArrays &nd, const WorkArrays &wk, const DevParams *dp, TxTiles tx,

@@ -215,103 +215,107 @@ cudaError_t launch_gather_records(const NodeArrays &nd, int rx_base, int n_tx, c
 }
 
 // ---- channel bucketing + fast-path constants ----------------------------------------------
-// One block.  For every receiver channel group g (in work order) the tick's records on that
-// channel are compacted, ARRIVAL ORDER PRESERVED (warp ballot + prefix sums), into bucket g of
-// the sweep's tx tiles; buckets are padded to kTile with infinitely weak dummies.
+// For every receiver channel group g (in work order) the tick's records on that channel are
+// compacted, ARRIVAL ORDER PRESERVED (warp ballot + prefix sums), into bucket g of the sweep's
+// tx tiles; buckets are padded to kTile with infinitely weak dummies.
 //   c_t     = P_t^(-1/n),  P_t = 10^((Ptx - PL0)/10) * d0^n        (power folded into geometry)
 //   theta_t = min(sensitivity (minus 0.05 dB), P_t * Dnear^-n)     (near threshold, mW)
 //   Dnear   = max(d0, n * delta_d / 1e-4), delta_d = fp32 geometry error of the centred copy
+// Three launches: init (bucket counters), per-transmission constants (one thread per tx, any
+// number of blocks), stable placement (one block per group).
+__global__ void prepare_init_kernel(int ngroups, int *gcount, float *theta_min_g)
+{
+    const int g = threadIdx.x;
+    if (g < ngroups) { gcount[g] = 0; theta_min_g[g] = FLT_MAX; }
+}
+
+__global__ void __launch_bounds__(256)
+prepare_tx_kernel(NodeArrays nd, const DevParams *dp, const Geom *geom, Groups groups, int n_tx,
+                  const rmb_tx_record *rec, TxStage stg, int *gcount, float *theta_min_g, Counters *ctr)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long decisions = 0;
+    if (t < n_tx) {
+        const rmb_tx_record r = rec[t];
+        int g = -1;
+        if (r.src >= 0)
+            for (int k = 0; k < groups.ngroups; ++k) if (groups.channel[k] == r.channel) { g = k; break; }
+        stg.gid[t] = g;
+        if (g >= 0) {
+            const double n = dp->pl_exponent, d0 = dp->d0_m;
+            const double delta_d = geom->maxabs * (geom->planar ? 1.7e-7 : 2.1e-7);
+            const double dnear = fmax(d0, n * delta_d / 1e-4);
+            const double theta_s = pow(10.0, (dp->sensitivity_dbm - 0.05) / 10.0);
+            const double P = pow(10.0, (r.power_dbm - dp->pl0_db) / 10.0) * pow(d0, n);
+            const float cf = (float)pow(P, -1.0 / n);
+            const double c = (double)cf;
+            stg.f[t] = make_float4((float)((r.x - geom->cx) * c), (float)((r.y - geom->cy) * c),
+                                   (float)((r.z - geom->cz) * c), cf);
+            const float th = (float)(fmin(theta_s, P * pow(dnear, -n)) * (1.0 - 1e-6));
+            stg.theta[t] = th;
+            atomicAdd(&gcount[g], 1);
+            atomicMin((int *)&theta_min_g[g], __float_as_int(th));        // th > 0: integer order == float order
+            // decisions of this packet: every enabled co-channel receiver except its own source
+            const int s = r.src - dp->rx_base;
+            const int self = (s >= 0 && s < nd.n && nd.enabled[s] && nd.channel[s] == r.channel) ? 1 : 0;
+            decisions = (unsigned long long)(groups.n_rx[g] - self);
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) decisions += __shfl_xor_sync(0xffffffffu, decisions, o);
+    if ((threadIdx.x & 31) == 0 && decisions) atomicAdd(&ctr->decisions, decisions);
+}
+
 __global__ void __launch_bounds__(1024)
-prepare_kernel(NodeArrays nd, const DevParams *dp, const Geom *geom, Groups groups, int n_tx,
-               const rmb_tx_record *rec, TxTiles tx, float *theta, float *theta_min_g, Counters *ctr)
+prepare_place_kernel(Groups groups, int n_tx, TxStage stg, TxTiles tx, float *theta)
 {
     __shared__ int s_warp[32];
     __shared__ int s_total;
-    __shared__ float s_min[32];
-    __shared__ unsigned long long s_dec[32];
-    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const double n = dp->pl_exponent, d0 = dp->d0_m;
-    const double d0n = pow(d0, n);
-    const double delta_d = geom->maxabs * (geom->planar ? 1.7e-7 : 2.1e-7);
-    const double dnear = fmax(d0, n * delta_d / 1e-4);
-    const double dnear_n = pow(dnear, -n);
-    const double theta_s = pow(10.0, (dp->sensitivity_dbm - 0.05) / 10.0);
+    const int g = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     int cursor = 0;
-    unsigned long long decisions = 0;
-    for (int g = 0; g < groups.ngroups; ++g) {
-        const int ch = groups.channel[g];
-        int count_g = 0;
-        float tmin = FLT_MAX;
-        for (int c0 = 0; c0 < n_tx; c0 += 1024) {
-            const int t = c0 + tid;
-            rmb_tx_record r;
-            bool match = false;
-            if (t < n_tx) { r = rec[t]; match = r.src >= 0 && r.channel == ch; }
-            unsigned b = __ballot_sync(0xffffffffu, match);
-            int rank = __popc(b & ((1u << lane) - 1));
-            if (lane == 0) s_warp[wid] = __popc(b);
-            __syncthreads();
-            if (wid == 0) {
-                int v = s_warp[lane], incl = v;
-                for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
-                s_warp[lane] = incl - v;
-                if (lane == 31) s_total = incl;
-            }
-            __syncthreads();
-            if (match) {
-                const int j = cursor + count_g + s_warp[wid] + rank;
-                const double P = pow(10.0, (r.power_dbm - dp->pl0_db) / 10.0) * d0n;
-                const float cf = (float)pow(P, -1.0 / n);
-                const double c = (double)cf;
-                tx.f[j] = make_float4((float)((r.x - geom->cx) * c), (float)((r.y - geom->cy) * c),
-                                      (float)((r.z - geom->cz) * c), cf);
-                const float th = (float)(fmin(theta_s, P * dnear_n) * (1.0 - 1e-6));
-                theta[j] = th;
-                tx.arrival[j] = t;
-                tmin = fminf(tmin, th);
-                // decisions of this packet: every enabled co-channel receiver except its own source
-                int s = r.src - dp->rx_base;
-                int self = (s >= 0 && s < nd.n && nd.enabled[s] && nd.channel[s] == ch) ? 1 : 0;
-                decisions += (unsigned long long)(groups.n_rx[g] - self);
-            }
-            count_g += s_total;
-            __syncthreads();
-        }
-        const int padded = (count_g + kTile - 1) / kTile * kTile;
-        for (int j = cursor + count_g + tid; j < cursor + padded; j += 1024) {
-            tx.f[j] = make_float4(1e18f, 1e18f, 1e18f, 0.f);      // d2' ~ 1e36 -> lin underflows to 0
-            theta[j] = FLT_MAX;
-            tx.arrival[j] = -1;
-        }
-        for (int o = 16; o > 0; o >>= 1) tmin = fminf(tmin, __shfl_xor_sync(0xffffffffu, tmin, o));
-        if (lane == 0) s_min[wid] = tmin;
+    for (int k = 0; k < g; ++k) cursor += (tx.gcount[k] + kTile - 1) / kTile * kTile;
+    int count_g = 0;
+    for (int c0 = 0; c0 < n_tx; c0 += 1024) {
+        const int t = c0 + tid;
+        const bool match = t < n_tx && stg.gid[t] == g;
+        const unsigned b = __ballot_sync(0xffffffffu, match);
+        const int rank = __popc(b & ((1u << lane) - 1));
+        if (lane == 0) s_warp[wid] = __popc(b);
         __syncthreads();
-        if (tid == 0) {
-            float m = FLT_MAX;
-            for (int i = 0; i < 32; ++i) m = fminf(m, s_min[i]);
-            theta_min_g[g] = m;
-            tx.goff[g] = cursor;
-            tx.gcount[g] = count_g;
+        if (wid == 0) {
+            int v = s_warp[lane], incl = v;
+            for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
+            s_warp[lane] = incl - v;
+            if (lane == 31) s_total = incl;
         }
         __syncthreads();
-        cursor += padded;
+        if (match) {
+            const int j = cursor + count_g + s_warp[wid] + rank;
+            tx.f[j] = stg.f[t]; theta[j] = stg.theta[t]; tx.arrival[j] = t;
+        }
+        count_g += s_total;
+        __syncthreads();
     }
-    for (int o = 16; o > 0; o >>= 1) decisions += __shfl_xor_sync(0xffffffffu, decisions, o);
-    if (lane == 0) s_dec[wid] = decisions;
-    __syncthreads();
+    const int padded = (count_g + kTile - 1) / kTile * kTile;
+    for (int j = cursor + count_g + tid; j < cursor + padded; j += 1024) {
+        tx.f[j] = make_float4(1e18f, 1e18f, 1e18f, 0.f);      // d2' ~ 1e36 -> lin underflows to 0
+        theta[j] = FLT_MAX;
+        tx.arrival[j] = -1;
+    }
     if (tid == 0) {
-        unsigned long long d = 0;
-        for (int i = 0; i < 32; ++i) d += s_dec[i];
-        tx.goff[groups.ngroups] = cursor;
-        ctr->decisions = d;
+        tx.goff[g] = cursor;
+        if (g == groups.ngroups - 1) tx.goff[groups.ngroups] = cursor + padded;
     }
 }
 
 cudaError_t launch_prepare(const NodeArrays &nd, const DevParams *dp, const Geom *geom, Groups groups, int n_tx,
-                           const rmb_tx_record *rec, TxTiles tx, float *theta, float *theta_min_g,
+                           const rmb_tx_record *rec, TxStage stg, TxTiles tx, float *theta, float *theta_min_g,
                            Counters *ctr, cudaStream_t st)
 {
-    prepare_kernel<<<1, 1024, 0, st>>>(nd, dp, geom, groups, n_tx, rec, tx, theta, theta_min_g, ctr);
+    prepare_init_kernel<<<1, kMaxGroups, 0, st>>>(groups.ngroups, tx.gcount, theta_min_g);
+    if (groups.ngroups <= 0) return cudaMemsetAsync(tx.goff, 0, sizeof(int), st);
+    if (n_tx > 0)
+        prepare_tx_kernel<<<(n_tx + 255) / 256, 256, 0, st>>>(nd, dp, geom, groups, n_tx, rec, stg, tx.gcount, theta_min_g, ctr);
+    prepare_place_kernel<<<groups.ngroups, 1024, 0, st>>>(groups, n_tx, stg, tx, theta);
     return cudaGetLastError();
 }
 
