@@ -71,7 +71,8 @@ struct rmb_handle {
     DevBuf<int> channel, id_int;
     DevBuf<uint8_t> enabled;
     int matrix_n = 0;
-    DevBuf<int> perm, gid; DevBuf<float> fx, fy, fz;
+    DevBuf<int> perm, gid; DevBuf<float> fx, fy, fz; DevBuf<double> wx, wy, wz, wrxp;
+    bool node_info_dirty = false;
     DevBuf<unsigned long long> ro_key, ro_key_alt; DevBuf<int> ro_val, ro_val_alt; DevBuf<char> ro_tmp;
     int n_work = 0;
     Groups groups{};
@@ -127,6 +128,7 @@ NodeArrays node_arrays(rmb_handle *h)
 WorkArrays work_arrays(rmb_handle *h)
 {
     WorkArrays w; w.n_work = h->n_work; w.perm = h->perm.p; w.fx = h->fx.p; w.fy = h->fy.p; w.fz = h->fz.p;
+    w.x64 = h->wx.p; w.y64 = h->wy.p; w.z64 = h->wz.p; w.rxp = h->wrxp.p;
     return w;
 }
 TxTiles tx_tiles(rmb_handle *h)
@@ -207,6 +209,9 @@ static int build_work_order(rmb_handle *h)
     // perm itself is built on the device (Morton order inside a group): refresh_geometry(h, true)
     const int nn = std::max(n, 1);
     RMB_CK(h, h->perm.ensure(std::max(w, 1))); RMB_CK(h, h->fx.ensure(w)); RMB_CK(h, h->fy.ensure(w)); RMB_CK(h, h->fz.ensure(w));
+    RMB_CK(h, h->wx.ensure(std::max(w, 1))); RMB_CK(h, h->wy.ensure(std::max(w, 1))); RMB_CK(h, h->wz.ensure(std::max(w, 1)));
+    RMB_CK(h, h->wrxp.ensure(std::max(w, 1)));
+    h->node_info_dirty = false;
     RMB_CK(h, h->gid.ensure(nn)); RMB_CK(h, h->ro_key.ensure(nn)); RMB_CK(h, h->ro_key_alt.ensure(nn));
     RMB_CK(h, h->ro_val.ensure(nn)); RMB_CK(h, h->ro_val_alt.ensure(nn)); RMB_CK(h, h->ro_tmp.ensure(reorder_tmp_bytes(nn)));
     if (n > 0) RMB_CK(h, cudaMemcpy(h->gid.p, gid.data(), (size_t)n * sizeof(int), cudaMemcpyHostToDevice));
@@ -328,7 +333,7 @@ int rmb_destroy(rmb_handle *h)
     cudaStreamSynchronize(h->st);
     // DevBuf/PinBuf have no destructors on purpose (explicit lifetime): free through cudaDeviceReset-safe calls
     h->x.release(); h->y.release(); h->z.release(); h->txpower.release(); h->rxprob.release(); h->txprob.release();
-    h->matrix.release(); h->channel.release(); h->id_int.release(); h->enabled.release(); h->perm.release(); h->gid.release(); h->ro_key.release(); h->ro_key_alt.release(); h->ro_val.release(); h->ro_val_alt.release(); h->ro_tmp.release();
+    h->matrix.release(); h->channel.release(); h->id_int.release(); h->enabled.release(); h->perm.release(); h->wx.release(); h->wy.release(); h->wz.release(); h->wrxp.release(); h->gid.release(); h->ro_key.release(); h->ro_key_alt.release(); h->ro_val.release(); h->ro_val_alt.release(); h->ro_tmp.release();
     h->fx.release(); h->fy.release(); h->fz.release(); h->dp.release(); h->geom.release(); h->geom_scratch.release();
     h->ctr.release(); h->h_ctr.release(); h->node_rssi.release(); h->node_recv.release(); h->pk_src.release();
     h->pk_channel.release(); h->pk_power.release(); h->pk_stage.release(); h->rec.release(); h->txf.release(); h->stg_f.release(); h->stg_theta.release(); h->stg_gid.release();
@@ -462,6 +467,7 @@ extern "C" int rmb_update_radio(rmb_handle *h, int32_t count, const int32_t *idx
         if (rc) return rc;
         return refresh_geometry(h, true);
     }
+    if (rxprob) return refresh_geometry(h, false);        // the work-order copy of rxProbability
     return RMB_OK;
 }
 
@@ -483,6 +489,10 @@ extern "C" int rmb_node_info(rmb_handle *h, float *rssi_dbm, uint8_t *receiving)
     std::lock_guard<std::mutex> lk(h->mu);
     if (!h->have_nodes) return h->fail(RMB_ERR_STATE, "rmb_node_info before rmb_set_nodes");
     RMB_CK(h, cudaSetDevice(h->cfg.device));
+    if (h->node_info_dirty) {
+        RMB_CK(h, launch_node_info(work_arrays(h), slot_arrays(h), h->node_rssi.p, h->node_recv.p, h->st));
+        h->node_info_dirty = false;
+    }
     RMB_CK(h, cudaStreamSynchronize(h->st));
     if (rssi_dbm && h->n) RMB_CK(h, cudaMemcpy(rssi_dbm, h->node_rssi.p, (size_t)h->n * sizeof(float), cudaMemcpyDeviceToHost));
     if (receiving && h->n) RMB_CK(h, cudaMemcpy(receiving, h->node_recv.p, (size_t)h->n, cudaMemcpyDeviceToHost));
@@ -573,7 +583,7 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
             RMB_CK(h, launch_sweep(mode, h->planar, h->sweep_variant, h->n_work, h->splits, a, h->st));
             ++launches; ++sweeps;
             RMB_CK(h, cudaEventRecord(h->ev[2], h->st));
-            RMB_CK(h, launch_resolve(nd, wk, h->dp.p, tx, d_rec, slot_arrays(h), h->node_rssi.p, h->node_recv.p, h->ctr.p, h->st));
+            RMB_CK(h, launch_resolve(nd, wk, h->dp.p, tx, d_rec, slot_arrays(h), h->ctr.p, h->st));
             ++launches;
             if ((rc = read_counters(h))) return rc;
             if (h->h_ctr.p->max_near <= h->K) break;
@@ -593,7 +603,8 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
         if ((rc = ensure_pairs(h, m))) return rc;
         SlotArrays sl = slot_arrays(h);
         const int nre = h->h_ctr.p->n_recheck;
-        if (nre > 0) { RMB_CK(h, launch_recheck(nd, wk, h->dp.p, h->groups, tx, d_rec, sl, nre, h->node_rssi.p, h->st)); ++launches; }
+        if (nre > 0) { RMB_CK(h, launch_recheck(nd, wk, h->dp.p, h->groups, tx, d_rec, sl, nre, h->st)); ++launches; }
+        h->node_info_dirty = true;
         RMB_CK(h, cudaEventRecord(h->ev[3], h->st));
         if (m > 0) {
             PairArrays pa = pair_arrays(h);

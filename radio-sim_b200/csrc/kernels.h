@@ -19,6 +19,7 @@ struct WorkArrays {
     int n_work;                       // multiple of 1024
     int *perm;                        // work slot -> local node index, -1 = padding
     float *fx, *fy, *fz;              // centred fp32 copy used by the sweep
+    double *x64, *y64, *z64, *rxp;    // exact coordinates and rxProbability in work order (resolve / recheck)
 };
 
 // ---- K4: state maintenance ----------------------------------------------------------------
@@ -74,11 +75,11 @@ struct SlotArrays {
     int *recheck;                     // receivers inside the SINR guard band
 };
 cudaError_t launch_resolve(const NodeArrays &nd, const WorkArrays &wk, const DevParams *dp, TxTiles tx,
-                           const rmb_tx_record *rec, SlotArrays sl, float *node_rssi, uint8_t *node_recv,
-                           Counters *ctr, cudaStream_t st);
+                           const rmb_tx_record *rec, SlotArrays sl, Counters *ctr, cudaStream_t st);
+// per-node RSSI (total in-band power, dBm) and receiving flag from the work-order results of the last tick
+cudaError_t launch_node_info(const WorkArrays &wk, SlotArrays sl, float *node_rssi, uint8_t *node_recv, cudaStream_t st);
 cudaError_t launch_recheck(const NodeArrays &nd, const WorkArrays &wk, const DevParams *dp, Groups groups, TxTiles tx,
-                           const rmb_tx_record *rec, SlotArrays sl, int n_recheck, float *node_rssi,
-                           cudaStream_t st);
+                           const rmb_tx_record *rec, SlotArrays sl, int n_recheck, cudaStream_t st);
 
 // ---- emission: compaction, (tx,rx) ordering, stochastic rule, outputs -------------------------
 struct PairArrays {

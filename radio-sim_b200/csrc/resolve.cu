@@ -50,7 +50,7 @@ __device__ __forceinline__ int owner_of(int i, int P)
 
 __global__ void __launch_bounds__(128)
 resolve_kernel(NodeArrays nd, WorkArrays wk, const DevParams *dp, TxTiles tx, const rmb_tx_record *rec,
-               SlotArrays sl, float *node_rssi, uint8_t *node_recv, Counters *ctr)
+               SlotArrays sl, Counters *ctr)
 {
     const int w = blockIdx.x * blockDim.x + threadIdx.x;       // n_work is a multiple of 1024: no partial warps
     const int lane = threadIdx.x & 31;
@@ -95,10 +95,11 @@ resolve_kernel(NodeArrays nd, WorkArrays wk, const DevParams *dp, TxTiles tx, co
             uint8_t f = 0;
             double prx = 0.0, lin = 0.0;
             if (r.src != dp->rx_base + po) {
-                const double d = xm::distance(r.x, r.y, r.z, nd.x[po], nd.y[po], nd.z[po]);
+                const int wo = w - lane + o;
+                const double d = xm::distance(r.x, r.y, r.z, wk.x64[wo], wk.y64[wo], wk.z64[wo]);
                 prx = rx_power_dbm(dp, r.power_dbm, d);
                 lin = xm::dbm_to_mw(prx);
-                if (prx >= dp->sensitivity_dbm && nd.rxprob[po] > 0.0) f = kHeard;
+                if (prx >= dp->sensitivity_dbm && wk.rxp[wo] > 0.0) f = kHeard;
             }
             sl.prx[q] = prx; sl.lin[q] = lin; sl.flags[q] = f;
         }
@@ -135,8 +136,6 @@ resolve_kernel(NodeArrays nd, WorkArrays wk, const DevParams *dp, TxTiles tx, co
         bool guard = false;
         for (int s = 0; s < c; ++s) guard |= (sl.flags[base + s] & kGuard) != 0;
         sl.itot[w] = itot;
-        node_rssi[p] = (float)xm::mw_to_dbm(itot);
-        node_recv[p] = nh > 0;
         if (guard && sl.cnt[w] <= K) sl.recheck[atomicAdd(&ctr->n_recheck, 1)] = w;
     }
     sl.hcnt[w] = nh;
@@ -147,11 +146,29 @@ resolve_kernel(NodeArrays nd, WorkArrays wk, const DevParams *dp, TxTiles tx, co
 }
 
 cudaError_t launch_resolve(const NodeArrays &nd, const WorkArrays &wk, const DevParams *dp, TxTiles tx,
-                           const rmb_tx_record *rec, SlotArrays sl, float *node_rssi, uint8_t *node_recv,
-                           Counters *ctr, cudaStream_t st)
+                           const rmb_tx_record *rec, SlotArrays sl, Counters *ctr, cudaStream_t st)
 {
     if (wk.n_work <= 0) return cudaSuccess;
-    resolve_kernel<<<(wk.n_work + 127) / 128, 128, 0, st>>>(nd, wk, dp, tx, rec, sl, node_rssi, node_recv, ctr);
+    resolve_kernel<<<(wk.n_work + 127) / 128, 128, 0, st>>>(nd, wk, dp, tx, rec, sl, ctr);
+    return cudaGetLastError();
+}
+
+// Transciever.getRSSI / getReceivingState for the per-tick node-info (Transciever.java:52-78,
+// JSONClientConnection.java:331-341), produced on demand from the work-order results.
+__global__ void node_info_kernel(WorkArrays wk, SlotArrays sl, float *node_rssi, uint8_t *node_recv)
+{
+    const int w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= wk.n_work) return;
+    const int p = wk.perm[w];
+    if (p < 0) return;
+    node_rssi[p] = (float)xm::mw_to_dbm(sl.itot[w]);
+    node_recv[p] = sl.hcnt[w] > 0;
+}
+
+cudaError_t launch_node_info(const WorkArrays &wk, SlotArrays sl, float *node_rssi, uint8_t *node_recv, cudaStream_t st)
+{
+    if (wk.n_work <= 0) return cudaSuccess;
+    node_info_kernel<<<(wk.n_work + 255) / 256, 256, 0, st>>>(wk, sl, node_rssi, node_recv);
     return cudaGetLastError();
 }
 
@@ -162,7 +179,7 @@ constexpr int kRecheckChunk = 2048;
 
 __global__ void __launch_bounds__(256)
 recheck_kernel(NodeArrays nd, WorkArrays wk, const DevParams *dp, Groups groups, TxTiles tx, const rmb_tx_record *rec,
-               SlotArrays sl, float *node_rssi)
+               SlotArrays sl)
 {
     __shared__ double s_lin[kRecheckChunk];
     __shared__ double s_itot;
@@ -171,7 +188,7 @@ recheck_kernel(NodeArrays nd, WorkArrays wk, const DevParams *dp, Groups groups,
     int g = 0;
     while (g + 1 < groups.ngroups && w >= groups.w_begin[g + 1]) ++g;
     const int j0 = tx.goff[g], nj = tx.gcount[g];
-    const double X = nd.x[p], Y = nd.y[p], Z = nd.z[p];
+    const double X = wk.x64[w], Y = wk.y64[w], Z = wk.z64[w];
     const int self = dp->rx_base + p;
     double itot = dp->n0_mw;
     for (int c0 = 0; c0 < nj; c0 += kRecheckChunk) {
@@ -190,7 +207,6 @@ recheck_kernel(NodeArrays nd, WorkArrays wk, const DevParams *dp, Groups groups,
     if (threadIdx.x == 0) {
         s_itot = itot;
         sl.itot[w] = itot;
-        node_rssi[p] = (float)xm::mw_to_dbm(itot);
     }
     __syncthreads();
     itot = s_itot;
@@ -206,11 +222,10 @@ recheck_kernel(NodeArrays nd, WorkArrays wk, const DevParams *dp, Groups groups,
 }
 
 cudaError_t launch_recheck(const NodeArrays &nd, const WorkArrays &wk, const DevParams *dp, Groups groups, TxTiles tx,
-                           const rmb_tx_record *rec, SlotArrays sl, int n_recheck, float *node_rssi,
-                           cudaStream_t st)
+                           const rmb_tx_record *rec, SlotArrays sl, int n_recheck, cudaStream_t st)
 {
     if (n_recheck <= 0) return cudaSuccess;
-    recheck_kernel<<<n_recheck, 256, 0, st>>>(nd, wk, dp, groups, tx, rec, sl, node_rssi);
+    recheck_kernel<<<n_recheck, 256, 0, st>>>(nd, wk, dp, groups, tx, rec, sl);
     return cudaGetLastError();
 }
 

@@ -140,10 +140,16 @@ __global__ void regather_kernel(NodeArrays nd, WorkArrays wk, const Geom *geom)
     int w = blockIdx.x * blockDim.x + threadIdx.x;
     if (w >= wk.n_work) return;
     int p = wk.perm[w];
-    if (p < 0) { wk.fx[w] = 1e18f; wk.fy[w] = 1e18f; wk.fz[w] = 1e18f; return; }   // padding: infinitely far
-    wk.fx[w] = (float)(nd.x[p] - geom->cx);
-    wk.fy[w] = (float)(nd.y[p] - geom->cy);
-    wk.fz[w] = (float)(nd.z[p] - geom->cz);
+    if (p < 0) {                                                                    // padding: infinitely far
+        wk.fx[w] = 1e18f; wk.fy[w] = 1e18f; wk.fz[w] = 1e18f;
+        wk.x64[w] = 0.0; wk.y64[w] = 0.0; wk.z64[w] = 0.0; wk.rxp[w] = 0.0;
+        return;
+    }
+    const double X = nd.x[p], Y = nd.y[p], Z = nd.z[p];
+    wk.fx[w] = (float)(X - geom->cx);
+    wk.fy[w] = (float)(Y - geom->cy);
+    wk.fz[w] = (float)(Z - geom->cz);
+    wk.x64[w] = X; wk.y64[w] = Y; wk.z64[w] = Z; wk.rxp[w] = nd.rxprob[p];
 }
 
 cudaError_t launch_regather(const NodeArrays &nd, const WorkArrays &wk, const Geom *geom, cudaStream_t st)
