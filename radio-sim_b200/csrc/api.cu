@@ -55,8 +55,8 @@ struct rmb_handle {
     rmb_config cfg{};
     std::mutex mu;
     std::string err;
-    cudaStream_t st = nullptr;
-    cudaEvent_t ev[6] = {};
+    cudaStream_t st = nullptr, st2 = nullptr;      // st2: guard-band recheck, overlapped with the pair ordering
+    cudaEvent_t ev[6] = {}, ev_fork = nullptr, ev_join = nullptr;
     rmb_timing timing{};
 
     // host mirrors of the radio state (work order + stochastic detection are host-built)
@@ -92,7 +92,8 @@ struct rmb_handle {
     DevBuf<double> sl_prx, sl_lin, sl_sinr, itot; DevBuf<uint8_t> sl_flags;
 
     // pairs
-    DevBuf<unsigned long long> key, key_alt; DevBuf<unsigned> val, val_alt;
+    DevBuf<unsigned long long> key, key_alt, fb_key, fb_key_alt; DevBuf<unsigned> val, val_alt, fb_val, fb_val_alt;
+    DevBuf<double> rec_prx, rec_sinr; DevBuf<uint8_t> rec_flags; DevBuf<int> rec_rank, tx_cnt, first;
     DevBuf<double> pr_p, pr_rssi, pr_sinr; DevBuf<uint8_t> pr_cand;
     DevBuf<int> draw_scan, seg, scan_tmp, blkcnt; DevBuf<long long> tx_base; DevBuf<uint8_t> tx_failed;
     DevBuf<char> cub_tmp;
@@ -140,7 +141,7 @@ SlotArrays slot_arrays(rmb_handle *h)
 {
     SlotArrays s; s.K = h->K; s.slots = h->slots.p; s.cnt = h->cnt.p; s.far_part = h->far_part.p; s.splits = h->splits; s.prx = h->sl_prx.p;
     s.lin = h->sl_lin.p; s.sinr = h->sl_sinr.p; s.flags = h->sl_flags.p; s.hcnt = h->hcnt.p; s.itot = h->itot.p;
-    s.recheck = h->recheck.p;
+    s.recheck = h->recheck.p; s.first = h->first.p;
     return s;
 }
 PairArrays pair_arrays(rmb_handle *h)
@@ -159,6 +160,17 @@ PairArrays pair_arrays(rmb_handle *h)
     return p;
 }
 
+PairRecs pair_recs(rmb_handle *h)
+{
+    PairRecs r{};
+    r.cap = (long long)h->key.cap; r.key = h->key.p; r.prx = h->rec_prx.p; r.sinr = h->rec_sinr.p; r.flags = h->rec_flags.p;
+    r.rank = h->rec_rank.p; r.tx_cnt = h->tx_cnt.p;
+    int bits = 1;
+    while (bits < 31 && (1ll << bits) < (long long)h->cfg.rx_base + h->n + 1) ++bits;
+    r.key_shift = bits;
+    return r;
+}
+
 int bits_for(long long v) { int b = 1; while (b < 62 && (1ll << b) < v + 1) ++b; return b; }
 
 }  // namespace
@@ -173,7 +185,7 @@ static int ensure_slots(rmb_handle *h)
     RMB_CK(h, h->slots.ensure(nk)); RMB_CK(h, h->sl_prx.ensure(nk)); RMB_CK(h, h->sl_lin.ensure(nk));
     RMB_CK(h, h->sl_sinr.ensure(nk)); RMB_CK(h, h->sl_flags.ensure(nk));
     RMB_CK(h, h->cnt.ensure(nw)); RMB_CK(h, h->hcnt.ensure(nw)); RMB_CK(h, h->hoff.ensure(nw + 2));
-    RMB_CK(h, h->recheck.ensure(nw)); RMB_CK(h, h->far_part.ensure(nw)); RMB_CK(h, h->itot.ensure(nw));
+    RMB_CK(h, h->recheck.ensure(nw)); RMB_CK(h, h->far_part.ensure(nw)); RMB_CK(h, h->first.ensure(nw)); RMB_CK(h, h->itot.ensure(nw));
     RMB_CK(h, h->scan_tmp.ensure(nw / 1024 + 8));
     return RMB_OK;
 }
@@ -308,7 +320,10 @@ int rmb_create(const rmb_config *cfg, rmb_handle **out)
     auto bail = [&](cudaError_t ce, const char *w) { g_create_error = std::string(w) + ": " + cudaGetErrorString(ce); delete h; return RMB_ERR_CUDA; };
     if ((e = cudaSetDevice(cfg->device)) != cudaSuccess) return bail(e, "cudaSetDevice");
     if ((e = cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+    if ((e = cudaStreamCreateWithFlags(&h->st2, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
     for (auto &ev : h->ev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) return bail(e, "cudaEventCreate");
+    if ((e = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming)) != cudaSuccess ||
+        (e = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
     if ((e = h->dp.ensure(1)) != cudaSuccess || (e = h->geom.ensure(1)) != cudaSuccess ||
         (e = h->geom_scratch.ensure(8)) != cudaSuccess || (e = h->ctr.ensure(1)) != cudaSuccess ||
         (e = h->h_ctr.ensure(1)) != cudaSuccess || (e = h->theta_min_g.ensure(kMaxGroups)) != cudaSuccess ||
@@ -347,7 +362,12 @@ int rmb_destroy(rmb_handle *h)
     h->o_sinr.release(); h->o_outcome.release(); h->o_rssi64.release(); h->o_sinr64.release(); h->ho_tx.release();
     h->ho_rx.release(); h->ho_rssi.release(); h->ho_sinr.release(); h->ho_outcome.release(); h->ho_failed.release();
     h->ho_rssi64.release(); h->ho_sinr64.release();
+    h->fb_key.release(); h->fb_key_alt.release(); h->fb_val.release(); h->fb_val_alt.release(); h->rec_prx.release();
+    h->rec_sinr.release(); h->rec_flags.release(); h->rec_rank.release(); h->tx_cnt.release(); h->first.release();
     for (auto &ev : h->ev) if (ev) cudaEventDestroy(ev);
+    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    if (h->ev_join) cudaEventDestroy(h->ev_join);
+    if (h->st2) { cudaStreamSynchronize(h->st2); cudaStreamDestroy(h->st2); }
     if (h->st) cudaStreamDestroy(h->st);
     delete h;
     return RMB_OK;
@@ -525,8 +545,9 @@ static int ensure_pairs(rmb_handle *h, long long m)
     if (h->cfg.flags & RMB_FLAG_F64_VALUES) { RMB_CK(h, h->o_rssi64.ensure(cap)); RMB_CK(h, h->o_sinr64.ensure(cap)); }
     RMB_CK(h, h->scan_tmp.ensure(cap / 1024 + 8));
     if (h->cfg.model == RMB_MODEL_SINR) {
-        RMB_CK(h, h->key_alt.ensure(cap)); RMB_CK(h, h->val.ensure(cap)); RMB_CK(h, h->val_alt.ensure(cap));
-        RMB_CK(h, h->cub_tmp.ensure(sort_pairs_tmp_bytes((long long)cap)));
+        RMB_CK(h, h->key_alt.ensure(cap)); RMB_CK(h, h->val.ensure(cap));
+        RMB_CK(h, h->rec_prx.ensure(cap)); RMB_CK(h, h->rec_sinr.ensure(cap)); RMB_CK(h, h->rec_flags.ensure(cap));
+        RMB_CK(h, h->rec_rank.ensure(cap));
     }
     return RMB_OK;
 }
@@ -564,11 +585,13 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
     if (h->cfg.model == RMB_MODEL_SINR) {
         const size_t tcap = (size_t)n_tx + (size_t)(h->groups.ngroups + 1) * kTile;
         RMB_CK(h, h->txf.ensure(tcap)); RMB_CK(h, h->theta.ensure(tcap)); RMB_CK(h, h->arrival.ensure(tcap));
+        RMB_CK(h, h->tx_cnt.ensure((size_t)n_tx + 1));
         TxTiles tx = tx_tiles(h);
         const int mode = sweep_mode_for_exponent(h->cfg.pl_exponent);
         h->splits = sweep_plan(mode, h->planar, h->sweep_variant, h->n_work, n_tx / std::max(1, h->groups.ngroups), h->forced_splits);
         RMB_CK(h, h->far_part.ensure((size_t)h->splits * (size_t)std::max(h->n_work, 1)));
         RMB_CK(h, h->stg_f.ensure(std::max(n_tx, 1))); RMB_CK(h, h->stg_theta.ensure(std::max(n_tx, 1))); RMB_CK(h, h->stg_gid.ensure(std::max(n_tx, 1)));
+        if (h->key.cap == 0 && (rc = ensure_pairs(h, std::min<long long>(h->cfg.max_pairs, std::max(2ll * h->n_work, 1024ll))))) return rc;
         TxStage stg{h->stg_f.p, h->stg_theta.p, h->stg_gid.p};
         RMB_CK(h, launch_prepare(nd, h->dp.p, h->geom.p, h->groups, n_tx, d_rec, stg, tx, h->theta.p, h->theta_min_g.p, h->ctr.p, h->st));
         launches += 3;
@@ -583,9 +606,21 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
             RMB_CK(h, launch_sweep(mode, h->planar, h->sweep_variant, h->n_work, h->splits, a, h->st));
             ++launches; ++sweeps;
             RMB_CK(h, cudaEventRecord(h->ev[2], h->st));
-            RMB_CK(h, launch_resolve(nd, wk, h->dp.p, tx, d_rec, slot_arrays(h), h->ctr.p, h->st));
-            ++launches;
-            if ((rc = read_counters(h))) return rc;
+            for (int redo = 0;; ++redo) {
+                // exact resolve: decisions + dense pair records; then the per-packet segment offsets
+                RMB_CK(h, cudaMemsetAsync(h->tx_cnt.p, 0, ((size_t)n_tx + 1) * sizeof(int), h->st));
+                RMB_CK(h, launch_resolve(nd, wk, h->dp.p, tx, d_rec, slot_arrays(h), pair_recs(h), h->ctr.p, h->st));
+                RMB_CK(h, launch_tx_scan(h->tx_cnt.p, n_tx, h->seg.p, h->ctr.p, h->st));
+                launches += 2;
+                if ((rc = read_counters(h))) return rc;
+                if ((long long)h->h_ctr.p->heard <= (long long)h->key.cap || redo > 1) break;
+                // more heard pairs than record capacity: grow and redo the resolve (records beyond cap were dropped)
+                if ((rc = ensure_pairs(h, (long long)h->h_ctr.p->heard))) return rc;
+                Counters keep = *h->h_ctr.p;
+                keep.heard = 0; keep.max_near = 0; keep.n_recheck = 0; keep.max_bucket = 0;
+                RMB_CK(h, cudaMemcpyAsync(h->ctr.p, &keep, sizeof(keep), cudaMemcpyHostToDevice, h->st));
+                RMB_CK(h, cudaStreamSynchronize(h->st));
+            }
             if (h->h_ctr.p->max_near <= h->K) break;
             // a receiver had more near candidates than slots: grow and redo the sweep (deterministic)
             int k = h->K;
@@ -595,27 +630,43 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
             h->K = k;
             if ((rc = ensure_slots(h))) return rc;
             Counters keep = *h->h_ctr.p;
-            keep.heard = 0; keep.max_near = 0; keep.n_recheck = 0;
+            keep.heard = 0; keep.max_near = 0; keep.n_recheck = 0; keep.max_bucket = 0;
             RMB_CK(h, cudaMemcpyAsync(h->ctr.p, &keep, sizeof(keep), cudaMemcpyHostToDevice, h->st));
             RMB_CK(h, cudaStreamSynchronize(h->st));
         }
         m = (long long)h->h_ctr.p->heard;
-        if ((rc = ensure_pairs(h, m))) return rc;
+        if (m > (long long)h->key.cap) return h->fail(RMB_ERR_CAPACITY, "pair record capacity could not be established");
         SlotArrays sl = slot_arrays(h);
+        PairRecs pr = pair_recs(h);
         const int nre = h->h_ctr.p->n_recheck;
-        if (nre > 0) { RMB_CK(h, launch_recheck(nd, wk, h->dp.p, h->groups, tx, d_rec, sl, nre, h->st)); ++launches; }
+        if (nre > 0) {
+            // guard-band receivers: exact sequential sum on a side stream, overlapped with the ordering
+            RMB_CK(h, cudaEventRecord(h->ev_fork, h->st));
+            RMB_CK(h, cudaStreamWaitEvent(h->st2, h->ev_fork, 0));
+            RMB_CK(h, launch_recheck(nd, wk, h->dp.p, h->groups, tx, d_rec, sl, pr, nre, h->st2)); ++launches;
+            RMB_CK(h, cudaEventRecord(h->ev_join, h->st2));
+        }
         h->node_info_dirty = true;
         RMB_CK(h, cudaEventRecord(h->ev[3], h->st));
+        PairArrays pa = pair_arrays(h);
         if (m > 0) {
-            PairArrays pa = pair_arrays(h);
-            RMB_CK(h, launch_exclusive_scan(h->hcnt.p, h->hoff.p, h->n_work, h->scan_tmp.p, nullptr, h->st)); launches += 3;
-            RMB_CK(h, launch_scatter_pairs(wk, h->dp.p, tx, sl, h->hoff.p, pa, h->st)); ++launches;
-            RMB_CK(h, launch_sort_pairs(pa, m, pa.key_shift + bits_for(n_tx), h->st)); launches += 6;
-            // the sort may have swapped the double buffers
-            if (pa.key != h->key.p) std::swap(h->key, h->key_alt);
-            if (pa.val != h->val.p) std::swap(h->val, h->val_alt);
-            pa = pair_arrays(h);
-            RMB_CK(h, launch_gather_sorted(nd, h->dp.p, sl, pa, m, h->st)); ++launches;
+            const int max_bucket = h->h_ctr.p->max_bucket;
+            if (max_bucket > kBucketSortMax) {
+                const size_t cap = h->key.cap;
+                RMB_CK(h, h->fb_key.ensure(cap)); RMB_CK(h, h->fb_key_alt.ensure(cap)); RMB_CK(h, h->fb_val.ensure(cap));
+                RMB_CK(h, h->fb_val_alt.ensure(cap)); RMB_CK(h, h->cub_tmp.ensure(sort_pairs_tmp_bytes((long long)cap)));
+            }
+            OrderScratch sc{h->key_alt.p, h->fb_key.p, h->fb_key_alt.p, h->fb_val.p, h->fb_val_alt.p, h->cub_tmp.p, h->cub_tmp.cap};
+            RMB_CK(h, launch_order_pairs(pr, m, n_tx, h->seg.p, max_bucket, pa.key_shift + bits_for(n_tx), sc, h->val.p, h->st));
+            launches += 2;
+        }
+        if (nre > 0) RMB_CK(h, cudaStreamWaitEvent(h->st, h->ev_join, 0));
+        if (draws) pa.key = h->key_alt.p;         // sorted keys for the draw-order stage (the bucket items are dead by now)
+        RMB_CK(h, launch_emit_sinr(nd, h->dp.p, d_rec, n_tx, pr, h->val.p, pa, m, draws, h->ctr.p, h->st));
+        launches += 2;
+        if (draws) {
+            RMB_CK(h, launch_emit(h->dp.p, d_rec, n_tx, pa, m, true, h->uniforms.p, nu, h->ctr.p, h->st));
+            launches += 6;
         }
     } else {
         const int nblk = refmedia_blocks_per_tx(h->n);
@@ -638,8 +689,10 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
             ++launches;
         }
     }
-    RMB_CK(h, launch_emit(h->dp.p, d_rec, n_tx, pair_arrays(h), m, draws, h->uniforms.p, nu, h->ctr.p, h->st));
-    launches += draws ? 7 : 2;
+    if (h->cfg.model != RMB_MODEL_SINR) {
+        RMB_CK(h, launch_emit(h->dp.p, d_rec, n_tx, pair_arrays(h), m, draws, h->uniforms.p, nu, h->ctr.p, h->st));
+        launches += draws ? 7 : 2;
+    }
     RMB_CK(h, cudaEventRecord(h->ev[4], h->st));
     if ((rc = read_counters(h))) return rc;
     const Counters &c = *h->h_ctr.p;

@@ -55,7 +55,7 @@ struct Counters {
     int n_interfered;
     long long uniforms_used;
     int uniforms_short;
-    int pad;
+    int max_bucket;                   // most heard pairs of any one packet (chooses the ordering path)
 };
 
 // slot flags

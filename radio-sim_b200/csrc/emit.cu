@@ -81,36 +81,87 @@ cudaError_t launch_exclusive_scan(const int *in, int *out, int n, int *tmp, int 
     return cudaGetLastError();
 }
 
-// ---- heard slots -> dense (key, slot reference) list ----------------------------------------
-__global__ void scatter_pairs_kernel(WorkArrays wk, const DevParams *dp, TxTiles tx, SlotArrays sl, const int *hoff,
-                                     PairArrays pa)
+// ---- SINR medium: pair records -> (packet arrival, node index) order --------------------------
+// seg[t] = first pair of packet t; one block, chunks of 1024 with a running carry
+__global__ void __launch_bounds__(1024) tx_scan_kernel(const int *tx_cnt, int n_tx, int *seg, Counters *ctr)
 {
-    const int w = blockIdx.x * blockDim.x + threadIdx.x;
-    if (w >= wk.n_work) return;
-    const int p = wk.perm[w];
-    if (p < 0 || sl.hcnt[w] == 0) return;
-    const int c = min(sl.cnt[w], sl.K);
-    const size_t base = (size_t)w * sl.K;
-    int o = hoff[w];
-    const unsigned rxg = (unsigned)(dp->rx_base + p);
-    for (int s = 0; s < c; ++s) {
-        if (!(sl.flags[base + s] & kHeard)) continue;
-        const unsigned t = (unsigned)tx.arrival[sl.slots[base + s]];
-        pa.key[o] = ((unsigned long long)t << pa.key_shift) | rxg;
-        pa.val[o] = (unsigned)(base + s);
-        ++o;
+    __shared__ int s_warp[33];
+    __shared__ int s_carry, s_max[32];
+    if (threadIdx.x == 0) s_carry = 0;
+    __syncthreads();
+    int mx = 0;
+    for (int c0 = 0; c0 < n_tx; c0 += 1024) {
+        const int t = c0 + threadIdx.x;
+        const int v = t < n_tx ? tx_cnt[t] : 0;
+        mx = max(mx, v);
+        int total;
+        const int ex = block_exclusive_scan_1024(v, s_warp, total);
+        const int carry = s_carry;
+        if (t < n_tx) seg[t] = carry + ex;
+        __syncthreads();
+        if (threadIdx.x == 0) s_carry = carry + total;
+        __syncthreads();
+    }
+    for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if ((threadIdx.x & 31) == 0) s_max[threadIdx.x >> 5] = mx;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int i = 1; i < 32; ++i) mx = max(mx, s_max[i]);
+        seg[n_tx] = s_carry;
+        ctr->max_bucket = mx;
     }
 }
 
-cudaError_t launch_scatter_pairs(const WorkArrays &wk, const DevParams *dp, TxTiles tx, SlotArrays sl, const int *hoff,
-                                 PairArrays pa, cudaStream_t st)
+cudaError_t launch_tx_scan(const int *tx_cnt, int n_tx, int *seg, Counters *ctr, cudaStream_t st)
 {
-    if (wk.n_work <= 0) return cudaSuccess;
-    scatter_pairs_kernel<<<(wk.n_work + 127) / 128, 128, 0, st>>>(wk, dp, tx, sl, hoff, pa);
+    tx_scan_kernel<<<1, 1024, 0, st>>>(tx_cnt, n_tx, seg, ctr);
     return cudaGetLastError();
 }
 
-// ---- (tx, rx) ordering: LSD radix sort of the 64-bit keys (CUB, not on the hot path) --------
+// record i -> its packet's bucket, at the rank its atomic drew: items = (global rx << 32) | record index
+__global__ void place_items_kernel(PairRecs pr, long long m, const int *seg, unsigned long long *items)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    const unsigned long long k = pr.key[i];
+    const int t = (int)(k >> pr.key_shift);
+    const unsigned long long rx = k & ((1ull << pr.key_shift) - 1);
+    items[seg[t] + pr.rank[i]] = (rx << 32) | (unsigned long long)i;
+}
+
+// one block per packet: bitonic sort of the bucket by rx in shared memory
+__global__ void __launch_bounds__(128) bucket_sort_kernel(const int *seg, const unsigned long long *items, unsigned *order)
+{
+    __shared__ unsigned long long s[kBucketSortMax];
+    const int t = blockIdx.x;
+    const int b0 = seg[t], n = seg[t + 1] - b0;
+    if (n <= 0) return;
+    if (n == 1) { if (threadIdx.x == 0) order[b0] = (unsigned)items[b0]; return; }
+    int np2 = 2;
+    while (np2 < n) np2 <<= 1;
+    for (int i = threadIdx.x; i < np2; i += blockDim.x) s[i] = i < n ? items[b0 + i] : ~0ull;
+    __syncthreads();
+    for (int k = 2; k <= np2; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = threadIdx.x; i < np2; i += blockDim.x) {
+                const int l = i ^ j;
+                if (l > i) {
+                    const unsigned long long a = s[i], b = s[l];
+                    if ((a > b) == ((i & k) == 0)) { s[i] = b; s[l] = a; }
+                }
+            }
+            __syncthreads();
+        }
+    for (int i = threadIdx.x; i < n; i += blockDim.x) order[b0 + i] = (unsigned)s[i];
+}
+
+// fallback for buckets that do not fit a block: radix sort of the whole (t, rx) key
+__global__ void fallback_fill_kernel(PairRecs pr, long long m, unsigned long long *key, unsigned *val)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < m) { key[i] = pr.key[i]; val[i] = (unsigned)i; }
+}
+
 size_t sort_pairs_tmp_bytes(long long n)
 {
     size_t bytes = 0;
@@ -120,37 +171,22 @@ size_t sort_pairs_tmp_bytes(long long n)
     return bytes;
 }
 
-cudaError_t launch_sort_pairs(PairArrays &pa, long long n, int key_bits, cudaStream_t st)
+cudaError_t launch_order_pairs(PairRecs pr, long long m, int n_tx, const int *seg, int max_bucket, int key_bits,
+                               OrderScratch sc, unsigned *order, cudaStream_t st)
 {
-    if (n <= 1) return cudaSuccess;
-    cub::DoubleBuffer<unsigned long long> k(pa.key, pa.key_alt);
-    cub::DoubleBuffer<unsigned> v(pa.val, pa.val_alt);
-    size_t bytes = pa.cub_tmp_bytes;
-    cudaError_t e = cub::DeviceRadixSort::SortPairs(pa.cub_tmp, bytes, k, v, (int)n, 0, key_bits, st);
-    if (e != cudaSuccess) return e;
-    if (k.Current() != pa.key) { unsigned long long *t = pa.key; pa.key = pa.key_alt; pa.key_alt = t; }
-    if (v.Current() != pa.val) { unsigned *t = pa.val; pa.val = pa.val_alt; pa.val_alt = t; }
-    return cudaSuccess;
-}
-
-__global__ void gather_sorted_kernel(NodeArrays nd, const DevParams *dp, SlotArrays sl, PairArrays pa, long long n)
-{
-    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const unsigned v = pa.val[i];
-    const int p = (int)(pa.key[i] & ((1ull << pa.key_shift) - 1)) - dp->rx_base;
-    pa.p[i] = nd.rxprob[p];
-    pa.rssi[i] = sl.prx[v];
-    pa.sinr[i] = sl.sinr[v];
-    pa.cand[i] = (sl.flags[v] & kDecodable) ? 1 : 0;
-}
-
-cudaError_t launch_gather_sorted(const NodeArrays &nd, const DevParams *dp, SlotArrays sl, PairArrays pa, long long n,
-                                 cudaStream_t st)
-{
-    if (n <= 0) return cudaSuccess;
-    gather_sorted_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(nd, dp, sl, pa, n);
-    return cudaGetLastError();
+    if (m <= 0) return cudaSuccess;
+    const unsigned blocks = (unsigned)((m + 255) / 256);
+    if (max_bucket <= kBucketSortMax) {
+        place_items_kernel<<<blocks, 256, 0, st>>>(pr, m, seg, sc.items);
+        bucket_sort_kernel<<<n_tx, 128, 0, st>>>(seg, sc.items, order);
+        return cudaGetLastError();
+    }
+    fallback_fill_kernel<<<blocks, 256, 0, st>>>(pr, m, sc.fb_key, sc.fb_val);
+    cub::DoubleBuffer<unsigned long long> k(sc.fb_key, sc.fb_key_alt);
+    cub::DoubleBuffer<unsigned> v(sc.fb_val, sc.fb_val_alt);
+    size_t bytes = sc.cub_tmp_bytes;
+    RMB_CUDA_OK(cub::DeviceRadixSort::SortPairs(sc.cub_tmp, bytes, k, v, (int)m, 0, key_bits, st));
+    return cudaMemcpyAsync(order, v.Current(), (size_t)m * sizeof(unsigned), cudaMemcpyDeviceToDevice, st);
 }
 
 // ---- stochastic rule + outputs ---------------------------------------------------------------
@@ -290,6 +326,62 @@ cudaError_t launch_emit(const DevParams *dp, const rmb_tx_record *rec, int n_tx,
     }
     if (n > 0)
         finalize_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(pa, n, stochastic, uniforms, n_uniforms, ctr);
+    return cudaGetLastError();
+}
+
+// ---- SINR medium: records in (packet, node) order -> outputs ------------------------------------
+// Deterministic reception (no probability < 1 anywhere): the three-way outcome is final here.
+// Stochastic reception: only the sorted pair arrays are produced; launch_emit applies the draws.
+template <bool STOCHASTIC>
+__global__ void emit_sinr_kernel(NodeArrays nd, const DevParams *dp, PairRecs pr, const unsigned *order, PairArrays pa,
+                                 long long m, Counters *ctr)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    int delivered = 0, interfered = 0;
+    if (i < m) {
+        const unsigned ri = order[i];
+        const unsigned long long k = pr.key[ri];
+        const double rssi = pr.prx[ri], sinr = pr.sinr[ri];
+        const bool cand = (pr.flags[ri] & kDecodable) != 0;
+        if (STOCHASTIC) {
+            const int p = (int)(k & ((1ull << pa.key_shift) - 1)) - dp->rx_base;
+            pa.key[i] = k; pa.p[i] = nd.rxprob[p]; pa.rssi[i] = rssi; pa.sinr[i] = sinr; pa.cand[i] = cand ? 1 : 0;
+        } else {
+            const int t = (int)(k >> pa.key_shift);
+            const int outcome = (pa.tx_failed[t] || !cand) ? RMB_INTERFERED : RMB_DELIVERED;
+            pa.o_tx[i] = t;
+            pa.o_rx[i] = (int)(k & ((1ull << pa.key_shift) - 1));
+            pa.o_rssi[i] = (float)rssi;
+            pa.o_sinr[i] = (float)sinr;
+            if (pa.o_rssi64) { pa.o_rssi64[i] = rssi; pa.o_sinr64[i] = sinr; }
+            pa.o_outcome[i] = (uint8_t)outcome;
+            delivered = outcome == RMB_DELIVERED; interfered = !delivered;
+        }
+    }
+    if (!STOCHASTIC) {
+        for (int o = 16; o > 0; o >>= 1) {
+            delivered += __shfl_xor_sync(0xffffffffu, delivered, o);
+            interfered += __shfl_xor_sync(0xffffffffu, interfered, o);
+        }
+        if ((threadIdx.x & 31) == 0) {
+            if (delivered) atomicAdd(&ctr->n_delivered, delivered);
+            if (interfered) atomicAdd(&ctr->n_interfered, interfered);
+        }
+    }
+}
+
+cudaError_t launch_emit_sinr(const NodeArrays &nd, const DevParams *dp, const rmb_tx_record *rec, int n_tx, PairRecs pr,
+                             const unsigned *order, PairArrays pa, long long m, bool stochastic, Counters *ctr,
+                             cudaStream_t st)
+{
+    if (n_tx <= 0) return cudaSuccess;
+    const unsigned blocks = (unsigned)((m + 255) / 256);
+    if (stochastic) {
+        if (m > 0) emit_sinr_kernel<true><<<blocks, 256, 0, st>>>(nd, dp, pr, order, pa, m, ctr);
+        return cudaGetLastError();
+    }
+    txfail_det_kernel<<<(n_tx + 255) / 256, 256, 0, st>>>(dp, rec, n_tx, pa.tx_failed, pa.tx_base);
+    if (m > 0) emit_sinr_kernel<false><<<blocks, 256, 0, st>>>(nd, dp, pr, order, pa, m, ctr);
     return cudaGetLastError();
 }
 

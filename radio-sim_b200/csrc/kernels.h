@@ -73,13 +73,24 @@ struct SlotArrays {
     int *hcnt;                        // [n_work] heard pairs of the receiver
     double *itot;                     // [n_work] total in-band power [mW]
     int *recheck;                     // receivers inside the SINR guard band
+    int *first;                       // [n_work] first pair record of the receiver (its heard slots follow in slot order)
+};
+// dense heard-pair records, appended by the resolve kernel (one warp-aggregated atomic per 32 receivers)
+struct PairRecs {
+    long long cap;                    // records beyond cap are dropped; the host grows and redoes the resolve
+    int key_shift;
+    unsigned long long *key;          // (t << key_shift) | global rx
+    double *prx, *sinr;
+    uint8_t *flags;                   // kHeard | kDecodable
+    int *rank;                        // position inside the packet's bucket (atomic counter, arbitrary order)
+    int *tx_cnt;                      // [n_tx] heard pairs per packet (zero on entry)
 };
 cudaError_t launch_resolve(const NodeArrays &nd, const WorkArrays &wk, const DevParams *dp, TxTiles tx,
-                           const rmb_tx_record *rec, SlotArrays sl, Counters *ctr, cudaStream_t st);
+                           const rmb_tx_record *rec, SlotArrays sl, PairRecs pr, Counters *ctr, cudaStream_t st);
 // per-node RSSI (total in-band power, dBm) and receiving flag from the work-order results of the last tick
 cudaError_t launch_node_info(const WorkArrays &wk, SlotArrays sl, float *node_rssi, uint8_t *node_recv, cudaStream_t st);
 cudaError_t launch_recheck(const NodeArrays &nd, const WorkArrays &wk, const DevParams *dp, Groups groups, TxTiles tx,
-                           const rmb_tx_record *rec, SlotArrays sl, int n_recheck, cudaStream_t st);
+                           const rmb_tx_record *rec, SlotArrays sl, PairRecs pr, int n_recheck, cudaStream_t st);
 
 // ---- emission: compaction, (tx,rx) ordering, stochastic rule, outputs -------------------------
 struct PairArrays {
@@ -101,12 +112,22 @@ struct PairArrays {
 };
 // exclusive scan of int32 (n elements) using tmp (>= n/1024+2 ints); total written to *total_out (device)
 cudaError_t launch_exclusive_scan(const int *in, int *out, int n, int *tmp, int *total_out, cudaStream_t st);
-cudaError_t launch_scatter_pairs(const WorkArrays &wk, const DevParams *dp, TxTiles tx, SlotArrays sl, const int *hoff,
-                                 PairArrays pa, cudaStream_t st);
+// SINR medium: pair records -> (packet arrival, node index) order.
+//   tx_scan : seg[t] = first pair of packet t (exclusive scan of tx_cnt), largest bucket -> ctr->max_bucket
+//   order   : order[pos] = record index of the pos-th pair.  Buckets are filled through the atomic ranks and
+//             sorted by rx inside one block each (shared-memory bitonic sort, buckets <= kBucketSortMax);
+//             larger buckets take the CUB radix-sort fallback over the whole key.
+//   emit    : gathers the records in that order and writes the outputs (or, for stochastic reception,
+//             the sorted pair arrays the draw-order stage consumes).
+constexpr int kBucketSortMax = 2048;
+struct OrderScratch { unsigned long long *items; unsigned long long *fb_key, *fb_key_alt; unsigned *fb_val, *fb_val_alt; void *cub_tmp; size_t cub_tmp_bytes; };
+cudaError_t launch_tx_scan(const int *tx_cnt, int n_tx, int *seg, Counters *ctr, cudaStream_t st);
 size_t      sort_pairs_tmp_bytes(long long n);
-cudaError_t launch_sort_pairs(PairArrays &pa, long long n, int key_bits, cudaStream_t st);   // result in key/val
-cudaError_t launch_gather_sorted(const NodeArrays &nd, const DevParams *dp, SlotArrays sl, PairArrays pa, long long n,
-                                 cudaStream_t st);
+cudaError_t launch_order_pairs(PairRecs pr, long long m, int n_tx, const int *seg, int max_bucket, int key_bits,
+                               OrderScratch sc, unsigned *order, cudaStream_t st);
+cudaError_t launch_emit_sinr(const NodeArrays &nd, const DevParams *dp, const rmb_tx_record *rec, int n_tx, PairRecs pr,
+                             const unsigned *order, PairArrays pa, long long m, bool stochastic, Counters *ctr,
+                             cudaStream_t st);
 cudaError_t launch_emit(const DevParams *dp, const rmb_tx_record *rec, int n_tx, PairArrays pa, long long n,
                         bool stochastic, const double *uniforms, long long n_uniforms, Counters *ctr,
                         cudaStream_t st);

@@ -50,7 +50,7 @@ __device__ __forceinline__ int owner_of(int i, int P)
 
 __global__ void __launch_bounds__(128)
 resolve_kernel(NodeArrays nd, WorkArrays wk, const DevParams *dp, TxTiles tx, const rmb_tx_record *rec,
-               SlotArrays sl, Counters *ctr)
+               SlotArrays sl, PairRecs pr, Counters *ctr)
 {
     const int w = blockIdx.x * blockDim.x + threadIdx.x;       // n_work is a multiple of 1024: no partial warps
     const int lane = threadIdx.x & 31;
@@ -113,22 +113,44 @@ resolve_kernel(NodeArrays nd, WorkArrays wk, const DevParams *dp, TxTiles tx, co
         nh += sl.flags[base + s] & kHeard;
     }
 
-    // pass 2 (pooled): SINR of every heard candidate
+    // the warp's heard pairs take one contiguous range of the record list (one atomic per warp);
+    // a receiver's records are contiguous in slot order, starting at first[w]
+    int hincl = nh;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, hincl, o); if (lane >= o) hincl += y; }
+    const int wtotal = __shfl_sync(0xffffffffu, hincl, 31);
+    unsigned long long rbase = 0;
+    if (lane == 0 && wtotal) rbase = atomicAdd(&ctr->heard, (unsigned long long)wtotal);
+    rbase = __shfl_sync(0xffffffffu, rbase, 0);
+    sl.first[w] = (int)rbase + hincl - nh;
+
+    // pass 2 (pooled): SINR of every heard candidate, pair record
+    int running = 0;
     for (int i0 = 0; i0 < total; i0 += 32) {
         const int i = i0 + lane;
         const int o = owner_of(i, P);
+        const int po = __shfl_sync(0xffffffffu, p, o);
         const int so = i - __shfl_sync(0xffffffffu, P, o);
         const double it = __shfl_sync(0xffffffffu, itot, o);
-        if (i < total) {
-            const size_t q = wbase + (size_t)o * K + so;
-            uint8_t f = sl.flags[q];
-            if (f & kHeard) {
-                const double sinr = sinr_db(sl.prx[q], it, sl.lin[q]);
-                if (sinr >= dp->sinr_threshold_db) f |= kDecodable;
-                if (fabs(sinr - dp->sinr_threshold_db) < dp->sinr_guard_db) f |= kGuard;
-                sl.sinr[q] = sinr; sl.flags[q] = f;
+        size_t q = 0;
+        uint8_t f = 0;
+        if (i < total) { q = wbase + (size_t)o * K + so; f = sl.flags[q]; }
+        const unsigned hb = __ballot_sync(0xffffffffu, (f & kHeard) != 0);
+        if (f & kHeard) {
+            const double prx = sl.prx[q];
+            const double sinr = sinr_db(prx, it, sl.lin[q]);
+            if (sinr >= dp->sinr_threshold_db) f |= kDecodable;
+            if (fabs(sinr - dp->sinr_threshold_db) < dp->sinr_guard_db) f |= kGuard;
+            sl.sinr[q] = sinr; sl.flags[q] = f;
+            const long long ri = (long long)rbase + running + __popc(hb & ((1u << lane) - 1));
+            const int t = tx.arrival[sl.slots[q]];
+            const int rank = atomicAdd(&pr.tx_cnt[t], 1);
+            if (ri < pr.cap) {
+                pr.key[ri] = ((unsigned long long)t << pr.key_shift) | (unsigned)(dp->rx_base + po);
+                pr.prx[ri] = prx; pr.sinr[ri] = sinr; pr.flags[ri] = f & (kHeard | kDecodable); pr.rank[ri] = rank;
             }
         }
+        running += __popc(hb);
     }
     __syncwarp();
 
@@ -139,17 +161,13 @@ resolve_kernel(NodeArrays nd, WorkArrays wk, const DevParams *dp, TxTiles tx, co
         if (guard && sl.cnt[w] <= K) sl.recheck[atomicAdd(&ctr->n_recheck, 1)] = w;
     }
     sl.hcnt[w] = nh;
-    // total heard pairs (capacity check on the host)
-    unsigned long long v = (unsigned long long)nh;
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if (lane == 0 && v) atomicAdd(&ctr->heard, v);
 }
 
 cudaError_t launch_resolve(const NodeArrays &nd, const WorkArrays &wk, const DevParams *dp, TxTiles tx,
-                           const rmb_tx_record *rec, SlotArrays sl, Counters *ctr, cudaStream_t st)
+                           const rmb_tx_record *rec, SlotArrays sl, PairRecs pr, Counters *ctr, cudaStream_t st)
 {
     if (wk.n_work <= 0) return cudaSuccess;
-    resolve_kernel<<<(wk.n_work + 127) / 128, 128, 0, st>>>(nd, wk, dp, tx, rec, sl, ctr);
+    resolve_kernel<<<(wk.n_work + 127) / 128, 128, 0, st>>>(nd, wk, dp, tx, rec, sl, pr, ctr);
     return cudaGetLastError();
 }
 
@@ -173,15 +191,18 @@ cudaError_t launch_node_info(const WorkArrays &wk, SlotArrays sl, float *node_rs
 }
 
 // Guard-band recheck: one block per flagged receiver.  The full co-channel sum is redone in
-// double, the per-packet terms in parallel, the ADDITION strictly sequential in arrival order
-// (thread 0), so the total is bit-identical to a sequential Java/C loop.
-constexpr int kRecheckChunk = 2048;
+// double: the per-packet terms in parallel (warps 1..31), the ADDITION strictly sequential in
+// arrival order (one thread of warp 0), so the total is bit-identical to a sequential Java/C
+// loop.  The two are pipelined over double-buffered chunks: the adder works on chunk k while
+// the other warps evaluate chunk k+1 (the dependent DADD chain is the critical path).
+constexpr int kRecheckChunk = 1984;           // 31 warps x 64 terms
+constexpr int kRecheckThreads = 1024;
 
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(kRecheckThreads)
 recheck_kernel(NodeArrays nd, WorkArrays wk, const DevParams *dp, Groups groups, TxTiles tx, const rmb_tx_record *rec,
-               SlotArrays sl)
+               SlotArrays sl, PairRecs pr)
 {
-    __shared__ double s_lin[kRecheckChunk];
+    __shared__ double s_lin[2][kRecheckChunk];
     __shared__ double s_itot;
     const int w = sl.recheck[blockIdx.x];
     const int p = wk.perm[w];
@@ -190,18 +211,25 @@ recheck_kernel(NodeArrays nd, WorkArrays wk, const DevParams *dp, Groups groups,
     const int j0 = tx.goff[g], nj = tx.gcount[g];
     const double X = wk.x64[w], Y = wk.y64[w], Z = wk.z64[w];
     const int self = dp->rx_base + p;
+    const int nchunks = (nj + kRecheckChunk - 1) / kRecheckChunk;
     double itot = dp->n0_mw;
-    for (int c0 = 0; c0 < nj; c0 += kRecheckChunk) {
-        const int nc = min(kRecheckChunk, nj - c0);
-        for (int i = threadIdx.x; i < nc; i += blockDim.x) {
-            const rmb_tx_record r = rec[tx.arrival[j0 + c0 + i]];
-            double lin = 0.0;     // itot + 0.0 == itot: skipping the source is the same as adding zero
-            if (r.src != self) lin = xm::dbm_to_mw(rx_power_dbm(dp, r.power_dbm, xm::distance(r.x, r.y, r.z, X, Y, Z)));
-            s_lin[i] = lin;
+    for (int k = 0; k <= nchunks; ++k) {
+        if (threadIdx.x >= 32) {
+            if (k < nchunks) {                                   // evaluate chunk k
+                const int c0 = k * kRecheckChunk, nc = min(kRecheckChunk, nj - c0);
+                for (int i = threadIdx.x - 32; i < nc; i += kRecheckThreads - 32) {
+                    const rmb_tx_record r = rec[tx.arrival[j0 + c0 + i]];
+                    double lin = 0.0;     // itot + 0.0 == itot: skipping the source is the same as adding zero
+                    if (r.src != self) lin = xm::dbm_to_mw(rx_power_dbm(dp, r.power_dbm, xm::distance(r.x, r.y, r.z, X, Y, Z)));
+                    s_lin[k & 1][i] = lin;
+                }
+            }
+        } else if (threadIdx.x == 0 && k > 0) {                  // add chunk k-1, in order
+            const int c0 = (k - 1) * kRecheckChunk, nc = min(kRecheckChunk, nj - c0);
+            const double *v = s_lin[(k - 1) & 1];
+#pragma unroll 8
+            for (int i = 0; i < nc; ++i) itot = xm::add(itot, v[i]);
         }
-        __syncthreads();
-        if (threadIdx.x == 0)
-            for (int i = 0; i < nc; ++i) itot = xm::add(itot, s_lin[i]);
         __syncthreads();
     }
     if (threadIdx.x == 0) {
@@ -218,14 +246,19 @@ recheck_kernel(NodeArrays nd, WorkArrays wk, const DevParams *dp, Groups groups,
         const double sinr = sinr_db(sl.prx[base + s], itot, sl.lin[base + s]);
         f = kHeard | (sinr >= dp->sinr_threshold_db ? kDecodable : 0);
         sl.sinr[base + s] = sinr; sl.flags[base + s] = f;
+        // the receiver's pair records follow first[w] in slot order (heard slots only)
+        int h = 0;
+        for (int b = 0; b < s; ++b) h += sl.flags[base + b] & kHeard;
+        const long long ri = (long long)sl.first[w] + h;
+        if (ri < pr.cap) { pr.sinr[ri] = sinr; pr.flags[ri] = f; }
     }
 }
 
 cudaError_t launch_recheck(const NodeArrays &nd, const WorkArrays &wk, const DevParams *dp, Groups groups, TxTiles tx,
-                           const rmb_tx_record *rec, SlotArrays sl, int n_recheck, cudaStream_t st)
+                           const rmb_tx_record *rec, SlotArrays sl, PairRecs pr, int n_recheck, cudaStream_t st)
 {
     if (n_recheck <= 0) return cudaSuccess;
-    recheck_kernel<<<n_recheck, 256, 0, st>>>(nd, wk, dp, groups, tx, rec, sl);
+    recheck_kernel<<<n_recheck, kRecheckThreads, 0, st>>>(nd, wk, dp, groups, tx, rec, sl, pr);
     return cudaGetLastError();
 }
 
