@@ -121,6 +121,7 @@ typedef struct rmb_timing {
     float ms_emit;                /* compaction, ordering, stochastic rule, outputs      */
     int32_t sweep_launches;
     int32_t kernel_launches;      /* all kernels launched by the last tick               */
+    int32_t recheck_sequential;   /* guard-band receivers that needed the sequential sum */
 } rmb_timing;
 
 int         rmb_version(void);

@@ -51,7 +51,8 @@ class Result(C.Structure):
 class Timing(C.Structure):
     _fields_ = [("ms_total", C.c_float), ("ms_prepare", C.c_float), ("ms_sweep", C.c_float),
                 ("ms_resolve", C.c_float), ("ms_emit", C.c_float),
-                ("sweep_launches", C.c_int32), ("kernel_launches", C.c_int32)]
+                ("sweep_launches", C.c_int32), ("kernel_launches", C.c_int32),
+                ("recheck_sequential", C.c_int32)]
 
 
 assert C.sizeof(TxRecord) == 48

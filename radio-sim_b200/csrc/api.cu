@@ -88,7 +88,7 @@ struct rmb_handle {
 
     // slots
     int K = 8;
-    DevBuf<int> slots, cnt, hcnt, hoff, recheck; DevBuf<float> far_part; int splits = 1, forced_splits = 0;
+    DevBuf<int> slots, cnt, hcnt, hoff, recheck, recheck2; DevBuf<float> far_part; int splits = 1, forced_splits = 0;
     DevBuf<double> sl_prx, sl_lin, sl_sinr, itot; DevBuf<uint8_t> sl_flags;
 
     // pairs
@@ -141,7 +141,7 @@ SlotArrays slot_arrays(rmb_handle *h)
 {
     SlotArrays s; s.K = h->K; s.slots = h->slots.p; s.cnt = h->cnt.p; s.far_part = h->far_part.p; s.splits = h->splits; s.prx = h->sl_prx.p;
     s.lin = h->sl_lin.p; s.sinr = h->sl_sinr.p; s.flags = h->sl_flags.p; s.hcnt = h->hcnt.p; s.itot = h->itot.p;
-    s.recheck = h->recheck.p; s.first = h->first.p;
+    s.recheck = h->recheck.p; s.recheck2 = h->recheck2.p; s.first = h->first.p;
     return s;
 }
 PairArrays pair_arrays(rmb_handle *h)
@@ -185,7 +185,7 @@ static int ensure_slots(rmb_handle *h)
     RMB_CK(h, h->slots.ensure(nk)); RMB_CK(h, h->sl_prx.ensure(nk)); RMB_CK(h, h->sl_lin.ensure(nk));
     RMB_CK(h, h->sl_sinr.ensure(nk)); RMB_CK(h, h->sl_flags.ensure(nk));
     RMB_CK(h, h->cnt.ensure(nw)); RMB_CK(h, h->hcnt.ensure(nw)); RMB_CK(h, h->hoff.ensure(nw + 2));
-    RMB_CK(h, h->recheck.ensure(nw)); RMB_CK(h, h->far_part.ensure(nw)); RMB_CK(h, h->first.ensure(nw)); RMB_CK(h, h->itot.ensure(nw));
+    RMB_CK(h, h->recheck.ensure(nw)); RMB_CK(h, h->recheck2.ensure(nw)); RMB_CK(h, h->far_part.ensure(nw)); RMB_CK(h, h->first.ensure(nw)); RMB_CK(h, h->itot.ensure(nw));
     RMB_CK(h, h->scan_tmp.ensure(nw / 1024 + 8));
     return RMB_OK;
 }
@@ -354,7 +354,7 @@ int rmb_destroy(rmb_handle *h)
     h->pk_channel.release(); h->pk_power.release(); h->pk_stage.release(); h->rec.release(); h->txf.release(); h->stg_f.release(); h->stg_theta.release(); h->stg_gid.release();
     h->theta.release(); h->theta_min_g.release(); h->arrival.release(); h->goff.release(); h->gcount.release();
     h->uniforms.release(); h->slots.release(); h->cnt.release(); h->hcnt.release(); h->hoff.release();
-    h->recheck.release(); h->far_part.release(); h->sl_prx.release(); h->sl_lin.release(); h->sl_sinr.release();
+    h->recheck.release(); h->recheck2.release(); h->far_part.release(); h->sl_prx.release(); h->sl_lin.release(); h->sl_sinr.release();
     h->itot.release(); h->sl_flags.release(); h->key.release(); h->key_alt.release(); h->val.release();
     h->val_alt.release(); h->pr_p.release(); h->pr_rssi.release(); h->pr_sinr.release(); h->pr_cand.release();
     h->draw_scan.release(); h->seg.release(); h->scan_tmp.release(); h->blkcnt.release(); h->tx_base.release();
@@ -617,7 +617,7 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
                 // more heard pairs than record capacity: grow and redo the resolve (records beyond cap were dropped)
                 if ((rc = ensure_pairs(h, (long long)h->h_ctr.p->heard))) return rc;
                 Counters keep = *h->h_ctr.p;
-                keep.heard = 0; keep.max_near = 0; keep.n_recheck = 0; keep.max_bucket = 0;
+                keep.heard = 0; keep.max_near = 0; keep.n_recheck = 0; keep.n_recheck2 = 0; keep.max_bucket = 0;
                 RMB_CK(h, cudaMemcpyAsync(h->ctr.p, &keep, sizeof(keep), cudaMemcpyHostToDevice, h->st));
                 RMB_CK(h, cudaStreamSynchronize(h->st));
             }
@@ -630,7 +630,7 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
             h->K = k;
             if ((rc = ensure_slots(h))) return rc;
             Counters keep = *h->h_ctr.p;
-            keep.heard = 0; keep.max_near = 0; keep.n_recheck = 0; keep.max_bucket = 0;
+            keep.heard = 0; keep.max_near = 0; keep.n_recheck = 0; keep.n_recheck2 = 0; keep.max_bucket = 0;
             RMB_CK(h, cudaMemcpyAsync(h->ctr.p, &keep, sizeof(keep), cudaMemcpyHostToDevice, h->st));
             RMB_CK(h, cudaStreamSynchronize(h->st));
         }
@@ -643,7 +643,7 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
             // guard-band receivers: exact sequential sum on a side stream, overlapped with the ordering
             RMB_CK(h, cudaEventRecord(h->ev_fork, h->st));
             RMB_CK(h, cudaStreamWaitEvent(h->st2, h->ev_fork, 0));
-            RMB_CK(h, launch_recheck(nd, wk, h->dp.p, h->groups, tx, d_rec, sl, pr, nre, h->st2)); ++launches;
+            RMB_CK(h, launch_recheck(nd, wk, h->dp.p, h->groups, tx, d_rec, sl, pr, nre, h->ctr.p, h->st2)); launches += 2;
             RMB_CK(h, cudaEventRecord(h->ev_join, h->st2));
         }
         h->node_info_dirty = true;
@@ -702,7 +702,7 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
     cudaEventElapsedTime(&t.ms_sweep, h->ev[1], h->ev[2]);
     cudaEventElapsedTime(&t.ms_resolve, h->ev[2], h->ev[3]);
     cudaEventElapsedTime(&t.ms_emit, h->ev[3], h->ev[4]);
-    t.sweep_launches = sweeps; t.kernel_launches = launches;
+    t.sweep_launches = sweeps; t.kernel_launches = launches; t.recheck_sequential = c.n_recheck2;
     rmb_result &r = h->last;
     memset(&r, 0, sizeof(r));
     r.n_pairs = m; r.n_delivered = c.n_delivered; r.n_interfered = c.n_interfered; r.n_decisions = c.decisions;

@@ -56,6 +56,8 @@ struct Counters {
     long long uniforms_used;
     int uniforms_short;
     int max_bucket;                   // most heard pairs of any one packet (chooses the ordering path)
+    int n_recheck2;                   // guard-band receivers that needed the sequential sum
+    int pad;
 };
 
 // slot flags

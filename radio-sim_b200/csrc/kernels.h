@@ -73,6 +73,7 @@ struct SlotArrays {
     int *hcnt;                        // [n_work] heard pairs of the receiver
     double *itot;                     // [n_work] total in-band power [mW]
     int *recheck;                     // receivers inside the SINR guard band
+    int *recheck2;                    // of those, the ones the tree sum cannot decide (sequential redo)
     int *first;                       // [n_work] first pair record of the receiver (its heard slots follow in slot order)
 };
 // dense heard-pair records, appended by the resolve kernel (one warp-aggregated atomic per 32 receivers)
@@ -90,7 +91,8 @@ cudaError_t launch_resolve(const NodeArrays &nd, const WorkArrays &wk, const Dev
 // per-node RSSI (total in-band power, dBm) and receiving flag from the work-order results of the last tick
 cudaError_t launch_node_info(const WorkArrays &wk, SlotArrays sl, float *node_rssi, uint8_t *node_recv, cudaStream_t st);
 cudaError_t launch_recheck(const NodeArrays &nd, const WorkArrays &wk, const DevParams *dp, Groups groups, TxTiles tx,
-                           const rmb_tx_record *rec, SlotArrays sl, PairRecs pr, int n_recheck, cudaStream_t st);
+                           const rmb_tx_record *rec, SlotArrays sl, PairRecs pr, int n_recheck, Counters *ctr,
+                           cudaStream_t st);
 
 // ---- emission: compaction, (tx,rx) ordering, stochastic rule, outputs -------------------------
 struct PairArrays {

@@ -190,20 +190,55 @@ cudaError_t launch_node_info(const WorkArrays &wk, SlotArrays sl, float *node_rs
     return cudaGetLastError();
 }
 
-// Guard-band recheck: one block per flagged receiver.  The full co-channel sum is redone in
-// double: the per-packet terms in parallel (warps 1..31), the ADDITION strictly sequential in
-// arrival order (one thread of warp 0), so the total is bit-identical to a sequential Java/C
-// loop.  The two are pipelined over double-buffered chunks: the adder works on chunk k while
-// the other warps evaluate chunk k+1 (the dependent DADD chain is the critical path).
-constexpr int kRecheckChunk = 1984;           // 31 warps x 64 terms
+// ---- guard-band recheck ----------------------------------------------------------------------
+// Receivers whose SINR lies within the guard band of the threshold cannot be decided from the
+// fp32 far-field sum.  Two tiers, both one block per receiver:
+//   tier 1: ALL co-channel terms in exact double, summed as a fixed tree (parallel).  A tree
+//           sum and the oracle's sequential sum of n positive terms differ by at most
+//           2 n u relative (u = 2^-53), i.e. ~1e-11 dB of SINR -- so the decision is certain
+//           unless |SINR - threshold| is below that bound;
+//   tier 2: for those (practically only constructed test cases) the ADDITION is redone strictly
+//           sequentially in arrival order, bit-identical to the Java/C loop, pipelined over
+//           double-buffered chunks (one adder thread, 31 warps evaluating the next chunk).
+__device__ __forceinline__ double exact_lin(const DevParams *dp, const rmb_tx_record &r, int self, double X, double Y, double Z)
+{
+    // itot + 0.0 == itot: skipping the source is the same as adding zero
+    if (r.src == self) return 0.0;
+    return xm::dbm_to_mw(rx_power_dbm(dp, r.power_dbm, xm::distance(r.x, r.y, r.z, X, Y, Z)));
+}
+
+// writes the receiver's total and the SINR / flags of its heard slots and pair records; returns
+// true if some decision is closer to the threshold than tol_rel (relative uncertainty of itot) allows
+__device__ bool apply_itot(const DevParams *dp, SlotArrays sl, PairRecs pr, int w, double itot, double tol_rel)
+{
+    bool close = false;
+    const int c = min(sl.cnt[w], sl.K);
+    const size_t base = (size_t)w * sl.K;
+    sl.itot[w] = itot;
+    int h = 0;                                   // the receiver's records follow first[w] in slot order (heard slots only)
+    for (int s = 0; s < c; ++s) {
+        if (!(sl.flags[base + s] & kHeard)) continue;
+        const double lin = sl.lin[base + s];
+        const double sinr = sinr_db(sl.prx[base + s], itot, lin);
+        const double ioth = itot - lin;
+        const double tol_db = ioth > 0.0 ? 4.342944819032518 * tol_rel * (itot / ioth) + 1e-12 : 0.0;
+        if (fabs(sinr - dp->sinr_threshold_db) <= tol_db) close = true;
+        const uint8_t f = kHeard | (sinr >= dp->sinr_threshold_db ? kDecodable : 0);
+        sl.sinr[base + s] = sinr; sl.flags[base + s] = f;
+        const long long ri = (long long)sl.first[w] + h;
+        if (ri < pr.cap) { pr.sinr[ri] = sinr; pr.flags[ri] = f; }
+        ++h;
+    }
+    return close;
+}
+
 constexpr int kRecheckThreads = 1024;
 
 __global__ void __launch_bounds__(kRecheckThreads)
-recheck_kernel(NodeArrays nd, WorkArrays wk, const DevParams *dp, Groups groups, TxTiles tx, const rmb_tx_record *rec,
-               SlotArrays sl, PairRecs pr)
+recheck_tree_kernel(WorkArrays wk, const DevParams *dp, Groups groups, TxTiles tx, const rmb_tx_record *rec,
+                    SlotArrays sl, PairRecs pr, Counters *ctr)
 {
-    __shared__ double s_lin[2][kRecheckChunk];
-    __shared__ double s_itot;
+    __shared__ double s_part[32];
     const int w = sl.recheck[blockIdx.x];
     const int p = wk.perm[w];
     int g = 0;
@@ -211,54 +246,66 @@ recheck_kernel(NodeArrays nd, WorkArrays wk, const DevParams *dp, Groups groups,
     const int j0 = tx.goff[g], nj = tx.gcount[g];
     const double X = wk.x64[w], Y = wk.y64[w], Z = wk.z64[w];
     const int self = dp->rx_base + p;
-    const int nchunks = (nj + kRecheckChunk - 1) / kRecheckChunk;
-    double itot = dp->n0_mw;
-    for (int k = 0; k <= nchunks; ++k) {
-        if (threadIdx.x >= 32) {
-            if (k < nchunks) {                                   // evaluate chunk k
-                const int c0 = k * kRecheckChunk, nc = min(kRecheckChunk, nj - c0);
-                for (int i = threadIdx.x - 32; i < nc; i += kRecheckThreads - 32) {
-                    const rmb_tx_record r = rec[tx.arrival[j0 + c0 + i]];
-                    double lin = 0.0;     // itot + 0.0 == itot: skipping the source is the same as adding zero
-                    if (r.src != self) lin = xm::dbm_to_mw(rx_power_dbm(dp, r.power_dbm, xm::distance(r.x, r.y, r.z, X, Y, Z)));
-                    s_lin[k & 1][i] = lin;
-                }
-            }
-        } else if (threadIdx.x == 0 && k > 0) {                  // add chunk k-1, in order
-            const int c0 = (k - 1) * kRecheckChunk, nc = min(kRecheckChunk, nj - c0);
-            const double *v = s_lin[(k - 1) & 1];
-#pragma unroll 8
-            for (int i = 0; i < nc; ++i) itot = xm::add(itot, v[i]);
-        }
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) {
-        s_itot = itot;
-        sl.itot[w] = itot;
-    }
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < nj; i += kRecheckThreads) acc += exact_lin(dp, rec[tx.arrival[j0 + i]], self, X, Y, Z);
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = acc;
     __syncthreads();
-    itot = s_itot;
-    const int c = min(sl.cnt[w], sl.K);
-    const size_t base = (size_t)w * sl.K;
-    for (int s = threadIdx.x; s < c; s += blockDim.x) {
-        uint8_t f = sl.flags[base + s];
-        if (!(f & kHeard)) continue;
-        const double sinr = sinr_db(sl.prx[base + s], itot, sl.lin[base + s]);
-        f = kHeard | (sinr >= dp->sinr_threshold_db ? kDecodable : 0);
-        sl.sinr[base + s] = sinr; sl.flags[base + s] = f;
-        // the receiver's pair records follow first[w] in slot order (heard slots only)
-        int h = 0;
-        for (int b = 0; b < s; ++b) h += sl.flags[base + b] & kHeard;
-        const long long ri = (long long)sl.first[w] + h;
-        if (ri < pr.cap) { pr.sinr[ri] = sinr; pr.flags[ri] = f; }
+    if (threadIdx.x == 0) {
+        double itot = dp->n0_mw;
+        for (int i = 0; i < kRecheckThreads / 32; ++i) itot += s_part[i];
+        const double tol_rel = 2.0 * (double)(nj + 64) * 1.1102230246251565e-16;
+        if (apply_itot(dp, sl, pr, w, itot, tol_rel)) sl.recheck2[atomicAdd(&ctr->n_recheck2, 1)] = w;
+    }
+}
+
+constexpr int kRecheckChunk = 1984;           // 31 warps x 64 terms
+constexpr int kRecheckSeqBlocks = 32;
+
+__global__ void __launch_bounds__(kRecheckThreads)
+recheck_seq_kernel(WorkArrays wk, const DevParams *dp, Groups groups, TxTiles tx, const rmb_tx_record *rec,
+                   SlotArrays sl, PairRecs pr, const Counters *ctr)
+{
+    __shared__ double s_lin[2][kRecheckChunk];
+    const int n2 = ctr->n_recheck2;
+    for (int b = blockIdx.x; b < n2; b += gridDim.x) {
+        const int w = sl.recheck2[b];
+        const int p = wk.perm[w];
+        int g = 0;
+        while (g + 1 < groups.ngroups && w >= groups.w_begin[g + 1]) ++g;
+        const int j0 = tx.goff[g], nj = tx.gcount[g];
+        const double X = wk.x64[w], Y = wk.y64[w], Z = wk.z64[w];
+        const int self = dp->rx_base + p;
+        const int nchunks = (nj + kRecheckChunk - 1) / kRecheckChunk;
+        double itot = dp->n0_mw;
+        for (int k = 0; k <= nchunks; ++k) {
+            if (threadIdx.x >= 32) {
+                if (k < nchunks) {                                   // evaluate chunk k
+                    const int c0 = k * kRecheckChunk, nc = min(kRecheckChunk, nj - c0);
+                    for (int i = threadIdx.x - 32; i < nc; i += kRecheckThreads - 32)
+                        s_lin[k & 1][i] = exact_lin(dp, rec[tx.arrival[j0 + c0 + i]], self, X, Y, Z);
+                }
+            } else if (threadIdx.x == 0 && k > 0) {                  // add chunk k-1, in order
+                const int c0 = (k - 1) * kRecheckChunk, nc = min(kRecheckChunk, nj - c0);
+                const double *v = s_lin[(k - 1) & 1];
+#pragma unroll 8
+                for (int i = 0; i < nc; ++i) itot = xm::add(itot, v[i]);
+            }
+            __syncthreads();
+        }
+        if (threadIdx.x == 0) apply_itot(dp, sl, pr, w, itot, 0.0);
+        __syncthreads();
     }
 }
 
 cudaError_t launch_recheck(const NodeArrays &nd, const WorkArrays &wk, const DevParams *dp, Groups groups, TxTiles tx,
-                           const rmb_tx_record *rec, SlotArrays sl, PairRecs pr, int n_recheck, cudaStream_t st)
+                           const rmb_tx_record *rec, SlotArrays sl, PairRecs pr, int n_recheck, Counters *ctr,
+                           cudaStream_t st)
 {
+    (void)nd;
     if (n_recheck <= 0) return cudaSuccess;
-    recheck_kernel<<<n_recheck, kRecheckThreads, 0, st>>>(nd, wk, dp, groups, tx, rec, sl, pr);
+    recheck_tree_kernel<<<n_recheck, kRecheckThreads, 0, st>>>(wk, dp, groups, tx, rec, sl, pr, ctr);
+    recheck_seq_kernel<<<min(n_recheck, kRecheckSeqBlocks), kRecheckThreads, 0, st>>>(wk, dp, groups, tx, rec, sl, pr, ctr);
     return cudaGetLastError();
 }
 

@@ -122,6 +122,48 @@ def test_guard_band_forces_exact_recheck(rsb, orc):
     assert total_recheck >= 4
 
 
+def test_threshold_among_many_interferers_takes_the_sequential_sum(rsb, orc):
+    """400 co-channel packets, one receiver whose SINR is bisected onto the threshold to the last ulp of
+    the interferer distance: the tree sum cannot decide (|SINR - 4 dB| ~ 1e-13 dB), so the strictly
+    sequential arrival-order sum must run and reproduce the oracle's decision on both sides."""
+    rng = np.random.default_rng(11)
+    n, t = 3000, 400
+    x, y = rng.uniform(0, 4000, n), rng.uniform(0, 4000, n)
+    x[0], y[0] = 2000.0, 2000.0            # the wanted transmitter
+    x[1], y[1] = 2025.0, 2000.0            # the receiver, 25 m away
+    src = np.concatenate([[0, 2], 3 + rng.permutation(n - 3)[:t - 2]]).astype(np.int32)
+    z, ch = np.zeros(n), np.full(n, 26, dtype=np.int32)
+    tiny = orc.params(orc.MODEL_SINR)
+
+    def decodable(d):
+        x[2], y[2] = 2025.0 + d, 2000.0    # the dominant interferer
+        ref = orc.tick(tiny, orc.NodeSet(x, y), orc.make_packets(src, 0.0, 26), threads=8)
+        p = ref["pairs"]
+        sel = (p["tx"] == 0) & (p["rx"] == 1)
+        assert sel.sum() == 1
+        return bool(p["outcome"][sel][0] == 2)
+    lo, hi = 5.0, 400.0
+    assert not decodable(lo) and decodable(hi)
+    for _ in range(200):
+        mid = 0.5 * (lo + hi)
+        if mid == lo or mid == hi:
+            break
+        if decodable(mid):
+            hi = mid
+        else:
+            lo = mid
+    seq = 0
+    for d in [lo, hi]:
+        x[2], y[2] = 2025.0 + d, 2000.0
+        with rsb.Medium("sinr", f64_values=True) as m:
+            m.set_nodes(x, y, z, channel=ch)
+            r = m.tick(src)
+            seq += m.timing()["recheck_sequential"]
+        ref = orc.tick(tiny, orc.NodeSet(x, y), orc.make_packets(src, 0.0, 26), threads=8)
+        compare(r, ref)
+    assert seq >= 1
+
+
 def test_position_and_radio_updates(rsb, orc):
     x, y, z, ch = random_deployment(10, 3000, 600.0, channels=4)
     src = pick_sources(10, 3000, 100)
