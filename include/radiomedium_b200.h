@@ -180,6 +180,13 @@ int rmb_fetch(rmb_handle *h, rmb_result *out);
 int rmb_node_info(rmb_handle *h, float *rssi_dbm, uint8_t *receiving);
 
 int rmb_last_timing(const rmb_handle *h, rmb_timing *out);
+/* CUDA stream the handle's kernels and copies run on (a cudaStream_t passed as void*).
+ * rmb_set_stream makes the handle use the caller's stream instead of its own, so that work the
+ * caller orders on that stream (e.g. the NCCL all-gather of the tx records) needs no host
+ * synchronisation with the tick; rmb_build_tx_records then does not synchronise either.
+ * NULL restores the handle's own stream.  No reference counterpart (device plumbing). */
+int rmb_get_stream(rmb_handle *h, void **stream);
+int rmb_set_stream(rmb_handle *h, void *stream);
 /* tuning knob for benchmarks/tests: sweep variant (0 = auto) and near-slot capacity */
 int rmb_set_tuning(rmb_handle *h, int32_t sweep_variant, int32_t near_slots);
 

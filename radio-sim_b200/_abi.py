@@ -19,7 +19,7 @@ FLAG_F64_VALUES = 1
 SYMBOLS = ("rmb_version", "rmb_config_default", "rmb_create", "rmb_destroy", "rmb_last_error",
            "rmb_set_nodes", "rmb_set_matrix", "rmb_update_positions", "rmb_update_radio", "rmb_tick",
            "rmb_build_tx_records", "rmb_tick_records", "rmb_tick_resident", "rmb_fetch",
-           "rmb_node_info", "rmb_last_timing", "rmb_set_tuning")
+           "rmb_node_info", "rmb_last_timing", "rmb_set_tuning", "rmb_get_stream", "rmb_set_stream")
 
 
 class Config(C.Structure):

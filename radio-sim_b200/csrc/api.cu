@@ -55,6 +55,7 @@ struct rmb_handle {
     rmb_config cfg{};
     std::mutex mu;
     std::string err;
+    cudaStream_t own_st = nullptr;                 // created by rmb_create; st == own_st unless rmb_set_stream
     cudaStream_t st = nullptr, st2 = nullptr;      // st2: guard-band recheck, overlapped with the pair ordering
     cudaEvent_t ev[6] = {}, ev_fork = nullptr, ev_join = nullptr;
     rmb_timing timing{};
@@ -319,7 +320,8 @@ int rmb_create(const rmb_config *cfg, rmb_handle **out)
     if (h->cfg.max_pairs <= 0) h->cfg.max_pairs = 64ll << 20;
     auto bail = [&](cudaError_t ce, const char *w) { g_create_error = std::string(w) + ": " + cudaGetErrorString(ce); delete h; return RMB_ERR_CUDA; };
     if ((e = cudaSetDevice(cfg->device)) != cudaSuccess) return bail(e, "cudaSetDevice");
-    if ((e = cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+    if ((e = cudaStreamCreateWithFlags(&h->own_st, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+    h->st = h->own_st;
     if ((e = cudaStreamCreateWithFlags(&h->st2, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
     for (auto &ev : h->ev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) return bail(e, "cudaEventCreate");
     if ((e = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming)) != cudaSuccess ||
@@ -368,7 +370,7 @@ int rmb_destroy(rmb_handle *h)
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     if (h->ev_join) cudaEventDestroy(h->ev_join);
     if (h->st2) { cudaStreamSynchronize(h->st2); cudaStreamDestroy(h->st2); }
-    if (h->st) cudaStreamDestroy(h->st);
+    if (h->own_st) cudaStreamDestroy(h->own_st);
     delete h;
     return RMB_OK;
 }
@@ -519,6 +521,24 @@ extern "C" int rmb_node_info(rmb_handle *h, float *rssi_dbm, uint8_t *receiving)
     return RMB_OK;
 }
 
+extern "C" int rmb_get_stream(rmb_handle *h, void **stream)
+{
+    if (!h || !stream) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    *stream = (void *)h->st;
+    return RMB_OK;
+}
+
+extern "C" int rmb_set_stream(rmb_handle *h, void *stream)
+{
+    if (!h) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    RMB_CK(h, cudaStreamSynchronize(h->st));
+    h->st = stream ? (cudaStream_t)stream : h->own_st;
+    return RMB_OK;
+}
+
 extern "C" int rmb_last_timing(const rmb_handle *h, rmb_timing *out)
 {
     if (!h || !out) return RMB_ERR_INVALID;
@@ -588,7 +608,9 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
         RMB_CK(h, h->tx_cnt.ensure((size_t)n_tx + 1));
         TxTiles tx = tx_tiles(h);
         const int mode = sweep_mode_for_exponent(h->cfg.pl_exponent);
-        h->splits = sweep_plan(mode, h->planar, h->sweep_variant, h->n_work, n_tx / std::max(1, h->groups.ngroups), h->forced_splits);
+        // auto: 8 receivers per thread once the shard is large enough to fill the GPU with 1024-receiver blocks
+        const int variant = h->sweep_variant ? h->sweep_variant : (h->n_work >= (1 << 19) ? 2 : 1);
+        h->splits = sweep_plan(mode, h->planar, variant, h->n_work, n_tx / std::max(1, h->groups.ngroups), h->forced_splits);
         RMB_CK(h, h->far_part.ensure((size_t)h->splits * (size_t)std::max(h->n_work, 1)));
         RMB_CK(h, h->stg_f.ensure(std::max(n_tx, 1))); RMB_CK(h, h->stg_theta.ensure(std::max(n_tx, 1))); RMB_CK(h, h->stg_gid.ensure(std::max(n_tx, 1)));
         if (h->key.cap == 0 && (rc = ensure_pairs(h, std::min<long long>(h->cfg.max_pairs, std::max(2ll * h->n_work, 1024ll))))) return rc;
@@ -603,7 +625,7 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
             a.far_part = h->far_part.p; a.cnt = h->cnt.p; a.slots = h->slots.p; a.K = h->K;
             RMB_CK(h, cudaMemsetAsync(h->cnt.p, 0, (size_t)h->n_work * sizeof(int), h->st));
             if (attempt) RMB_CK(h, cudaEventRecord(h->ev[1], h->st));
-            RMB_CK(h, launch_sweep(mode, h->planar, h->sweep_variant, h->n_work, h->splits, a, h->st));
+            RMB_CK(h, launch_sweep(mode, h->planar, variant, h->n_work, h->splits, a, h->st));
             ++launches; ++sweeps;
             RMB_CK(h, cudaEventRecord(h->ev[2], h->st));
             for (int redo = 0;; ++redo) {
@@ -789,7 +811,7 @@ int rmb_build_tx_records(rmb_handle *h, int32_t n_tx, const int32_t *src, const 
     RMB_CK(h, cudaSetDevice(h->cfg.device));
     int rc = stage_records(h, n_tx, src, power_dbm, channel, (rmb_tx_record *)d_records, false);
     if (rc) return rc;
-    RMB_CK(h, cudaStreamSynchronize(h->st));      // the caller hands d_records to another stream (NCCL)
+    if (h->st == h->own_st) RMB_CK(h, cudaStreamSynchronize(h->st));      // the caller hands d_records to another stream (NCCL)
     return RMB_OK;
 }
 

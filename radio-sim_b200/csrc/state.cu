@@ -141,7 +141,7 @@ __global__ void regather_kernel(NodeArrays nd, WorkArrays wk, const Geom *geom)
     if (w >= wk.n_work) return;
     int p = wk.perm[w];
     if (p < 0) {                                                                    // padding: infinitely far
-        wk.fx[w] = 1e18f; wk.fy[w] = 1e18f; wk.fz[w] = 1e18f;
+        wk.fx[w] = 1e15f; wk.fy[w] = 1e15f; wk.fz[w] = 1e15f;   // (1e15 c)^2 stays finite in fp32 for any sane c
         wk.x64[w] = 0.0; wk.y64[w] = 0.0; wk.z64[w] = 0.0; wk.rxp[w] = 0.0;
         return;
     }
@@ -257,7 +257,7 @@ prepare_tx_kernel(NodeArrays nd, const DevParams *dp, const Geom *geom, Groups g
             const double c = (double)cf;
             stg.f[t] = make_float4((float)((r.x - geom->cx) * c), (float)((r.y - geom->cy) * c),
                                    (float)((r.z - geom->cz) * c), cf);
-            const float th = (float)(fmin(theta_s, P * pow(dnear, -n)) * (1.0 - 1e-6));
+            const float th = (float)(fmin(theta_s, P * pow(dnear, -n)) * (1.0 - 3e-5));   // margin: fp32 / Newton rsqrt error of the sweep
             stg.theta[t] = th;
             atomicAdd(&gcount[g], 1);
             atomicMin((int *)&theta_min_g[g], __float_as_int(th));        // th > 0: integer order == float order

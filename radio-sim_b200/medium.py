@@ -193,5 +193,15 @@ class Medium:
         self._ck(self._lib.rmb_last_timing(self._h, C.byref(t)))
         return {k: getattr(t, k) for k, _ in A.Timing._fields_}
 
+    def stream(self):
+        """cudaStream_t (int) the handle's work runs on."""
+        p = C.c_void_p()
+        self._ck(self._lib.rmb_get_stream(self._h, C.byref(p)))
+        return p.value or 0
+
+    def set_stream(self, stream):
+        """Run on the caller's CUDA stream (int cudaStream_t; 0/None restores the handle's own)."""
+        self._ck(self._lib.rmb_set_stream(self._h, C.c_void_p(stream or None)))
+
     def set_tuning(self, sweep_variant=0, near_slots=0):
         self._ck(self._lib.rmb_set_tuning(self._h, sweep_variant, near_slots))

@@ -35,7 +35,7 @@ def run_case(rsb, orc, x, y, z, ch, src, power=None, pkt_channel=None, enabled=N
     return r, ref
 
 
-@pytest.mark.parametrize("variant", [0, 2, 3, 4, 5, 6])
+@pytest.mark.parametrize("variant", [0, 2, 3, 4, 5, 6, 7, 8])
 def test_config2_1k_nodes_50_tx(rsb, orc, variant):
     x, y, z, ch = random_deployment(1, 1000, 1000.0)
     r, _ = run_case(rsb, orc, x, y, z, ch, pick_sources(1, 1000, 50), variant=variant)
