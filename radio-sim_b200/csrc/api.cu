@@ -602,6 +602,7 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
     RMB_CK(h, cudaMemsetAsync(h->ctr.p, 0, sizeof(Counters), h->st));
     RMB_CK(h, cudaEventRecord(h->ev[0], h->st));
     long long m = 0;
+    bool final_sync = true;           // the SINR path usually synchronises once, inside its attempt loop
     if (h->cfg.model == RMB_MODEL_SINR) {
         const size_t tcap = (size_t)n_tx + (size_t)(h->groups.ngroups + 1) * kTile;
         RMB_CK(h, h->txf.ensure(tcap)); RMB_CK(h, h->theta.ensure(tcap)); RMB_CK(h, h->arrival.ensure(tcap));
@@ -618,77 +619,80 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
         RMB_CK(h, launch_prepare(nd, h->dp.p, h->geom.p, h->groups, n_tx, d_rec, stg, tx, h->theta.p, h->theta_min_g.p, h->ctr.p, h->st));
         launches += 3;
         RMB_CK(h, cudaEventRecord(h->ev[1], h->st));
+        // The whole tick is enqueued without a host round trip: the kernels downstream of the resolve read
+        // the pair / recheck counts on the device.  The host looks at the counters once, at the end, and
+        // redoes the tick only when a capacity was exceeded (near slots, pair records) -- both grow
+        // geometrically, so this happens a handful of times in the life of a handle.
+        bool fallback = false;
         for (int attempt = 0;; ++attempt) {
             SweepArgs a;
             a.fx = h->fx.p; a.fy = h->fy.p; a.fz = h->fz.p; a.groups = h->groups; a.tx = tx; a.theta = h->theta.p;
             a.theta_min_g = h->theta_min_g.p; a.neg_h = (float)(-0.5 * h->cfg.pl_exponent);
             a.far_part = h->far_part.p; a.cnt = h->cnt.p; a.slots = h->slots.p; a.K = h->K;
             RMB_CK(h, cudaMemsetAsync(h->cnt.p, 0, (size_t)h->n_work * sizeof(int), h->st));
+            RMB_CK(h, cudaMemsetAsync(h->tx_cnt.p, 0, ((size_t)n_tx + 1) * sizeof(int), h->st));
             if (attempt) RMB_CK(h, cudaEventRecord(h->ev[1], h->st));
             RMB_CK(h, launch_sweep(mode, h->planar, variant, h->n_work, h->splits, a, h->st));
             ++launches; ++sweeps;
             RMB_CK(h, cudaEventRecord(h->ev[2], h->st));
-            for (int redo = 0;; ++redo) {
-                // exact resolve: decisions + dense pair records; then the per-packet segment offsets
-                RMB_CK(h, cudaMemsetAsync(h->tx_cnt.p, 0, ((size_t)n_tx + 1) * sizeof(int), h->st));
-                RMB_CK(h, launch_resolve(nd, wk, h->dp.p, tx, d_rec, slot_arrays(h), pair_recs(h), h->ctr.p, h->st));
-                RMB_CK(h, launch_tx_scan(h->tx_cnt.p, n_tx, h->seg.p, h->ctr.p, h->st));
-                launches += 2;
-                if ((rc = read_counters(h))) return rc;
-                if ((long long)h->h_ctr.p->heard <= (long long)h->key.cap || redo > 1) break;
-                // more heard pairs than record capacity: grow and redo the resolve (records beyond cap were dropped)
-                if ((rc = ensure_pairs(h, (long long)h->h_ctr.p->heard))) return rc;
-                Counters keep = *h->h_ctr.p;
-                keep.heard = 0; keep.max_near = 0; keep.n_recheck = 0; keep.n_recheck2 = 0; keep.max_bucket = 0;
-                RMB_CK(h, cudaMemcpyAsync(h->ctr.p, &keep, sizeof(keep), cudaMemcpyHostToDevice, h->st));
-                RMB_CK(h, cudaStreamSynchronize(h->st));
+            // exact resolve: decisions + dense pair records; then the per-packet segment offsets
+            SlotArrays sl = slot_arrays(h);
+            PairRecs pr = pair_recs(h);
+            PairArrays pa = pair_arrays(h);
+            RMB_CK(h, launch_resolve(nd, wk, h->dp.p, tx, d_rec, sl, pr, h->ctr.p, h->st));
+            RMB_CK(h, launch_tx_scan(h->tx_cnt.p, n_tx, h->seg.p, h->ctr.p, h->st));
+            launches += 2;
+            // guard-band receivers: exact sums on a side stream, overlapped with the ordering
+            RMB_CK(h, cudaEventRecord(h->ev_fork, h->st));
+            RMB_CK(h, cudaStreamWaitEvent(h->st2, h->ev_fork, 0));
+            RMB_CK(h, launch_recheck(nd, wk, h->dp.p, h->groups, tx, d_rec, sl, pr, h->ctr.p, h->st2)); launches += 2;
+            RMB_CK(h, cudaEventRecord(h->ev_join, h->st2));
+            RMB_CK(h, cudaEventRecord(h->ev[3], h->st));
+            RMB_CK(h, launch_order_buckets(pr, h->ctr.p, n_tx, h->seg.p, h->key_alt.p, h->val.p, h->st)); launches += 2;
+            RMB_CK(h, cudaStreamWaitEvent(h->st, h->ev_join, 0));
+            if (!draws) { RMB_CK(h, launch_emit_sinr(nd, h->dp.p, d_rec, n_tx, pr, h->val.p, pa, -1, false, h->ctr.p, h->st)); launches += 2; }
+            RMB_CK(h, cudaEventRecord(h->ev[4], h->st));
+            if ((rc = read_counters(h))) return rc;
+            const Counters c = *h->h_ctr.p;
+            const bool slots_short = c.max_near > h->K, recs_short = (long long)c.heard > (long long)h->key.cap;
+            if (!slots_short && !recs_short) { fallback = c.max_bucket > kBucketSortMax; break; }
+            if (attempt > 5) return h->fail(RMB_ERR_CAPACITY, "near-slot / pair-record capacity could not be established");
+            if (slots_short) {
+                // a receiver had more near candidates than slots: grow and redo the tick (deterministic)
+                int k = h->K;
+                while (k < c.max_near) k *= 2;
+                if ((double)k * h->n_work > 3.0e9)
+                    return h->fail(RMB_ERR_CAPACITY, "too many near candidates per receiver (dense all-hear-all tick)");
+                h->K = k;
+                if ((rc = ensure_slots(h))) return rc;
             }
-            if (h->h_ctr.p->max_near <= h->K) break;
-            // a receiver had more near candidates than slots: grow and redo the sweep (deterministic)
-            int k = h->K;
-            while (k < h->h_ctr.p->max_near) k *= 2;
-            if ((double)k * h->n_work > 3.0e9 || attempt > 4)
-                return h->fail(RMB_ERR_CAPACITY, "too many near candidates per receiver (dense all-hear-all tick)");
-            h->K = k;
-            if ((rc = ensure_slots(h))) return rc;
-            Counters keep = *h->h_ctr.p;
-            keep.heard = 0; keep.max_near = 0; keep.n_recheck = 0; keep.n_recheck2 = 0; keep.max_bucket = 0;
+            // with too few slots the heard count is a lower bound only: the next attempt re-checks it
+            if (recs_short && (rc = ensure_pairs(h, (long long)c.heard))) return rc;
+            Counters keep{};
+            keep.decisions = c.decisions;
             RMB_CK(h, cudaMemcpyAsync(h->ctr.p, &keep, sizeof(keep), cudaMemcpyHostToDevice, h->st));
             RMB_CK(h, cudaStreamSynchronize(h->st));
         }
         m = (long long)h->h_ctr.p->heard;
-        if (m > (long long)h->key.cap) return h->fail(RMB_ERR_CAPACITY, "pair record capacity could not be established");
-        SlotArrays sl = slot_arrays(h);
-        PairRecs pr = pair_recs(h);
-        const int nre = h->h_ctr.p->n_recheck;
-        if (nre > 0) {
-            // guard-band receivers: exact sequential sum on a side stream, overlapped with the ordering
-            RMB_CK(h, cudaEventRecord(h->ev_fork, h->st));
-            RMB_CK(h, cudaStreamWaitEvent(h->st2, h->ev_fork, 0));
-            RMB_CK(h, launch_recheck(nd, wk, h->dp.p, h->groups, tx, d_rec, sl, pr, nre, h->ctr.p, h->st2)); launches += 2;
-            RMB_CK(h, cudaEventRecord(h->ev_join, h->st2));
-        }
         h->node_info_dirty = true;
-        RMB_CK(h, cudaEventRecord(h->ev[3], h->st));
+        final_sync = (fallback && m > 0) || draws;
+        PairRecs pr = pair_recs(h);
         PairArrays pa = pair_arrays(h);
-        if (m > 0) {
-            const int max_bucket = h->h_ctr.p->max_bucket;
-            if (max_bucket > kBucketSortMax) {
-                const size_t cap = h->key.cap;
-                RMB_CK(h, h->fb_key.ensure(cap)); RMB_CK(h, h->fb_key_alt.ensure(cap)); RMB_CK(h, h->fb_val.ensure(cap));
-                RMB_CK(h, h->fb_val_alt.ensure(cap)); RMB_CK(h, h->cub_tmp.ensure(sort_pairs_tmp_bytes((long long)cap)));
-            }
+        if (fallback && m > 0) {
+            // some packet was heard by more receivers than a block sorts: radix sort of the whole key instead
+            const size_t cap = h->key.cap;
+            RMB_CK(h, h->fb_key.ensure(cap)); RMB_CK(h, h->fb_key_alt.ensure(cap)); RMB_CK(h, h->fb_val.ensure(cap));
+            RMB_CK(h, h->fb_val_alt.ensure(cap)); RMB_CK(h, h->cub_tmp.ensure(sort_pairs_tmp_bytes((long long)cap)));
             OrderScratch sc{h->key_alt.p, h->fb_key.p, h->fb_key_alt.p, h->fb_val.p, h->fb_val_alt.p, h->cub_tmp.p, h->cub_tmp.cap};
-            RMB_CK(h, launch_order_pairs(pr, m, n_tx, h->seg.p, max_bucket, pa.key_shift + bits_for(n_tx), sc, h->val.p, h->st));
-            launches += 2;
+            RMB_CK(h, launch_order_fallback(pr, m, pa.key_shift + bits_for(n_tx), sc, h->val.p, h->st));
+            launches += 7;
+            if (!draws) { RMB_CK(h, launch_emit_sinr(nd, h->dp.p, d_rec, n_tx, pr, h->val.p, pa, m, false, h->ctr.p, h->st)); launches += 2; }
         }
-        if (nre > 0) RMB_CK(h, cudaStreamWaitEvent(h->st, h->ev_join, 0));
-        if (draws) pa.key = h->key_alt.p;         // sorted keys for the draw-order stage (the bucket items are dead by now)
-        RMB_CK(h, launch_emit_sinr(nd, h->dp.p, d_rec, n_tx, pr, h->val.p, pa, m, draws, h->ctr.p, h->st));
-        launches += 2;
         if (draws) {
+            pa.key = h->key_alt.p;         // sorted keys for the draw-order stage (the bucket items are dead by now)
+            RMB_CK(h, launch_emit_sinr(nd, h->dp.p, d_rec, n_tx, pr, h->val.p, pa, m, true, h->ctr.p, h->st));
             RMB_CK(h, launch_emit(h->dp.p, d_rec, n_tx, pa, m, true, h->uniforms.p, nu, h->ctr.p, h->st));
-            launches += 6;
+            launches += 7;
         }
     } else {
         const int nblk = refmedia_blocks_per_tx(h->n);
@@ -715,8 +719,10 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
         RMB_CK(h, launch_emit(h->dp.p, d_rec, n_tx, pair_arrays(h), m, draws, h->uniforms.p, nu, h->ctr.p, h->st));
         launches += draws ? 7 : 2;
     }
-    RMB_CK(h, cudaEventRecord(h->ev[4], h->st));
-    if ((rc = read_counters(h))) return rc;
+    if (final_sync) {
+        RMB_CK(h, cudaEventRecord(h->ev[4], h->st));
+        if ((rc = read_counters(h))) return rc;
+    }
     const Counters &c = *h->h_ctr.p;
     rmb_timing &t = h->timing;
     cudaEventElapsedTime(&t.ms_total, h->ev[0], h->ev[4]);

@@ -119,20 +119,25 @@ cudaError_t launch_tx_scan(const int *tx_cnt, int n_tx, int *seg, Counters *ctr,
 }
 
 // record i -> its packet's bucket, at the rank its atomic drew: items = (global rx << 32) | record index
-__global__ void place_items_kernel(PairRecs pr, long long m, const int *seg, unsigned long long *items)
+// (grid-stride over the device-side record count: the host does not know it yet)
+__global__ void place_items_kernel(PairRecs pr, const Counters *ctr, const int *seg, unsigned long long *items)
 {
-    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= m) return;
-    const unsigned long long k = pr.key[i];
-    const int t = (int)(k >> pr.key_shift);
-    const unsigned long long rx = k & ((1ull << pr.key_shift) - 1);
-    items[seg[t] + pr.rank[i]] = (rx << 32) | (unsigned long long)i;
+    const long long m = (long long)ctr->heard;
+    if (m > pr.cap) return;                      // record overflow: the host grows the lists and redoes the tick
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < m; i += (long long)gridDim.x * blockDim.x) {
+        const unsigned long long k = pr.key[i];
+        const int t = (int)(k >> pr.key_shift);
+        const unsigned long long rx = k & ((1ull << pr.key_shift) - 1);
+        items[seg[t] + pr.rank[i]] = (rx << 32) | (unsigned long long)i;
+    }
 }
 
 // one block per packet: bitonic sort of the bucket by rx in shared memory
-__global__ void __launch_bounds__(128) bucket_sort_kernel(const int *seg, const unsigned long long *items, unsigned *order)
+__global__ void __launch_bounds__(128) bucket_sort_kernel(PairRecs pr, const Counters *ctr, const int *seg,
+                                                          const unsigned long long *items, unsigned *order)
 {
     __shared__ unsigned long long s[kBucketSortMax];
+    if ((long long)ctr->heard > pr.cap || ctr->max_bucket > kBucketSortMax) return;   // host: redo / radix-sort fallback
     const int t = blockIdx.x;
     const int b0 = seg[t], n = seg[t + 1] - b0;
     if (n <= 0) return;
@@ -171,16 +176,19 @@ size_t sort_pairs_tmp_bytes(long long n)
     return bytes;
 }
 
-cudaError_t launch_order_pairs(PairRecs pr, long long m, int n_tx, const int *seg, int max_bucket, int key_bits,
-                               OrderScratch sc, unsigned *order, cudaStream_t st)
+cudaError_t launch_order_buckets(PairRecs pr, const Counters *ctr, int n_tx, const int *seg, unsigned long long *items,
+                                 unsigned *order, cudaStream_t st)
+{
+    if (n_tx <= 0) return cudaSuccess;
+    place_items_kernel<<<148 * 8, 256, 0, st>>>(pr, ctr, seg, items);
+    bucket_sort_kernel<<<n_tx, 128, 0, st>>>(pr, ctr, seg, items, order);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_order_fallback(PairRecs pr, long long m, int key_bits, OrderScratch sc, unsigned *order, cudaStream_t st)
 {
     if (m <= 0) return cudaSuccess;
     const unsigned blocks = (unsigned)((m + 255) / 256);
-    if (max_bucket <= kBucketSortMax) {
-        place_items_kernel<<<blocks, 256, 0, st>>>(pr, m, seg, sc.items);
-        bucket_sort_kernel<<<n_tx, 128, 0, st>>>(seg, sc.items, order);
-        return cudaGetLastError();
-    }
     fallback_fill_kernel<<<blocks, 256, 0, st>>>(pr, m, sc.fb_key, sc.fb_val);
     cub::DoubleBuffer<unsigned long long> k(sc.fb_key, sc.fb_key_alt);
     cub::DoubleBuffer<unsigned> v(sc.fb_val, sc.fb_val_alt);
@@ -332,13 +340,19 @@ cudaError_t launch_emit(const DevParams *dp, const rmb_tx_record *rec, int n_tx,
 // ---- SINR medium: records in (packet, node) order -> outputs ------------------------------------
 // Deterministic reception (no probability < 1 anywhere): the three-way outcome is final here.
 // Stochastic reception: only the sorted pair arrays are produced; launch_emit applies the draws.
+// m_host < 0: the pair count is read on the device (the host has not synchronised yet) and the kernel
+// stands down when the host will have to redo the tick or take the radix-sort fallback.
 template <bool STOCHASTIC>
 __global__ void emit_sinr_kernel(NodeArrays nd, const DevParams *dp, PairRecs pr, const unsigned *order, PairArrays pa,
-                                 long long m, Counters *ctr)
+                                 long long m_host, Counters *ctr)
 {
-    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    long long m = m_host;
+    if (m_host < 0) {
+        m = (long long)ctr->heard;
+        if (m > pr.cap || ctr->max_bucket > kBucketSortMax) return;
+    }
     int delivered = 0, interfered = 0;
-    if (i < m) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < m; i += (long long)gridDim.x * blockDim.x) {
         const unsigned ri = order[i];
         const unsigned long long k = pr.key[ri];
         const double rssi = pr.prx[ri], sinr = pr.sinr[ri];
@@ -355,7 +369,7 @@ __global__ void emit_sinr_kernel(NodeArrays nd, const DevParams *dp, PairRecs pr
             pa.o_sinr[i] = (float)sinr;
             if (pa.o_rssi64) { pa.o_rssi64[i] = rssi; pa.o_sinr64[i] = sinr; }
             pa.o_outcome[i] = (uint8_t)outcome;
-            delivered = outcome == RMB_DELIVERED; interfered = !delivered;
+            delivered += outcome == RMB_DELIVERED; interfered += outcome != RMB_DELIVERED;
         }
     }
     if (!STOCHASTIC) {
@@ -375,13 +389,13 @@ cudaError_t launch_emit_sinr(const NodeArrays &nd, const DevParams *dp, const rm
                              cudaStream_t st)
 {
     if (n_tx <= 0) return cudaSuccess;
-    const unsigned blocks = (unsigned)((m + 255) / 256);
+    const unsigned blocks = m < 0 ? 148u * 8u : (unsigned)((m + 255) / 256);
     if (stochastic) {
         if (m > 0) emit_sinr_kernel<true><<<blocks, 256, 0, st>>>(nd, dp, pr, order, pa, m, ctr);
         return cudaGetLastError();
     }
     txfail_det_kernel<<<(n_tx + 255) / 256, 256, 0, st>>>(dp, rec, n_tx, pa.tx_failed, pa.tx_base);
-    if (m > 0) emit_sinr_kernel<false><<<blocks, 256, 0, st>>>(nd, dp, pr, order, pa, m, ctr);
+    if (m != 0) emit_sinr_kernel<false><<<blocks, 256, 0, st>>>(nd, dp, pr, order, pa, m, ctr);
     return cudaGetLastError();
 }
 

@@ -91,8 +91,7 @@ cudaError_t launch_resolve(const NodeArrays &nd, const WorkArrays &wk, const Dev
 // per-node RSSI (total in-band power, dBm) and receiving flag from the work-order results of the last tick
 cudaError_t launch_node_info(const WorkArrays &wk, SlotArrays sl, float *node_rssi, uint8_t *node_recv, cudaStream_t st);
 cudaError_t launch_recheck(const NodeArrays &nd, const WorkArrays &wk, const DevParams *dp, Groups groups, TxTiles tx,
-                           const rmb_tx_record *rec, SlotArrays sl, PairRecs pr, int n_recheck, Counters *ctr,
-                           cudaStream_t st);
+                           const rmb_tx_record *rec, SlotArrays sl, PairRecs pr, Counters *ctr, cudaStream_t st);
 
 // ---- emission: compaction, (tx,rx) ordering, stochastic rule, outputs -------------------------
 struct PairArrays {
@@ -125,8 +124,9 @@ constexpr int kBucketSortMax = 2048;
 struct OrderScratch { unsigned long long *items; unsigned long long *fb_key, *fb_key_alt; unsigned *fb_val, *fb_val_alt; void *cub_tmp; size_t cub_tmp_bytes; };
 cudaError_t launch_tx_scan(const int *tx_cnt, int n_tx, int *seg, Counters *ctr, cudaStream_t st);
 size_t      sort_pairs_tmp_bytes(long long n);
-cudaError_t launch_order_pairs(PairRecs pr, long long m, int n_tx, const int *seg, int max_bucket, int key_bits,
-                               OrderScratch sc, unsigned *order, cudaStream_t st);
+cudaError_t launch_order_buckets(PairRecs pr, const Counters *ctr, int n_tx, const int *seg, unsigned long long *items,
+                                 unsigned *order, cudaStream_t st);
+cudaError_t launch_order_fallback(PairRecs pr, long long m, int key_bits, OrderScratch sc, unsigned *order, cudaStream_t st);
 cudaError_t launch_emit_sinr(const NodeArrays &nd, const DevParams *dp, const rmb_tx_record *rec, int n_tx, PairRecs pr,
                              const unsigned *order, PairArrays pa, long long m, bool stochastic, Counters *ctr,
                              cudaStream_t st);

@@ -233,29 +233,35 @@ __device__ bool apply_itot(const DevParams *dp, SlotArrays sl, PairRecs pr, int 
 }
 
 constexpr int kRecheckThreads = 1024;
+constexpr int kRecheckTreeBlocks = 148;       // one per SM; blocks stride over the flagged receivers
 
 __global__ void __launch_bounds__(kRecheckThreads)
 recheck_tree_kernel(WorkArrays wk, const DevParams *dp, Groups groups, TxTiles tx, const rmb_tx_record *rec,
                     SlotArrays sl, PairRecs pr, Counters *ctr)
 {
     __shared__ double s_part[32];
-    const int w = sl.recheck[blockIdx.x];
-    const int p = wk.perm[w];
-    int g = 0;
-    while (g + 1 < groups.ngroups && w >= groups.w_begin[g + 1]) ++g;
-    const int j0 = tx.goff[g], nj = tx.gcount[g];
-    const double X = wk.x64[w], Y = wk.y64[w], Z = wk.z64[w];
-    const int self = dp->rx_base + p;
-    double acc = 0.0;
-    for (int i = threadIdx.x; i < nj; i += kRecheckThreads) acc += exact_lin(dp, rec[tx.arrival[j0 + i]], self, X, Y, Z);
-    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = acc;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        double itot = dp->n0_mw;
-        for (int i = 0; i < kRecheckThreads / 32; ++i) itot += s_part[i];
-        const double tol_rel = 2.0 * (double)(nj + 64) * 1.1102230246251565e-16;
-        if (apply_itot(dp, sl, pr, w, itot, tol_rel)) sl.recheck2[atomicAdd(&ctr->n_recheck2, 1)] = w;
+    if ((long long)ctr->heard > pr.cap) return;           // the host grows the record lists and redoes the tick
+    const int n1 = ctr->n_recheck;               // the host launches a fixed grid before it knows the count
+    for (int b = blockIdx.x; b < n1; b += gridDim.x) {
+        const int w = sl.recheck[b];
+        const int p = wk.perm[w];
+        int g = 0;
+        while (g + 1 < groups.ngroups && w >= groups.w_begin[g + 1]) ++g;
+        const int j0 = tx.goff[g], nj = tx.gcount[g];
+        const double X = wk.x64[w], Y = wk.y64[w], Z = wk.z64[w];
+        const int self = dp->rx_base + p;
+        double acc = 0.0;
+        for (int i = threadIdx.x; i < nj; i += kRecheckThreads) acc += exact_lin(dp, rec[tx.arrival[j0 + i]], self, X, Y, Z);
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = acc;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double itot = dp->n0_mw;
+            for (int i = 0; i < kRecheckThreads / 32; ++i) itot += s_part[i];
+            const double tol_rel = 2.0 * (double)(nj + 64) * 1.1102230246251565e-16;
+            if (apply_itot(dp, sl, pr, w, itot, tol_rel)) sl.recheck2[atomicAdd(&ctr->n_recheck2, 1)] = w;
+        }
+        __syncthreads();
     }
 }
 
@@ -299,13 +305,12 @@ recheck_seq_kernel(WorkArrays wk, const DevParams *dp, Groups groups, TxTiles tx
 }
 
 cudaError_t launch_recheck(const NodeArrays &nd, const WorkArrays &wk, const DevParams *dp, Groups groups, TxTiles tx,
-                           const rmb_tx_record *rec, SlotArrays sl, PairRecs pr, int n_recheck, Counters *ctr,
-                           cudaStream_t st)
+                           const rmb_tx_record *rec, SlotArrays sl, PairRecs pr, Counters *ctr, cudaStream_t st)
 {
     (void)nd;
-    if (n_recheck <= 0) return cudaSuccess;
-    recheck_tree_kernel<<<n_recheck, kRecheckThreads, 0, st>>>(wk, dp, groups, tx, rec, sl, pr, ctr);
-    recheck_seq_kernel<<<min(n_recheck, kRecheckSeqBlocks), kRecheckThreads, 0, st>>>(wk, dp, groups, tx, rec, sl, pr, ctr);
+    if (wk.n_work <= 0) return cudaSuccess;
+    recheck_tree_kernel<<<kRecheckTreeBlocks, kRecheckThreads, 0, st>>>(wk, dp, groups, tx, rec, sl, pr, ctr);
+    recheck_seq_kernel<<<kRecheckSeqBlocks, kRecheckThreads, 0, st>>>(wk, dp, groups, tx, rec, sl, pr, ctr);
     return cudaGetLastError();
 }
 

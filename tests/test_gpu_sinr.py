@@ -164,6 +164,14 @@ def test_threshold_among_many_interferers_takes_the_sequential_sum(rsb, orc):
     assert seq >= 1
 
 
+def test_packet_heard_by_thousands_takes_the_radix_fallback(rsb, orc):
+    """3 packets heard by ~6000 receivers each: buckets larger than the in-block sort (2048) must be ordered
+    by the radix-sort fallback; record capacity (2 x receivers at first) has to grow as well."""
+    x, y, z, ch = random_deployment(12, 6000, 45.0)
+    r, _ = run_case(rsb, orc, x, y, z, ch, np.array([5, 17, 4000], dtype=np.int32))
+    assert r.n_pairs > 3 * 5000
+
+
 def test_position_and_radio_updates(rsb, orc):
     x, y, z, ch = random_deployment(10, 3000, 600.0, channels=4)
     src = pick_sources(10, 3000, 100)
