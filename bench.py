@@ -80,7 +80,7 @@ class ClockSampler(threading.Thread):
                     for k, bit in names.items():
                         if r & bit:
                             self.reasons.add(k)
-                time.sleep(0.005)
+                time.sleep(getattr(self, 'period', 0.005))
         except Exception as e:          # NVML missing: report that rather than invent clocks
             self.reasons.add(f"nvml_unavailable:{type(e).__name__}")
 
@@ -219,6 +219,7 @@ def run_ours(args):
 
     med.build_tx_records(mine_padded, rec_local.data_ptr())
     sampler = ClockSampler(local)
+    sampler.period = float(os.environ.get('RMB_BENCH_SAMPLE_PERIOD', '0.005'))
     sampler.start()
     timed(step_resident, args.warmup)
     times, walls, res, sweep_ms, launches = timed(step_resident, args.steps, sampler)

@@ -58,7 +58,7 @@ struct rmb_handle {
     cudaStream_t own_st = nullptr;                 // created by rmb_create; st == own_st unless rmb_set_stream
     cudaStream_t st = nullptr, st2 = nullptr;      // st2: guard-band recheck, overlapped with the pair ordering
     cudaEvent_t ev[6] = {}, ev_fork = nullptr, ev_join = nullptr;
-    rmb_timing timing{};
+    rmb_timing timing{}; bool timing_pending = false;
 
     // host mirrors of the radio state (work order + stochastic detection are host-built)
     int n = 0;
@@ -84,7 +84,7 @@ struct rmb_handle {
     // per tick: tx side
     DevBuf<int> pk_src, pk_channel; DevBuf<double> pk_power; PinBuf<char> pk_stage;
     DevBuf<rmb_tx_record> rec;
-    DevBuf<float4> txf, stg_f; DevBuf<float> theta, theta_min_g, stg_theta; DevBuf<int> stg_gid; DevBuf<int> arrival, goff, gcount;
+    DevBuf<float4> txf, stg_f; DevBuf<float> theta, theta_min_g, stg_theta; DevBuf<int> stg_gid; DevBuf<double> prep_const; DevBuf<int> arrival, goff, gcount;
     DevBuf<double> uniforms;
 
     // slots
@@ -353,7 +353,7 @@ int rmb_destroy(rmb_handle *h)
     h->matrix.release(); h->channel.release(); h->id_int.release(); h->enabled.release(); h->perm.release(); h->wx.release(); h->wy.release(); h->wz.release(); h->wrxp.release(); h->gid.release(); h->ro_key.release(); h->ro_key_alt.release(); h->ro_val.release(); h->ro_val_alt.release(); h->ro_tmp.release();
     h->fx.release(); h->fy.release(); h->fz.release(); h->dp.release(); h->geom.release(); h->geom_scratch.release();
     h->ctr.release(); h->h_ctr.release(); h->node_rssi.release(); h->node_recv.release(); h->pk_src.release();
-    h->pk_channel.release(); h->pk_power.release(); h->pk_stage.release(); h->rec.release(); h->txf.release(); h->stg_f.release(); h->stg_theta.release(); h->stg_gid.release();
+    h->pk_channel.release(); h->pk_power.release(); h->pk_stage.release(); h->rec.release(); h->txf.release(); h->stg_f.release(); h->stg_theta.release(); h->stg_gid.release(); h->prep_const.release();
     h->theta.release(); h->theta_min_g.release(); h->arrival.release(); h->goff.release(); h->gcount.release();
     h->uniforms.release(); h->slots.release(); h->cnt.release(); h->hcnt.release(); h->hoff.release();
     h->recheck.release(); h->recheck2.release(); h->far_part.release(); h->sl_prx.release(); h->sl_lin.release(); h->sl_sinr.release();
@@ -542,7 +542,19 @@ extern "C" int rmb_set_stream(rmb_handle *h, void *stream)
 extern "C" int rmb_last_timing(const rmb_handle *h, rmb_timing *out)
 {
     if (!h || !out) return RMB_ERR_INVALID;
-    *out = h->timing;
+    rmb_handle *m = const_cast<rmb_handle *>(h);
+    std::lock_guard<std::mutex> lk(m->mu);
+    if (m->timing_pending) {
+        rmb_timing &t = m->timing;
+        cudaEventElapsedTime(&t.ms_total, m->ev[0], m->ev[4]);
+        cudaEventElapsedTime(&t.ms_prepare, m->ev[0], m->ev[1]);
+        cudaEventElapsedTime(&t.ms_sweep, m->ev[1], m->ev[2]);
+        cudaEventElapsedTime(&t.ms_resolve, m->ev[2], m->ev[3]);
+        cudaEventElapsedTime(&t.ms_emit, m->ev[3], m->ev[4]);
+        cudaGetLastError();
+        m->timing_pending = false;
+    }
+    *out = m->timing;
     return RMB_OK;
 }
 
@@ -615,7 +627,8 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
         RMB_CK(h, h->far_part.ensure((size_t)h->splits * (size_t)std::max(h->n_work, 1)));
         RMB_CK(h, h->stg_f.ensure(std::max(n_tx, 1))); RMB_CK(h, h->stg_theta.ensure(std::max(n_tx, 1))); RMB_CK(h, h->stg_gid.ensure(std::max(n_tx, 1)));
         if (h->key.cap == 0 && (rc = ensure_pairs(h, std::min<long long>(h->cfg.max_pairs, std::max(2ll * h->n_work, 1024ll))))) return rc;
-        TxStage stg{h->stg_f.p, h->stg_theta.p, h->stg_gid.p};
+        RMB_CK(h, h->prep_const.ensure(4));
+        TxStage stg{h->stg_f.p, h->stg_theta.p, h->stg_gid.p, h->prep_const.p};
         RMB_CK(h, launch_prepare(nd, h->dp.p, h->geom.p, h->groups, n_tx, d_rec, stg, tx, h->theta.p, h->theta_min_g.p, h->ctr.p, h->st));
         launches += 3;
         RMB_CK(h, cudaEventRecord(h->ev[1], h->st));
@@ -725,11 +738,7 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
     }
     const Counters &c = *h->h_ctr.p;
     rmb_timing &t = h->timing;
-    cudaEventElapsedTime(&t.ms_total, h->ev[0], h->ev[4]);
-    cudaEventElapsedTime(&t.ms_prepare, h->ev[0], h->ev[1]);
-    cudaEventElapsedTime(&t.ms_sweep, h->ev[1], h->ev[2]);
-    cudaEventElapsedTime(&t.ms_resolve, h->ev[2], h->ev[3]);
-    cudaEventElapsedTime(&t.ms_emit, h->ev[3], h->ev[4]);
+    h->timing_pending = true;          // the event durations are read on demand (rmb_last_timing)
     t.sweep_launches = sweeps; t.kernel_launches = launches; t.recheck_sequential = c.n_recheck2;
     rmb_result &r = h->last;
     memset(&r, 0, sizeof(r));

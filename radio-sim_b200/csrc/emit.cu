@@ -142,6 +142,20 @@ __global__ void __launch_bounds__(128) bucket_sort_kernel(PairRecs pr, const Cou
     const int b0 = seg[t], n = seg[t + 1] - b0;
     if (n <= 0) return;
     if (n == 1) { if (threadIdx.x == 0) order[b0] = (unsigned)items[b0]; return; }
+    if (n <= 256) {
+        // small bucket (the common case): rank by counting, no barriers beyond the load.  The rx keys of one
+        // packet's bucket are distinct, so the ranks are a permutation.
+        for (int i = threadIdx.x; i < n; i += blockDim.x) s[i] = items[b0 + i];
+        __syncthreads();
+        for (int i = threadIdx.x; i < n; i += blockDim.x) {
+            const unsigned long long mine = s[i];
+            int rank = 0;
+#pragma unroll 8
+            for (int j = 0; j < n; ++j) rank += s[j] < mine;
+            order[b0 + rank] = (unsigned)mine;
+        }
+        return;
+    }
     int np2 = 2;
     while (np2 < n) np2 <<= 1;
     for (int i = threadIdx.x; i < np2; i += blockDim.x) s[i] = i < n ? items[b0 + i] : ~0ull;

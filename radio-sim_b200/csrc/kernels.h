@@ -40,7 +40,7 @@ cudaError_t launch_init_params(DevParams *dp, cudaStream_t st);
 cudaError_t launch_gather_records(const NodeArrays &nd, int rx_base, int n_tx, const int *src, const double *power,
                                   const int *channel, rmb_tx_record *rec, cudaStream_t st);
 // per-transmission staging in arrival order (before the stable placement into channel buckets)
-struct TxStage { float4 *f; float *theta; int *gid; };
+struct TxStage { float4 *f; float *theta; int *gid; double *pconst; };
 cudaError_t launch_prepare(const NodeArrays &nd, const DevParams *dp, const Geom *geom, Groups groups, int n_tx,
                            const rmb_tx_record *rec, TxStage stg, TxTiles tx, float *theta, float *theta_min_g,
                            Counters *ctr, cudaStream_t st);

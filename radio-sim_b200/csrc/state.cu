@@ -229,10 +229,19 @@ cudaError_t launch_gather_records(const NodeArrays &nd, int rx_base, int n_tx, c
 //   Dnear   = max(d0, n * delta_d / 1e-4), delta_d = fp32 geometry error of the centred copy
 // Three launches: init (bucket counters), per-transmission constants (one thread per tx, any
 // number of blocks), stable placement (one block per group).
-__global__ void prepare_init_kernel(int ngroups, int *gcount, float *theta_min_g)
+__global__ void prepare_init_kernel(const DevParams *dp, const Geom *geom, int ngroups, int *gcount, float *theta_min_g,
+                                    double *pconst)
 {
     const int g = threadIdx.x;
     if (g < ngroups) { gcount[g] = 0; theta_min_g[g] = FLT_MAX; }
+    if (g == 0) {                          // per-tick constants of the per-transmission kernel
+        const double n = dp->pl_exponent, d0 = dp->d0_m;
+        const double delta_d = geom->maxabs * (geom->planar ? 1.7e-7 : 2.1e-7);
+        const double dnear = fmax(d0, n * delta_d / 1e-4);
+        pconst[0] = pow(d0, n);
+        pconst[1] = pow(dnear, -n);
+        pconst[2] = pow(10.0, (dp->sensitivity_dbm - 0.05) / 10.0);
+    }
 }
 
 __global__ void __launch_bounds__(256)
@@ -248,16 +257,14 @@ prepare_tx_kernel(NodeArrays nd, const DevParams *dp, const Geom *geom, Groups g
             for (int k = 0; k < groups.ngroups; ++k) if (groups.channel[k] == r.channel) { g = k; break; }
         stg.gid[t] = g;
         if (g >= 0) {
-            const double n = dp->pl_exponent, d0 = dp->d0_m;
-            const double delta_d = geom->maxabs * (geom->planar ? 1.7e-7 : 2.1e-7);
-            const double dnear = fmax(d0, n * delta_d / 1e-4);
-            const double theta_s = pow(10.0, (dp->sensitivity_dbm - 0.05) / 10.0);
-            const double P = pow(10.0, (r.power_dbm - dp->pl0_db) / 10.0) * pow(d0, n);
+            const double n = dp->pl_exponent;
+            const double d0n = stg.pconst[0], dnear_n = stg.pconst[1], theta_s = stg.pconst[2];
+            const double P = pow(10.0, (r.power_dbm - dp->pl0_db) / 10.0) * d0n;
             const float cf = (float)pow(P, -1.0 / n);
             const double c = (double)cf;
             stg.f[t] = make_float4((float)((r.x - geom->cx) * c), (float)((r.y - geom->cy) * c),
                                    (float)((r.z - geom->cz) * c), cf);
-            const float th = (float)(fmin(theta_s, P * pow(dnear, -n)) * (1.0 - 3e-5));   // margin: fp32 / Newton rsqrt error of the sweep
+            const float th = (float)(fmin(theta_s, P * dnear_n) * (1.0 - 3e-5));   // margin: fp32 / Newton rsqrt error of the sweep
             stg.theta[t] = th;
             atomicAdd(&gcount[g], 1);
             atomicMin((int *)&theta_min_g[g], __float_as_int(th));        // th > 0: integer order == float order
@@ -280,24 +287,29 @@ prepare_place_kernel(Groups groups, int n_tx, TxStage stg, TxTiles tx, float *th
     int cursor = 0;
     for (int k = 0; k < g; ++k) cursor += (tx.gcount[k] + kTile - 1) / kTile * kTile;
     int count_g = 0;
-    for (int c0 = 0; c0 < n_tx; c0 += 1024) {
-        const int t = c0 + tid;
-        const bool match = t < n_tx && stg.gid[t] == g;
-        const unsigned b = __ballot_sync(0xffffffffu, match);
-        const int rank = __popc(b & ((1u << lane) - 1));
-        if (lane == 0) s_warp[wid] = __popc(b);
+    // every thread owns 4 consecutive transmissions of a 4096-chunk (arrival order = thread order)
+    for (int c0 = 0; c0 < n_tx; c0 += 4096) {
+        const int t0 = c0 + tid * 4;
+        bool match[4];
+        int mine = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { match[k] = t0 + k < n_tx && stg.gid[t0 + k] == g; mine += match[k]; }
+        int incl = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
+        if (lane == 31) s_warp[wid] = incl;
         __syncthreads();
         if (wid == 0) {
-            int v = s_warp[lane], incl = v;
-            for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
-            s_warp[lane] = incl - v;
-            if (lane == 31) s_total = incl;
+            int v = s_warp[lane], wi = v;
+            for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, wi, o); if (lane >= o) wi += y; }
+            s_warp[lane] = wi - v;
+            if (lane == 31) s_total = wi;
         }
         __syncthreads();
-        if (match) {
-            const int j = cursor + count_g + s_warp[wid] + rank;
-            tx.f[j] = stg.f[t]; theta[j] = stg.theta[t]; tx.arrival[j] = t;
-        }
+        int j = cursor + count_g + s_warp[wid] + incl - mine;
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            if (match[k]) { tx.f[j] = stg.f[t0 + k]; theta[j] = stg.theta[t0 + k]; tx.arrival[j] = t0 + k; ++j; }
         count_g += s_total;
         __syncthreads();
     }
@@ -317,7 +329,7 @@ cudaError_t launch_prepare(const NodeArrays &nd, const DevParams *dp, const Geom
                            const rmb_tx_record *rec, TxStage stg, TxTiles tx, float *theta, float *theta_min_g,
                            Counters *ctr, cudaStream_t st)
 {
-    prepare_init_kernel<<<1, kMaxGroups, 0, st>>>(groups.ngroups, tx.gcount, theta_min_g);
+    prepare_init_kernel<<<1, kMaxGroups, 0, st>>>(dp, geom, groups.ngroups, tx.gcount, theta_min_g, stg.pconst);
     if (groups.ngroups <= 0) return cudaMemsetAsync(tx.goff, 0, sizeof(int), st);
     if (n_tx > 0)
         prepare_tx_kernel<<<(n_tx + 255) / 256, 256, 0, st>>>(nd, dp, geom, groups, n_tx, rec, stg, tx.gcount, theta_min_g, ctr);
