@@ -84,7 +84,8 @@ struct rmb_handle {
     // per tick: tx side
     DevBuf<int> pk_src, pk_channel; DevBuf<double> pk_power; PinBuf<char> pk_stage;
     DevBuf<rmb_tx_record> rec;
-    DevBuf<float4> txf, stg_f; DevBuf<float> theta, theta_min_g, stg_theta; DevBuf<int> stg_gid; DevBuf<double> prep_const; DevBuf<int> arrival, goff, gcount;
+    DevBuf<float4> txf, stg_f; DevBuf<float> theta, theta_min_g, stg_theta; DevBuf<int> stg_gid; DevBuf<int> arrival, goff, gcount;
+    DevBuf<int> blk_cnt, blk_thmin; DevBuf<unsigned> bar; unsigned bar_count = 0, bar2_count = 0; DevBuf<double> recheck_part;   // fused tx preparation (cooperative launch)
     DevBuf<double> uniforms;
 
     // slots
@@ -186,7 +187,7 @@ static int ensure_slots(rmb_handle *h)
     RMB_CK(h, h->slots.ensure(nk)); RMB_CK(h, h->sl_prx.ensure(nk)); RMB_CK(h, h->sl_lin.ensure(nk));
     RMB_CK(h, h->sl_sinr.ensure(nk)); RMB_CK(h, h->sl_flags.ensure(nk));
     RMB_CK(h, h->cnt.ensure(nw)); RMB_CK(h, h->hcnt.ensure(nw)); RMB_CK(h, h->hoff.ensure(nw + 2));
-    RMB_CK(h, h->recheck.ensure(nw)); RMB_CK(h, h->recheck2.ensure(nw)); RMB_CK(h, h->far_part.ensure(nw)); RMB_CK(h, h->first.ensure(nw)); RMB_CK(h, h->itot.ensure(nw));
+    RMB_CK(h, h->recheck.ensure(nw)); RMB_CK(h, h->recheck2.ensure(nw)); RMB_CK(h, h->recheck_part.ensure(nw + 1024)); RMB_CK(h, h->first.ensure(nw)); RMB_CK(h, h->itot.ensure(nw));
     RMB_CK(h, h->scan_tmp.ensure(nw / 1024 + 8));
     return RMB_OK;
 }
@@ -329,8 +330,11 @@ int rmb_create(const rmb_config *cfg, rmb_handle **out)
     if ((e = h->dp.ensure(1)) != cudaSuccess || (e = h->geom.ensure(1)) != cudaSuccess ||
         (e = h->geom_scratch.ensure(8)) != cudaSuccess || (e = h->ctr.ensure(1)) != cudaSuccess ||
         (e = h->h_ctr.ensure(1)) != cudaSuccess || (e = h->theta_min_g.ensure(kMaxGroups)) != cudaSuccess ||
-        (e = h->goff.ensure(kMaxGroups + 1)) != cudaSuccess || (e = h->gcount.ensure(kMaxGroups)) != cudaSuccess)
+        (e = h->goff.ensure(kMaxGroups + 1)) != cudaSuccess || (e = h->gcount.ensure(kMaxGroups)) != cudaSuccess ||
+        (e = h->blk_cnt.ensure((size_t)kPrepMaxGrid * kMaxGroups)) != cudaSuccess ||
+        (e = h->blk_thmin.ensure((size_t)kPrepMaxGrid * kMaxGroups)) != cudaSuccess || (e = h->bar.ensure(4)) != cudaSuccess)
         return bail(e, "cudaMalloc");
+    if ((e = cudaMemset(h->bar.p, 0, 4 * sizeof(unsigned))) != cudaSuccess) return bail(e, "cudaMemset");
     DevParams dp{};
     dp.model = cfg->model; dp.success_ratio_rx = cfg->success_ratio_rx; dp.transmission_range = cfg->transmission_range;
     dp.constant_range = cfg->constant_range; dp.pl0_db = cfg->pl0_db; dp.pl_exponent = cfg->pl_exponent; dp.d0_m = cfg->d0_m;
@@ -353,7 +357,7 @@ int rmb_destroy(rmb_handle *h)
     h->matrix.release(); h->channel.release(); h->id_int.release(); h->enabled.release(); h->perm.release(); h->wx.release(); h->wy.release(); h->wz.release(); h->wrxp.release(); h->gid.release(); h->ro_key.release(); h->ro_key_alt.release(); h->ro_val.release(); h->ro_val_alt.release(); h->ro_tmp.release();
     h->fx.release(); h->fy.release(); h->fz.release(); h->dp.release(); h->geom.release(); h->geom_scratch.release();
     h->ctr.release(); h->h_ctr.release(); h->node_rssi.release(); h->node_recv.release(); h->pk_src.release();
-    h->pk_channel.release(); h->pk_power.release(); h->pk_stage.release(); h->rec.release(); h->txf.release(); h->stg_f.release(); h->stg_theta.release(); h->stg_gid.release(); h->prep_const.release();
+    h->pk_channel.release(); h->pk_power.release(); h->pk_stage.release(); h->rec.release(); h->txf.release(); h->stg_f.release(); h->stg_theta.release(); h->stg_gid.release(); h->blk_cnt.release(); h->blk_thmin.release(); h->bar.release(); h->recheck_part.release();
     h->theta.release(); h->theta_min_g.release(); h->arrival.release(); h->goff.release(); h->gcount.release();
     h->uniforms.release(); h->slots.release(); h->cnt.release(); h->hcnt.release(); h->hoff.release();
     h->recheck.release(); h->recheck2.release(); h->far_part.release(); h->sl_prx.release(); h->sl_lin.release(); h->sl_sinr.release();
@@ -611,7 +615,7 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
     } else {
         RMB_CK(h, h->uniforms.ensure(1));
     }
-    RMB_CK(h, cudaMemsetAsync(h->ctr.p, 0, sizeof(Counters), h->st));
+    if (h->cfg.model != RMB_MODEL_SINR) RMB_CK(h, cudaMemsetAsync(h->ctr.p, 0, sizeof(Counters), h->st));   // SINR: zeroed by the preparation kernel
     RMB_CK(h, cudaEventRecord(h->ev[0], h->st));
     long long m = 0;
     bool final_sync = true;           // the SINR path usually synchronises once, inside its attempt loop
@@ -621,16 +625,20 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
         RMB_CK(h, h->tx_cnt.ensure((size_t)n_tx + 1));
         TxTiles tx = tx_tiles(h);
         const int mode = sweep_mode_for_exponent(h->cfg.pl_exponent);
-        // auto: 8 receivers per thread once the shard is large enough to fill the GPU with 1024-receiver blocks
-        const int variant = h->sweep_variant ? h->sweep_variant : (h->n_work >= (1 << 19) ? 2 : 1);
+        // default: 4 receivers per thread, 128 threads (the fastest variant at every shard size once the blocks are short)
+        const int variant = h->sweep_variant ? h->sweep_variant : 1;
         h->splits = sweep_plan(mode, h->planar, variant, h->n_work, n_tx / std::max(1, h->groups.ngroups), h->forced_splits);
         RMB_CK(h, h->far_part.ensure((size_t)h->splits * (size_t)std::max(h->n_work, 1)));
         RMB_CK(h, h->stg_f.ensure(std::max(n_tx, 1))); RMB_CK(h, h->stg_theta.ensure(std::max(n_tx, 1))); RMB_CK(h, h->stg_gid.ensure(std::max(n_tx, 1)));
         if (h->key.cap == 0 && (rc = ensure_pairs(h, std::min<long long>(h->cfg.max_pairs, std::max(2ll * h->n_work, 1024ll))))) return rc;
-        RMB_CK(h, h->prep_const.ensure(4));
-        TxStage stg{h->stg_f.p, h->stg_theta.p, h->stg_gid.p, h->prep_const.p};
-        RMB_CK(h, launch_prepare(nd, h->dp.p, h->geom.p, h->groups, n_tx, d_rec, stg, tx, h->theta.p, h->theta_min_g.p, h->ctr.p, h->st));
-        launches += 3;
+        TxStage stg{h->stg_f.p, h->stg_theta.p, h->stg_gid.p};
+        const int pgrid = prepare_grid(n_tx);
+        h->bar_count += (unsigned)pgrid;
+        PrepareAux aux{};
+        aux.cnt = h->cnt.p; aux.n_work = h->n_work; aux.tx_cnt = h->tx_cnt.p; aux.tx_failed = h->tx_failed.p; aux.tx_base = h->tx_base.p;
+        aux.blk_cnt = h->blk_cnt.p; aux.blk_thmin = h->blk_thmin.p; aux.bar = h->bar.p; aux.bar_target = h->bar_count;
+        RMB_CK(h, launch_prepare(nd, h->dp.p, h->geom.p, h->groups, n_tx, d_rec, stg, tx, h->theta.p, h->theta_min_g.p, h->ctr.p, aux, pgrid, h->st));
+        launches += 1;
         RMB_CK(h, cudaEventRecord(h->ev[1], h->st));
         // The whole tick is enqueued without a host round trip: the kernels downstream of the resolve read
         // the pair / recheck counts on the device.  The host looks at the counters once, at the end, and
@@ -642,9 +650,11 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
             a.fx = h->fx.p; a.fy = h->fy.p; a.fz = h->fz.p; a.groups = h->groups; a.tx = tx; a.theta = h->theta.p;
             a.theta_min_g = h->theta_min_g.p; a.neg_h = (float)(-0.5 * h->cfg.pl_exponent);
             a.far_part = h->far_part.p; a.cnt = h->cnt.p; a.slots = h->slots.p; a.K = h->K;
-            RMB_CK(h, cudaMemsetAsync(h->cnt.p, 0, (size_t)h->n_work * sizeof(int), h->st));
-            RMB_CK(h, cudaMemsetAsync(h->tx_cnt.p, 0, ((size_t)n_tx + 1) * sizeof(int), h->st));
-            if (attempt) RMB_CK(h, cudaEventRecord(h->ev[1], h->st));
+            if (attempt) {               // attempt 0: the preparation kernel zeroed them
+                RMB_CK(h, cudaMemsetAsync(h->cnt.p, 0, (size_t)h->n_work * sizeof(int), h->st));
+                RMB_CK(h, cudaMemsetAsync(h->tx_cnt.p, 0, ((size_t)n_tx + 1) * sizeof(int), h->st));
+                RMB_CK(h, cudaEventRecord(h->ev[1], h->st));
+            }
             RMB_CK(h, launch_sweep(mode, h->planar, variant, h->n_work, h->splits, a, h->st));
             ++launches; ++sweeps;
             RMB_CK(h, cudaEventRecord(h->ev[2], h->st));
@@ -652,18 +662,20 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
             SlotArrays sl = slot_arrays(h);
             PairRecs pr = pair_recs(h);
             PairArrays pa = pair_arrays(h);
-            RMB_CK(h, launch_resolve(nd, wk, h->dp.p, tx, d_rec, sl, pr, h->ctr.p, h->st));
-            RMB_CK(h, launch_tx_scan(h->tx_cnt.p, n_tx, h->seg.p, h->ctr.p, h->st));
-            launches += 2;
+            RMB_CK(h, launch_resolve(nd, wk, h->dp.p, tx, d_rec, sl, pr, h->ctr.p, n_tx, h->seg.p, h->st));
+            launches += 1;
             // guard-band receivers: exact sums on a side stream, overlapped with the ordering
             RMB_CK(h, cudaEventRecord(h->ev_fork, h->st));
             RMB_CK(h, cudaStreamWaitEvent(h->st2, h->ev_fork, 0));
-            RMB_CK(h, launch_recheck(nd, wk, h->dp.p, h->groups, tx, d_rec, sl, pr, h->ctr.p, h->st2)); launches += 2;
+            const int rgrid = recheck_grid();
+            h->bar2_count += (unsigned)rgrid;
+            RMB_CK(h, launch_recheck(nd, wk, h->dp.p, h->groups, tx, d_rec, sl, pr, h->ctr.p, h->recheck_part.p, rgrid,
+                                     h->bar.p + 1, h->bar2_count, h->st2)); launches += 2;
             RMB_CK(h, cudaEventRecord(h->ev_join, h->st2));
             RMB_CK(h, cudaEventRecord(h->ev[3], h->st));
             RMB_CK(h, launch_order_buckets(pr, h->ctr.p, n_tx, h->seg.p, h->key_alt.p, h->val.p, h->st)); launches += 2;
             RMB_CK(h, cudaStreamWaitEvent(h->st, h->ev_join, 0));
-            if (!draws) { RMB_CK(h, launch_emit_sinr(nd, h->dp.p, d_rec, n_tx, pr, h->val.p, pa, -1, false, h->ctr.p, h->st)); launches += 2; }
+            if (!draws) { RMB_CK(h, launch_emit_sinr(nd, h->dp.p, d_rec, n_tx, pr, h->val.p, pa, -1, false, h->ctr.p, h->st)); launches += 1; }
             RMB_CK(h, cudaEventRecord(h->ev[4], h->st));
             if ((rc = read_counters(h))) return rc;
             const Counters c = *h->h_ctr.p;
@@ -699,7 +711,7 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
             OrderScratch sc{h->key_alt.p, h->fb_key.p, h->fb_key_alt.p, h->fb_val.p, h->fb_val_alt.p, h->cub_tmp.p, h->cub_tmp.cap};
             RMB_CK(h, launch_order_fallback(pr, m, pa.key_shift + bits_for(n_tx), sc, h->val.p, h->st));
             launches += 7;
-            if (!draws) { RMB_CK(h, launch_emit_sinr(nd, h->dp.p, d_rec, n_tx, pr, h->val.p, pa, m, false, h->ctr.p, h->st)); launches += 2; }
+            if (!draws) { RMB_CK(h, launch_emit_sinr(nd, h->dp.p, d_rec, n_tx, pr, h->val.p, pa, m, false, h->ctr.p, h->st)); launches += 1; }
         }
         if (draws) {
             pa.key = h->key_alt.p;         // sorted keys for the draw-order stage (the bucket items are dead by now)

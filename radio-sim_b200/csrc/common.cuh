@@ -57,11 +57,79 @@ struct Counters {
     int uniforms_short;
     int max_bucket;                   // most heard pairs of any one packet (chooses the ordering path)
     int n_recheck2;                   // guard-band receivers that needed the sequential sum
-    int pad;
+    int peer_timeout;                 // multi-GPU exchange: a peer's records did not arrive (see peer_wait)
+    unsigned resolve_done;            // blocks of the resolve kernel that have finished (the last one scans tx_cnt)
+    unsigned recheck_done;            // work units of the guard-band recheck that have finished
 };
 
 // slot flags
 constexpr uint8_t kHeard = 1, kDecodable = 2;
+
+// ---- grid-wide barrier for cooperative launches ------------------------------------------------
+// A monotonic arrival counter in global memory; the host passes the value the counter reaches when
+// every block of THIS launch has arrived (it adds the grid size per launch), so the counter is
+// never reset.  All blocks are co-resident (cudaLaunchCooperativeKernel), so spinning is safe.
+__device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned *p)
+{
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void grid_barrier(unsigned *bar, unsigned target)
+{
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(bar, 1u);
+        while ((int)(ld_acquire_gpu(bar) - target) < 0) { }
+        __threadfence();
+    }
+    __syncthreads();
+}
+
+// ---- multi-GPU exchange of the tick's tx records over NVLink peer memory ------------------------
+// Every rank stores its records straight into every peer's gather buffer and then raises its flag
+// there to the tick's epoch (release, system scope).  The consumer spins on its LOCAL flags.  A peer
+// that never arrives (crashed rank) must not hang the GPU: after kPeerWaitNs the wait gives up and
+// the tick is reported as failed.
+constexpr int kMaxPeers = 16;
+constexpr unsigned long long kPeerWaitNs = 20ull * 1000 * 1000 * 1000;
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned *p)
+{
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned *p, unsigned v)
+{
+    asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long global_timer_ns()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ bool peer_wait(const unsigned *flag, unsigned epoch)
+{
+    if ((int)(ld_acquire_sys(flag) - epoch) >= 0) return true;
+    const unsigned long long t0 = global_timer_ns();
+    while ((int)(ld_acquire_sys(flag) - epoch) < 0)
+        if (global_timer_ns() - t0 > kPeerWaitNs) return false;
+    return true;
+}
+
+// everything the fused tx-side preparation kernel needs beyond the tx arrays
+constexpr int kPrepThreads = 256;
+constexpr int kPrepMaxGrid = 256;
+struct PrepareAux {
+    int *cnt; int n_work;             // near-candidate counters of the receivers (zeroed here)
+    int *tx_cnt;                      // [n_tx+1] heard pairs per packet (zeroed here)
+    uint8_t *tx_failed; long long *tx_base;   // [n_tx] deterministic tx-failure rule (p_tx <= 0), draw base 0
+    int *blk_cnt, *blk_thmin;         // [grid][kMaxGroups] per-block bucket counts / min thresholds
+    unsigned *bar; unsigned bar_target;
+    const unsigned *peer_flags; int world; unsigned epoch;   // peer_flags == nullptr: no exchange to wait for
+};
 
 #define RMB_CUDA_OK(expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) return e__; } while (0)
 

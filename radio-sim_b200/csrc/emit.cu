@@ -408,7 +408,7 @@ cudaError_t launch_emit_sinr(const NodeArrays &nd, const DevParams *dp, const rm
         if (m > 0) emit_sinr_kernel<true><<<blocks, 256, 0, st>>>(nd, dp, pr, order, pa, m, ctr);
         return cudaGetLastError();
     }
-    txfail_det_kernel<<<(n_tx + 255) / 256, 256, 0, st>>>(dp, rec, n_tx, pa.tx_failed, pa.tx_base);
+    // tx_failed / tx_base of the deterministic rule were written by the tx preparation kernel
     if (m != 0) emit_sinr_kernel<false><<<blocks, 256, 0, st>>>(nd, dp, pr, order, pa, m, ctr);
     return cudaGetLastError();
 }

@@ -40,10 +40,12 @@ cudaError_t launch_init_params(DevParams *dp, cudaStream_t st);
 cudaError_t launch_gather_records(const NodeArrays &nd, int rx_base, int n_tx, const int *src, const double *power,
                                   const int *channel, rmb_tx_record *rec, cudaStream_t st);
 // per-transmission staging in arrival order (before the stable placement into channel buckets)
-struct TxStage { float4 *f; float *theta; int *gid; double *pconst; };
+struct TxStage { float4 *f; float *theta; int *gid; };
+// one cooperative launch: peer wait, counter zeroing, per-tx constants, tx-failure rule, stable bucketing
+int prepare_grid(int n_tx);
 cudaError_t launch_prepare(const NodeArrays &nd, const DevParams *dp, const Geom *geom, Groups groups, int n_tx,
                            const rmb_tx_record *rec, TxStage stg, TxTiles tx, float *theta, float *theta_min_g,
-                           Counters *ctr, cudaStream_t st);
+                           Counters *ctr, PrepareAux aux, int grid, cudaStream_t st);
 
 // ---- K1 ---------------------------------------------------------------------------------------
 struct SweepArgs {
@@ -86,12 +88,19 @@ struct PairRecs {
     int *rank;                        // position inside the packet's bucket (atomic counter, arbitrary order)
     int *tx_cnt;                      // [n_tx] heard pairs per packet (zero on entry)
 };
+// also turns the per-packet heard counts into segment offsets (seg[t] = first pair of packet t, exclusive scan
+// of pr.tx_cnt; largest bucket -> ctr->max_bucket): done by the last block to finish
 cudaError_t launch_resolve(const NodeArrays &nd, const WorkArrays &wk, const DevParams *dp, TxTiles tx,
-                           const rmb_tx_record *rec, SlotArrays sl, PairRecs pr, Counters *ctr, cudaStream_t st);
+                           const rmb_tx_record *rec, SlotArrays sl, PairRecs pr, Counters *ctr, int n_tx, int *seg,
+                           cudaStream_t st);
 // per-node RSSI (total in-band power, dBm) and receiving flag from the work-order results of the last tick
 cudaError_t launch_node_info(const WorkArrays &wk, SlotArrays sl, float *node_rssi, uint8_t *node_recv, cudaStream_t st);
+// part: >= n_work + grid doubles of scratch; cooperative launch of `grid` (= recheck_grid()) blocks with its
+// own barrier counter
+int recheck_grid();
 cudaError_t launch_recheck(const NodeArrays &nd, const WorkArrays &wk, const DevParams *dp, Groups groups, TxTiles tx,
-                           const rmb_tx_record *rec, SlotArrays sl, PairRecs pr, Counters *ctr, cudaStream_t st);
+                           const rmb_tx_record *rec, SlotArrays sl, PairRecs pr, Counters *ctr, double *part, int grid,
+                           unsigned *bar, unsigned bar_target, cudaStream_t st);
 
 // ---- emission: compaction, (tx,rx) ordering, stochastic rule, outputs -------------------------
 struct PairArrays {

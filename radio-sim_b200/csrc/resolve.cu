@@ -48,10 +48,49 @@ __device__ __forceinline__ int owner_of(int i, int P)
     return lo;
 }
 
+// seg[t] = first pair of packet t (exclusive scan of the per-packet heard counts), largest bucket ->
+// ctr->max_bucket.  Run by the LAST block of the resolve kernel to finish (128 threads, every thread a
+// contiguous range), which saves a launch on the tick's critical path.
+constexpr int kScanTile = 4096;       // 128 threads x 32 counts, staged through shared memory
+__device__ void scan_tx_counts(const int *tx_cnt, int n_tx, int *seg, Counters *ctr)
+{
+    __shared__ int s_tile[kScanTile + kScanTile / 32];       // one pad word per 32: thread-contiguous reads are conflict-free
+    __shared__ int s_w[4], s_m[4];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    int carry = 0, mx = 0;
+    for (int c0 = 0; c0 < n_tx; c0 += kScanTile) {
+        const int nt = min(kScanTile, n_tx - c0);
+        for (int i = tid; i < kScanTile; i += 128) s_tile[i + (i >> 5)] = i < nt ? __ldcg(tx_cnt + c0 + i) : 0;   // coalesced, independent
+        __syncthreads();
+        int *mine = s_tile + 33 * tid;
+        int sum = 0;
+#pragma unroll
+        for (int k = 0; k < 32; ++k) { const int v = mine[k]; sum += v; mx = max(mx, v); }
+        int incl = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
+        if (lane == 31) s_w[wid] = incl;
+        __syncthreads();
+        int run = carry + incl - sum;
+        for (int w = 0; w < wid; ++w) run += s_w[w];
+#pragma unroll
+        for (int k = 0; k < 32; ++k) { const int v = mine[k]; mine[k] = run; run += v; }
+        carry += s_w[0] + s_w[1] + s_w[2] + s_w[3];
+        __syncthreads();
+        for (int i = tid; i < nt; i += 128) seg[c0 + i] = s_tile[i + (i >> 5)];
+        __syncthreads();
+    }
+    for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (lane == 0) s_m[wid] = mx;
+    __syncthreads();
+    if (tid == 0) { seg[n_tx] = carry; ctr->max_bucket = max(max(s_m[0], s_m[1]), max(s_m[2], s_m[3])); }
+}
+
 __global__ void __launch_bounds__(128)
 resolve_kernel(NodeArrays nd, WorkArrays wk, const DevParams *dp, TxTiles tx, const rmb_tx_record *rec,
-               SlotArrays sl, PairRecs pr, Counters *ctr)
+               SlotArrays sl, PairRecs pr, Counters *ctr, int n_tx, int *seg)
 {
+    __shared__ int s_last;
     const int w = blockIdx.x * blockDim.x + threadIdx.x;       // n_work is a multiple of 1024: no partial warps
     const int lane = threadIdx.x & 31;
     const int K = sl.K;
@@ -161,13 +200,21 @@ resolve_kernel(NodeArrays nd, WorkArrays wk, const DevParams *dp, TxTiles tx, co
         if (guard && sl.cnt[w] <= K) sl.recheck[atomicAdd(&ctr->n_recheck, 1)] = w;
     }
     sl.hcnt[w] = nh;
+
+    // the last block to finish turns the per-packet counts into segment offsets
+    // (barrier, then ONE fence + arrival by thread 0: the release pattern of a grid-wide semaphore)
+    __syncthreads();
+    if (threadIdx.x == 0) { __threadfence(); s_last = atomicAdd(&ctr->resolve_done, 1u) == gridDim.x - 1; }
+    __syncthreads();
+    if (s_last) { __threadfence(); scan_tx_counts(pr.tx_cnt, n_tx, seg, ctr); }
 }
 
 cudaError_t launch_resolve(const NodeArrays &nd, const WorkArrays &wk, const DevParams *dp, TxTiles tx,
-                           const rmb_tx_record *rec, SlotArrays sl, PairRecs pr, Counters *ctr, cudaStream_t st)
+                           const rmb_tx_record *rec, SlotArrays sl, PairRecs pr, Counters *ctr, int n_tx, int *seg,
+                           cudaStream_t st)
 {
     if (wk.n_work <= 0) return cudaSuccess;
-    resolve_kernel<<<(wk.n_work + 127) / 128, 128, 0, st>>>(nd, wk, dp, tx, rec, sl, pr, ctr);
+    resolve_kernel<<<(wk.n_work + 127) / 128, 128, 0, st>>>(nd, wk, dp, tx, rec, sl, pr, ctr, n_tx, seg);
     return cudaGetLastError();
 }
 
@@ -232,36 +279,52 @@ __device__ bool apply_itot(const DevParams *dp, SlotArrays sl, PairRecs pr, int 
     return close;
 }
 
-constexpr int kRecheckThreads = 1024;
-constexpr int kRecheckTreeBlocks = 148;       // one per SM; blocks stride over the flagged receivers
+constexpr int kRecheckThreads = 1024;          // tier 2 (sequential sum)
+constexpr int kTreeThreads = 256;              // tier 1: work unit = (flagged receiver, part of its bucket)
+constexpr int kTreeMaxParts = 64;
 
-__global__ void __launch_bounds__(kRecheckThreads)
+// Tier 1.  Few receivers are flagged (C4: ~1e-4 of them), each needs ALL its co-channel terms in
+// double: a receiver's bucket is cut into Q parts so that the flagged receivers fill the GPU; a part
+// is summed by one block as a fixed tree, the parts in order by one thread after a grid barrier.
+__global__ void __launch_bounds__(kTreeThreads, 2)
 recheck_tree_kernel(WorkArrays wk, const DevParams *dp, Groups groups, TxTiles tx, const rmb_tx_record *rec,
-                    SlotArrays sl, PairRecs pr, Counters *ctr)
+                    SlotArrays sl, PairRecs pr, Counters *ctr, double *part, unsigned *bar, unsigned bar_target)
 {
-    __shared__ double s_part[32];
-    if ((long long)ctr->heard > pr.cap) return;           // the host grows the record lists and redoes the tick
-    const int n1 = ctr->n_recheck;               // the host launches a fixed grid before it knows the count
-    for (int b = blockIdx.x; b < n1; b += gridDim.x) {
+    __shared__ double s_part[kTreeThreads / 32];
+    const bool stand_down = (long long)ctr->heard > pr.cap;      // the host grows the record lists and redoes the tick
+    const int n1 = stand_down ? 0 : ctr->n_recheck;               // the host launches a fixed grid before it knows the count
+    const int Q = n1 > 0 ? max(1, min(kTreeMaxParts, (int)gridDim.x / n1)) : 1;
+    for (long long u = blockIdx.x; u < (long long)n1 * Q; u += gridDim.x) {
+        const int b = (int)(u / Q), q = (int)(u % Q);
         const int w = sl.recheck[b];
         const int p = wk.perm[w];
         int g = 0;
         while (g + 1 < groups.ngroups && w >= groups.w_begin[g + 1]) ++g;
         const int j0 = tx.goff[g], nj = tx.gcount[g];
+        const int len = (nj + Q - 1) / Q, i0 = min(nj, q * len), i1 = min(nj, i0 + len);
         const double X = wk.x64[w], Y = wk.y64[w], Z = wk.z64[w];
         const int self = dp->rx_base + p;
         double acc = 0.0;
-        for (int i = threadIdx.x; i < nj; i += kRecheckThreads) acc += exact_lin(dp, rec[tx.arrival[j0 + i]], self, X, Y, Z);
+        for (int i = i0 + threadIdx.x; i < i1; i += kTreeThreads) acc += exact_lin(dp, rec[tx.arrival[j0 + i]], self, X, Y, Z);
         for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
         if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = acc;
         __syncthreads();
         if (threadIdx.x == 0) {
-            double itot = dp->n0_mw;
-            for (int i = 0; i < kRecheckThreads / 32; ++i) itot += s_part[i];
-            const double tol_rel = 2.0 * (double)(nj + 64) * 1.1102230246251565e-16;
-            if (apply_itot(dp, sl, pr, w, itot, tol_rel)) sl.recheck2[atomicAdd(&ctr->n_recheck2, 1)] = w;
+            double v = 0.0;
+            for (int i = 0; i < kTreeThreads / 32; ++i) v += s_part[i];
+            part[u] = v;
         }
         __syncthreads();
+    }
+    grid_barrier(bar, bar_target);
+    for (int b = blockIdx.x * kTreeThreads + threadIdx.x; b < n1; b += gridDim.x * kTreeThreads) {
+        const int w = sl.recheck[b];
+        int g = 0;
+        while (g + 1 < groups.ngroups && w >= groups.w_begin[g + 1]) ++g;
+        double itot = dp->n0_mw;
+        for (int q = 0; q < Q; ++q) itot += __ldcg(&part[(long long)b * Q + q]);
+        const double tol_rel = 2.0 * (double)(tx.gcount[g] + 64) * 1.1102230246251565e-16;
+        if (apply_itot(dp, sl, pr, w, itot, tol_rel)) sl.recheck2[atomicAdd(&ctr->n_recheck2, 1)] = w;
     }
 }
 
@@ -304,12 +367,24 @@ recheck_seq_kernel(WorkArrays wk, const DevParams *dp, Groups groups, TxTiles tx
     }
 }
 
+int recheck_grid()
+{
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    return 2 * sms;                            // __launch_bounds__(kTreeThreads, 2): always co-resident
+}
+
 cudaError_t launch_recheck(const NodeArrays &nd, const WorkArrays &wk, const DevParams *dp, Groups groups, TxTiles tx,
-                           const rmb_tx_record *rec, SlotArrays sl, PairRecs pr, Counters *ctr, cudaStream_t st)
+                           const rmb_tx_record *rec, SlotArrays sl, PairRecs pr, Counters *ctr, double *part, int grid,
+                           unsigned *bar, unsigned bar_target, cudaStream_t st)
 {
     (void)nd;
     if (wk.n_work <= 0) return cudaSuccess;
-    recheck_tree_kernel<<<kRecheckTreeBlocks, kRecheckThreads, 0, st>>>(wk, dp, groups, tx, rec, sl, pr, ctr);
+    WorkArrays a_wk = wk; Groups a_groups = groups;
+    void *args[] = {(void *)&a_wk, (void *)&dp, (void *)&a_groups, (void *)&tx, (void *)&rec, (void *)&sl, (void *)&pr,
+                    (void *)&ctr, (void *)&part, (void *)&bar, (void *)&bar_target};
+    RMB_CUDA_OK(cudaLaunchCooperativeKernel((const void *)&recheck_tree_kernel, dim3((unsigned)grid), dim3(kTreeThreads), args, 0, st));
     recheck_seq_kernel<<<kRecheckSeqBlocks, kRecheckThreads, 0, st>>>(wk, dp, groups, tx, rec, sl, pr, ctr);
     return cudaGetLastError();
 }

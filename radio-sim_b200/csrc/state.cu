@@ -222,119 +222,185 @@ cudaError_t launch_gather_records(const NodeArrays &nd, int rx_base, int n_tx, c
 
 // ---- channel bucketing + fast-path constants ----------------------------------------------
 // For every receiver channel group g (in work order) the tick's records on that channel are
-// compacted, ARRIVAL ORDER PRESERVED (warp ballot + prefix sums), into bucket g of the sweep's
+// compacted, ARRIVAL ORDER PRESERVED (warp match/ballot + prefix sums), into bucket g of the sweep's
 // tx tiles; buckets are padded to kTile with infinitely weak dummies.
 //   c_t     = P_t^(-1/n),  P_t = 10^((Ptx - PL0)/10) * d0^n        (power folded into geometry)
 //   theta_t = min(sensitivity (minus 0.05 dB), P_t * Dnear^-n)     (near threshold, mW)
 //   Dnear   = max(d0, n * delta_d / 1e-4), delta_d = fp32 geometry error of the centred copy
-// Three launches: init (bucket counters), per-transmission constants (one thread per tx, any
-// number of blocks), stable placement (one block per group).
-__global__ void prepare_init_kernel(const DevParams *dp, const Geom *geom, int ngroups, int *gcount, float *theta_min_g,
-                                    double *pconst)
+// ONE cooperative launch does the whole tx side of a tick (it used to be three kernels and three
+// memsets): wait for the peers' records (multi-GPU exchange), zero the tick's counters, per-
+// transmission constants + the deterministic tx-failure rule, grid barrier, stable placement.
+// Block b owns the contiguous arrival range [b*per, (b+1)*per), so "blocks in order, threads in
+// order" is arrival order.
+__device__ __forceinline__ double tx_success_p(const DevParams *dp, const rmb_tx_record &r)
 {
-    const int g = threadIdx.x;
-    if (g < ngroups) { gcount[g] = 0; theta_min_g[g] = FLT_MAX; }
-    if (g == 0) {                          // per-tick constants of the per-transmission kernel
+    if (dp->model == RMB_MODEL_UDGM) return dp->success_ratio_rx * r.txprob;   // UDGMRadioMedium.java:63-65 (sic: Rx)
+    if (dp->model == RMB_MODEL_N2N || dp->model == RMB_MODEL_SINR) return r.txprob;   // N2NRadioMedium.java:24-26
+    return 1.0;
+}
+
+__global__ void __launch_bounds__(kPrepThreads)
+prepare_all_kernel(NodeArrays nd, const DevParams *dp, const Geom *geom, Groups groups, int n_tx,
+                   const rmb_tx_record *rec, TxStage stg, TxTiles tx, float *theta, float *theta_min_g,
+                   Counters *ctr, PrepareAux aux)
+{
+    constexpr int kWarps = kPrepThreads / 32;
+    __shared__ double s_const[3];
+    __shared__ int s_cnt[kMaxGroups], s_base[kMaxGroups], s_goff[kMaxGroups + 1], s_thmin[kMaxGroups];
+    __shared__ int s_wcnt[kWarps][kMaxGroups];
+    __shared__ unsigned long long s_dec;
+    __shared__ int s_timeout;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int ng = groups.ngroups;
+
+    // the peers' records of this tick must have landed before anybody reads `rec`
+    if (tid == 0) s_timeout = 0;
+    __syncthreads();
+    if (aux.peer_flags && tid < aux.world && !peer_wait(aux.peer_flags + tid, aux.epoch)) s_timeout = 1;
+
+    if (tid < 3) {
         const double n = dp->pl_exponent, d0 = dp->d0_m;
         const double delta_d = geom->maxabs * (geom->planar ? 1.7e-7 : 2.1e-7);
         const double dnear = fmax(d0, n * delta_d / 1e-4);
-        pconst[0] = pow(d0, n);
-        pconst[1] = pow(dnear, -n);
-        pconst[2] = pow(10.0, (dp->sensitivity_dbm - 0.05) / 10.0);
+        s_const[tid] = tid == 0 ? pow(d0, n) : tid == 1 ? pow(dnear, -n) : pow(10.0, (dp->sensitivity_dbm - 0.05) / 10.0);
     }
-}
+    if (tid < kMaxGroups) { s_cnt[tid] = 0; s_thmin[tid] = __float_as_int(FLT_MAX); }
+    if (tid == 0) s_dec = 0ull;
+    // counters of the tick (they used to be cudaMemsetAsync nodes on the critical path)
+    {
+        const int gtid = blockIdx.x * kPrepThreads + tid, gsz = gridDim.x * kPrepThreads;
+        int4 *c4 = reinterpret_cast<int4 *>(aux.cnt);                    // n_work is a multiple of 1024
+        for (int i = gtid; i < aux.n_work / 4; i += gsz) c4[i] = make_int4(0, 0, 0, 0);
+        for (int i = gtid; i <= n_tx; i += gsz) aux.tx_cnt[i] = 0;
+        if (gtid == 0) *ctr = Counters{};
+    }
+    __syncthreads();
 
-__global__ void __launch_bounds__(256)
-prepare_tx_kernel(NodeArrays nd, const DevParams *dp, const Geom *geom, Groups groups, int n_tx,
-                  const rmb_tx_record *rec, TxStage stg, int *gcount, float *theta_min_g, Counters *ctr)
-{
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    // 1. per-transmission constants of this block's arrival range
+    const int per = (n_tx + (int)gridDim.x - 1) / (int)gridDim.x;
+    const int t_begin = min(n_tx, (int)blockIdx.x * per), t_end = min(n_tx, t_begin + per);
     unsigned long long decisions = 0;
-    if (t < n_tx) {
-        const rmb_tx_record r = rec[t];
-        int g = -1;
-        if (r.src >= 0)
-            for (int k = 0; k < groups.ngroups; ++k) if (groups.channel[k] == r.channel) { g = k; break; }
-        stg.gid[t] = g;
-        if (g >= 0) {
-            const double n = dp->pl_exponent;
-            const double d0n = stg.pconst[0], dnear_n = stg.pconst[1], theta_s = stg.pconst[2];
-            const double P = pow(10.0, (r.power_dbm - dp->pl0_db) / 10.0) * d0n;
-            const float cf = (float)pow(P, -1.0 / n);
-            const double c = (double)cf;
-            stg.f[t] = make_float4((float)((r.x - geom->cx) * c), (float)((r.y - geom->cy) * c),
-                                   (float)((r.z - geom->cz) * c), cf);
-            const float th = (float)(fmin(theta_s, P * dnear_n) * (1.0 - 3e-5));   // margin: fp32 / Newton rsqrt error of the sweep
-            stg.theta[t] = th;
-            atomicAdd(&gcount[g], 1);
-            atomicMin((int *)&theta_min_g[g], __float_as_int(th));        // th > 0: integer order == float order
-            // decisions of this packet: every enabled co-channel receiver except its own source
-            const int s = r.src - dp->rx_base;
-            const int self = (s >= 0 && s < nd.n && nd.enabled[s] && nd.channel[s] == r.channel) ? 1 : 0;
-            decisions = (unsigned long long)(groups.n_rx[g] - self);
+    for (int c0 = t_begin; c0 < t_end; c0 += kPrepThreads) {
+        const int t = c0 + tid;
+        if (t < t_end) {
+            const rmb_tx_record r = rec[t];
+            int g = -1;
+            if (r.src >= 0)
+                for (int k = 0; k < ng; ++k) if (groups.channel[k] == r.channel) { g = k; break; }
+            stg.gid[t] = g;
+            aux.tx_failed[t] = (r.src >= 0 && tx_success_p(dp, r) <= 0.0) ? 1 : 0;   // no draws: the tx rule is p_tx <= 0
+            aux.tx_base[t] = 0;
+            if (g >= 0) {
+                const double n = dp->pl_exponent;
+                const double d0n = s_const[0], dnear_n = s_const[1], theta_s = s_const[2];
+                const double P = pow(10.0, (r.power_dbm - dp->pl0_db) / 10.0) * d0n;
+                const float cf = (float)pow(P, -1.0 / n);
+                const double c = (double)cf;
+                stg.f[t] = make_float4((float)((r.x - geom->cx) * c), (float)((r.y - geom->cy) * c),
+                                       (float)((r.z - geom->cz) * c), cf);
+                const float th = (float)(fmin(theta_s, P * dnear_n) * (1.0 - 3e-5));   // margin: fp32 / Newton rsqrt error of the sweep
+                stg.theta[t] = th;
+                atomicAdd(&s_cnt[g], 1);
+                atomicMin(&s_thmin[g], __float_as_int(th));           // th > 0: integer order == float order
+                // decisions of this packet: every enabled co-channel receiver except its own source
+                const int s = r.src - dp->rx_base;
+                const int self = (s >= 0 && s < nd.n && nd.enabled[s] && nd.channel[s] == r.channel) ? 1 : 0;
+                decisions += (unsigned long long)(groups.n_rx[g] - self);
+            }
         }
     }
     for (int o = 16; o > 0; o >>= 1) decisions += __shfl_xor_sync(0xffffffffu, decisions, o);
-    if ((threadIdx.x & 31) == 0 && decisions) atomicAdd(&ctr->decisions, decisions);
-}
+    if (lane == 0 && decisions) atomicAdd(&s_dec, decisions);
+    __syncthreads();
+    if (tid < ng) {
+        aux.blk_cnt[blockIdx.x * kMaxGroups + tid] = s_cnt[tid];
+        aux.blk_thmin[blockIdx.x * kMaxGroups + tid] = s_thmin[tid];
+    }
+    grid_barrier(aux.bar, aux.bar_target);
 
-__global__ void __launch_bounds__(1024)
-prepare_place_kernel(Groups groups, int n_tx, TxStage stg, TxTiles tx, float *theta)
-{
-    __shared__ int s_warp[32];
-    __shared__ int s_total;
-    const int g = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    int cursor = 0;
-    for (int k = 0; k < g; ++k) cursor += (tx.gcount[k] + kTile - 1) / kTile * kTile;
-    int count_g = 0;
-    // every thread owns 4 consecutive transmissions of a 4096-chunk (arrival order = thread order)
-    for (int c0 = 0; c0 < n_tx; c0 += 4096) {
-        const int t0 = c0 + tid * 4;
-        bool match[4];
-        int mine = 0;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) { match[k] = t0 + k < n_tx && stg.gid[t0 + k] == g; mine += match[k]; }
-        int incl = mine;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
-        if (lane == 31) s_warp[wid] = incl;
+    // 2. bucket offsets: groups in order, blocks in order inside a group
+    for (int g = wid; g < ng; g += kWarps) {
+        int before = 0, total = 0, thm = __float_as_int(FLT_MAX);
+        for (int b = lane; b < (int)gridDim.x; b += 32) {
+            const int v = __ldcg(&aux.blk_cnt[b * kMaxGroups + g]);
+            total += v;
+            if (b < (int)blockIdx.x) before += v;
+            if (blockIdx.x == 0) thm = min(thm, __ldcg(&aux.blk_thmin[b * kMaxGroups + g]));
+        }
+        for (int o = 16; o > 0; o >>= 1) {
+            before += __shfl_xor_sync(0xffffffffu, before, o);
+            total += __shfl_xor_sync(0xffffffffu, total, o);
+            thm = min(thm, __shfl_xor_sync(0xffffffffu, thm, o));
+        }
+        if (lane == 0) {
+            s_cnt[g] = total; s_base[g] = before;
+            if (blockIdx.x == 0) { theta_min_g[g] = __int_as_float(thm); tx.gcount[g] = total; }
+        }
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int cursor = 0;
+        for (int g = 0; g < ng; ++g) { s_goff[g] = cursor; s_base[g] += cursor; cursor += (s_cnt[g] + kTile - 1) / kTile * kTile; }
+        s_goff[ng] = cursor;
+        if (s_dec) atomicAdd(&ctr->decisions, s_dec);
+        if (s_timeout) ctr->peer_timeout = 1;
+    }
+    __syncthreads();
+    if (blockIdx.x == 0) {
+        for (int g = tid; g <= ng; g += kPrepThreads) tx.goff[g] = s_goff[g];
+        for (int i = tid; i < ng * kTile; i += kPrepThreads) {           // pad every bucket to a whole tile
+            const int g = i / kTile, j = s_goff[g] + s_cnt[g] + i % kTile;
+            if (j < s_goff[g + 1]) {
+                tx.f[j] = make_float4(1e18f, 1e18f, 1e18f, 0.f);           // d2' ~ 1e36 -> lin underflows to 0
+                theta[j] = FLT_MAX;
+                tx.arrival[j] = -1;
+            }
+        }
+    }
+
+    // 3. stable placement of this block's range
+    for (int c0 = t_begin; c0 < t_end; c0 += kPrepThreads) {
+        const int t = c0 + tid;
+        const int g = t < t_end ? stg.gid[t] : -1;
+        for (int i = tid; i < kWarps * kMaxGroups; i += kPrepThreads) (&s_wcnt[0][0])[i] = 0;
         __syncthreads();
-        if (wid == 0) {
-            int v = s_warp[lane], wi = v;
-            for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, wi, o); if (lane >= o) wi += y; }
-            s_warp[lane] = wi - v;
-            if (lane == 31) s_total = wi;
+        const unsigned m = __match_any_sync(0xffffffffu, g);
+        const int r = __popc(m & ((1u << lane) - 1));
+        if (g >= 0 && r == 0) s_wcnt[wid][g] = __popc(m);
+        __syncthreads();
+        if (tid < ng) {
+            int acc = s_base[tid];
+            for (int w = 0; w < kWarps; ++w) { const int v = s_wcnt[w][tid]; s_wcnt[w][tid] = acc; acc += v; }
+            s_base[tid] = acc;
         }
         __syncthreads();
-        int j = cursor + count_g + s_warp[wid] + incl - mine;
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
-            if (match[k]) { tx.f[j] = stg.f[t0 + k]; theta[j] = stg.theta[t0 + k]; tx.arrival[j] = t0 + k; ++j; }
-        count_g += s_total;
+        if (g >= 0) {
+            const int j = s_wcnt[wid][g] + r;
+            tx.f[j] = stg.f[t]; theta[j] = stg.theta[t]; tx.arrival[j] = t;
+        }
         __syncthreads();
     }
-    const int padded = (count_g + kTile - 1) / kTile * kTile;
-    for (int j = cursor + count_g + tid; j < cursor + padded; j += 1024) {
-        tx.f[j] = make_float4(1e18f, 1e18f, 1e18f, 0.f);      // d2' ~ 1e36 -> lin underflows to 0
-        theta[j] = FLT_MAX;
-        tx.arrival[j] = -1;
-    }
-    if (tid == 0) {
-        tx.goff[g] = cursor;
-        if (g == groups.ngroups - 1) tx.goff[groups.ngroups] = cursor + padded;
-    }
+}
+
+int prepare_grid(int n_tx)
+{
+    // every SM takes one block: the tick's counters are zeroed by the whole grid, the per-transmission
+    // double-precision pow() chains are latency bound and spread best thin
+    (void)n_tx;
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    return sms < kPrepMaxGrid ? sms : kPrepMaxGrid;
 }
 
 cudaError_t launch_prepare(const NodeArrays &nd, const DevParams *dp, const Geom *geom, Groups groups, int n_tx,
                            const rmb_tx_record *rec, TxStage stg, TxTiles tx, float *theta, float *theta_min_g,
-                           Counters *ctr, cudaStream_t st)
+                           Counters *ctr, PrepareAux aux, int grid, cudaStream_t st)
 {
-    prepare_init_kernel<<<1, kMaxGroups, 0, st>>>(dp, geom, groups.ngroups, tx.gcount, theta_min_g, stg.pconst);
-    if (groups.ngroups <= 0) return cudaMemsetAsync(tx.goff, 0, sizeof(int), st);
-    if (n_tx > 0)
-        prepare_tx_kernel<<<(n_tx + 255) / 256, 256, 0, st>>>(nd, dp, geom, groups, n_tx, rec, stg, tx.gcount, theta_min_g, ctr);
-    prepare_place_kernel<<<groups.ngroups, 1024, 0, st>>>(groups, n_tx, stg, tx, theta);
-    return cudaGetLastError();
+    NodeArrays a_nd = nd; Groups a_groups = groups;
+    void *args[] = {(void *)&a_nd, (void *)&dp, (void *)&geom, (void *)&a_groups, (void *)&n_tx, (void *)&rec, (void *)&stg,
+                    (void *)&tx, (void *)&theta, (void *)&theta_min_g, (void *)&ctr, (void *)&aux};
+    return cudaLaunchCooperativeKernel((const void *)&prepare_all_kernel, dim3((unsigned)grid), dim3(kPrepThreads), args, 0, st);
 }
 
 }  // namespace rmb

@@ -141,27 +141,44 @@ sweep_kernel(const float *__restrict__ fx, const float *__restrict__ fy, const f
             float m = s[0];
 #pragma unroll
             for (int r = 1; r < R; ++r) m = fmaxf(m, s[r]);
-            if (!(m < th_min)) {
-                // rare: some pair of this tile may be near -- re-scan the affected receivers
+            if (__any_sync(0xffffffffu, !(m < th_min))) {
+                // rare: some pair of this tile may be near.  The warp re-scans the affected receivers TOGETHER:
+                // a flagged (lane, r) is broadcast and the tile's kTile transmissions are spread over a half warp,
+                // two flagged receivers per pass.  (A per-thread scalar re-scan costs the whole warp kTile
+                // iterations per event: 8 % of the kernel's instructions on a 1/8 shard, whose warps cover 8x the area.)
+                const int lane = threadIdx.x & 31, half = lane >> 4, uu = lane & (kTile - 1);
+                static_assert(kTile == 16, "the cooperative re-scan maps one tile onto a half warp");
+                const float c = s_c[j + uu], nx = s_nx[j + uu], ny = s_ny[j + uu], th = s_theta[j + uu];
+                const float nz = PLANAR ? 0.f : s_nz[j + uu];
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
-                    if (!(s[r] < th_min)) {
-                        float far = 0.f;
-                        for (int u = 0; u < kTile; ++u) {
-                            const float c = s_c[j + u];
-                            const float dx = __fmaf_rn(rx[r], c, s_nx[j + u]), dy = __fmaf_rn(ry[r], c, s_ny[j + u]);
-                            float d2 = __fmaf_rn(dy, dy, __fmul_rn(dx, dx));
-                            if (!PLANAR) { const float dz = __fmaf_rn(rz[r], c, s_nz[j + u]); d2 = __fmaf_rn(dz, dz, d2); }
-                            const float lin = lin_of<MODE>(d2, neg_h);
-                            if (!(lin < s_theta[j + u])) {
-                                // order of arrival in the slots is arbitrary; resolve sorts them
-                                const int pos = atomicAdd(&cnt[w0 + r], 1);
-                                if (pos < K) slots[(size_t)(w0 + r) * K + pos] = s0 + j + u;
-                            } else {
-                                far = __fadd_rn(far, lin);
-                            }
+                    unsigned fl = __ballot_sync(0xffffffffu, !(s[r] < th_min));
+                    while (fl) {
+                        const int a = __ffs(fl) - 1;
+                        fl &= fl - 1;
+                        const bool two = fl != 0;
+                        const int b = two ? __ffs(fl) - 1 : a;
+                        fl &= fl - 1;                                  // (0 & anything) stays 0
+                        const int src = half ? b : a;
+                        const bool active = half == 0 || two;
+                        const float qx = __shfl_sync(0xffffffffu, rx[r], src), qy = __shfl_sync(0xffffffffu, ry[r], src);
+                        const float dx = __fmaf_rn(qx, c, nx), dy = __fmaf_rn(qy, c, ny);
+                        float d2 = __fmaf_rn(dy, dy, __fmul_rn(dx, dx));
+                        if (!PLANAR) { const float qz = __shfl_sync(0xffffffffu, rz[r], src); const float dz = __fmaf_rn(qz, c, nz); d2 = __fmaf_rn(dz, dz, d2); }
+                        const float lin = lin_of<MODE>(d2, neg_h);
+                        const bool near = !(lin < th);
+                        if (active && near) {
+                            // order of arrival in the slots is arbitrary; resolve sorts them
+                            const int w = w0 + (src - lane) * R + r;
+                            const int pos = atomicAdd(&cnt[w], 1);
+                            if (pos < K) slots[(size_t)w * K + pos] = s0 + j + uu;
                         }
-                        s[r] = far;
+                        float far = (active && !near) ? lin : 0.f;
+#pragma unroll
+                        for (int o = kTile / 2; o > 0; o >>= 1) far = __fadd_rn(far, __shfl_xor_sync(0xffffffffu, far, o));   // fixed tree: deterministic
+                        const float far_a = __shfl_sync(0xffffffffu, far, 0), far_b = __shfl_sync(0xffffffffu, far, 16);
+                        if (lane == a) s[r] = far_a;                 // the owners may sit in either half
+                        if (two && lane == b) s[r] = far_b;
                     }
                 }
             }
@@ -212,12 +229,16 @@ int sweep_mode_for_exponent(double n)
     return MODE_GEN;
 }
 
-// Number of tx splits S: the smallest S whose grid (rx blocks x S) fills the resident block
-// slots of the GPU to >= 95 % over its waves (quantisation tail), each split keeping at least
-// kMinSplitTx transmissions; if none reaches 95 % the best one.
+// Number of tx splits S.  Two requirements: (1) the grid (rx blocks x S) must fill the resident block
+// slots of the GPU over its waves (quantisation tail): the smallest S reaching >= 95 %, else the best one;
+// (2) blocks should be SHORT, about kTargetSplitTx transmissions each: the warp scheduler favours the
+// oldest warps, so the blocks of an SM finish one after the other and long blocks leave the XU pipe
+// under-occupied at the end of every wave (measured on B200: 1 M receivers x 10 k tx, R=4: 2521 us at
+// S=4, 2374 us at S=16..20; a single resident wave of equal "stream-K" blocks was the slowest at 2600 us).
+// Each split keeps at least kMinSplitTx transmissions.
 int sweep_plan(int mode, bool planar, int variant, int n_work, int n_tx_bucket, int forced_splits)
 {
-    constexpr int kMinSplitTx = 256, kMaxSplits = 64;
+    constexpr int kMinSplitTx = 256, kTargetSplitTx = 512, kMaxSplits = 64;
     const SweepVariant v = pick(mode, planar, variant);
     const int max_s = max(1, min(kMaxSplits, n_tx_bucket / kMinSplitTx));
     if (forced_splits > 0) return min(forced_splits, kMaxSplits);
@@ -234,7 +255,7 @@ int sweep_plan(int mode, bool planar, int variant, int n_work, int n_tx_bucket, 
         if (eff > best_eff + 1e-9) { best_eff = eff; best = s; }
         if (eff >= 0.95) { best = s; break; }
     }
-    return best;
+    return min(max_s, max(best, n_tx_bucket / kTargetSplitTx));
 }
 
 cudaError_t launch_sweep(int mode, bool planar, int variant, int n_work, int splits, const SweepArgs &a, cudaStream_t st)
