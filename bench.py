@@ -5,7 +5,10 @@ Workload (config.workload): BASELINE.json configs[3], the tick the metric and no
 on -- 1 000 000 nodes uniform in a 10 km square, 10 000 concurrent transmitters, one channel,
 log-distance path loss + co-channel interference + SINR decisions.  It fits one B200, so the same
 tick is used at every N; at N > 1 the receivers are block-partitioned over the ranks (strong
-scaling, as north_star asks) and the tick's tx records are all-gathered with NCCL.
+scaling, as north_star asks) and the tick's tx records are exchanged by the library's own kernel over
+NVLink peer memory (rmb_peer_push: every rank stores its records into every peer's gather buffer and
+raises a flag the consumers' first kernel waits on; `--exchange nccl` runs the same tick behind an
+NCCL all-gather instead, for comparison).
 
 A "step" is one tick.  `value` = decisions / time with the tick's tx records resident in HBM and the
 result lists left in HBM; `e2e` = the same tick through the public C-ABI call (rmb_tick /
@@ -178,17 +181,36 @@ def run_ours(args):
     n_rec = G * tpad
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
+    p2p = G > 1 and args.exchange == "p2p"
+    if p2p:
+        # map every rank's gather buffer (CUDA IPC): the 128-byte blobs travel through one NCCL all-gather at setup
+        blob = torch.frombuffer(bytearray(med.peer_export(G, rank, tpad)), dtype=torch.uint8).to(dev)
+        blobs = torch.empty(G * blob.numel(), dtype=torch.uint8, device=dev)
+        dist.all_gather_into_tensor(blobs, blob)
+        raw = blobs.cpu().numpy().tobytes()
+        med.peer_open([raw[i * blob.numel():(i + 1) * blob.numel()] for i in range(G)])
+
     def exchange():
         if G > 1:
             dist.all_gather_into_tensor(rec_all, rec_local)       # stream-ordered before the tick, no host sync
 
     def step_resident():
-        exchange()
-        return med.tick_resident(n_rec, rec_all.data_ptr())
+        # asynchronous form: the whole step is enqueued, the stop event fires when the GPU work is done;
+        # timed() settles it (counts, capacity check) after the stop event
+        if p2p:
+            med.peer_push_records(tpad, rec_local.data_ptr())
+            med.tick_peers_enqueue()
+        else:
+            exchange()
+            med.tick_enqueue(n_rec, rec_all.data_ptr())
+        return None
 
     def step_e2e():
         if G == 1:
             return med.tick(src, copy=False)
+        if p2p:
+            med.peer_push(mine_padded)
+            return med.tick_peers(copy=False)
         med.build_tx_records(mine_padded, rec_local.data_ptr())
         exchange()
         return med.tick_records(n_rec, rec_all.data_ptr(), copy=False)
@@ -210,6 +232,8 @@ def run_ours(args):
             e1.record(stream)
             torch.cuda.synchronize()
             walls.append(time.perf_counter() - t0)
+            if res is None:
+                res = med.tick_finish()
             times.append(e0.elapsed_time(e1) * 1e-3)
             if sampler:
                 sampler.active = False
@@ -261,6 +285,7 @@ def run_ours(args):
                 "data": "synthetic",
                 "config": {"workload": WORKLOAD, "deployment": "grid" if args.grid else "random", "nodes": N_NODES,
                            "transmitters": N_TX, "parallelism": f"receivers sharded x{G}",
+                           "exchange": "none" if G == 1 else ("peer-memory stores + flags (rmb_peer_push)" if p2p else "NCCL all-gather"),
                            "l2": "flushed (256 MiB write) before every timed step",
                            "timing": "CUDA events on the stream the library and NCCL run on, per step, summed, max over ranks; "
                                      "e2e: host wall clock around the public C-ABI call with host buffers"},
@@ -296,6 +321,7 @@ def main():
     ap.add_argument("--grid", action="store_true", help="1000x1000 grid deployment (10 m pitch) instead of random")
     ap.add_argument("--variant", type=int, default=0, help="sweep kernel variant (tuning)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"], help="N>1: how the tick's tx records travel")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

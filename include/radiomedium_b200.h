@@ -35,7 +35,8 @@ enum rmb_status {
     RMB_ERR_CAPACITY  = -4,   /* more heard pairs than max_pairs                        */
     RMB_ERR_UNIFORMS  = -5,   /* uniform stream too short (missing draws read as 0.0)   */
     RMB_ERR_STATE     = -6,   /* call order (e.g. tick before set_nodes)                */
-    RMB_ERR_UNSUPPORTED = -7
+    RMB_ERR_UNSUPPORTED = -7,
+    RMB_ERR_PEER      = -8    /* multi-GPU exchange: a peer's records did not arrive in time */
 };
 
 /* which RadioMedium implementation the handle behaves as */
@@ -172,6 +173,40 @@ int rmb_tick_records(rmb_handle *h, int32_t n_tx, const void *d_records,
  * (out gets counts only, pointers NULL).  rmb_fetch downloads the lists afterwards. */
 int rmb_tick_resident(rmb_handle *h, int32_t n_tx, const void *d_records, rmb_result *out);
 int rmb_fetch(rmb_handle *h, rmb_result *out);
+/* Asynchronous form: rmb_tick_enqueue puts the whole tick on the handle's stream and returns at once
+ * (d_records must stay valid until the tick is settled); rmb_tick_finish waits for it and returns the
+ * counts (pointers NULL; rmb_fetch downloads the lists).  Any other call on the handle settles an
+ * enqueued tick first.  Lets the Java side overlap the next tick's marshalling with the GPU
+ * (Simulator.emulatorTimeStepDone, Simulator.java:155-161) and keeps the host round trip out of the
+ * device time of a tick.  Stochastic reception (draws) is evaluated synchronously inside the call. */
+int rmb_tick_enqueue(rmb_handle *h, int32_t n_tx, const void *d_records);
+int rmb_tick_finish(rmb_handle *h, rmb_result *out);
+
+/* Multi-GPU, second form: the exchange of the tick's tx records done by the library itself over
+ * NVLink peer memory instead of a collective the caller runs (north_star: "the small per-tick
+ * active-transmitter set is all-gathered").  One handle per GPU, in one process or one process per
+ * GPU.  Setup: every handle allocates its gather buffer and describes it (rmb_peer_export:
+ * RMB_PEER_HANDLE_BYTES bytes holding a CUDA IPC handle plus, for peers living in the same process, the
+ * raw pointer); the host passes the blobs around by any means (torch.distributed in this repo) and
+ * every handle maps its peers' buffers (rmb_peer_open, blobs in rank order).
+ * Per tick, on every rank with the same `slots` (<= max_slots):
+ *   rmb_peer_push          builds the records of the locally owned sources -- src[slot] is a global node
+ *                          index owned by this handle, or -1 for padding -- STORES them into every
+ *                          peer's buffer and then raises this rank's epoch flag there;
+ *   rmb_peer_push_records  the same for records already in this GPU's memory (16-byte aligned);
+ *   rmb_tick_peers         waits ON THE DEVICE for all ranks' flags (no host synchronisation, no
+ *                          collective) and evaluates the world*slots gathered records exactly like
+ *                          rmb_tick_records; arrival index of a record = rank*slots + slot.
+ * Pushes and ticks must alternate, in step on all ranks (buffers are double-buffered by tick parity).
+ * A rank that never pushes makes the others fail with RMB_ERR_PEER after ~20 s instead of hanging. */
+#define RMB_PEER_HANDLE_BYTES 128
+int rmb_peer_export(rmb_handle *h, int32_t world, int32_t rank, int32_t max_slots, void *blob_out);
+int rmb_peer_open(rmb_handle *h, const void *blobs /* world * RMB_PEER_HANDLE_BYTES */);
+int rmb_peer_push(rmb_handle *h, int32_t slots, const int32_t *src, const double *power_dbm, const int32_t *channel);
+int rmb_peer_push_records(rmb_handle *h, int32_t slots, const void *d_records);
+int rmb_tick_peers(rmb_handle *h, const double *uniforms, size_t n_uniforms, rmb_result *out);
+int rmb_tick_peers_resident(rmb_handle *h, rmb_result *out);   /* results stay on the device, see rmb_fetch */
+int rmb_tick_peers_enqueue(rmb_handle *h);                     /* asynchronous, settled by rmb_tick_finish */
 
 /* Replaces Transciever.getRSSI / RadioMedium.getBaseRSSI for the per-tick node-info
  * (Transciever.java:52-61, net/JSONClientConnection.java:331-341): total in-band power

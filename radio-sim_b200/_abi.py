@@ -11,6 +11,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "librmb200.so")
 
 OK, ERR_INVALID, ERR_NO_DEVICE, ERR_CUDA, ERR_CAPACITY, ERR_UNIFORMS, ERR_STATE, ERR_UNSUPPORTED = 0, -1, -2, -3, -4, -5, -6, -7
+ERR_PEER = -8
+PEER_HANDLE_BYTES = 128
 MODEL_NULL, MODEL_UDGM, MODEL_UDGM_CONSTANT, MODEL_N2N, MODEL_SINR = 0, 1, 2, 3, 4
 NOT_HEARD, INTERFERED, DELIVERED = 0, 1, 2
 FLAG_F64_VALUES = 1
@@ -19,7 +21,9 @@ FLAG_F64_VALUES = 1
 SYMBOLS = ("rmb_version", "rmb_config_default", "rmb_create", "rmb_destroy", "rmb_last_error",
            "rmb_set_nodes", "rmb_set_matrix", "rmb_update_positions", "rmb_update_radio", "rmb_tick",
            "rmb_build_tx_records", "rmb_tick_records", "rmb_tick_resident", "rmb_fetch",
-           "rmb_node_info", "rmb_last_timing", "rmb_set_tuning", "rmb_get_stream", "rmb_set_stream")
+           "rmb_node_info", "rmb_last_timing", "rmb_set_tuning", "rmb_get_stream", "rmb_set_stream",
+           "rmb_peer_export", "rmb_peer_open", "rmb_peer_push", "rmb_peer_push_records", "rmb_tick_peers",
+           "rmb_tick_peers_resident", "rmb_tick_enqueue", "rmb_tick_finish", "rmb_tick_peers_enqueue")
 
 
 class Config(C.Structure):
@@ -90,6 +94,15 @@ def load():
     L.rmb_node_info.argtypes = [H, pf, pu8]
     L.rmb_last_timing.argtypes = [H, C.POINTER(Timing)]
     L.rmb_set_tuning.argtypes = [H, C.c_int32, C.c_int32]
+    L.rmb_peer_export.argtypes = [H, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
+    L.rmb_peer_open.argtypes = [H, C.c_void_p]
+    L.rmb_peer_push.argtypes = [H, C.c_int32, pi, pd, pi]
+    L.rmb_peer_push_records.argtypes = [H, C.c_int32, C.c_void_p]
+    L.rmb_tick_peers.argtypes = [H, pd, C.c_size_t, C.POINTER(Result)]
+    L.rmb_tick_peers_resident.argtypes = [H, C.POINTER(Result)]
+    L.rmb_tick_enqueue.argtypes = [H, C.c_int32, C.c_void_p]
+    L.rmb_tick_finish.argtypes = [H, C.POINTER(Result)]
+    L.rmb_tick_peers_enqueue.argtypes = [H]
     for s in SYMBOLS:
         if s not in ("rmb_config_default", "rmb_last_error"):
             getattr(L, s).restype = C.c_int

@@ -11,6 +11,7 @@
 #include <cstdio>
 #include <cstring>
 #include <mutex>
+#include <unistd.h>
 #include <string>
 #include <vector>
 
@@ -103,6 +104,23 @@ struct rmb_handle {
     PinBuf<int> ho_tx, ho_rx; PinBuf<float> ho_rssi, ho_sinr; PinBuf<uint8_t> ho_outcome, ho_failed;
     PinBuf<double> ho_rssi64, ho_sinr64;
 
+    // multi-GPU exchange over peer memory (rmb_peer_*)
+    struct Peer {
+        int world = 0, rank = 0, max_slots = 0, slots = 0;
+        unsigned epoch = 0;               // ticks pushed so far (flags carry this value)
+        bool pushed = false;              // a push is waiting for its tick
+        char *buf = nullptr;              // this handle's gather buffer: flags, then 2 x world x max_slots records
+        char *peer[kMaxPeers] = {};       // every rank's buffer as mapped here (peer[rank] == buf)
+        bool ipc[kMaxPeers] = {};         // mapped with cudaIpcOpenMemHandle (must be closed)
+        unsigned *done = nullptr;         // arrival counter of the push kernel's blocks
+        size_t rec_off(unsigned e) const { return kPeerFlagBytes + (size_t)(e & 1u) * (size_t)world * max_slots * sizeof(rmb_tx_record); }
+    } peer;
+    const unsigned *wait_flags = nullptr; unsigned wait_epoch = 0; int wait_world = 0;   // set around compute() by rmb_tick_peers
+    // asynchronous tick (rmb_tick_enqueue / rmb_tick_peers_enqueue): enqueued, counters not looked at yet
+    bool async_mode = false, pending = false;
+    struct Pending { int n_tx = 0; const rmb_tx_record *rec = nullptr; const unsigned *flags = nullptr; unsigned epoch = 0; int world = 0;
+                     int launches = 0, sweeps = 0; } pend;
+
     // last tick
     long long last_pairs = 0; int last_ntx = 0;
     rmb_result last{};
@@ -118,6 +136,9 @@ struct rmb_handle {
 };
 
 #define RMB_CK(h, expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) return (h)->cuda_fail(e__, #expr); } while (0)
+// an enqueued tick (rmb_tick_enqueue) is settled before anything else touches the handle
+static int finish_pending(rmb_handle *h);
+#define RMB_SETTLE(h) do { int rc__ = finish_pending(h); if (rc__) return rc__; } while (0)
 
 namespace {
 
@@ -349,6 +370,7 @@ int rmb_create(const rmb_config *cfg, rmb_handle **out)
 
 int rmb_destroy(rmb_handle *h)
 {
+    if (h) h->pending = false;
     if (!h) return RMB_ERR_INVALID;
     cudaSetDevice(h->cfg.device);
     cudaStreamSynchronize(h->st);
@@ -373,6 +395,9 @@ int rmb_destroy(rmb_handle *h)
     for (auto &ev : h->ev) if (ev) cudaEventDestroy(ev);
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     if (h->ev_join) cudaEventDestroy(h->ev_join);
+    for (int r = 0; r < kMaxPeers; ++r) if (h->peer.ipc[r] && h->peer.peer[r]) cudaIpcCloseMemHandle(h->peer.peer[r]);
+    if (h->peer.buf) cudaFree(h->peer.buf);
+    if (h->peer.done) cudaFree(h->peer.done);
     if (h->st2) { cudaStreamSynchronize(h->st2); cudaStreamDestroy(h->st2); }
     if (h->own_st) cudaStreamDestroy(h->own_st);
     delete h;
@@ -385,6 +410,7 @@ int rmb_set_nodes(rmb_handle *h, int32_t n, const double *x, const double *y, co
 {
     if (!h) return RMB_ERR_INVALID;
     std::lock_guard<std::mutex> lk(h->mu);
+    RMB_SETTLE(h);
     if (n < 0 || (n > 0 && (!x || !y))) return h->fail(RMB_ERR_INVALID, "rmb_set_nodes: n < 0 or missing x/y");
     RMB_CK(h, cudaSetDevice(h->cfg.device));
     h->n = n;
@@ -413,6 +439,7 @@ int rmb_set_matrix(rmb_handle *h, int32_t n, const double *matrix)
 {
     if (!h) return RMB_ERR_INVALID;
     std::lock_guard<std::mutex> lk(h->mu);
+    RMB_SETTLE(h);
     if (n < 0 || (n > 0 && !matrix)) return h->fail(RMB_ERR_INVALID, "rmb_set_matrix: bad arguments");
     RMB_CK(h, cudaSetDevice(h->cfg.device));
     RMB_CK(h, h->matrix.ensure(std::max<size_t>((size_t)n * n, 1)));
@@ -431,6 +458,7 @@ extern "C" int rmb_update_positions(rmb_handle *h, int32_t count, const int32_t 
 {
     if (!h) return RMB_ERR_INVALID;
     std::lock_guard<std::mutex> lk(h->mu);
+    RMB_SETTLE(h);
     if (!h->have_nodes) return h->fail(RMB_ERR_STATE, "rmb_update_positions before rmb_set_nodes");
     if (count < 0 || (count > 0 && (!x || !y))) return h->fail(RMB_ERR_INVALID, "rmb_update_positions: bad arguments");
     RMB_CK(h, cudaSetDevice(h->cfg.device));
@@ -464,6 +492,7 @@ extern "C" int rmb_update_radio(rmb_handle *h, int32_t count, const int32_t *idx
 {
     if (!h) return RMB_ERR_INVALID;
     std::lock_guard<std::mutex> lk(h->mu);
+    RMB_SETTLE(h);
     if (!h->have_nodes) return h->fail(RMB_ERR_STATE, "rmb_update_radio before rmb_set_nodes");
     if (count < 0) return h->fail(RMB_ERR_INVALID, "rmb_update_radio: count < 0");
     if (!idx && count != h->n && count != 0) return h->fail(RMB_ERR_INVALID, "dense radio update needs count == n");
@@ -501,6 +530,7 @@ extern "C" int rmb_set_tuning(rmb_handle *h, int32_t sweep_variant, int32_t near
 {
     if (!h) return RMB_ERR_INVALID;
     std::lock_guard<std::mutex> lk(h->mu);
+    RMB_SETTLE(h);
     RMB_CK(h, cudaSetDevice(h->cfg.device));
     // low byte: kernel variant; bits 8..15: forced number of tx splits (0 = planned per tick)
     h->sweep_variant = sweep_variant & 0xff;
@@ -513,6 +543,7 @@ extern "C" int rmb_node_info(rmb_handle *h, float *rssi_dbm, uint8_t *receiving)
 {
     if (!h) return RMB_ERR_INVALID;
     std::lock_guard<std::mutex> lk(h->mu);
+    RMB_SETTLE(h);
     if (!h->have_nodes) return h->fail(RMB_ERR_STATE, "rmb_node_info before rmb_set_nodes");
     RMB_CK(h, cudaSetDevice(h->cfg.device));
     if (h->node_info_dirty) {
@@ -537,6 +568,7 @@ extern "C" int rmb_set_stream(rmb_handle *h, void *stream)
 {
     if (!h) return RMB_ERR_INVALID;
     std::lock_guard<std::mutex> lk(h->mu);
+    RMB_SETTLE(h);
     RMB_CK(h, cudaSetDevice(h->cfg.device));
     RMB_CK(h, cudaStreamSynchronize(h->st));
     h->st = stream ? (cudaStream_t)stream : h->own_st;
@@ -548,6 +580,7 @@ extern "C" int rmb_last_timing(const rmb_handle *h, rmb_timing *out)
     if (!h || !out) return RMB_ERR_INVALID;
     rmb_handle *m = const_cast<rmb_handle *>(h);
     std::lock_guard<std::mutex> lk(m->mu);
+    finish_pending(m);
     if (m->timing_pending) {
         rmb_timing &t = m->timing;
         cudaEventElapsedTime(&t.ms_total, m->ev[0], m->ev[4]);
@@ -595,6 +628,48 @@ static int read_counters(rmb_handle *h)
     return RMB_OK;
 }
 
+// counters (host copy) -> timing bookkeeping and the counts of h->last
+static int publish(rmb_handle *h, int n_tx, long long m, bool draws, int launches, int sweeps)
+{
+    const Counters &c = *h->h_ctr.p;
+    rmb_timing &t = h->timing;
+    h->timing_pending = true;          // the event durations are read on demand (rmb_last_timing)
+    t.sweep_launches = sweeps; t.kernel_launches = launches; t.recheck_sequential = c.n_recheck2;
+    rmb_result &r = h->last;
+    memset(&r, 0, sizeof(r));
+    r.n_pairs = m; r.n_delivered = c.n_delivered; r.n_interfered = c.n_interfered; r.n_decisions = c.decisions;
+    r.n_uniforms_used = draws ? c.uniforms_used : 0; r.n_recheck = c.n_recheck; r.n_tx = n_tx; r.near_slots = h->K;
+    h->last_pairs = m; h->last_ntx = n_tx;
+    if (draws && c.uniforms_short) { h->err = "uniform stream exhausted; missing draws were read as 0.0"; return RMB_ERR_UNIFORMS; }
+    return RMB_OK;
+}
+
+static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const double *uniforms, size_t n_uniforms);
+
+// An enqueued tick is settled the first time the host needs anything from the handle: wait for it, look at the
+// counters, and in the rare case a capacity was exceeded (or a packet's bucket needs the radix-sort path) redo the
+// tick synchronously -- the computation is deterministic, so the redo gives the same lists.
+static int finish_pending(rmb_handle *h)
+{
+    if (!h->pending) return RMB_OK;
+    h->pending = false;
+    RMB_CK(h, cudaStreamSynchronize(h->st));
+    const Counters c = *h->h_ctr.p;
+    if (c.peer_timeout) return h->fail(RMB_ERR_PEER, "peer exchange: a rank's tx records did not arrive (no rmb_peer_push on that rank?)");
+    const bool redo = c.max_near > h->K || (long long)c.heard > (long long)h->key.cap || c.max_bucket > kBucketSortMax;
+    if (redo) {
+        const bool am = h->async_mode;
+        h->async_mode = false;
+        h->wait_flags = h->pend.flags; h->wait_epoch = h->pend.epoch; h->wait_world = h->pend.world;
+        const int rc = compute(h, h->pend.n_tx, h->pend.rec, nullptr, 0);
+        h->wait_flags = nullptr; h->wait_world = 0;
+        h->async_mode = am;
+        return rc;
+    }
+    h->node_info_dirty = true;
+    return publish(h, h->pend.n_tx, (long long)c.heard, false, h->pend.launches, h->pend.sweeps);
+}
+
 // d_rec: n_tx records in device memory.  Leaves the result lists on the device.
 static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const double *uniforms, size_t n_uniforms)
 {
@@ -637,6 +712,7 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
         PrepareAux aux{};
         aux.cnt = h->cnt.p; aux.n_work = h->n_work; aux.tx_cnt = h->tx_cnt.p; aux.tx_failed = h->tx_failed.p; aux.tx_base = h->tx_base.p;
         aux.blk_cnt = h->blk_cnt.p; aux.blk_thmin = h->blk_thmin.p; aux.bar = h->bar.p; aux.bar_target = h->bar_count;
+        aux.peer_flags = h->wait_flags; aux.world = h->wait_world; aux.epoch = h->wait_epoch;
         RMB_CK(h, launch_prepare(nd, h->dp.p, h->geom.p, h->groups, n_tx, d_rec, stg, tx, h->theta.p, h->theta_min_g.p, h->ctr.p, aux, pgrid, h->st));
         launches += 1;
         RMB_CK(h, cudaEventRecord(h->ev[1], h->st));
@@ -677,8 +753,19 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
             RMB_CK(h, cudaStreamWaitEvent(h->st, h->ev_join, 0));
             if (!draws) { RMB_CK(h, launch_emit_sinr(nd, h->dp.p, d_rec, n_tx, pr, h->val.p, pa, -1, false, h->ctr.p, h->st)); launches += 1; }
             RMB_CK(h, cudaEventRecord(h->ev[4], h->st));
+            if (h->async_mode && attempt == 0 && !draws) {
+                // enqueue only: the counters travel to the host behind the tick, finish_pending looks at them
+                RMB_CK(h, cudaMemcpyAsync(h->h_ctr.p, h->ctr.p, sizeof(Counters), cudaMemcpyDeviceToHost, h->st));
+                h->pending = true;
+                h->pend.n_tx = n_tx; h->pend.rec = d_rec; h->pend.flags = h->wait_flags; h->pend.epoch = h->wait_epoch;
+                h->pend.world = h->wait_world; h->pend.launches = launches; h->pend.sweeps = sweeps;
+                memset(&h->last, 0, sizeof(h->last));
+                h->last.n_tx = n_tx; h->last_pairs = 0; h->last_ntx = n_tx;
+                return RMB_OK;
+            }
             if ((rc = read_counters(h))) return rc;
             const Counters c = *h->h_ctr.p;
+            if (c.peer_timeout) return h->fail(RMB_ERR_PEER, "peer exchange: a rank's tx records did not arrive (no rmb_peer_push on that rank?)");
             const bool slots_short = c.max_near > h->K, recs_short = (long long)c.heard > (long long)h->key.cap;
             if (!slots_short && !recs_short) { fallback = c.max_bucket > kBucketSortMax; break; }
             if (attempt > 5) return h->fail(RMB_ERR_CAPACITY, "near-slot / pair-record capacity could not be established");
@@ -748,17 +835,7 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
         RMB_CK(h, cudaEventRecord(h->ev[4], h->st));
         if ((rc = read_counters(h))) return rc;
     }
-    const Counters &c = *h->h_ctr.p;
-    rmb_timing &t = h->timing;
-    h->timing_pending = true;          // the event durations are read on demand (rmb_last_timing)
-    t.sweep_launches = sweeps; t.kernel_launches = launches; t.recheck_sequential = c.n_recheck2;
-    rmb_result &r = h->last;
-    memset(&r, 0, sizeof(r));
-    r.n_pairs = m; r.n_delivered = c.n_delivered; r.n_interfered = c.n_interfered; r.n_decisions = c.decisions;
-    r.n_uniforms_used = draws ? c.uniforms_used : 0; r.n_recheck = c.n_recheck; r.n_tx = n_tx; r.near_slots = h->K;
-    h->last_pairs = m; h->last_ntx = n_tx;
-    if (draws && c.uniforms_short) { h->err = "uniform stream exhausted; missing draws were read as 0.0"; return RMB_ERR_UNIFORMS; }
-    return RMB_OK;
+    return publish(h, n_tx, m, draws, launches, sweeps);
 }
 
 static int download(rmb_handle *h, rmb_result *out)
@@ -816,6 +893,7 @@ int rmb_tick(rmb_handle *h, int32_t n_tx, const int32_t *src, const double *powe
 {
     if (!h) return RMB_ERR_INVALID;
     std::lock_guard<std::mutex> lk(h->mu);
+    RMB_SETTLE(h);
     if (!h->have_nodes) return h->fail(RMB_ERR_STATE, "rmb_tick before rmb_set_nodes");
     if (n_tx < 0 || (n_tx > 0 && !src) || !out) return h->fail(RMB_ERR_INVALID, "rmb_tick: bad arguments");
     RMB_CK(h, cudaSetDevice(h->cfg.device));
@@ -833,6 +911,7 @@ int rmb_build_tx_records(rmb_handle *h, int32_t n_tx, const int32_t *src, const 
 {
     if (!h) return RMB_ERR_INVALID;
     std::lock_guard<std::mutex> lk(h->mu);
+    RMB_SETTLE(h);
     if (!h->have_nodes) return h->fail(RMB_ERR_STATE, "rmb_build_tx_records before rmb_set_nodes");
     if (n_tx < 0 || (n_tx > 0 && (!src || !d_records))) return h->fail(RMB_ERR_INVALID, "rmb_build_tx_records: bad arguments");
     RMB_CK(h, cudaSetDevice(h->cfg.device));
@@ -847,6 +926,7 @@ int rmb_tick_records(rmb_handle *h, int32_t n_tx, const void *d_records, const d
 {
     if (!h) return RMB_ERR_INVALID;
     std::lock_guard<std::mutex> lk(h->mu);
+    RMB_SETTLE(h);
     if (!h->have_nodes) return h->fail(RMB_ERR_STATE, "rmb_tick_records before rmb_set_nodes");
     if (n_tx < 0 || (n_tx > 0 && !d_records) || !out) return h->fail(RMB_ERR_INVALID, "rmb_tick_records: bad arguments");
     RMB_CK(h, cudaSetDevice(h->cfg.device));
@@ -860,6 +940,7 @@ int rmb_tick_resident(rmb_handle *h, int32_t n_tx, const void *d_records, rmb_re
 {
     if (!h) return RMB_ERR_INVALID;
     std::lock_guard<std::mutex> lk(h->mu);
+    RMB_SETTLE(h);
     if (!h->have_nodes) return h->fail(RMB_ERR_STATE, "rmb_tick_resident before rmb_set_nodes");
     if (n_tx < 0 || (n_tx > 0 && !d_records)) return h->fail(RMB_ERR_INVALID, "rmb_tick_resident: bad arguments");
     RMB_CK(h, cudaSetDevice(h->cfg.device));
@@ -872,8 +953,186 @@ int rmb_fetch(rmb_handle *h, rmb_result *out)
 {
     if (!h || !out) return RMB_ERR_INVALID;
     std::lock_guard<std::mutex> lk(h->mu);
+    RMB_SETTLE(h);
     RMB_CK(h, cudaSetDevice(h->cfg.device));
     return download(h, out);
+}
+
+// ---- asynchronous tick ---------------------------------------------------------------------------
+int rmb_tick_enqueue(rmb_handle *h, int32_t n_tx, const void *d_records)
+{
+    if (!h) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    RMB_SETTLE(h);
+    if (!h->have_nodes) return h->fail(RMB_ERR_STATE, "rmb_tick_enqueue before rmb_set_nodes");
+    if (n_tx < 0 || (n_tx > 0 && !d_records)) return h->fail(RMB_ERR_INVALID, "rmb_tick_enqueue: bad arguments");
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    h->async_mode = true;
+    const int rc = compute(h, n_tx, (const rmb_tx_record *)d_records, nullptr, 0);
+    h->async_mode = false;
+    return rc;
+}
+
+int rmb_tick_finish(rmb_handle *h, rmb_result *out)
+{
+    if (!h) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    const int rc = finish_pending(h);
+    if (out) *out = h->last;
+    return rc;
+}
+
+// ---- multi-GPU exchange over peer memory ------------------------------------------------------
+namespace {
+struct PeerBlob {                     // what rmb_peer_export writes (RMB_PEER_HANDLE_BYTES)
+    uint32_t magic; int32_t world, rank, max_slots, device; int32_t pad;
+    int64_t pid; uint64_t raw;        // same-process peers use the raw device pointer
+    cudaIpcMemHandle_t ipc;           // other processes map this
+};
+static_assert(sizeof(PeerBlob) <= RMB_PEER_HANDLE_BYTES, "peer blob does not fit");
+constexpr uint32_t kPeerMagic = 0x524d4250u;   // "RMBP"
+}
+
+int rmb_peer_export(rmb_handle *h, int32_t world, int32_t rank, int32_t max_slots, void *blob_out)
+{
+    if (!h) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (!blob_out || world < 1 || world > kMaxPeers || rank < 0 || rank >= world || max_slots < 1)
+        return h->fail(RMB_ERR_INVALID, "rmb_peer_export: bad arguments (world <= 16)");
+    if (h->peer.buf) return h->fail(RMB_ERR_STATE, "rmb_peer_export: already exported");
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    auto &P = h->peer;
+    P.world = world; P.rank = rank; P.max_slots = max_slots;
+    const size_t bytes = kPeerFlagBytes + 2 * (size_t)world * max_slots * sizeof(rmb_tx_record);
+    RMB_CK(h, cudaMalloc((void **)&P.buf, bytes));
+    RMB_CK(h, cudaMemset(P.buf, 0, bytes));
+    RMB_CK(h, cudaMalloc((void **)&P.done, sizeof(unsigned)));
+    RMB_CK(h, cudaMemset(P.done, 0, sizeof(unsigned)));
+    PeerBlob b{};
+    b.magic = kPeerMagic; b.world = world; b.rank = rank; b.max_slots = max_slots; b.device = h->cfg.device;
+    b.pid = (int64_t)getpid(); b.raw = (uint64_t)(uintptr_t)P.buf;
+    RMB_CK(h, cudaIpcGetMemHandle(&b.ipc, P.buf));
+    memset(blob_out, 0, RMB_PEER_HANDLE_BYTES);
+    memcpy(blob_out, &b, sizeof(b));
+    return RMB_OK;
+}
+
+int rmb_peer_open(rmb_handle *h, const void *blobs)
+{
+    if (!h) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    auto &P = h->peer;
+    if (!P.buf) return h->fail(RMB_ERR_STATE, "rmb_peer_open before rmb_peer_export");
+    if (!blobs) return h->fail(RMB_ERR_INVALID, "rmb_peer_open: null blobs");
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    for (int r = 0; r < P.world; ++r) {
+        PeerBlob b;
+        memcpy(&b, (const char *)blobs + (size_t)r * RMB_PEER_HANDLE_BYTES, sizeof(b));
+        if (b.magic != kPeerMagic || b.world != P.world || b.rank != r || b.max_slots != P.max_slots)
+            return h->fail(RMB_ERR_INVALID, "rmb_peer_open: blob does not match (world / rank order / max_slots)");
+        if (r == P.rank) { P.peer[r] = P.buf; continue; }
+        if (b.pid == (int64_t)getpid()) {
+            // a peer handle in this very process: use its pointer (peer access between the two devices)
+            if (b.device != h->cfg.device) {
+                cudaError_t e = cudaDeviceEnablePeerAccess(b.device, 0);
+                if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return h->cuda_fail(e, "cudaDeviceEnablePeerAccess");
+                cudaGetLastError();
+            }
+            P.peer[r] = (char *)(uintptr_t)b.raw;
+        } else {
+            void *ptr = nullptr;
+            RMB_CK(h, cudaIpcOpenMemHandle(&ptr, b.ipc, cudaIpcMemLazyEnablePeerAccess));
+            P.peer[r] = (char *)ptr; P.ipc[r] = true;
+        }
+    }
+    return RMB_OK;
+}
+
+static int peer_push_locked(rmb_handle *h, int slots, const rmb_tx_record *d_local)
+{
+    auto &P = h->peer;
+    for (int r = 0; r < P.world; ++r) if (!P.peer[r]) return h->fail(RMB_ERR_STATE, "rmb_peer_push before rmb_peer_open");
+    if (P.pushed) return h->fail(RMB_ERR_STATE, "rmb_peer_push twice without a tick in between");
+    P.slots = slots; ++P.epoch; P.pushed = true;
+    PeerPush pp{};
+    for (int r = 0; r < P.world; ++r) pp.peer[r] = P.peer[r];
+    pp.world = P.world; pp.rank = P.rank; pp.rec_off = P.rec_off(P.epoch); pp.epoch = P.epoch; pp.done = P.done;
+    RMB_CK(h, launch_peer_push(d_local, slots, pp, h->st));
+    return RMB_OK;
+}
+
+int rmb_peer_push(rmb_handle *h, int32_t slots, const int32_t *src, const double *power_dbm, const int32_t *channel)
+{
+    if (!h) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    RMB_SETTLE(h);
+    if (!h->have_nodes) return h->fail(RMB_ERR_STATE, "rmb_peer_push before rmb_set_nodes");
+    if (slots < 0 || slots > h->peer.max_slots || (slots > 0 && !src)) return h->fail(RMB_ERR_INVALID, "rmb_peer_push: bad arguments (slots <= max_slots)");
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    RMB_CK(h, h->rec.ensure(std::max(slots, 1)));
+    int rc = stage_records(h, slots, src, power_dbm, channel, h->rec.p, false);
+    if (rc) return rc;
+    return peer_push_locked(h, slots, h->rec.p);
+}
+
+int rmb_peer_push_records(rmb_handle *h, int32_t slots, const void *d_records)
+{
+    if (!h) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    RMB_SETTLE(h);
+    if (slots < 0 || slots > h->peer.max_slots || (slots > 0 && !d_records) || ((uintptr_t)d_records & 15))
+        return h->fail(RMB_ERR_INVALID, "rmb_peer_push_records: bad arguments (slots <= max_slots, 16-byte aligned records)");
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    return peer_push_locked(h, slots, (const rmb_tx_record *)d_records);
+}
+
+static int tick_peers_locked(rmb_handle *h, const double *uniforms, size_t n_uniforms)
+{
+    auto &P = h->peer;
+    if (!h->have_nodes) return h->fail(RMB_ERR_STATE, "rmb_tick_peers before rmb_set_nodes");
+    if (!P.pushed) return h->fail(RMB_ERR_STATE, "rmb_tick_peers without a preceding rmb_peer_push");
+    P.pushed = false;
+    h->wait_flags = (const unsigned *)P.buf; h->wait_world = P.world; h->wait_epoch = P.epoch;
+    const rmb_tx_record *gathered = (const rmb_tx_record *)(P.buf + P.rec_off(P.epoch));
+    int rc = compute(h, P.world * P.slots, gathered, uniforms, n_uniforms);
+    h->wait_flags = nullptr; h->wait_world = 0;
+    return rc;
+}
+
+int rmb_tick_peers(rmb_handle *h, const double *uniforms, size_t n_uniforms, rmb_result *out)
+{
+    if (!h || !out) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    RMB_SETTLE(h);
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    int rc = tick_peers_locked(h, uniforms, n_uniforms);
+    if (rc && rc != RMB_ERR_UNIFORMS) return rc;
+    int rc2 = download(h, out);
+    return rc2 ? rc2 : rc;
+}
+
+int rmb_tick_peers_enqueue(rmb_handle *h)
+{
+    if (!h) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    RMB_SETTLE(h);
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    h->async_mode = true;
+    const int rc = tick_peers_locked(h, nullptr, 0);
+    h->async_mode = false;
+    return rc;
+}
+
+int rmb_tick_peers_resident(rmb_handle *h, rmb_result *out)
+{
+    if (!h) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    RMB_SETTLE(h);
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    int rc = tick_peers_locked(h, nullptr, 0);
+    if (out) *out = h->last;
+    return rc;
 }
 
 }  // extern "C"

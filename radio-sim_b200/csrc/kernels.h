@@ -40,6 +40,10 @@ cudaError_t launch_init_params(DevParams *dp, cudaStream_t st);
 cudaError_t launch_gather_records(const NodeArrays &nd, int rx_base, int n_tx, const int *src, const double *power,
                                   const int *channel, rmb_tx_record *rec, cudaStream_t st);
 // per-transmission staging in arrival order (before the stable placement into channel buckets)
+// multi-GPU exchange: store `slots` local records into every peer's gather buffer, then raise this rank's flag
+constexpr size_t kPeerFlagBytes = 256;       // flags[kMaxPeers] at the start of a gather buffer, records follow
+struct PeerPush { char *peer[kMaxPeers]; int world, rank; size_t rec_off; unsigned epoch; unsigned *done; };
+cudaError_t launch_peer_push(const rmb_tx_record *local, int slots, const PeerPush &pp, cudaStream_t st);
 struct TxStage { float4 *f; float *theta; int *gid; };
 // one cooperative launch: peer wait, counter zeroing, per-tx constants, tx-failure rule, stable bucketing
 int prepare_grid(int n_tx);

@@ -220,6 +220,38 @@ cudaError_t launch_gather_records(const NodeArrays &nd, int rx_base, int n_tx, c
     return cudaGetLastError();
 }
 
+// ---- multi-GPU exchange of the tick's records (replaces an all-gather collective) -------------
+// Every thread moves one 48-byte record as three 16-byte stores per peer, straight into the peers'
+// HBM over NVLink.  When the last block has arrived, one thread raises this rank's flag in every
+// peer's buffer (release, system scope): the consumers' preparation kernels spin on their LOCAL copy.
+__global__ void __launch_bounds__(256) peer_push_kernel(const rmb_tx_record *local, int slots, PeerPush pp)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < slots) {
+        const uint4 *s = reinterpret_cast<const uint4 *>(local + t);
+        const uint4 a = s[0], b = s[1], c = s[2];
+        for (int p = 0; p < pp.world; ++p) {
+            uint4 *d = reinterpret_cast<uint4 *>(pp.peer[p] + pp.rec_off) + ((size_t)pp.rank * slots + t) * 3;
+            d[0] = a; d[1] = b; d[2] = c;
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        if (atomicAdd(pp.done, 1u) == gridDim.x - 1) {
+            *pp.done = 0u;
+            __threadfence_system();
+            for (int p = 0; p < pp.world; ++p) st_release_sys(reinterpret_cast<unsigned *>(pp.peer[p]) + pp.rank, pp.epoch);
+        }
+    }
+}
+
+cudaError_t launch_peer_push(const rmb_tx_record *local, int slots, const PeerPush &pp, cudaStream_t st)
+{
+    peer_push_kernel<<<max(1, (slots + 255) / 256), 256, 0, st>>>(local, slots, pp);
+    return cudaGetLastError();
+}
+
 // ---- channel bucketing + fast-path constants ----------------------------------------------
 // For every receiver channel group g (in work order) the tick's records on that channel are
 // compacted, ARRIVAL ORDER PRESERVED (warp match/ballot + prefix sums), into bucket g of the sweep's

@@ -176,10 +176,57 @@ class Medium:
         self._ck(self._lib.rmb_tick_resident(self._h, n_tx, C.c_void_p(d_records), C.byref(r)))
         return TickResult(r, False, True)
 
+    def tick_enqueue(self, n_tx, d_records):
+        """Asynchronous tick on records resident in HBM: returns as soon as the work is on the stream."""
+        self._ck(self._lib.rmb_tick_enqueue(self._h, n_tx, C.c_void_p(d_records)))
+
+    def tick_peers_enqueue(self):
+        self._ck(self._lib.rmb_tick_peers_enqueue(self._h))
+
+    def tick_finish(self):
+        """Settle an enqueued tick; counts only (fetch() downloads the lists)."""
+        r = A.Result()
+        self._ck(self._lib.rmb_tick_finish(self._h, C.byref(r)))
+        return TickResult(r, False, True)
+
     def fetch(self, copy=True):
         r = A.Result()
         self._ck(self._lib.rmb_fetch(self._h, C.byref(r)))
         return TickResult(r, self._f64, copy)
+
+    # -- multi-GPU exchange over NVLink peer memory (rmb_peer_*) -------------------------------------
+    def peer_export(self, world, rank, max_slots):
+        """Allocate this handle's gather buffer; returns the blob (bytes) the peers need to map it."""
+        blob = C.create_string_buffer(A.PEER_HANDLE_BYTES)
+        self._ck(self._lib.rmb_peer_export(self._h, world, rank, max_slots, blob))
+        return blob.raw
+
+    def peer_open(self, blobs):
+        """blobs: every rank's peer_export() result, in rank order."""
+        raw = b"".join(bytes(b) for b in blobs)
+        buf = C.create_string_buffer(raw, len(raw))
+        self._ck(self._lib.rmb_peer_open(self._h, buf))
+
+    def peer_push(self, src, power_dbm=None, channel=None):
+        """src: this rank's padded local packet list (global node indices, -1 = padding)."""
+        src = _arr(src, np.int32)
+        t = src.shape[0]
+        power_dbm, channel = _arr(power_dbm, np.float64, t), _arr(channel, np.int32, t)
+        self._ck(self._lib.rmb_peer_push(self._h, t, _ptr(src, C.c_int32), _ptr(power_dbm, C.c_double), _ptr(channel, C.c_int32)))
+
+    def peer_push_records(self, slots, d_records):
+        self._ck(self._lib.rmb_peer_push_records(self._h, slots, C.c_void_p(d_records)))
+
+    def tick_peers(self, uniforms=None, copy=True):
+        uniforms = _arr(uniforms, np.float64)
+        r = A.Result()
+        self._ck(self._lib.rmb_tick_peers(self._h, _ptr(uniforms, C.c_double), 0 if uniforms is None else uniforms.shape[0], C.byref(r)))
+        return TickResult(r, self._f64, copy)
+
+    def tick_peers_resident(self):
+        r = A.Result()
+        self._ck(self._lib.rmb_tick_peers_resident(self._h, C.byref(r)))
+        return TickResult(r, False, True)
 
     # -- node-info (Transciever.getRSSI / getBaseRSSI) ---------------------------------------------
     def node_info(self):

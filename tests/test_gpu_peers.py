@@ -1,0 +1,85 @@
+"""GPU: the tick's tx records exchanged by the library itself over peer memory (rmb_peer_*),
+instead of a collective run by the caller.  Two receiver shards live as two handles in ONE process on
+cuda:0 (the same-process form of the exchange, as a single Java host driving several GPUs would use
+it); every tick both shards push, then both tick, and the merged lists must equal the oracle's
+unsharded tick.  The one-process-per-GPU form (CUDA IPC) is exercised by bench.py --gpus N."""
+import numpy as np
+import pytest
+
+from helpers import random_deployment, pick_sources, SINR_TOL_DB
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def rsb():
+    import radio_sim_b200
+    radio_sim_b200.load()
+    return radio_sim_b200
+
+
+def _shards(rsb, x, y, z, ch, world, max_slots):
+    from radio_sim_b200.sharding import shard_bounds
+    bounds = shard_bounds(len(x), world)
+    meds = []
+    for r, (lo, hi) in enumerate(bounds):
+        m = rsb.Medium("sinr", f64_values=True, rx_base=lo, n_shards=world)
+        m.set_nodes(x[lo:hi], y[lo:hi], z[lo:hi], channel=ch[lo:hi])
+        meds.append(m)
+    blobs = [m.peer_export(world, r, max_slots) for r, m in enumerate(meds)]
+    for m in meds:
+        m.peer_open(blobs)
+    return bounds, meds
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_peer_exchange_matches_the_unsharded_oracle(rsb, orc, world):
+    from radio_sim_b200.sharding import TickPlan, merge_results
+    n = 3000
+    x, y, z, ch = random_deployment(41, n, 500.0, channels=2)
+    bounds, meds = _shards(rsb, x, y, z, ch, world, max_slots=128)
+    try:
+        for tick in range(4):                          # both buffer parities, growing epochs, changing slot counts
+            t = [90, 40, 0, 120][tick]
+            src = pick_sources(41 + tick, n, t)
+            power = np.random.default_rng(tick).choice([-7.0, 0.0], size=t)
+            plan = TickPlan(src, bounds)
+            for r, m in enumerate(meds):
+                m.peer_push(plan.local_src[r], plan.local_fields(r, power, 0.0))
+            parts = []
+            for m in meds:
+                res = m.tick_peers()
+                assert res.n_tx == world * plan.tpad
+                parts.append(dict(tx=res.tx, rx=res.rx, outcome=res.outcome, rssi=res.rssi_dbm_f64, sinr=res.sinr_db_f64))
+            merged = merge_results(plan, parts)
+            full = orc.tick(orc.params(orc.MODEL_SINR), orc.NodeSet(x, y, z, channel=ch), orc.make_packets(src, power, ch[src]))["pairs"]
+            assert np.array_equal(merged["tx"], full["tx"]) and np.array_equal(merged["rx"], full["rx"])
+            assert np.array_equal(merged["outcome"], full["outcome"])
+            assert np.array_equal(merged["rssi"], full["rssi_dbm"])
+            if len(full["tx"]):
+                fin = np.isfinite(full["sinr_db"])
+                assert np.abs(merged["sinr"][fin] - full["sinr_db"][fin]).max() < SINR_TOL_DB
+    finally:
+        for m in meds:
+            m.close()
+
+
+def test_peer_call_order_is_checked(rsb):
+    x, y, z, ch = random_deployment(5, 200, 100.0)
+    with rsb.Medium("sinr") as m:
+        m.set_nodes(x, y)
+        with pytest.raises(rsb.MediumError):           # push before export/open
+            m.peer_push(np.array([1], dtype=np.int32))
+        blob = m.peer_export(1, 0, 8)
+        m.peer_open([blob])
+        with pytest.raises(rsb.MediumError):           # tick without a push
+            m.tick_peers()
+        with pytest.raises(rsb.MediumError):           # more slots than exported
+            m.peer_push(np.arange(9, dtype=np.int32))
+        m.peer_push(np.array([3, 7, -1], dtype=np.int32))
+        with pytest.raises(rsb.MediumError):           # second push without a tick
+            m.peer_push(np.array([3], dtype=np.int32))
+        r = m.tick_peers()
+        assert r.n_tx == 3 and r.n_pairs > 0
+        ref = m.tick(np.array([3, 7], dtype=np.int32))
+        assert np.array_equal(r.rx, ref.rx) and np.array_equal(r.outcome, ref.outcome)

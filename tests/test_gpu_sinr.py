@@ -196,3 +196,24 @@ def test_position_and_radio_updates(rsb, orc):
         r = m.tick(src)
         ref = orc.tick(orc.params(orc.MODEL_SINR), orc.NodeSet(x2, y2, z2, channel=ch2, enabled=en), orc.make_packets(src, -3.0, ch2[src]))
         compare(r, ref)
+
+
+def test_enqueued_tick_equals_the_synchronous_one(rsb, orc):
+    """rmb_tick_enqueue + rmb_tick_finish + rmb_fetch: same lists as rmb_tick; an enqueued tick whose
+    near-slot capacity is exceeded is redone when it is settled."""
+    import torch
+    x, y, z, ch = random_deployment(77, 4000, 600.0)
+    src = pick_sources(77, 4000, 120)
+    ref = orc.tick(orc.params(orc.MODEL_SINR), orc.NodeSet(x, y, z, channel=ch), orc.make_packets(src, 0.0, 26))
+    rec = torch.zeros(120 * 48, dtype=torch.uint8, device="cuda")
+    with rsb.Medium("sinr", f64_values=True) as m:
+        m.set_nodes(x, y, z, channel=ch)
+        m.set_tuning(0, 1)                             # one near slot: the first enqueued tick overflows
+        m.build_tx_records(src, rec.data_ptr())
+        for _ in range(2):
+            m.tick_enqueue(120, rec.data_ptr())
+            counts = m.tick_finish()
+            assert counts.n_pairs == ref["n_pairs"] and counts.n_decisions == ref["n_decisions"]
+            compare(m.fetch(), ref)
+        m.tick_enqueue(120, rec.data_ptr())            # settled implicitly by the next call
+        compare(m.fetch(), ref)

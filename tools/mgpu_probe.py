@@ -1,4 +1,6 @@
-"""Where does a sharded tick spend its time? (development aid; run under torchrun)"""
+"""Where does a sharded tick spend its time? (development aid; run under torchrun)
+Per rank: device time of exchange+tick with the start aligned on the device (an NCCL barrier enqueued on
+the stream right before the start event) and with a host-side barrier only; phases of the last tick."""
 import os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch, torch.distributed as dist
@@ -18,28 +20,37 @@ counts = [int(((src >= r * N // G) & (src < (r + 1) * N // G)).sum()) for r in r
 tpad = max(counts)
 mine = np.full(tpad, -1, dtype=np.int32); m = src[(src >= lo) & (src < hi)]; mine[:m.size] = m
 rec_local = torch.zeros(tpad * 48, dtype=torch.uint8, device=dev)
-rec_all = torch.zeros(G * tpad * 48, dtype=torch.uint8, device=dev)
 med.build_tx_records(mine, rec_local.data_ptr())
+blob = torch.frombuffer(bytearray(med.peer_export(G, rank, tpad)), dtype=torch.uint8).to(dev)
+blobs = torch.empty(G * blob.numel(), dtype=torch.uint8, device=dev)
+dist.all_gather_into_tensor(blobs, blob)
+raw = blobs.cpu().numpy().tobytes()
+med.peer_open([raw[i * 128:(i + 1) * 128] for i in range(G)])
+flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+token = torch.zeros(1, device=dev)
 
-def timeit(fn, reps=30):
+def step():
+    med.peer_push_records(tpad, rec_local.data_ptr())
+    med.tick_peers_resident()
+
+def timeit(aligned, reps=30):
     ts = []
     for _ in range(reps):
-        torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+        flush.fill_(1); torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        t0 = time.perf_counter(); e0.record(stream); fn(); e1.record(stream); torch.cuda.synchronize()
-        ts.append((e0.elapsed_time(e1) * 1e3, (time.perf_counter() - t0) * 1e6))
-    ts = ts[5:]
-    return np.median([a for a, _ in ts]), np.median([b for _, b in ts])
+        if aligned:
+            dist.all_reduce(token)           # stream-ordered: every GPU passes this point at the same device time
+        e0.record(stream); step(); e1.record(stream); torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1) * 1e3)
+    return float(np.median(ts[5:]))
 
-ag = timeit(lambda: dist.all_gather_into_tensor(rec_all, rec_local))
-tk = timeit(lambda: med.tick_resident(G * tpad, rec_all.data_ptr()))
-both = timeit(lambda: (dist.all_gather_into_tensor(rec_all, rec_local), med.tick_resident(G * tpad, rec_all.data_ptr())))
+a, b = timeit(True), timeit(False)
 tm = med.timing()
-out = torch.tensor([ag[0], ag[1], tk[0], tk[1], both[0], both[1], tm["ms_prepare"] * 1e3, tm["ms_sweep"] * 1e3, tm["ms_resolve"] * 1e3, tm["ms_emit"] * 1e3], device=dev)
+out = torch.tensor([a, b, tm["ms_prepare"] * 1e3, tm["ms_sweep"] * 1e3, tm["ms_resolve"] * 1e3, tm["ms_emit"] * 1e3, tm["ms_total"] * 1e3], device=dev)
 allv = [torch.zeros_like(out) for _ in range(G)]
 dist.all_gather(allv, out)
 if rank == 0:
-    print("per rank: allgather(dev,wall) tick(dev,wall) both(dev,wall) | prepare sweep resolve emit  [us]")
+    print("per rank [us]: step(aligned start) step(host barrier) | prepare sweep resolve emit total")
     for r, v in enumerate(allv):
-        print(r, " ".join(f"{float(a):8.1f}" for a in v))
+        print(r, " ".join(f"{float(q):8.1f}" for q in v))
 med.close(); dist.barrier(); dist.destroy_process_group()
