@@ -198,8 +198,7 @@ def run_ours(args):
         # asynchronous form: the whole step is enqueued, the stop event fires when the GPU work is done;
         # timed() settles it (counts, capacity check) after the stop event
         if p2p:
-            med.peer_push_records(tpad, rec_local.data_ptr())
-            med.tick_peers_enqueue()
+            med.peer_exchange_tick_enqueue(tpad, rec_local.data_ptr())      # exchange fused into the tick's first kernel
         else:
             exchange()
             med.tick_enqueue(n_rec, rec_all.data_ptr())

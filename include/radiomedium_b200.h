@@ -207,6 +207,12 @@ int rmb_peer_push_records(rmb_handle *h, int32_t slots, const void *d_records);
 int rmb_tick_peers(rmb_handle *h, const double *uniforms, size_t n_uniforms, rmb_result *out);
 int rmb_tick_peers_resident(rmb_handle *h, rmb_result *out);   /* results stay on the device, see rmb_fetch */
 int rmb_tick_peers_enqueue(rmb_handle *h);                     /* asynchronous, settled by rmb_tick_finish */
+/* rmb_peer_push_records + rmb_tick_peers_enqueue as ONE step: the tick's first kernel stores this rank's
+ * records into the peers' buffers, raises the flags and then waits for the peers' -- exchange and the
+ * preparation that consumes it in a single launch.  Asynchronous; every rank must call it for the tick.
+ * Needs one GPU per handle: the preparation kernel is a cooperative launch, and two cooperative kernels do not
+ * run side by side on one device (handles sharing a GPU use rmb_peer_push + rmb_tick_peers). */
+int rmb_peer_exchange_tick_enqueue(rmb_handle *h, int32_t slots, const void *d_records);
 
 /* Replaces Transciever.getRSSI / RadioMedium.getBaseRSSI for the per-tick node-info
  * (Transciever.java:52-61, net/JSONClientConnection.java:331-341): total in-band power

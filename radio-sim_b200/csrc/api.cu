@@ -86,7 +86,7 @@ struct rmb_handle {
     DevBuf<int> pk_src, pk_channel; DevBuf<double> pk_power; PinBuf<char> pk_stage;
     DevBuf<rmb_tx_record> rec;
     DevBuf<float4> txf, stg_f; DevBuf<float> theta, theta_min_g, stg_theta; DevBuf<int> stg_gid; DevBuf<int> arrival, goff, gcount;
-    DevBuf<int> blk_cnt, blk_thmin; DevBuf<unsigned> bar; unsigned bar_count = 0, bar2_count = 0; DevBuf<double> recheck_part;   // fused tx preparation (cooperative launch)
+    DevBuf<int> blk_cnt, blk_thmin; DevBuf<unsigned> bar; unsigned bar_count = 0, bar2_count = 0; DevBuf<double> recheck_part; DevBuf<int> rx_done;   // fused tx preparation (cooperative launch)
     DevBuf<double> uniforms;
 
     // slots
@@ -116,6 +116,7 @@ struct rmb_handle {
         size_t rec_off(unsigned e) const { return kPeerFlagBytes + (size_t)(e & 1u) * (size_t)world * max_slots * sizeof(rmb_tx_record); }
     } peer;
     const unsigned *wait_flags = nullptr; unsigned wait_epoch = 0; int wait_world = 0;   // set around compute() by rmb_tick_peers
+    const rmb_tx_record *fused_push = nullptr;   // rmb_peer_exchange_tick_enqueue: the preparation kernel pushes these itself
     // asynchronous tick (rmb_tick_enqueue / rmb_tick_peers_enqueue): enqueued, counters not looked at yet
     bool async_mode = false, pending = false;
     struct Pending { int n_tx = 0; const rmb_tx_record *rec = nullptr; const unsigned *flags = nullptr; unsigned epoch = 0; int world = 0;
@@ -125,6 +126,7 @@ struct rmb_handle {
     long long last_pairs = 0; int last_ntx = 0;
     rmb_result last{};
     int sweep_variant = 0;
+    bool fuse_resolve = true;          // rmb_set_tuning bit 16 turns the fused epilogue off (stand-alone resolve kernel)
     bool have_nodes = false;
 
     int fail(int code, const std::string &m) { err = m; return code; }
@@ -208,7 +210,7 @@ static int ensure_slots(rmb_handle *h)
     RMB_CK(h, h->slots.ensure(nk)); RMB_CK(h, h->sl_prx.ensure(nk)); RMB_CK(h, h->sl_lin.ensure(nk));
     RMB_CK(h, h->sl_sinr.ensure(nk)); RMB_CK(h, h->sl_flags.ensure(nk));
     RMB_CK(h, h->cnt.ensure(nw)); RMB_CK(h, h->hcnt.ensure(nw)); RMB_CK(h, h->hoff.ensure(nw + 2));
-    RMB_CK(h, h->recheck.ensure(nw)); RMB_CK(h, h->recheck2.ensure(nw)); RMB_CK(h, h->recheck_part.ensure(nw + 1024)); RMB_CK(h, h->first.ensure(nw)); RMB_CK(h, h->itot.ensure(nw));
+    RMB_CK(h, h->recheck.ensure(nw)); RMB_CK(h, h->recheck2.ensure(nw)); RMB_CK(h, h->recheck_part.ensure(nw + 1024)); RMB_CK(h, h->rx_done.ensure(nw / 32 + 1)); RMB_CK(h, h->first.ensure(nw)); RMB_CK(h, h->itot.ensure(nw));
     RMB_CK(h, h->scan_tmp.ensure(nw / 1024 + 8));
     return RMB_OK;
 }
@@ -379,7 +381,7 @@ int rmb_destroy(rmb_handle *h)
     h->matrix.release(); h->channel.release(); h->id_int.release(); h->enabled.release(); h->perm.release(); h->wx.release(); h->wy.release(); h->wz.release(); h->wrxp.release(); h->gid.release(); h->ro_key.release(); h->ro_key_alt.release(); h->ro_val.release(); h->ro_val_alt.release(); h->ro_tmp.release();
     h->fx.release(); h->fy.release(); h->fz.release(); h->dp.release(); h->geom.release(); h->geom_scratch.release();
     h->ctr.release(); h->h_ctr.release(); h->node_rssi.release(); h->node_recv.release(); h->pk_src.release();
-    h->pk_channel.release(); h->pk_power.release(); h->pk_stage.release(); h->rec.release(); h->txf.release(); h->stg_f.release(); h->stg_theta.release(); h->stg_gid.release(); h->blk_cnt.release(); h->blk_thmin.release(); h->bar.release(); h->recheck_part.release();
+    h->pk_channel.release(); h->pk_power.release(); h->pk_stage.release(); h->rec.release(); h->txf.release(); h->stg_f.release(); h->stg_theta.release(); h->stg_gid.release(); h->blk_cnt.release(); h->blk_thmin.release(); h->bar.release(); h->recheck_part.release(); h->rx_done.release();
     h->theta.release(); h->theta_min_g.release(); h->arrival.release(); h->goff.release(); h->gcount.release();
     h->uniforms.release(); h->slots.release(); h->cnt.release(); h->hcnt.release(); h->hoff.release();
     h->recheck.release(); h->recheck2.release(); h->far_part.release(); h->sl_prx.release(); h->sl_lin.release(); h->sl_sinr.release();
@@ -535,6 +537,7 @@ extern "C" int rmb_set_tuning(rmb_handle *h, int32_t sweep_variant, int32_t near
     // low byte: kernel variant; bits 8..15: forced number of tx splits (0 = planned per tick)
     h->sweep_variant = sweep_variant & 0xff;
     h->forced_splits = (sweep_variant >> 8) & 0xff;
+    h->fuse_resolve = ((sweep_variant >> 16) & 1) == 0;
     if (near_slots > 0 && near_slots != h->K) { h->K = near_slots; return ensure_slots(h); }
     return RMB_OK;
 }
@@ -712,7 +715,13 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
         PrepareAux aux{};
         aux.cnt = h->cnt.p; aux.n_work = h->n_work; aux.tx_cnt = h->tx_cnt.p; aux.tx_failed = h->tx_failed.p; aux.tx_base = h->tx_base.p;
         aux.blk_cnt = h->blk_cnt.p; aux.blk_thmin = h->blk_thmin.p; aux.bar = h->bar.p; aux.bar_target = h->bar_count;
+        aux.rx_done = h->rx_done.p; aux.n_rx_done = h->n_work / 32 + 1;
         aux.peer_flags = h->wait_flags; aux.world = h->wait_world; aux.epoch = h->wait_epoch;
+        if (h->fused_push) {
+            aux.push_local = h->fused_push; aux.push_slots = h->peer.slots; aux.push_rank = h->peer.rank;
+            aux.push_off = h->peer.rec_off(h->peer.epoch); aux.push_done = h->peer.done;
+            for (int r = 0; r < h->peer.world; ++r) aux.push_peer[r] = h->peer.peer[r];
+        }
         RMB_CK(h, launch_prepare(nd, h->dp.p, h->geom.p, h->groups, n_tx, d_rec, stg, tx, h->theta.p, h->theta_min_g.p, h->ctr.p, aux, pgrid, h->st));
         launches += 1;
         RMB_CK(h, cudaEventRecord(h->ev[1], h->st));
@@ -729,17 +738,27 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
             if (attempt) {               // attempt 0: the preparation kernel zeroed them
                 RMB_CK(h, cudaMemsetAsync(h->cnt.p, 0, (size_t)h->n_work * sizeof(int), h->st));
                 RMB_CK(h, cudaMemsetAsync(h->tx_cnt.p, 0, ((size_t)n_tx + 1) * sizeof(int), h->st));
+                RMB_CK(h, cudaMemsetAsync(h->rx_done.p, 0, ((size_t)h->n_work / 32 + 1) * sizeof(int), h->st));
                 RMB_CK(h, cudaEventRecord(h->ev[1], h->st));
             }
-            RMB_CK(h, launch_sweep(mode, h->planar, variant, h->n_work, h->splits, a, h->st));
-            ++launches; ++sweeps;
-            RMB_CK(h, cudaEventRecord(h->ev[2], h->st));
-            // exact resolve: decisions + dense pair records; then the per-packet segment offsets
+            // exact resolve (decisions + dense pair records, then the per-packet segment offsets): fused into the
+            // sweep as the epilogue of every rx block's last tx split; a kernel of its own for the other variants
             SlotArrays sl = slot_arrays(h);
             PairRecs pr = pair_recs(h);
             PairArrays pa = pair_arrays(h);
-            RMB_CK(h, launch_resolve(nd, wk, h->dp.p, tx, d_rec, sl, pr, h->ctr.p, n_tx, h->seg.p, h->st));
-            launches += 1;
+            SweepFuse fuse{};
+            fuse.rb_fused = h->fuse_resolve ? sweep_fused_rx_blocks(mode, h->planar, variant, h->n_work, h->splits) : 0;
+            fuse.enabled = fuse.rb_fused > 0 ? 1 : 0;
+            fuse.wk = wk; fuse.dp = h->dp.p; fuse.rec = d_rec; fuse.sl = sl; fuse.pr = pr; fuse.ctr = h->ctr.p;
+            fuse.n_tx = n_tx; fuse.seg = h->seg.p; fuse.rx_done = h->rx_done.p;
+            RMB_CK(h, launch_sweep(mode, h->planar, variant, h->n_work, h->splits, a, fuse, h->st));
+            ++launches; ++sweeps;
+            RMB_CK(h, cudaEventRecord(h->ev[2], h->st));
+            const int w_first = fuse.rb_fused * sweep_block_rx(mode, h->planar, variant);
+            if (w_first < h->n_work) {
+                RMB_CK(h, launch_resolve(nd, wk, h->dp.p, tx, d_rec, sl, pr, h->ctr.p, n_tx, h->seg.p, w_first, h->st));
+                launches += 1;
+            }
             // guard-band receivers: exact sums on a side stream, overlapped with the ordering
             RMB_CK(h, cudaEventRecord(h->ev_fork, h->st));
             RMB_CK(h, cudaStreamWaitEvent(h->st2, h->ev_fork, 0));
@@ -751,11 +770,13 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
             RMB_CK(h, cudaEventRecord(h->ev[3], h->st));
             RMB_CK(h, launch_order_buckets(pr, h->ctr.p, n_tx, h->seg.p, h->key_alt.p, h->val.p, h->st)); launches += 2;
             RMB_CK(h, cudaStreamWaitEvent(h->st, h->ev_join, 0));
-            if (!draws) { RMB_CK(h, launch_emit_sinr(nd, h->dp.p, d_rec, n_tx, pr, h->val.p, pa, -1, false, h->ctr.p, h->st)); launches += 1; }
+            // deterministic reception: the emit kernel's last block stores the counters into the pinned host copy
+            const bool dev_publish = !draws && n_tx > 0;
+            if (!draws) { RMB_CK(h, launch_emit_sinr(nd, h->dp.p, d_rec, n_tx, pr, h->val.p, pa, -1, false, h->ctr.p, h->h_ctr.p, h->st)); launches += 1; }
             RMB_CK(h, cudaEventRecord(h->ev[4], h->st));
             if (h->async_mode && attempt == 0 && !draws) {
                 // enqueue only: the counters travel to the host behind the tick, finish_pending looks at them
-                RMB_CK(h, cudaMemcpyAsync(h->h_ctr.p, h->ctr.p, sizeof(Counters), cudaMemcpyDeviceToHost, h->st));
+                if (!dev_publish) RMB_CK(h, cudaMemcpyAsync(h->h_ctr.p, h->ctr.p, sizeof(Counters), cudaMemcpyDeviceToHost, h->st));
                 h->pending = true;
                 h->pend.n_tx = n_tx; h->pend.rec = d_rec; h->pend.flags = h->wait_flags; h->pend.epoch = h->wait_epoch;
                 h->pend.world = h->wait_world; h->pend.launches = launches; h->pend.sweeps = sweeps;
@@ -763,7 +784,8 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
                 h->last.n_tx = n_tx; h->last_pairs = 0; h->last_ntx = n_tx;
                 return RMB_OK;
             }
-            if ((rc = read_counters(h))) return rc;
+            if (dev_publish) RMB_CK(h, cudaStreamSynchronize(h->st));
+            else if ((rc = read_counters(h))) return rc;
             const Counters c = *h->h_ctr.p;
             if (c.peer_timeout) return h->fail(RMB_ERR_PEER, "peer exchange: a rank's tx records did not arrive (no rmb_peer_push on that rank?)");
             const bool slots_short = c.max_near > h->K, recs_short = (long long)c.heard > (long long)h->key.cap;
@@ -798,11 +820,11 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
             OrderScratch sc{h->key_alt.p, h->fb_key.p, h->fb_key_alt.p, h->fb_val.p, h->fb_val_alt.p, h->cub_tmp.p, h->cub_tmp.cap};
             RMB_CK(h, launch_order_fallback(pr, m, pa.key_shift + bits_for(n_tx), sc, h->val.p, h->st));
             launches += 7;
-            if (!draws) { RMB_CK(h, launch_emit_sinr(nd, h->dp.p, d_rec, n_tx, pr, h->val.p, pa, m, false, h->ctr.p, h->st)); launches += 1; }
+            if (!draws) { RMB_CK(h, launch_emit_sinr(nd, h->dp.p, d_rec, n_tx, pr, h->val.p, pa, m, false, h->ctr.p, nullptr, h->st)); launches += 1; }
         }
         if (draws) {
             pa.key = h->key_alt.p;         // sorted keys for the draw-order stage (the bucket items are dead by now)
-            RMB_CK(h, launch_emit_sinr(nd, h->dp.p, d_rec, n_tx, pr, h->val.p, pa, m, true, h->ctr.p, h->st));
+            RMB_CK(h, launch_emit_sinr(nd, h->dp.p, d_rec, n_tx, pr, h->val.p, pa, m, true, h->ctr.p, nullptr, h->st));
             RMB_CK(h, launch_emit(h->dp.p, d_rec, n_tx, pa, m, true, h->uniforms.p, nu, h->ctr.p, h->st));
             launches += 7;
         }
@@ -1120,6 +1142,28 @@ int rmb_tick_peers_enqueue(rmb_handle *h)
     RMB_CK(h, cudaSetDevice(h->cfg.device));
     h->async_mode = true;
     const int rc = tick_peers_locked(h, nullptr, 0);
+    h->async_mode = false;
+    return rc;
+}
+
+int rmb_peer_exchange_tick_enqueue(rmb_handle *h, int32_t slots, const void *d_records)
+{
+    if (!h) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    RMB_SETTLE(h);
+    auto &P = h->peer;
+    if (slots < 0 || slots > P.max_slots || (slots > 0 && !d_records) || ((uintptr_t)d_records & 15))
+        return h->fail(RMB_ERR_INVALID, "rmb_peer_exchange_tick_enqueue: bad arguments (slots <= max_slots, 16-byte aligned records)");
+    for (int r = 0; r < P.world; ++r) if (!P.peer[r]) return h->fail(RMB_ERR_STATE, "rmb_peer_exchange_tick_enqueue before rmb_peer_open");
+    if (P.world < 1) return h->fail(RMB_ERR_STATE, "rmb_peer_exchange_tick_enqueue before rmb_peer_export");
+    if (P.pushed) return h->fail(RMB_ERR_STATE, "a pushed tick is still waiting for rmb_tick_peers");
+    if (h->cfg.model != RMB_MODEL_SINR) return h->fail(RMB_ERR_UNSUPPORTED, "the fused exchange exists for the SINR medium only");
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    P.slots = slots; ++P.epoch; P.pushed = true;
+    h->async_mode = true;
+    h->fused_push = (const rmb_tx_record *)d_records;
+    const int rc = tick_peers_locked(h, nullptr, 0);
+    h->fused_push = nullptr;
     h->async_mode = false;
     return rc;
 }

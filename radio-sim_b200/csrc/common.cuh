@@ -60,6 +60,8 @@ struct Counters {
     int peer_timeout;                 // multi-GPU exchange: a peer's records did not arrive (see peer_wait)
     unsigned resolve_done;            // blocks of the resolve kernel that have finished (the last one scans tx_cnt)
     unsigned recheck_done;            // work units of the guard-band recheck that have finished
+    unsigned emit_done;               // blocks of the emit kernel that have finished (the last one publishes the counters)
+    unsigned pad;
 };
 
 // slot flags
@@ -125,11 +127,31 @@ constexpr int kPrepMaxGrid = 256;
 struct PrepareAux {
     int *cnt; int n_work;             // near-candidate counters of the receivers (zeroed here)
     int *tx_cnt;                      // [n_tx+1] heard pairs per packet (zeroed here)
+    int *rx_done; int n_rx_done;      // per-rx-block split counters of the sweep's fused epilogue (zeroed here)
     uint8_t *tx_failed; long long *tx_base;   // [n_tx] deterministic tx-failure rule (p_tx <= 0), draw base 0
     int *blk_cnt, *blk_thmin;         // [grid][kMaxGroups] per-block bucket counts / min thresholds
     unsigned *bar; unsigned bar_target;
     const unsigned *peer_flags; int world; unsigned epoch;   // peer_flags == nullptr: no exchange to wait for
+    // exchange fused into this kernel (push_local != nullptr): store this rank's records into every peer's gather
+    // buffer, raise the flags, then wait -- one kernel does the "all-gather" and the preparation that consumes it
+    const rmb_tx_record *push_local; int push_slots, push_rank; size_t push_off; unsigned *push_done;
+    char *push_peer[kMaxPeers];
 };
+
+// SM count of the current device (queried once per device: this sits on the tick's launch path)
+inline int device_sms()
+{
+    static int cache[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) return 148;
+    if (cache[dev] == 0) {
+        int sms = 148;
+        if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) { sms = 148; cudaGetLastError(); }
+        cache[dev] = sms;
+    }
+    return cache[dev];
+}
 
 #define RMB_CUDA_OK(expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) return e__; } while (0)
 

@@ -356,14 +356,16 @@ cudaError_t launch_emit(const DevParams *dp, const rmb_tx_record *rec, int n_tx,
 // Stochastic reception: only the sorted pair arrays are produced; launch_emit applies the draws.
 // m_host < 0: the pair count is read on the device (the host has not synchronised yet) and the kernel
 // stands down when the host will have to redo the tick or take the radix-sort fallback.
+// host_ctr (pinned host memory, may be null): the last block to finish stores the tick's counters there, so
+// that the host needs no copy operation behind the tick -- a stream synchronisation is enough.
 template <bool STOCHASTIC>
 __global__ void emit_sinr_kernel(NodeArrays nd, const DevParams *dp, PairRecs pr, const unsigned *order, PairArrays pa,
-                                 long long m_host, Counters *ctr)
+                                 long long m_host, Counters *ctr, Counters *host_ctr)
 {
     long long m = m_host;
     if (m_host < 0) {
         m = (long long)ctr->heard;
-        if (m > pr.cap || ctr->max_bucket > kBucketSortMax) return;
+        if (m > pr.cap || ctr->max_bucket > kBucketSortMax) m = 0;       // stand down: the host redoes / re-orders
     }
     int delivered = 0, interfered = 0;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < m; i += (long long)gridDim.x * blockDim.x) {
@@ -396,20 +398,31 @@ __global__ void emit_sinr_kernel(NodeArrays nd, const DevParams *dp, PairRecs pr
             if (interfered) atomicAdd(&ctr->n_interfered, interfered);
         }
     }
+    if (host_ctr) {
+        __shared__ int s_last;
+        __syncthreads();
+        if (threadIdx.x == 0) { __threadfence(); s_last = atomicAdd(&ctr->emit_done, 1u) == gridDim.x - 1; }
+        __syncthreads();
+        if (s_last && threadIdx.x < sizeof(Counters) / sizeof(unsigned)) {
+            __threadfence();
+            reinterpret_cast<volatile unsigned *>(host_ctr)[threadIdx.x] = __ldcg(reinterpret_cast<const unsigned *>(ctr) + threadIdx.x);
+            __threadfence_system();
+        }
+    }
 }
 
 cudaError_t launch_emit_sinr(const NodeArrays &nd, const DevParams *dp, const rmb_tx_record *rec, int n_tx, PairRecs pr,
                              const unsigned *order, PairArrays pa, long long m, bool stochastic, Counters *ctr,
-                             cudaStream_t st)
+                             Counters *host_ctr, cudaStream_t st)
 {
     if (n_tx <= 0) return cudaSuccess;
     const unsigned blocks = m < 0 ? 148u * 8u : (unsigned)((m + 255) / 256);
     if (stochastic) {
-        if (m > 0) emit_sinr_kernel<true><<<blocks, 256, 0, st>>>(nd, dp, pr, order, pa, m, ctr);
+        if (m > 0) emit_sinr_kernel<true><<<blocks, 256, 0, st>>>(nd, dp, pr, order, pa, m, ctr, nullptr);
         return cudaGetLastError();
     }
     // tx_failed / tx_base of the deterministic rule were written by the tx preparation kernel
-    if (m != 0) emit_sinr_kernel<false><<<blocks, 256, 0, st>>>(nd, dp, pr, order, pa, m, ctr);
+    if (m != 0) emit_sinr_kernel<false><<<blocks, 256, 0, st>>>(nd, dp, pr, order, pa, m, ctr, host_ctr);
     return cudaGetLastError();
 }
 

@@ -65,7 +65,11 @@ struct SweepArgs {
 int sweep_mode_for_exponent(double n);
 // number of tx splits (grid.y) for a bucket of about n_tx_bucket transmissions; forced_splits > 0 overrides
 int sweep_plan(int mode, bool planar, int variant, int n_work, int n_tx_bucket, int forced_splits);
-cudaError_t launch_sweep(int mode, bool planar, int variant, int n_work, int splits, const SweepArgs &a, cudaStream_t st);
+// The sweep's fused epilogue (128-thread variants): the last tx-split block of an rx block resolves its receivers
+// (exact decisions, pair records) and the last rx block scans the per-packet counts -- see resolve_body.cuh.
+struct SlotArrays; struct PairRecs;
+int sweep_fused_rx_blocks(int mode, bool planar, int variant, int n_work, int splits);
+int sweep_block_rx(int mode, bool planar, int variant);
 
 // ---- exact resolve of the near candidates + guard-band recheck --------------------------------
 struct SlotArrays {
@@ -92,11 +96,20 @@ struct PairRecs {
     int *rank;                        // position inside the packet's bucket (atomic counter, arbitrary order)
     int *tx_cnt;                      // [n_tx] heard pairs per packet (zero on entry)
 };
+struct SweepFuse {
+    int enabled;
+    WorkArrays wk; const DevParams *dp; const rmb_tx_record *rec; SlotArrays sl; PairRecs pr; Counters *ctr;
+    int n_tx; int *seg;
+    int *rx_done;                     // [rx blocks] splits finished (zero on entry)
+    int rb_fused;                     // rx blocks [0, rb_fused) are resolved by the sweep, the rest by launch_resolve
+};
+cudaError_t launch_sweep(int mode, bool planar, int variant, int n_work, int splits, const SweepArgs &a, const SweepFuse &fuse,
+                         cudaStream_t st);
 // also turns the per-packet heard counts into segment offsets (seg[t] = first pair of packet t, exclusive scan
 // of pr.tx_cnt; largest bucket -> ctr->max_bucket): done by the last block to finish
 cudaError_t launch_resolve(const NodeArrays &nd, const WorkArrays &wk, const DevParams *dp, TxTiles tx,
                            const rmb_tx_record *rec, SlotArrays sl, PairRecs pr, Counters *ctr, int n_tx, int *seg,
-                           cudaStream_t st);
+                           int w_first, cudaStream_t st);   // receivers [w_first, n_work) (a multiple of 128)
 // per-node RSSI (total in-band power, dBm) and receiving flag from the work-order results of the last tick
 cudaError_t launch_node_info(const WorkArrays &wk, SlotArrays sl, float *node_rssi, uint8_t *node_recv, cudaStream_t st);
 // part: >= n_work + grid doubles of scratch; cooperative launch of `grid` (= recheck_grid()) blocks with its
@@ -142,7 +155,7 @@ cudaError_t launch_order_buckets(PairRecs pr, const Counters *ctr, int n_tx, con
 cudaError_t launch_order_fallback(PairRecs pr, long long m, int key_bits, OrderScratch sc, unsigned *order, cudaStream_t st);
 cudaError_t launch_emit_sinr(const NodeArrays &nd, const DevParams *dp, const rmb_tx_record *rec, int n_tx, PairRecs pr,
                              const unsigned *order, PairArrays pa, long long m, bool stochastic, Counters *ctr,
-                             cudaStream_t st);
+                             Counters *host_ctr, cudaStream_t st);
 cudaError_t launch_emit(const DevParams *dp, const rmb_tx_record *rec, int n_tx, PairArrays pa, long long n,
                         bool stochastic, const double *uniforms, long long n_uniforms, Counters *ctr,
                         cudaStream_t st);

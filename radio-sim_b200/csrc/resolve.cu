@@ -9,212 +9,34 @@
 //   Itot = N0 + sum of lin over co-channel packets (arrival order, source != rx)
 //   heard iff Prx >= sensitivity && rxProbability > 0
 //   SINR = Prx - 10 log10(Itot - lin);  decodable iff SINR >= threshold
-#include "common.cuh"
-#include "kernels.h"
-#include "exact_math.cuh"
+#include "resolve_body.cuh"
 
 namespace rmb {
 
-__device__ __forceinline__ double rx_power_dbm(const DevParams *dp, double power_dbm, double d)
-{
-    double dd = d < dp->d0_m ? dp->d0_m : d;
-    double pl = xm::add(dp->pl0_db, xm::mul(xm::mul(10.0, dp->pl_exponent), xm::log10_strict(xm::dvd(dd, dp->d0_m))));
-    return xm::sub(power_dbm, pl);
-}
-
-__device__ __forceinline__ double sinr_db(double prx, double itot, double lin)
-{
-    double ioth = xm::sub(itot, lin);
-    return ioth > 0.0 ? xm::sub(prx, xm::mw_to_dbm(ioth)) : __longlong_as_double(0x7ff0000000000000ll);
-}
-
-// One warp per 32 receivers (work order).  The exact evaluation of the near candidates is the
-// expensive part (fdlibm log10 + exp in strict double) and the candidate counts differ between
-// receivers, so the warp pools its candidates: candidate i of the warp (prefix sum of the
-// per-lane counts) is evaluated by lane i % 32, whoever owns it.  The per-receiver parts (far
-// sum, the ordered addition of the near terms, flags) stay on the owning lane.
-constexpr uint8_t kGuard = 4;         // slot flag, resolve-internal: SINR within the guard band
-
-__device__ __forceinline__ int owner_of(int i, int P)
-{
-    // largest lane o with P_o <= i (P = exclusive prefix of the per-lane candidate counts)
-    int lo = 0, hi = 31;
-#pragma unroll
-    for (int step = 0; step < 5; ++step) {
-        const int mid = (lo + hi + 1) >> 1;
-        const int pm = __shfl_sync(0xffffffffu, P, mid);
-        if (pm <= i) lo = mid; else hi = mid - 1;
-    }
-    return lo;
-}
-
-// seg[t] = first pair of packet t (exclusive scan of the per-packet heard counts), largest bucket ->
-// ctr->max_bucket.  Run by the LAST block of the resolve kernel to finish (128 threads, every thread a
-// contiguous range), which saves a launch on the tick's critical path.
-constexpr int kScanTile = 4096;       // 128 threads x 32 counts, staged through shared memory
-__device__ void scan_tx_counts(const int *tx_cnt, int n_tx, int *seg, Counters *ctr)
-{
-    __shared__ int s_tile[kScanTile + kScanTile / 32];       // one pad word per 32: thread-contiguous reads are conflict-free
-    __shared__ int s_w[4], s_m[4];
-    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    int carry = 0, mx = 0;
-    for (int c0 = 0; c0 < n_tx; c0 += kScanTile) {
-        const int nt = min(kScanTile, n_tx - c0);
-        for (int i = tid; i < kScanTile; i += 128) s_tile[i + (i >> 5)] = i < nt ? __ldcg(tx_cnt + c0 + i) : 0;   // coalesced, independent
-        __syncthreads();
-        int *mine = s_tile + 33 * tid;
-        int sum = 0;
-#pragma unroll
-        for (int k = 0; k < 32; ++k) { const int v = mine[k]; sum += v; mx = max(mx, v); }
-        int incl = sum;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
-        if (lane == 31) s_w[wid] = incl;
-        __syncthreads();
-        int run = carry + incl - sum;
-        for (int w = 0; w < wid; ++w) run += s_w[w];
-#pragma unroll
-        for (int k = 0; k < 32; ++k) { const int v = mine[k]; mine[k] = run; run += v; }
-        carry += s_w[0] + s_w[1] + s_w[2] + s_w[3];
-        __syncthreads();
-        for (int i = tid; i < nt; i += 128) seg[c0 + i] = s_tile[i + (i >> 5)];
-        __syncthreads();
-    }
-    for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    if (lane == 0) s_m[wid] = mx;
-    __syncthreads();
-    if (tid == 0) { seg[n_tx] = carry; ctr->max_bucket = max(max(s_m[0], s_m[1]), max(s_m[2], s_m[3])); }
-}
-
 __global__ void __launch_bounds__(128)
 resolve_kernel(NodeArrays nd, WorkArrays wk, const DevParams *dp, TxTiles tx, const rmb_tx_record *rec,
-               SlotArrays sl, PairRecs pr, Counters *ctr, int n_tx, int *seg)
+               SlotArrays sl, PairRecs pr, Counters *ctr, int n_tx, int *seg, int w_first)
 {
     __shared__ int s_last;
-    const int w = blockIdx.x * blockDim.x + threadIdx.x;       // n_work is a multiple of 1024: no partial warps
-    const int lane = threadIdx.x & 31;
-    const int K = sl.K;
-    const int p = wk.perm[w];
-    const size_t base = (size_t)w * K;
-    int c = 0;
-    double itot = dp->n0_mw;
-    if (p >= 0) {
-        const int found = sl.cnt[w];
-        if (found > K) atomicMax(&ctr->max_near, found);      // slot overflow: the host grows K and redoes the sweep
-        c = min(found, K);
-        // far field: the sweep's per-split partial sums, added in split order (deterministic)
-        double far = 0.0;
-        for (int s = 0; s < sl.splits; ++s) far = xm::add(far, (double)sl.far_part[(size_t)s * wk.n_work + w]);
-        itot = xm::add(itot, far);
-        // the sweep appends near candidates in arbitrary order: sort by bucket position (= arrival order)
-        for (int a = 1; a < c; ++a) {
-            const int v = sl.slots[base + a];
-            int b = a - 1;
-            while (b >= 0 && sl.slots[base + b] > v) { sl.slots[base + b + 1] = sl.slots[base + b]; --b; }
-            sl.slots[base + b + 1] = v;
-        }
-    }
-    int incl = c;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
-    const int P = incl - c;
-    const int total = __shfl_sync(0xffffffffu, incl, 31);
-    const size_t wbase = (size_t)(w - lane) * K;
-    __syncwarp();
-
-    // pass 1 (pooled): link budget of every candidate
-    for (int i0 = 0; i0 < total; i0 += 32) {
-        const int i = i0 + lane;
-        const int o = owner_of(i, P);
-        const int po = __shfl_sync(0xffffffffu, p, o);
-        const int so = i - __shfl_sync(0xffffffffu, P, o);
-        if (i < total) {
-            const size_t q = wbase + (size_t)o * K + so;
-            const rmb_tx_record r = rec[tx.arrival[sl.slots[q]]];
-            uint8_t f = 0;
-            double prx = 0.0, lin = 0.0;
-            if (r.src != dp->rx_base + po) {
-                const int wo = w - lane + o;
-                const double d = xm::distance(r.x, r.y, r.z, wk.x64[wo], wk.y64[wo], wk.z64[wo]);
-                prx = rx_power_dbm(dp, r.power_dbm, d);
-                lin = xm::dbm_to_mw(prx);
-                if (prx >= dp->sensitivity_dbm && wk.rxp[wo] > 0.0) f = kHeard;
-            }
-            sl.prx[q] = prx; sl.lin[q] = lin; sl.flags[q] = f;
-        }
-    }
-    __syncwarp();
-
-    // per receiver: total in-band power, near terms added in arrival order
-    int nh = 0;
-    for (int s = 0; s < c; ++s) {
-        itot = xm::add(itot, sl.lin[base + s]);       // the source's own packet contributes lin = 0
-        nh += sl.flags[base + s] & kHeard;
-    }
-
-    // the warp's heard pairs take one contiguous range of the record list (one atomic per warp);
-    // a receiver's records are contiguous in slot order, starting at first[w]
-    int hincl = nh;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, hincl, o); if (lane >= o) hincl += y; }
-    const int wtotal = __shfl_sync(0xffffffffu, hincl, 31);
-    unsigned long long rbase = 0;
-    if (lane == 0 && wtotal) rbase = atomicAdd(&ctr->heard, (unsigned long long)wtotal);
-    rbase = __shfl_sync(0xffffffffu, rbase, 0);
-    sl.first[w] = (int)rbase + hincl - nh;
-
-    // pass 2 (pooled): SINR of every heard candidate, pair record
-    int running = 0;
-    for (int i0 = 0; i0 < total; i0 += 32) {
-        const int i = i0 + lane;
-        const int o = owner_of(i, P);
-        const int po = __shfl_sync(0xffffffffu, p, o);
-        const int so = i - __shfl_sync(0xffffffffu, P, o);
-        const double it = __shfl_sync(0xffffffffu, itot, o);
-        size_t q = 0;
-        uint8_t f = 0;
-        if (i < total) { q = wbase + (size_t)o * K + so; f = sl.flags[q]; }
-        const unsigned hb = __ballot_sync(0xffffffffu, (f & kHeard) != 0);
-        if (f & kHeard) {
-            const double prx = sl.prx[q];
-            const double sinr = sinr_db(prx, it, sl.lin[q]);
-            if (sinr >= dp->sinr_threshold_db) f |= kDecodable;
-            if (fabs(sinr - dp->sinr_threshold_db) < dp->sinr_guard_db) f |= kGuard;
-            sl.sinr[q] = sinr; sl.flags[q] = f;
-            const long long ri = (long long)rbase + running + __popc(hb & ((1u << lane) - 1));
-            const int t = tx.arrival[sl.slots[q]];
-            const int rank = atomicAdd(&pr.tx_cnt[t], 1);
-            if (ri < pr.cap) {
-                pr.key[ri] = ((unsigned long long)t << pr.key_shift) | (unsigned)(dp->rx_base + po);
-                pr.prx[ri] = prx; pr.sinr[ri] = sinr; pr.flags[ri] = f & (kHeard | kDecodable); pr.rank[ri] = rank;
-            }
-        }
-        running += __popc(hb);
-    }
-    __syncwarp();
-
-    if (p >= 0) {
-        bool guard = false;
-        for (int s = 0; s < c; ++s) guard |= (sl.flags[base + s] & kGuard) != 0;
-        sl.itot[w] = itot;
-        if (guard && sl.cnt[w] <= K) sl.recheck[atomicAdd(&ctr->n_recheck, 1)] = w;
-    }
-    sl.hcnt[w] = nh;
+    const int w = w_first + blockIdx.x * blockDim.x + threadIdx.x;       // n_work is a multiple of 1024: no partial warps
+    resolve_receiver<false>(w, wk, dp, tx, rec, sl, pr, ctr);
 
     // the last block to finish turns the per-packet counts into segment offsets
     // (barrier, then ONE fence + arrival by thread 0: the release pattern of a grid-wide semaphore)
     __syncthreads();
-    if (threadIdx.x == 0) { __threadfence(); s_last = atomicAdd(&ctr->resolve_done, 1u) == gridDim.x - 1; }
+    // (resolve_done counts groups of 128 receivers: the sweep's fused epilogue resolves the others)
+    if (threadIdx.x == 0) { __threadfence(); s_last = atomicAdd(&ctr->resolve_done, 1u) + 1u == (unsigned)(wk.n_work / 128); }
     __syncthreads();
     if (s_last) { __threadfence(); scan_tx_counts(pr.tx_cnt, n_tx, seg, ctr); }
 }
 
+
 cudaError_t launch_resolve(const NodeArrays &nd, const WorkArrays &wk, const DevParams *dp, TxTiles tx,
                            const rmb_tx_record *rec, SlotArrays sl, PairRecs pr, Counters *ctr, int n_tx, int *seg,
-                           cudaStream_t st)
+                           int w_first, cudaStream_t st)
 {
-    if (wk.n_work <= 0) return cudaSuccess;
-    resolve_kernel<<<(wk.n_work + 127) / 128, 128, 0, st>>>(nd, wk, dp, tx, rec, sl, pr, ctr, n_tx, seg);
+    if (wk.n_work - w_first <= 0) return cudaSuccess;
+    resolve_kernel<<<(wk.n_work - w_first) / 128, 128, 0, st>>>(nd, wk, dp, tx, rec, sl, pr, ctr, n_tx, seg, w_first);
     return cudaGetLastError();
 }
 
@@ -369,10 +191,7 @@ recheck_seq_kernel(WorkArrays wk, const DevParams *dp, Groups groups, TxTiles tx
 
 int recheck_grid()
 {
-    int dev = 0, sms = 148;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    return 2 * sms;                            // __launch_bounds__(kTreeThreads, 2): always co-resident
+    return 2 * device_sms();                            // __launch_bounds__(kTreeThreads, 2): always co-resident
 }
 
 cudaError_t launch_recheck(const NodeArrays &nd, const WorkArrays &wk, const DevParams *dp, Groups groups, TxTiles tx,

@@ -285,7 +285,27 @@ prepare_all_kernel(NodeArrays nd, const DevParams *dp, const Geom *geom, Groups 
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int ng = groups.ngroups;
 
-    // the peers' records of this tick must have landed before anybody reads `rec`
+    // fused exchange: this rank's records go out first (16-byte stores over NVLink, a record per thread) ...
+    if (aux.push_local) {
+        for (int t = blockIdx.x * kPrepThreads + tid; t < aux.push_slots; t += gridDim.x * kPrepThreads) {
+            const uint4 *s = reinterpret_cast<const uint4 *>(aux.push_local + t);
+            const uint4 a = s[0], b = s[1], c = s[2];
+            for (int p = 0; p < aux.world; ++p) {
+                uint4 *d = reinterpret_cast<uint4 *>(aux.push_peer[p] + aux.push_off) + ((size_t)aux.push_rank * aux.push_slots + t) * 3;
+                d[0] = a; d[1] = b; d[2] = c;
+            }
+        }
+        __syncthreads();
+        if (tid == 0) {
+            __threadfence_system();
+            if (atomicAdd(aux.push_done, 1u) == gridDim.x - 1) {
+                *aux.push_done = 0u;
+                __threadfence_system();
+                for (int p = 0; p < aux.world; ++p) st_release_sys(reinterpret_cast<unsigned *>(aux.push_peer[p]) + aux.push_rank, aux.epoch);
+            }
+        }
+    }
+    // ... and the peers' records of this tick must have landed before anybody reads `rec`
     if (tid == 0) s_timeout = 0;
     __syncthreads();
     if (aux.peer_flags && tid < aux.world && !peer_wait(aux.peer_flags + tid, aux.epoch)) s_timeout = 1;
@@ -304,6 +324,7 @@ prepare_all_kernel(NodeArrays nd, const DevParams *dp, const Geom *geom, Groups 
         int4 *c4 = reinterpret_cast<int4 *>(aux.cnt);                    // n_work is a multiple of 1024
         for (int i = gtid; i < aux.n_work / 4; i += gsz) c4[i] = make_int4(0, 0, 0, 0);
         for (int i = gtid; i <= n_tx; i += gsz) aux.tx_cnt[i] = 0;
+        for (int i = gtid; i < aux.n_rx_done; i += gsz) aux.rx_done[i] = 0;
         if (gtid == 0) *ctr = Counters{};
     }
     __syncthreads();
@@ -419,9 +440,7 @@ int prepare_grid(int n_tx)
     // every SM takes one block: the tick's counters are zeroed by the whole grid, the per-transmission
     // double-precision pow() chains are latency bound and spread best thin
     (void)n_tx;
-    int dev = 0, sms = 148;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int sms = device_sms();
     return sms < kPrepMaxGrid ? sms : kPrepMaxGrid;
 }
 

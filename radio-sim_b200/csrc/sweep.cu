@@ -29,6 +29,7 @@
 // sum only ever holds weak far-field terms, and every decision is taken in double.
 #include "common.cuh"
 #include "kernels.h"
+#include "resolve_body.cuh"
 
 namespace rmb {
 
@@ -72,24 +73,30 @@ __device__ __forceinline__ f32x2 accumulate2(f32x2 d2, f32x2 acc, float neg_h)
 constexpr int kStage = 1024;          // tx per shared-memory stage (SoA: c, -x', -y', -z', theta)
 
 template <int MODE, bool PLANAR, int R, int THREADS>
-__global__ void __launch_bounds__(THREADS)
+__global__ void __launch_bounds__(THREADS, (THREADS == 128 && R == 4) ? 9 : 1)
 sweep_kernel(const float *__restrict__ fx, const float *__restrict__ fy, const float *__restrict__ fz,
              Groups groups, TxTiles tx, const float *__restrict__ theta, const float *__restrict__ theta_min_g,
              float neg_h, float *__restrict__ far_part, int *__restrict__ cnt, int *__restrict__ slots,
-             int K, int n_work)
+             int K, int n_work, int S, SweepFuse fuse)
 {
-    __shared__ __align__(16) float s_c[kStage], s_nx[kStage], s_ny[kStage], s_nz[PLANAR ? 4 : kStage], s_theta[kStage];
+    // one stage buffer, carved
+    __shared__ __align__(16) float s_stage[(PLANAR ? 4 : 5) * kStage];
+    float *const s_c = s_stage, *const s_nx = s_stage + kStage, *const s_ny = s_stage + 2 * kStage,
+          *const s_theta = s_stage + 3 * kStage, *const s_nz = s_stage + (PLANAR ? 0 : 4 * kStage);
 
-    const int w0 = (blockIdx.x * THREADS + threadIdx.x) * R;
+    // block = (rx block, tx split), splits of one rx block adjacent: receivers complete progressively
+    // over the launch, so the fused exact resolve runs in the shadow of the other blocks' sweeps
+    const int rb = blockIdx.x / S, split = blockIdx.x - rb * S;
+    const int w0 = (rb * THREADS + threadIdx.x) * R;
     // the block's receivers all belong to one channel group (groups are padded to 1024)
-    const int wb = blockIdx.x * THREADS * R;
+    const int wb = rb * THREADS * R;
     int g = 0;
     while (g + 1 < groups.ngroups && wb >= groups.w_begin[g + 1]) ++g;
 
-    // this block's share of the bucket: split blockIdx.y of gridDim.y, a multiple of kTile
+    // this block's share of the bucket: split `split` of S, a multiple of kTile
     const int b0 = tx.goff[g], b1 = tx.goff[g + 1];
-    const int per = ((b1 - b0 + (int)gridDim.y - 1) / (int)gridDim.y + kTile - 1) / kTile * kTile;
-    const int j_begin = min(b1, b0 + (int)blockIdx.y * per), j_end = min(b1, j_begin + per);
+    const int per = ((b1 - b0 + S - 1) / S + kTile - 1) / kTile * kTile;
+    const int j_begin = min(b1, b0 + split * per), j_end = min(b1, j_begin + per);
 
     float rx[R], ry[R], rz[R], sum[R];
     f32x2 X[R], Y[R], Z[R];
@@ -186,9 +193,32 @@ sweep_kernel(const float *__restrict__ fx, const float *__restrict__ fy, const f
             for (int r = 0; r < R; ++r) sum[r] = __fadd_rn(sum[r], s[r]);
         }
     }
-    float *out = far_part + (size_t)blockIdx.y * n_work + w0;
+    float *out = far_part + (size_t)split * n_work + w0;
 #pragma unroll
     for (int r = 0; r < R; ++r) out[r] = sum[r];
+
+    // ---- fused epilogue: the LAST split of an rx block to finish takes the exact decisions of its receivers
+    // (resolve_body.cuh) -- double-precision, latency-bound work on pipes the sweep leaves idle, hidden
+    // behind the other resident blocks instead of being a kernel of its own after the sweep.
+    // The rx blocks of the launch's final wave are left to the stand-alone resolve kernel: resolved here they would
+    // be a serial tail (R passes of a latency-bound routine in ~70 blocks, the rest of the GPU idle).
+    if (THREADS == 128 && fuse.enabled && rb < fuse.rb_fused) {
+        __shared__ int s_flag;
+        __syncthreads();
+        if (threadIdx.x == 0) { __threadfence(); s_flag = atomicAdd(&fuse.rx_done[rb], 1) == S - 1; }
+        __syncthreads();
+        if (s_flag) {
+            __threadfence();
+#pragma unroll 1
+            for (int q = 0; q < R; ++q)
+                resolve_receiver<true>(wb + q * THREADS + (int)threadIdx.x, fuse.wk, fuse.dp, tx, fuse.rec, fuse.sl, fuse.pr, fuse.ctr);
+            // the last rx block of the launch turns the per-packet heard counts into segment offsets
+            __syncthreads();
+            if (threadIdx.x == 0) { __threadfence(); s_flag = atomicAdd(&fuse.ctr->resolve_done, (unsigned)R) + R == (unsigned)(n_work / 128); }
+            __syncthreads();
+            if (s_flag) { __threadfence(); scan_tx_counts(fuse.pr.tx_cnt, fuse.n_tx, fuse.seg, fuse.ctr); }
+        }
+    }
 }
 
 // ---- host side: variant table, split planning, launch ---------------------------------------
@@ -221,6 +251,17 @@ static SweepVariant pick(int mode, bool planar, int variant)
     }
 }
 
+// resident blocks per SM of a variant (queried once per kernel: this sits on the tick's launch path)
+static int variant_occupancy(const SweepVariant &v)
+{
+    static const void *fn[64]; static int occ[64]; static int n = 0;
+    for (int i = 0; i < n; ++i) if (fn[i] == v.fn) return occ[i];
+    int o = 1;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, v.fn, v.threads, 0) != cudaSuccess || o < 1) { o = 1; cudaGetLastError(); }
+    if (n < 64) { fn[n] = v.fn; occ[n] = o; ++n; }
+    return o;
+}
+
 int sweep_mode_for_exponent(double n)
 {
     if (n == 2.0) return MODE_N2;
@@ -242,10 +283,7 @@ int sweep_plan(int mode, bool planar, int variant, int n_work, int n_tx_bucket, 
     const SweepVariant v = pick(mode, planar, variant);
     const int max_s = max(1, min(kMaxSplits, n_tx_bucket / kMinSplitTx));
     if (forced_splits > 0) return min(forced_splits, kMaxSplits);
-    int dev = 0, sms = 148, occ = 1;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, v.fn, v.threads, 0) != cudaSuccess || occ < 1) { occ = 1; cudaGetLastError(); }
+    const int sms = device_sms(), occ = variant_occupancy(v);
     const double slots = (double)sms * occ;
     const int rx_blocks = max(1, n_work / (v.R * v.threads));
     int best = 1; double best_eff = 0.0;
@@ -258,17 +296,34 @@ int sweep_plan(int mode, bool planar, int variant, int n_work, int n_tx_bucket, 
     return min(max_s, max(best, n_tx_bucket / kTargetSplitTx));
 }
 
-cudaError_t launch_sweep(int mode, bool planar, int variant, int n_work, int splits, const SweepArgs &a, cudaStream_t st)
+// number of leading rx blocks the sweep resolves itself (0: variant cannot fuse); the rest -- about the final wave of
+// the launch, with a margin -- goes to launch_resolve
+int sweep_fused_rx_blocks(int mode, bool planar, int variant, int n_work, int splits)
+{
+    const SweepVariant v = pick(mode, planar, variant);
+    if (v.threads != 128) return 0;
+    const int sms = device_sms(), occ = variant_occupancy(v);
+    const int nb = n_work / (v.R * v.threads);
+    const int tail = (int)ceil(1.25 * sms * occ / max(1, splits));
+    return max(0, nb - tail);
+}
+int sweep_block_rx(int mode, bool planar, int variant) { const SweepVariant v = pick(mode, planar, variant); return v.R * v.threads; }
+
+cudaError_t launch_sweep(int mode, bool planar, int variant, int n_work, int splits, const SweepArgs &a, const SweepFuse &fuse,
+                         cudaStream_t st)
 {
     if (n_work <= 0) return cudaSuccess;
     const SweepVariant v = pick(mode, planar, variant);
     SweepArgs b = a;
-    int nw = n_work;
+    SweepFuse f = fuse;
+    if (v.threads != 128) { f.enabled = 0; f.rb_fused = 0; }
+    int nw = n_work, S = max(1, splits);
     void *args[] = {(void *)&b.fx, (void *)&b.fy, (void *)&b.fz, (void *)&b.groups, (void *)&b.tx, (void *)&b.theta,
                     (void *)&b.theta_min_g, (void *)&b.neg_h, (void *)&b.far_part, (void *)&b.cnt, (void *)&b.slots,
-                    (void *)&b.K, (void *)&nw};
-    dim3 grid((unsigned)(n_work / (v.R * v.threads)), (unsigned)max(1, splits));
-    return cudaLaunchKernel(v.fn, grid, dim3((unsigned)v.threads), args, 0, st);
+                    (void *)&b.K, (void *)&nw, (void *)&S, (void *)&f};
+    const long long blocks = (long long)(n_work / (v.R * v.threads)) * S;
+    if (blocks > 0x7fffffffll) return cudaErrorInvalidConfiguration;
+    return cudaLaunchKernel(v.fn, dim3((unsigned)blocks), dim3((unsigned)v.threads), args, 0, st);
 }
 
 }  // namespace rmb

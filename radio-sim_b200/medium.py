@@ -183,6 +183,10 @@ class Medium:
     def tick_peers_enqueue(self):
         self._ck(self._lib.rmb_tick_peers_enqueue(self._h))
 
+    def peer_exchange_tick_enqueue(self, slots, d_records):
+        """Exchange + tick in one step (the preparation kernel pushes the records itself); asynchronous."""
+        self._ck(self._lib.rmb_peer_exchange_tick_enqueue(self._h, slots, C.c_void_p(d_records)))
+
     def tick_finish(self):
         """Settle an enqueued tick; counts only (fetch() downloads the lists)."""
         r = A.Result()

@@ -83,3 +83,29 @@ def test_peer_call_order_is_checked(rsb):
         assert r.n_tx == 3 and r.n_pairs > 0
         ref = m.tick(np.array([3, 7], dtype=np.int32))
         assert np.array_equal(r.rx, ref.rx) and np.array_equal(r.outcome, ref.outcome)
+
+
+def test_fused_exchange_in_the_preparation_kernel(rsb, orc):
+    """rmb_peer_exchange_tick_enqueue: the preparation kernel itself pushes the records, raises the flags and
+    waits.  Two cooperative kernels of one process do not run side by side on ONE device, so on this single-GPU
+    box the fused form is exercised with a world of one rank (push -> own gather buffer -> flag -> wait); with
+    one GPU per rank it is what bench.py --gpus N runs, checked there against the single-GPU pair count."""
+    import torch
+    n = 3000
+    x, y, z, ch = random_deployment(43, n, 500.0)
+    with rsb.Medium("sinr", f64_values=True) as m:
+        m.set_nodes(x, y, z, channel=ch)
+        m.peer_open([m.peer_export(1, 0, 128)])
+        for tick in range(3):
+            src = pick_sources(50 + tick, n, 70)
+            padded = np.concatenate([src[:40], [-1, -1], src[40:]]).astype(np.int32)      # padding keeps its arrival slot
+            rec = torch.zeros(padded.size * 48, dtype=torch.uint8, device="cuda")
+            m.build_tx_records(padded, rec.data_ptr())
+            m.peer_exchange_tick_enqueue(padded.size, rec.data_ptr())
+            counts = m.tick_finish()
+            res = m.fetch()
+            full = orc.tick(orc.params(orc.MODEL_SINR), orc.NodeSet(x, y, z, channel=ch), orc.make_packets(src, 0.0, 26))["pairs"]
+            assert counts.n_pairs == len(full["tx"])
+            slot_of = np.flatnonzero(padded >= 0)
+            assert np.array_equal(res.tx, slot_of[full["tx"]]) and np.array_equal(res.rx, full["rx"])
+            assert np.array_equal(res.outcome, full["outcome"]) and np.array_equal(res.rssi_dbm_f64, full["rssi_dbm"])

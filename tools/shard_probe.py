@@ -9,6 +9,7 @@ import bench
 
 G = int(sys.argv[1]) if len(sys.argv) > 1 else 8
 reps = int(sys.argv[2]) if len(sys.argv) > 2 else 20
+tuning = int(sys.argv[3], 0) if len(sys.argv) > 3 else 0
 N, T = bench.N_NODES, bench.N_TX
 x, y, src = bench.deployment()
 dev = torch.device("cuda", 0)
@@ -20,6 +21,7 @@ torch.cuda.synchronize()
 lo, hi = 0, N // G
 med = rsb.Medium("sinr", rx_base=lo, n_shards=G)
 med.set_nodes(x[lo:hi], y[lo:hi])
+med.set_tuning(tuning, 0)
 stream = torch.cuda.Stream(device=dev); torch.cuda.set_stream(stream); med.set_stream(stream.cuda_stream)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 rows = []
@@ -32,7 +34,7 @@ for i in range(reps):
     rows.append((e0.elapsed_time(e1) * 1e3, wall * 1e6, tm["ms_prepare"] * 1e3, tm["ms_sweep"] * 1e3, tm["ms_resolve"] * 1e3,
                  tm["ms_emit"] * 1e3, tm["ms_total"] * 1e3))
 rows = np.array(rows[3:])
-print("G", G, "pairs", r.n_pairs, "decisions", r.n_decisions, "launches", tm["kernel_launches"])
+print("G", G, "tuning", hex(tuning), "pairs", r.n_pairs, "decisions", r.n_decisions, "launches", tm["kernel_launches"])
 print("median us: events %.1f wall %.1f | prepare %.1f sweep %.1f resolve %.1f emit %.1f total %.1f" % tuple(np.median(rows, axis=0)))
 print("ideal sweep at 1/G of the 1-GPU launch: %.1f us" % (2418.0 / G))
 med.close()
