@@ -311,6 +311,149 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def run_c5(args):
+    """BASELINE configs[4]: 1M nodes on 16 channels (node i on 11 + i % 16), every node moves by (U-0.5, U-0.5) m per
+    tick (clamped to the area), 10k fresh sources per tick.  `value`: the tick alone, positions and tx records of the
+    tick already in HBM (the dense position upload and the record gather happen before the start event);
+    `e2e`: position upload from host arrays + tick with host packet lists in and host result lists out."""
+    import torch
+    import torch.distributed as dist
+    import radio_sim_b200 as rsb
+
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the medium has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    G = world
+    rng = np.random.default_rng(4)
+    x, y = rng.uniform(0, SIDE, N_NODES), rng.uniform(0, SIDE, N_NODES)
+    ch = (11 + np.arange(N_NODES) % 16).astype(np.int32)
+    lo, hi = rank * N_NODES // G, (rank + 1) * N_NODES // G
+    med = rsb.Medium("sinr", device=local, rx_base=lo, n_shards=G)
+    med.set_nodes(x[lo:hi], y[lo:hi], channel=ch[lo:hi])
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    med.set_stream(stream.cuda_stream)
+    max_slots = int(N_TX / G * 1.3) + 64
+    if G > 1:
+        blob = torch.frombuffer(bytearray(med.peer_export(G, rank, max_slots)), dtype=torch.uint8).to(dev)
+        blobs = torch.empty(G * blob.numel(), dtype=torch.uint8, device=dev)
+        dist.all_gather_into_tensor(blobs, blob)
+        raw = blobs.cpu().numpy().tobytes()
+        med.peer_open([raw[i * blob.numel():(i + 1) * blob.numel()] for i in range(G)])
+    rec_local = torch.zeros(max_slots * 48 if G > 1 else N_TX * 48, dtype=torch.uint8, device=dev)
+    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    tick_no = [0]
+
+    def next_tick():
+        """positions and sources of the next tick (every rank draws the same streams)"""
+        k = tick_no[0]; tick_no[0] += 1
+        r = np.random.default_rng(4 + 1 + k)
+        np.clip(x + r.uniform(-0.5, 0.5, N_NODES), 0.0, SIDE, out=x)
+        np.clip(y + r.uniform(-0.5, 0.5, N_NODES), 0.0, SIDE, out=y)
+        src = r.permutation(N_NODES)[:N_TX].astype(np.int32)
+        if G == 1:
+            return src, src, N_TX
+        counts = [int(((src >= q * N_NODES // G) & (src < (q + 1) * N_NODES // G)).sum()) for q in range(G)]
+        tpad = max(counts)
+        mine = np.full(tpad, -1, dtype=np.int32)
+        m = src[(src >= lo) & (src < hi)]
+        mine[:m.size] = m
+        return src, mine, tpad
+
+    def timed(kind, steps, sampler=None):
+        times, dec, pairs, sweep_ms, launches = [], 0, 0, [], 0
+        for _ in range(steps):
+            src, mine, tpad = next_tick()
+            if kind == "resident":
+                med.update_positions(x[lo:hi], y[lo:hi])
+                med.build_tx_records(mine, rec_local.data_ptr())
+            flush_buf.fill_(1)
+            torch.cuda.synchronize()
+            if G > 1:
+                dist.barrier()
+                torch.cuda.synchronize()
+            if sampler:
+                sampler.active = True
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0 = time.perf_counter()
+            e0.record(stream)
+            if kind == "resident":
+                if G == 1:
+                    med.tick_enqueue(N_TX, rec_local.data_ptr())
+                else:
+                    med.peer_exchange_tick_enqueue(tpad, rec_local.data_ptr())
+            else:
+                med.update_positions(x[lo:hi], y[lo:hi])
+                if G == 1:
+                    res = med.tick(src, copy=False)
+                else:
+                    med.peer_push(mine)
+                    res = med.tick_peers(copy=False)
+            e1.record(stream)
+            torch.cuda.synchronize()
+            wall = time.perf_counter() - t0
+            if sampler:
+                sampler.active = False
+            if kind == "resident":
+                res = med.tick_finish()
+                times.append(e0.elapsed_time(e1) * 1e-3)
+            else:
+                times.append(wall)
+            tm = med.timing()
+            dec += res.n_decisions; pairs += res.n_pairs
+            sweep_ms.append(tm["ms_sweep"]); launches += tm["kernel_launches"]
+        return times, dec, pairs, sweep_ms, launches
+
+    sampler = ClockSampler(local)
+    sampler.period = 0.0003            # the timed windows are ~0.3 ms
+    sampler.start()
+    timed("resident", args.warmup)
+    times, dec, _, sweep_ms, launches = timed("resident", args.steps, sampler)
+    timed("e2e", max(1, args.warmup // 2))
+    e_times, e_dec, e_pairs, _, _ = timed("e2e", args.steps)
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+    tot = torch.tensor([sum(times), sum(e_times)], dtype=torch.float64, device=dev)
+    cnt = torch.tensor([float(dec), float(e_dec), float(e_pairs)], dtype=torch.float64, device=dev)
+    if G > 1:
+        dist.all_reduce(tot, op=dist.ReduceOp.MAX)
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+    if rank == 0:
+        clocks = sampler.summary()
+        f_max = (clocks["sm_max_mhz"] or 1965.0) * 1e6
+        ms_sweep = float(np.mean(sweep_ms))
+        achieved = dec / args.steps / (ms_sweep * 1e-3)
+        peak = SMS * XU_LANES * f_max
+        line = {"metric": METRIC, "value": float(cnt[0]) / float(tot[0]), "unit": UNIT, "n_gpus": G, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": 1e3 * float(tot[0]) / args.steps, "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f32+f64", "data": "synthetic",
+                "config": {"workload": "1M-node 16-channel 802.15.4 deployment, per-tick mobility of every node, 10k fresh "
+                                       "transmitters per tick (BASELINE configs[4])", "nodes": N_NODES, "transmitters": N_TX,
+                           "channels": 16, "parallelism": f"receivers sharded x{G}",
+                           "l2": "flushed (256 MiB write) before every timed step",
+                           "timing": "value: CUDA events around the enqueued tick (positions and records of the tick "
+                                     "resident); e2e: host wall clock around position upload + tick with host lists"},
+                "clocks": clocks,
+                "e2e": {"value": float(cnt[1]) / float(tot[1]), "unit": UNIT, "ms_per_step": 1e3 * float(tot[1]) / args.steps,
+                        "h2d_bytes_per_step": int(16 * (hi - lo) + 4 * N_TX / G), "d2h_bytes_per_step": int(17 * float(cnt[2]) / args.steps / G),
+                        "heard_pairs_per_tick": float(cnt[2]) / args.steps},
+                "gpu_launches": int(launches),
+                "roofline": {"bound": "sfu", "kernel": "sweep_kernel", "achieved": achieved / 1e9, "peak": peak / 1e9,
+                             "unit": "G MUFU-op/s (1 rsqrt per decision; peak = 148 SM x 16 lanes x sm_max_mhz)",
+                             "frac": achieved / peak, "ms_per_launch": ms_sweep, "traffic": None},
+                "cpu_baseline": None}
+        print(json.dumps(line), flush=True)
+    med.close()
+    if G > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -320,11 +463,15 @@ def main():
     ap.add_argument("--grid", action="store_true", help="1000x1000 grid deployment (10 m pitch) instead of random")
     ap.add_argument("--variant", type=int, default=0, help="sweep kernel variant (tuning)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--workload", default="c4", choices=["c4", "c5"],
+                    help="c4 = BASELINE configs[3] (the metric's workload, default); c5 = configs[4], 16 channels + mobility")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"], help="N>1: how the tick's tx records travel")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "c5":
+        run_c5(args)
     else:
         run_ours(args)
 
