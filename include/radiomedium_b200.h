@@ -173,6 +173,23 @@ int rmb_tick_records(rmb_handle *h, int32_t n_tx, const void *d_records,
  * (out gets counts only, pointers NULL).  rmb_fetch downloads the lists afterwards. */
 int rmb_tick_resident(rmb_handle *h, int32_t n_tx, const void *d_records, rmb_result *out);
 int rmb_fetch(rmb_handle *h, rmb_result *out);
+/* Stochastic reception (rx-loss / tx-loss < 1) when the receivers are sharded over several handles.  The
+ * reference draws from ONE java.util.Random in a global order -- per packet the tx draw, then one draw per
+ * receiver that needs it in node-array order (UDGMRadioMedium.java:85-92,104-111) -- so a shard has to know
+ * how many draws the shards before it make for every packet:
+ *   rmb_tick_draws_begin  evaluates the tick up to the draw flags and writes, to DEVICE memory, the draws this
+ *                         shard's receivers would make per record (int32[n_tx]);
+ *   (the caller all-gathers these: all_counts[world][n_tx], shards in node-index order)
+ *   rmb_tick_draws_end    walks the global sequence -- every shard evaluates every tx draw, identically -- and
+ *                         finishes the tick; `uniforms` is the SAME host-supplied stream on every shard, and
+ *                         n_uniforms_used is the global count.  d_order (DEVICE int32[n_order], may be NULL =
+ *                         as stored): the record positions in the tick's original packet arrival order -- an
+ *                         exchanged record list is grouped by owner rank, the reference draws in arrival order.
+ * Works on an unsharded handle too (world = 1).  SINR medium only. */
+int rmb_tick_draws_begin(rmb_handle *h, int32_t n_tx, const void *d_records, int32_t *d_counts_out);
+int rmb_tick_draws_end(rmb_handle *h, const int32_t *d_all_counts, int32_t world, int32_t rank,
+                       const int32_t *d_order, int32_t n_order,
+                       const double *uniforms, size_t n_uniforms, rmb_result *out);
 /* Asynchronous form: rmb_tick_enqueue puts the whole tick on the handle's stream and returns at once
  * (d_records must stay valid until the tick is settled); rmb_tick_finish waits for it and returns the
  * counts (pointers NULL; rmb_fetch downloads the lists).  Any other call on the handle settles an
@@ -207,6 +224,7 @@ int rmb_peer_push_records(rmb_handle *h, int32_t slots, const void *d_records);
 int rmb_tick_peers(rmb_handle *h, const double *uniforms, size_t n_uniforms, rmb_result *out);
 int rmb_tick_peers_resident(rmb_handle *h, rmb_result *out);   /* results stay on the device, see rmb_fetch */
 int rmb_tick_peers_enqueue(rmb_handle *h);                     /* asynchronous, settled by rmb_tick_finish */
+int rmb_tick_peers_draws_begin(rmb_handle *h, int32_t *d_counts_out);   /* rmb_tick_draws_begin on the gathered records */
 /* rmb_peer_push_records + rmb_tick_peers_enqueue as ONE step: the tick's first kernel stores this rank's
  * records into the peers' buffers, raises the flags and then waits for the peers' -- exchange and the
  * preparation that consumes it in a single launch.  Asynchronous; every rank must call it for the tick.

@@ -117,6 +117,10 @@ struct rmb_handle {
     } peer;
     const unsigned *wait_flags = nullptr; unsigned wait_epoch = 0; int wait_world = 0;   // set around compute() by rmb_tick_peers
     const rmb_tx_record *fused_push = nullptr;   // rmb_peer_exchange_tick_enqueue: the preparation kernel pushes these itself
+    // stochastic reception on sharded receivers (rmb_tick_draws_begin / _end): the tick stops after the draw flags,
+    // the host side gathers the per-packet draw counts of all shards, the second half walks the global sequence
+    int32_t *split_counts = nullptr;      // non-null while compute() runs for rmb_tick_draws_begin
+    struct Split { bool active = false; int n_tx = 0; long long m = 0; const rmb_tx_record *rec = nullptr; int launches = 0, sweeps = 0; } split;
     // asynchronous tick (rmb_tick_enqueue / rmb_tick_peers_enqueue): enqueued, counters not looked at yet
     bool async_mode = false, pending = false;
     struct Pending { int n_tx = 0; const rmb_tx_record *rec = nullptr; const unsigned *flags = nullptr; unsigned epoch = 0; int world = 0;
@@ -680,9 +684,14 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
     int launches = 0, sweeps = 0;
     const NodeArrays nd = node_arrays(h);
     const WorkArrays wk = work_arrays(h);
-    const bool draws = h->maybe_draws;
-    if (draws && h->cfg.n_shards > 1)
-        return h->fail(RMB_ERR_UNSUPPORTED, "stochastic reception (rx/tx probability < 1) is not supported on a sharded handle");
+    // a shard takes the stochastic path whenever the split API is used: a packet's source may sit on another shard
+    const bool draws = h->maybe_draws || h->split_counts != nullptr;
+    if (draws && h->cfg.n_shards > 1 && !h->split_counts)
+        return h->fail(RMB_ERR_UNSUPPORTED, "stochastic reception (rx/tx probability < 1) on sharded receivers needs "
+                                            "rmb_tick_draws_begin / rmb_tick_draws_end (the draw order is global)");
+    if (h->split_counts && h->cfg.model != RMB_MODEL_SINR)
+        return h->fail(RMB_ERR_UNSUPPORTED, "rmb_tick_draws_begin exists for the SINR medium only");
+    h->split.active = false;
     RMB_CK(h, h->seg.ensure((size_t)n_tx + 2)); RMB_CK(h, h->tx_base.ensure((size_t)n_tx + 1));
     RMB_CK(h, h->tx_failed.ensure((size_t)n_tx + 1));
     long long nu = 0;
@@ -825,6 +834,13 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
         if (draws) {
             pa.key = h->key_alt.p;         // sorted keys for the draw-order stage (the bucket items are dead by now)
             RMB_CK(h, launch_emit_sinr(nd, h->dp.p, d_rec, n_tx, pr, h->val.p, pa, m, true, h->ctr.p, nullptr, h->st));
+            if (h->split_counts) {
+                RMB_CK(h, launch_emit_draw_prepare(n_tx, pa, m, h->split_counts, h->st));
+                h->split.active = true; h->split.n_tx = n_tx; h->split.m = m; h->split.rec = d_rec;
+                h->split.launches = launches + 6; h->split.sweeps = sweeps;
+                if (h->st == h->own_st) RMB_CK(h, cudaStreamSynchronize(h->st));    // the caller gathers the counts on another stream
+                return RMB_OK;
+            }
             RMB_CK(h, launch_emit(h->dp.p, d_rec, n_tx, pa, m, true, h->uniforms.p, nu, h->ctr.p, h->st));
             launches += 7;
         }
@@ -978,6 +994,52 @@ int rmb_fetch(rmb_handle *h, rmb_result *out)
     RMB_SETTLE(h);
     RMB_CK(h, cudaSetDevice(h->cfg.device));
     return download(h, out);
+}
+
+// ---- stochastic reception on sharded receivers ------------------------------------------------------
+int rmb_tick_draws_begin(rmb_handle *h, int32_t n_tx, const void *d_records, int32_t *d_counts_out)
+{
+    if (!h) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    RMB_SETTLE(h);
+    if (!h->have_nodes) return h->fail(RMB_ERR_STATE, "rmb_tick_draws_begin before rmb_set_nodes");
+    if (n_tx < 0 || (n_tx > 0 && (!d_records || !d_counts_out))) return h->fail(RMB_ERR_INVALID, "rmb_tick_draws_begin: bad arguments");
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    int32_t dummy = 0;
+    h->split_counts = d_counts_out ? d_counts_out : &dummy;
+    const int rc = compute(h, n_tx, (const rmb_tx_record *)d_records, nullptr, 0);
+    h->split_counts = nullptr;
+    return rc;
+}
+
+int rmb_tick_draws_end(rmb_handle *h, const int32_t *d_all_counts, int32_t world, int32_t rank,
+                       const int32_t *d_order, int32_t n_order,
+                       const double *uniforms, size_t n_uniforms, rmb_result *out)
+{
+    if (!h || !out) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (!h->split.active) return h->fail(RMB_ERR_STATE, "rmb_tick_draws_end without rmb_tick_draws_begin");
+    if (world < 1 || rank < 0 || rank >= world || (h->split.n_tx > 0 && !d_all_counts) || n_order < 0 || n_order > h->split.n_tx)
+        return h->fail(RMB_ERR_INVALID, "rmb_tick_draws_end: bad arguments");
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    h->split.active = false;
+    long long nu = 0;
+    if (uniforms && n_uniforms) {
+        RMB_CK(h, h->uniforms.ensure(n_uniforms));
+        RMB_CK(h, cudaMemcpyAsync(h->uniforms.p, uniforms, n_uniforms * sizeof(double), cudaMemcpyHostToDevice, h->st));
+        nu = (long long)n_uniforms;
+    }
+    PairArrays pa = pair_arrays(h);
+    pa.key = h->key_alt.p;
+    RMB_CK(h, launch_emit_draw_finish(h->dp.p, h->split.rec, h->split.n_tx, pa, h->split.m, h->uniforms.p, nu, h->ctr.p,
+                                      d_all_counts, world, rank, d_order, n_order, h->st));
+    RMB_CK(h, cudaEventRecord(h->ev[4], h->st));
+    int rc = read_counters(h);
+    if (rc) return rc;
+    rc = publish(h, h->split.n_tx, h->split.m, true, h->split.launches + 2, h->split.sweeps);
+    if (rc && rc != RMB_ERR_UNIFORMS) return rc;
+    const int rc2 = download(h, out);
+    return rc2 ? rc2 : rc;
 }
 
 // ---- asynchronous tick ---------------------------------------------------------------------------
@@ -1143,6 +1205,19 @@ int rmb_tick_peers_enqueue(rmb_handle *h)
     h->async_mode = true;
     const int rc = tick_peers_locked(h, nullptr, 0);
     h->async_mode = false;
+    return rc;
+}
+
+int rmb_tick_peers_draws_begin(rmb_handle *h, int32_t *d_counts_out)
+{
+    if (!h) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    RMB_SETTLE(h);
+    if (!d_counts_out) return h->fail(RMB_ERR_INVALID, "rmb_tick_peers_draws_begin: null counts");
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    h->split_counts = d_counts_out;
+    const int rc = tick_peers_locked(h, nullptr, 0);
+    h->split_counts = nullptr;
     return rc;
 }
 

@@ -250,21 +250,40 @@ __global__ void txfail_det_kernel(const DevParams *dp, const rmb_tx_record *rec,
 // The draw order is inherently sequential over packets (whether packet t consumes its
 // receivers' uniforms depends on its own tx draw).  One block: all threads stage a chunk of
 // per-packet (p_tx, draws) into shared memory, thread 0 walks it.
+// Sharded receivers: all_counts[g][t] = draws the receivers of shard g would make for packet t (every shard's
+// per-packet counts, gathered by the host side); a packet's draws are laid out tx draw, shard 0, shard 1, ...
+// as in the unsharded node order, and every shard walks the same global sequence.  all_counts == nullptr:
+// unsharded, the counts come from this handle's own scan.
 __global__ void __launch_bounds__(1024)
 txloop_kernel(const DevParams *dp, const rmb_tx_record *rec, int n_tx, const int *seg, const int *draw_scan,
-              const double *uniforms, long long n_uniforms, uint8_t *failed, long long *base, Counters *ctr)
+              const double *uniforms, long long n_uniforms, uint8_t *failed, long long *base, Counters *ctr,
+              const int *all_counts, int world, int rank, const int *order, int n_order)
 {
+    // order (may be null): the records in the tick's ORIGINAL packet arrival order -- the gathered record list of
+    // a sharded tick is grouped by owner rank, but the reference draws packet by packet as they arrived
+    __shared__ int s_before[1024], s_t[1024];
+    const int n_rec = n_tx;
+    if (order) n_tx = n_order;
     __shared__ double s_ptx[1024];
     __shared__ int s_draws[1024];
     __shared__ long long s_u;
     __shared__ int s_short;
     if (threadIdx.x == 0) { s_u = 0; s_short = 0; }
     for (int c0 = 0; c0 < n_tx; c0 += 1024) {
-        const int t = c0 + threadIdx.x;
-        if (t < n_tx) {
+        const int k = c0 + threadIdx.x;
+        if (k < n_tx) {
+            const int t = order ? order[k] : k;
+            s_t[threadIdx.x] = t;
             const rmb_tx_record r = rec[t];
             s_ptx[threadIdx.x] = r.src >= 0 ? tx_success(dp, r) : 1.0;
-            s_draws[threadIdx.x] = draw_scan[seg[t + 1]] - draw_scan[seg[t]];
+            if (all_counts) {
+                int tot = 0, before = 0;
+                for (int g = 0; g < world; ++g) { const int c = all_counts[(size_t)g * n_rec + t]; if (g < rank) before += c; tot += c; }
+                s_draws[threadIdx.x] = tot; s_before[threadIdx.x] = before;
+            } else {
+                s_draws[threadIdx.x] = draw_scan[seg[t + 1]] - draw_scan[seg[t]];
+                s_before[threadIdx.x] = 0;
+            }
         }
         __syncthreads();
         if (threadIdx.x == 0) {
@@ -281,8 +300,8 @@ txloop_kernel(const DevParams *dp, const rmb_tx_record *rec, int n_tx, const int
                     ++u;
                     if (uu > ptx) f = 1;
                 }
-                failed[c0 + i] = (uint8_t)f;
-                base[c0 + i] = u;
+                failed[s_t[i]] = (uint8_t)f;
+                base[s_t[i]] = u + s_before[i];
                 if (!f) u += s_draws[i];
             }
             s_u = u; s_short = sh;
@@ -331,23 +350,51 @@ __global__ void finalize_kernel(PairArrays pa, long long n, bool stochastic, con
     }
 }
 
+// draws the local receivers of packet t would make if the packet does not fail
+__global__ void draw_counts_kernel(const int *seg, const int *draw_scan, int n_tx, int *counts)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < n_tx) counts[t] = draw_scan[seg[t + 1]] - draw_scan[seg[t]];
+}
+
+// stochastic rule, first half: segments, draw flags and their scan; optionally the per-packet draw counts
+cudaError_t launch_emit_draw_prepare(int n_tx, PairArrays pa, long long n, int *counts_out, cudaStream_t st)
+{
+    if (n_tx <= 0) return cudaSuccess;
+    seg_kernel<<<(n_tx + 1 + 255) / 256, 256, 0, st>>>(pa.key, n, n_tx, pa.key_shift, pa.seg);
+    if (n > 0) drawflag_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(pa.cand, pa.p, n, pa.draw_scan);
+    // in-place exclusive scan (n+1 entries)
+    cudaError_t e = launch_exclusive_scan(pa.draw_scan, pa.draw_scan, (int)n, pa.scan_tmp, nullptr, st);
+    if (e != cudaSuccess) return e;
+    if (counts_out) draw_counts_kernel<<<(n_tx + 255) / 256, 256, 0, st>>>(pa.seg, pa.draw_scan, n_tx, counts_out);
+    return cudaGetLastError();
+}
+
+// second half: the sequential walk over the packets (tx draws, bases) and the per-pair outcomes
+cudaError_t launch_emit_draw_finish(const DevParams *dp, const rmb_tx_record *rec, int n_tx, PairArrays pa, long long n,
+                                    const double *uniforms, long long n_uniforms, Counters *ctr,
+                                    const int *all_counts, int world, int rank, const int *order, int n_order,
+                                    cudaStream_t st)
+{
+    if (n_tx <= 0) return cudaSuccess;
+    txloop_kernel<<<1, 1024, 0, st>>>(dp, rec, n_tx, pa.seg, pa.draw_scan, uniforms, n_uniforms, pa.tx_failed,
+                                      pa.tx_base, ctr, all_counts, world, rank, order, n_order);
+    if (n > 0)
+        finalize_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(pa, n, true, uniforms, n_uniforms, ctr);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_emit(const DevParams *dp, const rmb_tx_record *rec, int n_tx, PairArrays pa, long long n,
                         bool stochastic, const double *uniforms, long long n_uniforms, Counters *ctr, cudaStream_t st)
 {
     if (n_tx <= 0) return cudaSuccess;
     if (stochastic) {
-        seg_kernel<<<(n_tx + 1 + 255) / 256, 256, 0, st>>>(pa.key, n, n_tx, pa.key_shift, pa.seg);
-        if (n > 0) drawflag_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(pa.cand, pa.p, n, pa.draw_scan);
-        // in-place exclusive scan (n+1 entries)
-        cudaError_t e = launch_exclusive_scan(pa.draw_scan, pa.draw_scan, (int)n, pa.scan_tmp, nullptr, st);
-        if (e != cudaSuccess) return e;
-        txloop_kernel<<<1, 1024, 0, st>>>(dp, rec, n_tx, pa.seg, pa.draw_scan, uniforms, n_uniforms, pa.tx_failed,
-                                          pa.tx_base, ctr);
-    } else {
-        txfail_det_kernel<<<(n_tx + 255) / 256, 256, 0, st>>>(dp, rec, n_tx, pa.tx_failed, pa.tx_base);
+        RMB_CUDA_OK(launch_emit_draw_prepare(n_tx, pa, n, nullptr, st));
+        return launch_emit_draw_finish(dp, rec, n_tx, pa, n, uniforms, n_uniforms, ctr, nullptr, 1, 0, nullptr, 0, st);
     }
+    txfail_det_kernel<<<(n_tx + 255) / 256, 256, 0, st>>>(dp, rec, n_tx, pa.tx_failed, pa.tx_base);
     if (n > 0)
-        finalize_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(pa, n, stochastic, uniforms, n_uniforms, ctr);
+        finalize_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(pa, n, false, uniforms, n_uniforms, ctr);
     return cudaGetLastError();
 }
 

@@ -160,6 +160,15 @@ cudaError_t launch_emit(const DevParams *dp, const rmb_tx_record *rec, int n_tx,
                         bool stochastic, const double *uniforms, long long n_uniforms, Counters *ctr,
                         cudaStream_t st);
 
+// the stochastic rule in two halves, for receivers sharded over several handles: every shard reports the draws
+// its receivers would make per packet (counts_out[n_tx]), the host side gathers them (all_counts[world][n_tx]),
+// and every shard then walks the same global uniform sequence.  all_counts == nullptr: unsharded.
+cudaError_t launch_emit_draw_prepare(int n_tx, PairArrays pa, long long n, int *counts_out, cudaStream_t st);
+cudaError_t launch_emit_draw_finish(const DevParams *dp, const rmb_tx_record *rec, int n_tx, PairArrays pa, long long n,
+                                    const double *uniforms, long long n_uniforms, Counters *ctr,
+                                    const int *all_counts, int world, int rank, const int *order, int n_order,
+                                    cudaStream_t st);   // order: records in original packet arrival order (null = as stored)
+
 // ---- K2: the reference media (Null / UDGM / UDGMConstantLoss / N2N), exact double --------------
 cudaError_t launch_refmedia_count(const NodeArrays &nd, const DevParams *dp, const double *matrix, int matrix_n,
                                   int n_tx, const rmb_tx_record *rec, int *blkcnt, Counters *ctr, cudaStream_t st);

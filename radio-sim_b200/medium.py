@@ -176,6 +176,27 @@ class Medium:
         self._ck(self._lib.rmb_tick_resident(self._h, n_tx, C.c_void_p(d_records), C.byref(r)))
         return TickResult(r, False, True)
 
+    # -- stochastic reception on sharded receivers (global draw order) ----------------------------------
+    def tick_draws_begin(self, n_tx, d_records, d_counts):
+        """First half: writes this shard's per-record draw counts (int32[n_tx]) to DEVICE memory d_counts."""
+        self._ck(self._lib.rmb_tick_draws_begin(self._h, n_tx, C.c_void_p(d_records), C.c_void_p(d_counts)))
+
+    def tick_peers_draws_begin(self, d_counts):
+        self._ck(self._lib.rmb_tick_peers_draws_begin(self._h, C.c_void_p(d_counts)))
+
+    def tick_draws_end(self, d_all_counts, world, rank, uniforms, d_order=0, n_order=0, copy=True, allow_short_uniforms=False):
+        """Second half: d_all_counts = int32[world][n_tx] on the device (all shards' counts, rank order); d_order =
+        device int32[n_order], the record positions in original packet arrival order (0 = as stored)."""
+        uniforms = _arr(uniforms, np.float64)
+        r = A.Result()
+        rc = self._lib.rmb_tick_draws_end(self._h, C.c_void_p(d_all_counts), world, rank, C.c_void_p(d_order or None), n_order,
+                                          _ptr(uniforms, C.c_double),
+                                          0 if uniforms is None else uniforms.shape[0], C.byref(r))
+        self._ck(rc, allow=(A.ERR_UNIFORMS,) if allow_short_uniforms else ())
+        res = TickResult(r, self._f64, copy)
+        res.status = rc
+        return res
+
     def tick_enqueue(self, n_tx, d_records):
         """Asynchronous tick on records resident in HBM: returns as soon as the work is on the stream."""
         self._ck(self._lib.rmb_tick_enqueue(self._h, n_tx, C.c_void_p(d_records)))

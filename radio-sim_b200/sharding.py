@@ -39,6 +39,11 @@ class TickPlan:
             self.local_packet.append(mine)
             self.packet_of[r * self.tpad: r * self.tpad + mine.size] = mine
 
+        # original packet k -> its position in the gathered list (the order the reference's draws follow)
+        self.order = np.zeros(src.size, dtype=np.int32)
+        valid = np.flatnonzero(self.packet_of >= 0)
+        self.order[self.packet_of[valid]] = valid
+
     def local_fields(self, rank, values, fill):
         """Per-packet values (power, channel) re-ordered for rank's padded local list."""
         out = np.full(self.tpad, fill, dtype=np.asarray(values).dtype)

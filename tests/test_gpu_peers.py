@@ -109,3 +109,61 @@ def test_fused_exchange_in_the_preparation_kernel(rsb, orc):
             slot_of = np.flatnonzero(padded >= 0)
             assert np.array_equal(res.tx, slot_of[full["tx"]]) and np.array_equal(res.rx, full["rx"])
             assert np.array_equal(res.outcome, full["outcome"]) and np.array_equal(res.rssi_dbm_f64, full["rssi_dbm"])
+
+
+@pytest.mark.parametrize("world", [1, 3])
+def test_stochastic_reception_on_sharded_receivers_follows_the_global_draw_order(rsb, orc, world):
+    """rx-loss / tx-loss < 1 with the receivers sharded: rmb_tick_draws_begin -> gather of the per-packet draw
+    counts -> rmb_tick_draws_end; outcomes, tx failures and the number of uniforms consumed must equal the
+    oracle's unsharded tick fed with the same java.util.Random(42) stream."""
+    import torch
+    from radio_sim_b200.sharding import shard_bounds, TickPlan, merge_results
+    n, t = 2400, 140
+    x, y, z, ch = random_deployment(61, n, 650.0)
+    rng = np.random.default_rng(61)
+    rxprob = np.where(rng.uniform(size=n) < 0.5, 0.9, 1.0); rxprob[::50] = 0.0
+    txprob = np.where(rng.uniform(size=n) < 0.3, 0.8, 1.0); txprob[::97] = 0.0
+    if world > 1:
+        rxprob[:n // world] = 1.0                  # shard 0 alone would see no probability < 1: it still has to follow
+    u = orc.jrandom_doubles(42, 100000)
+    bounds = shard_bounds(n, world)
+    meds = []
+    for r, (lo, hi) in enumerate(bounds):
+        m = rsb.Medium("sinr", f64_values=True, rx_base=lo, n_shards=world)
+        m.set_nodes(x[lo:hi], y[lo:hi], z[lo:hi], channel=ch[lo:hi], rxprob=rxprob[lo:hi], txprob=txprob[lo:hi])
+        meds.append(m)
+    blobs = [m.peer_export(world, r, 256) for r, m in enumerate(meds)]
+    for m in meds:
+        m.peer_open(blobs)
+    try:
+        for tick in range(2):
+            src = pick_sources(61 + tick, n, t)
+            plan = TickPlan(src, bounds)
+            n_rec = world * plan.tpad
+            for r, m in enumerate(meds):
+                m.peer_push(plan.local_src[r])
+            counts = torch.zeros(world * n_rec, dtype=torch.int32, device="cuda")      # [world][n_rec], "all-gathered" in place
+            for r, m in enumerate(meds):
+                m.tick_peers_draws_begin(counts.data_ptr() + 4 * r * n_rec)
+            order = torch.from_numpy(plan.order).cuda()
+            torch.cuda.synchronize()
+            parts, used, failed = [], [], []
+            for r, m in enumerate(meds):
+                res = m.tick_draws_end(counts.data_ptr(), world, r, u, d_order=order.data_ptr(), n_order=t)
+                parts.append(dict(tx=res.tx, rx=res.rx, outcome=res.outcome, rssi=res.rssi_dbm_f64))
+                used.append(res.n_uniforms_used); failed.append(res.tx_failed.copy())
+            merged = merge_results(plan, parts)
+            ref = orc.tick(orc.params(orc.MODEL_SINR), orc.NodeSet(x, y, z, channel=ch, rxprob=rxprob, txprob=txprob),
+                           orc.make_packets(src, 0.0, 26), uniforms=u)
+            full = ref["pairs"]
+            assert ref["n_uniforms_used"] > 50 and ref["tx_failed"].sum() > 0
+            assert all(v == ref["n_uniforms_used"] for v in used)
+            valid = np.flatnonzero(plan.packet_of >= 0)
+            for f in failed:                            # every shard walks the same tx draws
+                got = np.zeros(t, dtype=np.uint8); got[plan.packet_of[valid]] = f[valid]
+                assert np.array_equal(got, ref["tx_failed"])
+            assert np.array_equal(merged["tx"], full["tx"]) and np.array_equal(merged["rx"], full["rx"])
+            assert np.array_equal(merged["outcome"], full["outcome"]) and np.array_equal(merged["rssi"], full["rssi_dbm"])
+    finally:
+        for m in meds:
+            m.close()
