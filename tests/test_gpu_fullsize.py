@@ -1,0 +1,88 @@
+"""-m gpu: BASELINE's larger configurations.  configs[2] (100k nodes x 1k tx) is still within the oracle's
+reach (1e8 pairs, a few seconds on the host threads) and is compared pair for pair; configs[3] (1M x 10k) is
+checked through size-independent properties: the decision count is the closed-form number of filter-passing
+pairs, the receiver-sharded tick (2 shards exchanging their records over peer memory) reproduces the unsharded
+lists exactly, a second identical tick is bit-identical (determinism of the atomically appended candidates),
+and a sample of receivers agrees with the oracle evaluated on those receivers alone against all 10k packets."""
+import numpy as np
+import pytest
+from helpers import compare, SINR_TOL_DB
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def rsb():
+    import radio_sim_b200
+    return radio_sim_b200
+
+
+def test_config3_100k_nodes_1k_tx_against_the_oracle(rsb, orc):
+    rng = np.random.default_rng(2)
+    n, t, side = 100_000, 1_000, 3162.0
+    x, y = rng.uniform(0, side, n), rng.uniform(0, side, n)
+    src = rng.permutation(n)[:t].astype(np.int32)
+    with rsb.Medium("sinr", f64_values=True) as m:
+        m.set_nodes(x, y)
+        r = m.tick(src)
+    ref = orc.tick(orc.params(orc.MODEL_SINR), orc.NodeSet(x, y), orc.make_packets(src, 0.0, 26), threads=16)
+    assert ref["n_pairs"] > 100_000
+    compare(r, ref)
+
+
+def test_config4_1m_nodes_10k_tx_properties(rsb, orc):
+    from radio_sim_b200.sharding import shard_bounds, TickPlan, merge_results
+    rng = np.random.default_rng(3)
+    n, t, side = 1_000_000, 10_000, 10_000.0
+    x, y = rng.uniform(0, side, n), rng.uniform(0, side, n)
+    src = rng.permutation(n)[:t].astype(np.int32)
+    with rsb.Medium("sinr", f64_values=True) as m:
+        m.set_nodes(x, y)
+        a = m.tick(src)
+        b = m.tick(src)
+    assert a.n_decisions == t * (n - 1)                       # one channel, everyone enabled: every pair but (src, src)
+    assert a.n_pairs == a.n_delivered + a.n_interfered and a.n_pairs > 1_000_000
+    for k in ("tx", "rx", "outcome", "rssi_dbm_f64", "sinr_db_f64"):
+        assert np.array_equal(getattr(a, k), getattr(b, k)), k
+    order = np.lexsort((a.rx, a.tx))
+    assert np.array_equal(order, np.arange(a.n_pairs))        # sorted by (packet, node index), no duplicates
+    assert np.all((np.diff(a.tx) > 0) | (np.diff(a.rx) > 0))
+
+    # receiver-sharded over two handles (same GPU), records exchanged over peer memory
+    bounds = shard_bounds(n, 2)
+    plan = TickPlan(src, bounds)
+    meds = []
+    for r, (lo, hi) in enumerate(bounds):
+        s = rsb.Medium("sinr", f64_values=True, rx_base=lo, n_shards=2)
+        s.set_nodes(x[lo:hi], y[lo:hi])
+        meds.append(s)
+    blobs = [s.peer_export(2, r, plan.tpad) for r, s in enumerate(meds)]
+    parts = []
+    try:
+        for s in meds:
+            s.peer_open(blobs)
+        for r, s in enumerate(meds):
+            s.peer_push(plan.local_src[r])
+        for s in meds:
+            res = s.tick_peers()
+            parts.append(dict(tx=res.tx, rx=res.rx, outcome=res.outcome, rssi=res.rssi_dbm_f64, sinr=res.sinr_db_f64))
+    finally:
+        for s in meds:
+            s.close()
+    merged = merge_results(plan, parts)
+    assert np.array_equal(merged["tx"], a.tx) and np.array_equal(merged["rx"], a.rx)
+    assert np.array_equal(merged["outcome"], a.outcome) and np.array_equal(merged["rssi"], a.rssi_dbm_f64)
+    assert np.abs(merged["sinr"] - a.sinr_db_f64).max() < SINR_TOL_DB
+
+    # a sample of receivers against the oracle: those receivers alone, all 10k packets
+    pick = np.sort(rng.permutation(n)[:3000])
+    keep = np.union1d(pick, src)                              # sources must exist as nodes; only `pick` is enabled
+    remap = -np.ones(n, dtype=np.int64); remap[keep] = np.arange(keep.size)
+    en = np.zeros(keep.size, dtype=np.uint8); en[remap[pick]] = 1
+    ref = orc.tick(orc.params(orc.MODEL_SINR), orc.NodeSet(x[keep], y[keep], enabled=en),
+                   orc.make_packets(remap[src].astype(np.int32), 0.0, 26), threads=16)["pairs"]
+    sel = np.isin(a.rx, pick)
+    assert np.array_equal(a.tx[sel], ref["tx"]) and np.array_equal(remap[a.rx[sel]], ref["rx"])
+    assert np.array_equal(a.outcome[sel], ref["outcome"]) and np.array_equal(a.rssi_dbm_f64[sel], ref["rssi_dbm"])
+    fin = np.isfinite(ref["sinr_db"])
+    assert np.abs(a.sinr_db_f64[sel][fin] - ref["sinr_db"][fin]).max() < SINR_TOL_DB
