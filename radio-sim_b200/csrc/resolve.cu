@@ -203,7 +203,7 @@ cudaError_t launch_recheck(const NodeArrays &nd, const WorkArrays &wk, const Dev
     WorkArrays a_wk = wk; Groups a_groups = groups;
     void *args[] = {(void *)&a_wk, (void *)&dp, (void *)&a_groups, (void *)&tx, (void *)&rec, (void *)&sl, (void *)&pr,
                     (void *)&ctr, (void *)&part, (void *)&bar, (void *)&bar_target};
-    RMB_CUDA_OK(cudaLaunchCooperativeKernel((const void *)&recheck_tree_kernel, dim3((unsigned)grid), dim3(kTreeThreads), args, 0, st));
+    RMB_CUDA_OK(launch_grid_synced((const void *)&recheck_tree_kernel, dim3((unsigned)grid), dim3(kTreeThreads), args, st));
     recheck_seq_kernel<<<kRecheckSeqBlocks, kRecheckThreads, 0, st>>>(wk, dp, groups, tx, rec, sl, pr, ctr);
     return cudaGetLastError();
 }

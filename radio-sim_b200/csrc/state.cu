@@ -451,7 +451,7 @@ cudaError_t launch_prepare(const NodeArrays &nd, const DevParams *dp, const Geom
     NodeArrays a_nd = nd; Groups a_groups = groups;
     void *args[] = {(void *)&a_nd, (void *)&dp, (void *)&geom, (void *)&a_groups, (void *)&n_tx, (void *)&rec, (void *)&stg,
                     (void *)&tx, (void *)&theta, (void *)&theta_min_g, (void *)&ctr, (void *)&aux};
-    return cudaLaunchCooperativeKernel((const void *)&prepare_all_kernel, dim3((unsigned)grid), dim3(kPrepThreads), args, 0, st);
+    return launch_grid_synced((const void *)&prepare_all_kernel, dim3((unsigned)grid), dim3(kPrepThreads), args, st);
 }
 
 }  // namespace rmb
