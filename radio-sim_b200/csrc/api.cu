@@ -214,7 +214,7 @@ static int ensure_slots(rmb_handle *h)
     RMB_CK(h, h->slots.ensure(nk)); RMB_CK(h, h->sl_prx.ensure(nk)); RMB_CK(h, h->sl_lin.ensure(nk));
     RMB_CK(h, h->sl_sinr.ensure(nk)); RMB_CK(h, h->sl_flags.ensure(nk));
     RMB_CK(h, h->cnt.ensure(nw)); RMB_CK(h, h->hcnt.ensure(nw)); RMB_CK(h, h->hoff.ensure(nw + 2));
-    RMB_CK(h, h->recheck.ensure(nw)); RMB_CK(h, h->recheck2.ensure(nw)); RMB_CK(h, h->recheck_part.ensure(nw + 1024)); RMB_CK(h, h->rx_done.ensure(nw / 32 + 1)); RMB_CK(h, h->first.ensure(nw)); RMB_CK(h, h->itot.ensure(nw));
+    RMB_CK(h, h->recheck.ensure(nw)); RMB_CK(h, h->recheck2.ensure(nw)); RMB_CK(h, h->recheck_part.ensure(nw + 1024)); RMB_CK(h, h->rx_done.ensure(2 * (nw / 32 + 1))); RMB_CK(h, h->first.ensure(nw)); RMB_CK(h, h->itot.ensure(nw));
     RMB_CK(h, h->scan_tmp.ensure(nw / 1024 + 8));
     return RMB_OK;
 }
@@ -724,7 +724,7 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
         PrepareAux aux{};
         aux.cnt = h->cnt.p; aux.n_work = h->n_work; aux.tx_cnt = h->tx_cnt.p; aux.tx_failed = h->tx_failed.p; aux.tx_base = h->tx_base.p;
         aux.blk_cnt = h->blk_cnt.p; aux.blk_thmin = h->blk_thmin.p; aux.bar = h->bar.p; aux.bar_target = h->bar_count;
-        aux.rx_done = h->rx_done.p; aux.n_rx_done = h->n_work / 32 + 1;
+        aux.rx_done = h->rx_done.p; aux.n_rx_done = 2 * (h->n_work / 32 + 1);
         aux.peer_flags = h->wait_flags; aux.world = h->wait_world; aux.epoch = h->wait_epoch;
         if (h->fused_push) {
             aux.push_local = h->fused_push; aux.push_slots = h->peer.slots; aux.push_rank = h->peer.rank;
@@ -747,7 +747,7 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
             if (attempt) {               // attempt 0: the preparation kernel zeroed them
                 RMB_CK(h, cudaMemsetAsync(h->cnt.p, 0, (size_t)h->n_work * sizeof(int), h->st));
                 RMB_CK(h, cudaMemsetAsync(h->tx_cnt.p, 0, ((size_t)n_tx + 1) * sizeof(int), h->st));
-                RMB_CK(h, cudaMemsetAsync(h->rx_done.p, 0, ((size_t)h->n_work / 32 + 1) * sizeof(int), h->st));
+                RMB_CK(h, cudaMemsetAsync(h->rx_done.p, 0, 2 * ((size_t)h->n_work / 32 + 1) * sizeof(int), h->st));
                 RMB_CK(h, cudaEventRecord(h->ev[1], h->st));
             }
             // exact resolve (decisions + dense pair records, then the per-packet segment offsets): fused into the
@@ -756,16 +756,15 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
             PairRecs pr = pair_recs(h);
             PairArrays pa = pair_arrays(h);
             SweepFuse fuse{};
-            fuse.rb_fused = h->fuse_resolve ? sweep_fused_rx_blocks(mode, h->planar, variant, h->n_work, h->splits) : 0;
-            fuse.enabled = fuse.rb_fused > 0 ? 1 : 0;
+            fuse.rb_spin = h->fuse_resolve ? sweep_spin_first_rx_block(mode, h->planar, variant, h->n_work, h->splits) : -1;
+            fuse.enabled = fuse.rb_spin >= 0 ? 1 : 0;
             fuse.wk = wk; fuse.dp = h->dp.p; fuse.rec = d_rec; fuse.sl = sl; fuse.pr = pr; fuse.ctr = h->ctr.p;
-            fuse.n_tx = n_tx; fuse.seg = h->seg.p; fuse.rx_done = h->rx_done.p;
+            fuse.n_tx = n_tx; fuse.seg = h->seg.p; fuse.rx_done = h->rx_done.p; fuse.rx_pass = h->rx_done.p + (h->n_work / 32 + 1);
             RMB_CK(h, launch_sweep(mode, h->planar, variant, h->n_work, h->splits, a, fuse, h->st));
             ++launches; ++sweeps;
             RMB_CK(h, cudaEventRecord(h->ev[2], h->st));
-            const int w_first = fuse.rb_fused * sweep_block_rx(mode, h->planar, variant);
-            if (w_first < h->n_work) {
-                RMB_CK(h, launch_resolve(nd, wk, h->dp.p, tx, d_rec, sl, pr, h->ctr.p, n_tx, h->seg.p, w_first, h->st));
+            if (!fuse.enabled) {
+                RMB_CK(h, launch_resolve(nd, wk, h->dp.p, tx, d_rec, sl, pr, h->ctr.p, n_tx, h->seg.p, 0, h->st));
                 launches += 1;
             }
             // guard-band receivers: exact sums on a side stream, overlapped with the ordering

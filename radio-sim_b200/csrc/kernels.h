@@ -68,7 +68,7 @@ int sweep_plan(int mode, bool planar, int variant, int n_work, int n_tx_bucket, 
 // The sweep's fused epilogue (128-thread variants): the last tx-split block of an rx block resolves its receivers
 // (exact decisions, pair records) and the last rx block scans the per-packet counts -- see resolve_body.cuh.
 struct SlotArrays; struct PairRecs;
-int sweep_fused_rx_blocks(int mode, bool planar, int variant, int n_work, int splits);
+int sweep_spin_first_rx_block(int mode, bool planar, int variant, int n_work, int splits);
 int sweep_block_rx(int mode, bool planar, int variant);
 
 // ---- exact resolve of the near candidates + guard-band recheck --------------------------------
@@ -100,8 +100,8 @@ struct SweepFuse {
     int enabled;
     WorkArrays wk; const DevParams *dp; const rmb_tx_record *rec; SlotArrays sl; PairRecs pr; Counters *ctr;
     int n_tx; int *seg;
-    int *rx_done;                     // [rx blocks] splits finished (zero on entry)
-    int rb_fused;                     // rx blocks [0, rb_fused) are resolved by the sweep, the rest by launch_resolve
+    int *rx_done, *rx_pass;           // [rx blocks] splits finished / resolve passes claimed (zero on entry)
+    int rb_spin;                      // rx blocks >= rb_spin: the last R finishers share the resolve passes
 };
 cudaError_t launch_sweep(int mode, bool planar, int variant, int n_work, int splits, const SweepArgs &a, const SweepFuse &fuse,
                          cudaStream_t st);

@@ -197,26 +197,43 @@ sweep_kernel(const float *__restrict__ fx, const float *__restrict__ fy, const f
 #pragma unroll
     for (int r = 0; r < R; ++r) out[r] = sum[r];
 
-    // ---- fused epilogue: the LAST split of an rx block to finish takes the exact decisions of its receivers
-    // (resolve_body.cuh) -- double-precision, latency-bound work on pipes the sweep leaves idle, hidden
-    // behind the other resident blocks instead of being a kernel of its own after the sweep.
-    // The rx blocks of the launch's final wave are left to the stand-alone resolve kernel: resolved here they would
-    // be a serial tail (R passes of a latency-bound routine in ~70 blocks, the rest of the GPU idle).
-    if (THREADS == 128 && fuse.enabled && rb < fuse.rb_fused) {
-        __shared__ int s_flag;
+    // ---- fused epilogue: the exact decisions of the rx block's receivers (resolve_body.cuh) are taken by the
+    // sweep blocks themselves -- double-precision, latency-bound work on pipes the sweep leaves idle, hidden behind
+    // the other resident blocks instead of being a kernel of its own after the sweep.  The LAST split of an rx
+    // block to finish does it, in R passes of 128 receivers claimed through a per-rx-block counter.  In the
+    // launch's final wave (rb >= rb_spin; nothing is waiting for a block slot there) the R-1 finishers before the
+    // last one wait for it and share the passes, so that the end of the launch is ONE pass deep, not R.
+    if (THREADS == 128 && fuse.enabled) {
+        __shared__ int s_role, s_q, s_flag;
         __syncthreads();
-        if (threadIdx.x == 0) { __threadfence(); s_flag = atomicAdd(&fuse.rx_done[rb], 1) == S - 1; }
-        __syncthreads();
-        if (s_flag) {
+        if (threadIdx.x == 0) {
             __threadfence();
-#pragma unroll 1
-            for (int q = 0; q < R; ++q)
+            const int k = atomicAdd(&fuse.rx_done[rb], 1);
+            int role = k == S - 1;
+            if (!role && rb >= fuse.rb_spin && k >= S - R) {
+                const unsigned *done = reinterpret_cast<const unsigned *>(&fuse.rx_done[rb]);
+                const unsigned long long t0 = global_timer_ns();
+                while (ld_acquire_gpu(done) < (unsigned)S && global_timer_ns() - t0 < 500000ull) __nanosleep(200);
+                role = ld_acquire_gpu(done) >= (unsigned)S;        // gave up waiting: the last finisher does the passes
+            }
+            s_role = role;
+        }
+        __syncthreads();
+        if (s_role) {
+            __threadfence();
+            for (;;) {
+                if (threadIdx.x == 0) s_q = atomicAdd(&fuse.rx_pass[rb], 1);
+                __syncthreads();
+                const int q = s_q;
+                __syncthreads();
+                if (q >= R) break;
                 resolve_receiver<true>(wb + q * THREADS + (int)threadIdx.x, fuse.wk, fuse.dp, tx, fuse.rec, fuse.sl, fuse.pr, fuse.ctr);
-            // the last rx block of the launch turns the per-packet heard counts into segment offsets
-            __syncthreads();
-            if (threadIdx.x == 0) { __threadfence(); s_flag = atomicAdd(&fuse.ctr->resolve_done, (unsigned)R) + R == (unsigned)(n_work / 128); }
-            __syncthreads();
-            if (s_flag) { __threadfence(); scan_tx_counts(fuse.pr.tx_cnt, fuse.n_tx, fuse.seg, fuse.ctr); }
+                // the last group of 128 receivers of the launch turns the per-packet heard counts into segment offsets
+                __syncthreads();
+                if (threadIdx.x == 0) { __threadfence(); s_flag = atomicAdd(&fuse.ctr->resolve_done, 1u) + 1u == (unsigned)(n_work / 128); }
+                __syncthreads();
+                if (s_flag) { __threadfence(); scan_tx_counts(fuse.pr.tx_cnt, fuse.n_tx, fuse.seg, fuse.ctr); }
+            }
         }
     }
 }
@@ -296,12 +313,12 @@ int sweep_plan(int mode, bool planar, int variant, int n_work, int n_tx_bucket, 
     return min(max_s, max(best, n_tx_bucket / kTargetSplitTx));
 }
 
-// number of leading rx blocks the sweep resolves itself (0: variant cannot fuse); the rest -- about the final wave of
-// the launch, with a margin -- goes to launch_resolve
-int sweep_fused_rx_blocks(int mode, bool planar, int variant, int n_work, int splits)
+// first rx block of the launch's final wave (with a margin), where the finishers of an rx block share the resolve
+// passes; -1: the variant cannot fuse the resolve (launch_resolve does it)
+int sweep_spin_first_rx_block(int mode, bool planar, int variant, int n_work, int splits)
 {
     const SweepVariant v = pick(mode, planar, variant);
-    if (v.threads != 128) return 0;
+    if (v.threads != 128) return -1;
     const int sms = device_sms(), occ = variant_occupancy(v);
     const int nb = n_work / (v.R * v.threads);
     const int tail = (int)ceil(1.25 * sms * occ / max(1, splits));
@@ -316,7 +333,7 @@ cudaError_t launch_sweep(int mode, bool planar, int variant, int n_work, int spl
     const SweepVariant v = pick(mode, planar, variant);
     SweepArgs b = a;
     SweepFuse f = fuse;
-    if (v.threads != 128) { f.enabled = 0; f.rb_fused = 0; }
+    if (v.threads != 128) f.enabled = 0;
     int nw = n_work, S = max(1, splits);
     void *args[] = {(void *)&b.fx, (void *)&b.fy, (void *)&b.fz, (void *)&b.groups, (void *)&b.tx, (void *)&b.theta,
                     (void *)&b.theta_min_g, (void *)&b.neg_h, (void *)&b.far_part, (void *)&b.cnt, (void *)&b.slots,
