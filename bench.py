@@ -271,7 +271,9 @@ def run_ours(args):
         ms_sweep = float(np.mean(sweep_ms))
         achieved = local_dec / (ms_sweep * 1e-3)                       # MUFU ops (== decisions) per second, this GPU
         peak = SMS * XU_LANES * f_max
-        hbm_bytes = 32.0 * (hi - lo) + 32.0 * N_TX                     # algorithmic bytes of one sweep launch
+        # algorithmic bytes of one sweep launch incl. its fused resolve: coordinates fp32 + exact, totals
+        # per receiver; one pair record per heard pair; one record per tx
+        hbm_bytes = 56.0 * (hi - lo) + 29.0 * pairs / G + 32.0 * N_TX
         traffic = None
         try:
             traffic = json.load(open(os.path.join(ROOT, "profiles", "sweep_traffic.json")))["dram_bytes_per_launch"]
@@ -299,7 +301,7 @@ def run_ours(args):
                              "frac_at_sampled_clock": (achieved / (SMS * XU_LANES * f_run)) if f_run else None,
                              "ms_per_launch": ms_sweep, "traffic": traffic,
                              "hbm": {"achieved_gbs": hbm_bytes / (ms_sweep * 1e-3) / 1e9, "peak_gbs": peaks.get("hbm_gbs"),
-                                     "note": "algorithmic bytes (32 B/receiver + 32 B/tx) / sweep time: HBM is not the binding roofline"}}}
+                                     "note": "algorithmic bytes (56 B/receiver + 29 B/heard pair + 32 B/tx) / sweep time: HBM is not the binding roofline"}}}
         if G == 1 and not args.no_cpu:
             cores = host_threads()
             dec_c, t_c, sample = cpu_reference_sample(cores)
