@@ -162,7 +162,8 @@ def run_ours(args):
 
     x, y, src = deployment(args.grid)
     lo, hi = rank * N_NODES // G, (rank + 1) * N_NODES // G
-    med = rsb.Medium("sinr", device=local, rx_base=lo, n_shards=G)
+    # compact result form: what the reference-side adapter consumes (rx, rssi, outcome per row + first row per packet)
+    med = rsb.Medium("sinr", device=local, rx_base=lo, n_shards=G, compact=True)
     med.set_nodes(x[lo:hi], y[lo:hi])
     stream = torch.cuda.Stream(device=dev)
     torch.cuda.set_stream(stream)                   # NCCL collectives and the library share this stream
@@ -293,7 +294,8 @@ def run_ours(args):
                 "clocks": clocks,
                 "e2e": {"value": decisions * args.steps / t_e2e, "unit": UNIT, "ms_per_step": 1e3 * t_e2e / args.steps,
                         "h2d_bytes_per_step": int(4 * (src.size if G == 1 else tpad)),
-                        "d2h_bytes_per_step": int(17 * pairs / G + n_rec + 96), "heard_pairs": int(pairs)},
+                        "d2h_bytes_per_step": int(9 * pairs / G + 5 * n_rec + 4 + 96), "heard_pairs": int(pairs),
+                        "result_form": "compact (RMB_FLAG_COMPACT): int32 rx + float rssi + uint8 outcome per heard pair, int32 first row per packet"},
                 "gpu_launches": int(launches),
                 "roofline": {"bound": "sfu", "kernel": "sweep_kernel", "achieved": achieved / 1e9, "peak": peak / 1e9,
                              "unit": "G MUFU-op/s (1 rsqrt per decision; peak = 148 SM x 16 lanes x sm_max_mhz)",
@@ -335,7 +337,7 @@ def run_c5(args):
     x, y = rng.uniform(0, SIDE, N_NODES), rng.uniform(0, SIDE, N_NODES)
     ch = (11 + np.arange(N_NODES) % 16).astype(np.int32)
     lo, hi = rank * N_NODES // G, (rank + 1) * N_NODES // G
-    med = rsb.Medium("sinr", device=local, rx_base=lo, n_shards=G)
+    med = rsb.Medium("sinr", device=local, rx_base=lo, n_shards=G, compact=True)
     med.set_nodes(x[lo:hi], y[lo:hi], channel=ch[lo:hi])
     stream = torch.cuda.Stream(device=dev)
     torch.cuda.set_stream(stream)
@@ -442,7 +444,7 @@ def run_c5(args):
                                      "resident); e2e: host wall clock around position upload + tick with host lists"},
                 "clocks": clocks,
                 "e2e": {"value": float(cnt[1]) / float(tot[1]), "unit": UNIT, "ms_per_step": 1e3 * float(tot[1]) / args.steps,
-                        "h2d_bytes_per_step": int(16 * (hi - lo) + 4 * N_TX / G), "d2h_bytes_per_step": int(17 * float(cnt[2]) / args.steps / G),
+                        "h2d_bytes_per_step": int(16 * (hi - lo) + 4 * N_TX / G), "d2h_bytes_per_step": int(9 * float(cnt[2]) / args.steps / G + 5 * N_TX),
                         "heard_pairs_per_tick": float(cnt[2]) / args.steps},
                 "gpu_launches": int(launches),
                 "roofline": {"bound": "sfu", "kernel": "sweep_kernel", "achieved": achieved / 1e9, "peak": peak / 1e9,

@@ -16,6 +16,7 @@ PEER_HANDLE_BYTES = 128
 MODEL_NULL, MODEL_UDGM, MODEL_UDGM_CONSTANT, MODEL_N2N, MODEL_SINR = 0, 1, 2, 3, 4
 NOT_HEARD, INTERFERED, DELIVERED = 0, 1, 2
 FLAG_F64_VALUES = 1
+FLAG_COMPACT = 2
 
 # every symbol include/radiomedium_b200.h declares
 SYMBOLS = ("rmb_version", "rmb_config_default", "rmb_create", "rmb_destroy", "rmb_last_error",
@@ -50,7 +51,7 @@ class Result(C.Structure):
                 ("rssi_dbm", C.POINTER(C.c_float)), ("sinr_db", C.POINTER(C.c_float)),
                 ("outcome", C.POINTER(C.c_uint8)),
                 ("rssi_dbm_f64", C.POINTER(C.c_double)), ("sinr_db_f64", C.POINTER(C.c_double)),
-                ("tx_failed", C.POINTER(C.c_uint8))]
+                ("tx_failed", C.POINTER(C.c_uint8)), ("tx_first", C.POINTER(C.c_int32))]
 
 
 class Timing(C.Structure):

@@ -101,7 +101,7 @@ struct rmb_handle {
     DevBuf<int> draw_scan, seg, scan_tmp, blkcnt; DevBuf<long long> tx_base; DevBuf<uint8_t> tx_failed;
     DevBuf<char> cub_tmp;
     DevBuf<int> o_tx, o_rx; DevBuf<float> o_rssi, o_sinr; DevBuf<uint8_t> o_outcome; DevBuf<double> o_rssi64, o_sinr64;
-    PinBuf<int> ho_tx, ho_rx; PinBuf<float> ho_rssi, ho_sinr; PinBuf<uint8_t> ho_outcome, ho_failed;
+    PinBuf<int> ho_tx, ho_rx, ho_first; DevBuf<int> o_first; PinBuf<float> ho_rssi, ho_sinr; PinBuf<uint8_t> ho_outcome, ho_failed;
     PinBuf<double> ho_rssi64, ho_sinr64;
 
     // multi-GPU exchange over peer memory (rmb_peer_*)
@@ -394,7 +394,7 @@ int rmb_destroy(rmb_handle *h)
     h->draw_scan.release(); h->seg.release(); h->scan_tmp.release(); h->blkcnt.release(); h->tx_base.release();
     h->tx_failed.release(); h->cub_tmp.release(); h->o_tx.release(); h->o_rx.release(); h->o_rssi.release();
     h->o_sinr.release(); h->o_outcome.release(); h->o_rssi64.release(); h->o_sinr64.release(); h->ho_tx.release();
-    h->ho_rx.release(); h->ho_rssi.release(); h->ho_sinr.release(); h->ho_outcome.release(); h->ho_failed.release();
+    h->ho_rx.release(); h->ho_first.release(); h->o_first.release(); h->ho_rssi.release(); h->ho_sinr.release(); h->ho_outcome.release(); h->ho_failed.release();
     h->ho_rssi64.release(); h->ho_sinr64.release();
     h->fb_key.release(); h->fb_key_alt.release(); h->fb_val.release(); h->fb_val_alt.release(); h->rec_prx.release();
     h->rec_sinr.release(); h->rec_flags.release(); h->rec_rank.release(); h->tx_cnt.release(); h->first.release();
@@ -880,25 +880,35 @@ static int download(rmb_handle *h, rmb_result *out)
     const long long m = h->last_pairs;
     const int nt = h->last_ntx;
     const size_t c = (size_t)std::max<long long>(m, 1);
-    RMB_CK(h, h->ho_tx.ensure(c)); RMB_CK(h, h->ho_rx.ensure(c)); RMB_CK(h, h->ho_rssi.ensure(c));
-    RMB_CK(h, h->ho_sinr.ensure(c)); RMB_CK(h, h->ho_outcome.ensure(c)); RMB_CK(h, h->ho_failed.ensure((size_t)nt + 1));
-    const bool f64 = (h->cfg.flags & RMB_FLAG_F64_VALUES) != 0;
+    const bool f64 = (h->cfg.flags & RMB_FLAG_F64_VALUES) != 0, compact = (h->cfg.flags & RMB_FLAG_COMPACT) != 0;
+    RMB_CK(h, h->ho_rx.ensure(c)); RMB_CK(h, h->ho_rssi.ensure(c));
+    RMB_CK(h, h->ho_outcome.ensure(c)); RMB_CK(h, h->ho_failed.ensure((size_t)nt + 1));
+    if (!compact) { RMB_CK(h, h->ho_tx.ensure(c)); RMB_CK(h, h->ho_sinr.ensure(c)); }
+    else { RMB_CK(h, h->ho_first.ensure((size_t)nt + 2)); RMB_CK(h, h->o_first.ensure((size_t)nt + 2)); }
     if (f64) { RMB_CK(h, h->ho_rssi64.ensure(c)); RMB_CK(h, h->ho_sinr64.ensure(c)); }
     if (m > 0) {
-        RMB_CK(h, cudaMemcpyAsync(h->ho_tx.p, h->o_tx.p, m * sizeof(int), cudaMemcpyDeviceToHost, h->st));
         RMB_CK(h, cudaMemcpyAsync(h->ho_rx.p, h->o_rx.p, m * sizeof(int), cudaMemcpyDeviceToHost, h->st));
         RMB_CK(h, cudaMemcpyAsync(h->ho_rssi.p, h->o_rssi.p, m * sizeof(float), cudaMemcpyDeviceToHost, h->st));
-        RMB_CK(h, cudaMemcpyAsync(h->ho_sinr.p, h->o_sinr.p, m * sizeof(float), cudaMemcpyDeviceToHost, h->st));
         RMB_CK(h, cudaMemcpyAsync(h->ho_outcome.p, h->o_outcome.p, m, cudaMemcpyDeviceToHost, h->st));
+        if (!compact) {
+            RMB_CK(h, cudaMemcpyAsync(h->ho_tx.p, h->o_tx.p, m * sizeof(int), cudaMemcpyDeviceToHost, h->st));
+            RMB_CK(h, cudaMemcpyAsync(h->ho_sinr.p, h->o_sinr.p, m * sizeof(float), cudaMemcpyDeviceToHost, h->st));
+        }
         if (f64) {
             RMB_CK(h, cudaMemcpyAsync(h->ho_rssi64.p, h->o_rssi64.p, m * sizeof(double), cudaMemcpyDeviceToHost, h->st));
             RMB_CK(h, cudaMemcpyAsync(h->ho_sinr64.p, h->o_sinr64.p, m * sizeof(double), cudaMemcpyDeviceToHost, h->st));
         }
     }
+    if (compact) {
+        RMB_CK(h, launch_tx_first(h->o_tx.p, m, nt, h->o_first.p, h->st));
+        RMB_CK(h, cudaMemcpyAsync(h->ho_first.p, h->o_first.p, ((size_t)nt + 1) * sizeof(int), cudaMemcpyDeviceToHost, h->st));
+    }
     if (nt > 0) RMB_CK(h, cudaMemcpyAsync(h->ho_failed.p, h->tx_failed.p, nt, cudaMemcpyDeviceToHost, h->st));
     RMB_CK(h, cudaStreamSynchronize(h->st));
     rmb_result &r = h->last;
-    r.tx = h->ho_tx.p; r.rx = h->ho_rx.p; r.rssi_dbm = h->ho_rssi.p; r.sinr_db = h->ho_sinr.p; r.outcome = h->ho_outcome.p;
+    r.rx = h->ho_rx.p; r.rssi_dbm = h->ho_rssi.p; r.outcome = h->ho_outcome.p;
+    r.tx = compact ? nullptr : h->ho_tx.p; r.sinr_db = compact ? nullptr : h->ho_sinr.p;
+    r.tx_first = compact ? h->ho_first.p : nullptr;
     r.rssi_dbm_f64 = f64 ? h->ho_rssi64.p : nullptr; r.sinr_db_f64 = f64 ? h->ho_sinr64.p : nullptr;
     r.tx_failed = h->ho_failed.p;
     if (out) *out = r;

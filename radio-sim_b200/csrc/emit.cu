@@ -223,6 +223,22 @@ __global__ void seg_kernel(const unsigned long long *key, long long n, int n_tx,
     seg[t] = (int)lo;
 }
 
+// first result row of every packet (lower bound of t in the sorted tx column): the compact result form
+__global__ void tx_first_kernel(const int *o_tx, long long n, int n_tx, int *first)
+{
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t > n_tx) return;
+    long long lo = 0, hi = n;
+    while (lo < hi) { long long mid = (lo + hi) >> 1; if (o_tx[mid] < t) lo = mid + 1; else hi = mid; }
+    first[t] = (int)lo;
+}
+
+cudaError_t launch_tx_first(const int *o_tx, long long n, int n_tx, int *first, cudaStream_t st)
+{
+    tx_first_kernel<<<(n_tx + 1 + 255) / 256, 256, 0, st>>>(o_tx, n, n_tx, first);
+    return cudaGetLastError();
+}
+
 // 1 where the pair would consume a uniform if its packet did not fail
 __global__ void drawflag_kernel(const uint8_t *cand, const double *p, long long n, int *flag)
 {

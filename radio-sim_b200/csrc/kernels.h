@@ -156,6 +156,8 @@ cudaError_t launch_order_fallback(PairRecs pr, long long m, int key_bits, OrderS
 cudaError_t launch_emit_sinr(const NodeArrays &nd, const DevParams *dp, const rmb_tx_record *rec, int n_tx, PairRecs pr,
                              const unsigned *order, PairArrays pa, long long m, bool stochastic, Counters *ctr,
                              Counters *host_ctr, cudaStream_t st);
+// first[t] = first row of packet t in the (sorted) tx column, first[n_tx] = n
+cudaError_t launch_tx_first(const int *o_tx, long long n, int n_tx, int *first, cudaStream_t st);
 cudaError_t launch_emit(const DevParams *dp, const rmb_tx_record *rec, int n_tx, PairArrays pa, long long n,
                         bool stochastic, const double *uniforms, long long n_uniforms, Counters *ctr,
                         cudaStream_t st);

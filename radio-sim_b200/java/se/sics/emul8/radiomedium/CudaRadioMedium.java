@@ -41,8 +41,8 @@ public class CudaRadioMedium extends AbstractRadioMedium {
 
     /* struct rmb_config (include/radiomedium_b200.h): 4 x int32, 10 x double, int64, 2 x int32 = 112 bytes */
     private static final long CFG_SIZE = 112, CFG_MODEL = 4, CFG_PL0 = 48, CFG_EXPONENT = 56, CFG_SENS = 72, CFG_THR = 80;
-    /* struct rmb_result: 6 x int64, 2 x int32, 8 pointers = 120 bytes */
-    private static final long RES_SIZE = 120, RES_NPAIRS = 0, RES_TX = 56, RES_RX = 64, RES_RSSI = 72, RES_OUTCOME = 88;
+    /* struct rmb_result: 6 x int64, 2 x int32, 9 pointers = 128 bytes */
+    private static final long RES_SIZE = 128, RES_NPAIRS = 0, RES_TX = 56, RES_RX = 64, RES_RSSI = 72, RES_OUTCOME = 88;
 
     private final Arena arena = Arena.ofShared();
     private final MemorySegment handle;

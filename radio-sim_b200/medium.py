@@ -51,6 +51,14 @@ class TickResult:
         self.rssi_dbm_f64 = view(r.rssi_dbm_f64, np.float64, n) if f64 else None
         self.sinr_db_f64 = view(r.sinr_db_f64, np.float64, n) if f64 else None
         self.tx_failed = view(r.tx_failed, np.uint8, self.n_tx)
+        # compact form (RMB_FLAG_COMPACT): no tx / sinr columns, rows of packet t are tx_first[t] .. tx_first[t+1]
+        self.tx_first = view(r.tx_first, np.int32, self.n_tx + 1) if r.tx_first else None
+
+    def tx_column(self):
+        """The tx column, rebuilt from tx_first when the result is in the compact form."""
+        if self.tx_first is None:
+            return self.tx
+        return np.repeat(np.arange(self.n_tx, dtype=np.int32), np.diff(self.tx_first))
 
 
 class Medium:
@@ -60,13 +68,15 @@ class Medium:
               "udgm-constant": A.MODEL_UDGM_CONSTANT, "n2n": A.MODEL_N2N, "n2n-link": A.MODEL_N2N,
               "sinr": A.MODEL_SINR, "sinr-b200": A.MODEL_SINR}
 
-    def __init__(self, model="sinr", device=0, f64_values=False, rx_base=0, n_shards=1, max_pairs=0, **params):
+    def __init__(self, model="sinr", device=0, f64_values=False, rx_base=0, n_shards=1, max_pairs=0, compact=False, **params):
         self._lib = A.load()
         cfg = A.Config()
         self._lib.rmb_config_default(C.byref(cfg), self.MODELS[model] if isinstance(model, str) else int(model))
         cfg.device, cfg.rx_base, cfg.n_shards, cfg.max_pairs = device, rx_base, n_shards, max_pairs
         if f64_values:
             cfg.flags |= A.FLAG_F64_VALUES
+        if compact:
+            cfg.flags |= A.FLAG_COMPACT
         for k, v in params.items():
             if not hasattr(cfg, k):
                 raise AttributeError(f"unknown medium parameter {k}")

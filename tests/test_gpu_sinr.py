@@ -217,3 +217,20 @@ def test_enqueued_tick_equals_the_synchronous_one(rsb, orc):
             compare(m.fetch(), ref)
         m.tick_enqueue(120, rec.data_ptr())            # settled implicitly by the next call
         compare(m.fetch(), ref)
+
+
+@pytest.mark.parametrize("model", ["sinr", "udgm"])
+def test_compact_result_form(rsb, orc, model):
+    """RMB_FLAG_COMPACT: rx / rssi / outcome per row + tx_first per packet, exactly what the reference's
+    generateReceptionEvents calls need; the tx and sinr columns are not transferred."""
+    x, y, z, ch = random_deployment(5, 3000, 400.0)
+    src = pick_sources(5, 3000, 80)
+    with rsb.Medium(model) as full, rsb.Medium(model, compact=True) as cm:
+        full.set_nodes(x, y, z, channel=ch)
+        cm.set_nodes(x, y, z, channel=ch)
+        a, b = full.tick(src), cm.tick(src)
+    assert b.tx.size == 0 and b.sinr_db.size == 0 and b.tx_first is not None
+    assert b.tx_first[0] == 0 and b.tx_first[-1] == a.n_pairs == b.n_pairs
+    assert np.array_equal(b.tx_column(), a.tx) and np.array_equal(b.rx, a.rx)
+    assert np.array_equal(b.outcome, a.outcome) and np.array_equal(b.rssi_dbm, a.rssi_dbm)
+    assert np.array_equal(b.tx_failed, a.tx_failed)
