@@ -82,42 +82,7 @@ cudaError_t launch_exclusive_scan(const int *in, int *out, int n, int *tmp, int 
 }
 
 // ---- SINR medium: pair records -> (packet arrival, node index) order --------------------------
-// seg[t] = first pair of packet t; one block, chunks of 1024 with a running carry
-__global__ void __launch_bounds__(1024) tx_scan_kernel(const int *tx_cnt, int n_tx, int *seg, Counters *ctr)
-{
-    __shared__ int s_warp[33];
-    __shared__ int s_carry, s_max[32];
-    if (threadIdx.x == 0) s_carry = 0;
-    __syncthreads();
-    int mx = 0;
-    for (int c0 = 0; c0 < n_tx; c0 += 1024) {
-        const int t = c0 + threadIdx.x;
-        const int v = t < n_tx ? tx_cnt[t] : 0;
-        mx = max(mx, v);
-        int total;
-        const int ex = block_exclusive_scan_1024(v, s_warp, total);
-        const int carry = s_carry;
-        if (t < n_tx) seg[t] = carry + ex;
-        __syncthreads();
-        if (threadIdx.x == 0) s_carry = carry + total;
-        __syncthreads();
-    }
-    for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    if ((threadIdx.x & 31) == 0) s_max[threadIdx.x >> 5] = mx;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        for (int i = 1; i < 32; ++i) mx = max(mx, s_max[i]);
-        seg[n_tx] = s_carry;
-        ctr->max_bucket = mx;
-    }
-}
-
-cudaError_t launch_tx_scan(const int *tx_cnt, int n_tx, int *seg, Counters *ctr, cudaStream_t st)
-{
-    tx_scan_kernel<<<1, 1024, 0, st>>>(tx_cnt, n_tx, seg, ctr);
-    return cudaGetLastError();
-}
-
+// (seg[t] = first pair of packet t comes from the resolve: scan_tx_counts in resolve_body.cuh)
 // record i -> its packet's bucket, at the rank its atomic drew: items = (global rx << 32) | record index
 // (grid-stride over the device-side record count: the host does not know it yet)
 __global__ void place_items_kernel(PairRecs pr, const Counters *ctr, const int *seg, unsigned long long *items)

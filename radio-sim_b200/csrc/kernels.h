@@ -69,7 +69,6 @@ int sweep_plan(int mode, bool planar, int variant, int n_work, int n_tx_bucket, 
 // (exact decisions, pair records) and the last rx block scans the per-packet counts -- see resolve_body.cuh.
 struct SlotArrays; struct PairRecs;
 int sweep_spin_first_rx_block(int mode, bool planar, int variant, int n_work, int splits);
-int sweep_block_rx(int mode, bool planar, int variant);
 
 // ---- exact resolve of the near candidates + guard-band recheck --------------------------------
 struct SlotArrays {
@@ -140,7 +139,7 @@ struct PairArrays {
 // exclusive scan of int32 (n elements) using tmp (>= n/1024+2 ints); total written to *total_out (device)
 cudaError_t launch_exclusive_scan(const int *in, int *out, int n, int *tmp, int *total_out, cudaStream_t st);
 // SINR medium: pair records -> (packet arrival, node index) order.
-//   tx_scan : seg[t] = first pair of packet t (exclusive scan of tx_cnt), largest bucket -> ctr->max_bucket
+//   seg     : seg[t] = first pair of packet t (exclusive scan of tx_cnt, done by the resolve), largest bucket -> ctr->max_bucket
 //   order   : order[pos] = record index of the pos-th pair.  Buckets are filled through the atomic ranks and
 //             sorted by rx inside one block each (shared-memory bitonic sort, buckets <= kBucketSortMax);
 //             larger buckets take the CUB radix-sort fallback over the whole key.
@@ -148,7 +147,6 @@ cudaError_t launch_exclusive_scan(const int *in, int *out, int n, int *tmp, int 
 //             the sorted pair arrays the draw-order stage consumes).
 constexpr int kBucketSortMax = 2048;
 struct OrderScratch { unsigned long long *items; unsigned long long *fb_key, *fb_key_alt; unsigned *fb_val, *fb_val_alt; void *cub_tmp; size_t cub_tmp_bytes; };
-cudaError_t launch_tx_scan(const int *tx_cnt, int n_tx, int *seg, Counters *ctr, cudaStream_t st);
 size_t      sort_pairs_tmp_bytes(long long n);
 cudaError_t launch_order_buckets(PairRecs pr, const Counters *ctr, int n_tx, const int *seg, unsigned long long *items,
                                  unsigned *order, cudaStream_t st);

@@ -324,7 +324,6 @@ int sweep_spin_first_rx_block(int mode, bool planar, int variant, int n_work, in
     const int tail = (int)ceil(1.25 * sms * occ / max(1, splits));
     return max(0, nb - tail);
 }
-int sweep_block_rx(int mode, bool planar, int variant) { const SweepVariant v = pick(mode, planar, variant); return v.R * v.threads; }
 
 cudaError_t launch_sweep(int mode, bool planar, int variant, int n_work, int splits, const SweepArgs &a, const SweepFuse &fuse,
                          cudaStream_t st)
