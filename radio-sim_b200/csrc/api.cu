@@ -75,6 +75,7 @@ struct rmb_handle {
     int matrix_n = 0;
     DevBuf<int> perm, gid; DevBuf<float> fx, fy, fz; DevBuf<double> wx, wy, wz, wrxp;
     bool node_info_dirty = false;
+    int dense_updates = 0;
     DevBuf<unsigned long long> ro_key, ro_key_alt; DevBuf<int> ro_val, ro_val_alt; DevBuf<char> ro_tmp;
     int n_work = 0;
     Groups groups{};
@@ -489,8 +490,13 @@ extern "C" int rmb_update_positions(rmb_handle *h, int32_t count, const int32_t 
         if (z) RMB_CK(h, cudaMemcpyAsync(dz, z, b, cudaMemcpyHostToDevice, h->st));
         RMB_CK(h, launch_scatter_positions(node_arrays(h), count, h->pk_src.p, dx, dy, z ? dz : nullptr, h->st));
     }
-    // a dense update re-sorts the work order; a sparse one keeps it (the order only affects speed)
-    return refresh_geometry(h, idx == nullptr);
+    // The work order (Morton order inside a channel group) only affects speed -- warp-coherent near re-scans in the
+    // sweep -- never results.  A sparse update keeps it; dense updates (per-tick mobility, BASELINE configs[4])
+    // re-sort on the first and then every kReorderEvery-th call: nodes that move a little per tick stay sorted
+    // well enough, and the re-sort (radix sort of all receivers) costs as much as the upload itself.
+    constexpr int kReorderEvery = 8;
+    const bool reorder = idx == nullptr && (h->dense_updates++ % kReorderEvery) == 0;
+    return refresh_geometry(h, reorder);
 }
 
 extern "C" int rmb_update_radio(rmb_handle *h, int32_t count, const int32_t *idx, const double *txpower_dbm,
