@@ -92,7 +92,7 @@ struct rmb_handle {
 
     // slots
     int K = 8;
-    DevBuf<int> slots, cnt, hcnt, hoff, recheck, recheck2; DevBuf<float> far_part; int splits = 1, forced_splits = 0;
+    DevBuf<int> slots, cnt, hcnt, hoff, recheck, recheck2, recheck_cnt; DevBuf<float> far_part; SweepSplits splits{1, 1, 0, 512, false}; int forced_splits = 0, taper = 2;
     DevBuf<double> sl_prx, sl_lin, sl_sinr, itot; DevBuf<uint8_t> sl_flags;
 
     // pairs
@@ -132,6 +132,7 @@ struct rmb_handle {
     rmb_result last{};
     int sweep_variant = 0;
     bool fuse_resolve = true;          // rmb_set_tuning bit 16 turns the fused epilogue off (stand-alone resolve kernel)
+    bool fuse_finish = true;           // rmb_set_tuning bit 20: separate recheck / ordering / emit kernels instead of finish.cu
     bool have_nodes = false;
 
     int fail(int code, const std::string &m) { err = m; return code; }
@@ -169,9 +170,9 @@ TxTiles tx_tiles(rmb_handle *h)
 }
 SlotArrays slot_arrays(rmb_handle *h)
 {
-    SlotArrays s; s.K = h->K; s.slots = h->slots.p; s.cnt = h->cnt.p; s.far_part = h->far_part.p; s.splits = h->splits; s.prx = h->sl_prx.p;
+    SlotArrays s; s.K = h->K; s.slots = h->slots.p; s.cnt = h->cnt.p; s.far_part = h->far_part.p; s.splits = h->splits.s1; s.splits2 = h->splits.s2; s.w_taper = h->splits.rb_taper * h->splits.block_rx; s.prx = h->sl_prx.p;
     s.lin = h->sl_lin.p; s.sinr = h->sl_sinr.p; s.flags = h->sl_flags.p; s.hcnt = h->hcnt.p; s.itot = h->itot.p;
-    s.recheck = h->recheck.p; s.recheck2 = h->recheck2.p; s.first = h->first.p;
+    s.recheck = h->recheck.p; s.recheck2 = h->recheck2.p; s.recheck_cnt = h->recheck_cnt.p; s.first = h->first.p;
     return s;
 }
 PairArrays pair_arrays(rmb_handle *h)
@@ -215,7 +216,7 @@ static int ensure_slots(rmb_handle *h)
     RMB_CK(h, h->slots.ensure(nk)); RMB_CK(h, h->sl_prx.ensure(nk)); RMB_CK(h, h->sl_lin.ensure(nk));
     RMB_CK(h, h->sl_sinr.ensure(nk)); RMB_CK(h, h->sl_flags.ensure(nk));
     RMB_CK(h, h->cnt.ensure(nw)); RMB_CK(h, h->hcnt.ensure(nw)); RMB_CK(h, h->hoff.ensure(nw + 2));
-    RMB_CK(h, h->recheck.ensure(nw)); RMB_CK(h, h->recheck2.ensure(nw)); RMB_CK(h, h->recheck_part.ensure(nw + 1024)); RMB_CK(h, h->rx_done.ensure(2 * (nw / 32 + 1))); RMB_CK(h, h->first.ensure(nw)); RMB_CK(h, h->itot.ensure(nw));
+    RMB_CK(h, h->recheck.ensure(nw)); RMB_CK(h, h->recheck2.ensure(nw)); RMB_CK(h, h->recheck_cnt.ensure(nw)); RMB_CK(h, h->recheck_part.ensure(nw + 1024)); RMB_CK(h, h->rx_done.ensure(2 * (nw / 32 + 1))); RMB_CK(h, h->first.ensure(nw)); RMB_CK(h, h->itot.ensure(nw));
     RMB_CK(h, h->scan_tmp.ensure(nw / 1024 + 8));
     return RMB_OK;
 }
@@ -389,7 +390,7 @@ int rmb_destroy(rmb_handle *h)
     h->pk_channel.release(); h->pk_power.release(); h->pk_stage.release(); h->rec.release(); h->txf.release(); h->stg_f.release(); h->stg_theta.release(); h->stg_gid.release(); h->blk_cnt.release(); h->blk_thmin.release(); h->bar.release(); h->recheck_part.release(); h->rx_done.release();
     h->theta.release(); h->theta_min_g.release(); h->arrival.release(); h->goff.release(); h->gcount.release();
     h->uniforms.release(); h->slots.release(); h->cnt.release(); h->hcnt.release(); h->hoff.release();
-    h->recheck.release(); h->recheck2.release(); h->far_part.release(); h->sl_prx.release(); h->sl_lin.release(); h->sl_sinr.release();
+    h->recheck.release(); h->recheck2.release(); h->recheck_cnt.release(); h->far_part.release(); h->sl_prx.release(); h->sl_lin.release(); h->sl_sinr.release();
     h->itot.release(); h->sl_flags.release(); h->key.release(); h->key_alt.release(); h->val.release();
     h->val_alt.release(); h->pr_p.release(); h->pr_rssi.release(); h->pr_sinr.release(); h->pr_cand.release();
     h->draw_scan.release(); h->seg.release(); h->scan_tmp.release(); h->blkcnt.release(); h->tx_base.release();
@@ -548,6 +549,8 @@ extern "C" int rmb_set_tuning(rmb_handle *h, int32_t sweep_variant, int32_t near
     h->sweep_variant = sweep_variant & 0xff;
     h->forced_splits = (sweep_variant >> 8) & 0xff;
     h->fuse_resolve = ((sweep_variant >> 16) & 1) == 0;
+    h->fuse_finish = ((sweep_variant >> 20) & 1) == 0;
+    h->taper = ((sweep_variant >> 17) & 7) ? ((sweep_variant >> 17) & 7) : 2;      // bits 17..19: split multiplier of the final wave
     if (near_slots > 0 && near_slots != h->K) { h->K = near_slots; return ensure_slots(h); }
     return RMB_OK;
 }
@@ -720,8 +723,10 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
         const int mode = sweep_mode_for_exponent(h->cfg.pl_exponent);
         // default: 4 receivers per thread, 128 threads (the fastest variant at every shard size once the blocks are short)
         const int variant = h->sweep_variant ? h->sweep_variant : 1;
-        h->splits = sweep_plan(mode, h->planar, variant, h->n_work, n_tx / std::max(1, h->groups.ngroups), h->forced_splits);
-        RMB_CK(h, h->far_part.ensure((size_t)h->splits * (size_t)std::max(h->n_work, 1)));
+        const int n_tx_bucket = n_tx / std::max(1, h->groups.ngroups);
+        h->splits = sweep_splits(mode, h->planar, variant, h->n_work, n_tx_bucket,
+                                 sweep_plan(mode, h->planar, variant, h->n_work, n_tx_bucket, h->forced_splits), h->taper);
+        RMB_CK(h, h->far_part.ensure((size_t)h->splits.s2 * (size_t)std::max(h->n_work, 1)));
         RMB_CK(h, h->stg_f.ensure(std::max(n_tx, 1))); RMB_CK(h, h->stg_theta.ensure(std::max(n_tx, 1))); RMB_CK(h, h->stg_gid.ensure(std::max(n_tx, 1)));
         if (h->key.cap == 0 && (rc = ensure_pairs(h, std::min<long long>(h->cfg.max_pairs, std::max(2ll * h->n_work, 1024ll))))) return rc;
         TxStage stg{h->stg_f.p, h->stg_theta.p, h->stg_gid.p};
@@ -754,6 +759,7 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
                 RMB_CK(h, cudaMemsetAsync(h->cnt.p, 0, (size_t)h->n_work * sizeof(int), h->st));
                 RMB_CK(h, cudaMemsetAsync(h->tx_cnt.p, 0, ((size_t)n_tx + 1) * sizeof(int), h->st));
                 RMB_CK(h, cudaMemsetAsync(h->rx_done.p, 0, 2 * ((size_t)h->n_work / 32 + 1) * sizeof(int), h->st));
+                RMB_CK(h, cudaMemsetAsync(h->bar.p + 2, 0, sizeof(unsigned), h->st));
                 RMB_CK(h, cudaEventRecord(h->ev[1], h->st));
             }
             // exact resolve (decisions + dense pair records, then the per-packet segment offsets): fused into the
@@ -762,8 +768,8 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
             PairRecs pr = pair_recs(h);
             PairArrays pa = pair_arrays(h);
             SweepFuse fuse{};
-            fuse.rb_spin = h->fuse_resolve ? sweep_spin_first_rx_block(mode, h->planar, variant, h->n_work, h->splits) : -1;
-            fuse.enabled = fuse.rb_spin >= 0 ? 1 : 0;
+            fuse.rb_spin = h->splits.rb_taper;
+            fuse.enabled = (h->fuse_resolve && h->splits.can_fuse) ? 1 : 0;
             fuse.wk = wk; fuse.dp = h->dp.p; fuse.rec = d_rec; fuse.sl = sl; fuse.pr = pr; fuse.ctr = h->ctr.p;
             fuse.n_tx = n_tx; fuse.seg = h->seg.p; fuse.rx_done = h->rx_done.p; fuse.rx_pass = h->rx_done.p + (h->n_work / 32 + 1);
             RMB_CK(h, launch_sweep(mode, h->planar, variant, h->n_work, h->splits, a, fuse, h->st));
@@ -773,20 +779,30 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
                 RMB_CK(h, launch_resolve(nd, wk, h->dp.p, tx, d_rec, sl, pr, h->ctr.p, n_tx, h->seg.p, 0, h->st));
                 launches += 1;
             }
-            // guard-band receivers: exact sums on a side stream, overlapped with the ordering
-            RMB_CK(h, cudaEventRecord(h->ev_fork, h->st));
-            RMB_CK(h, cudaStreamWaitEvent(h->st2, h->ev_fork, 0));
-            const int rgrid = recheck_grid();
-            h->bar2_count += (unsigned)rgrid;
-            RMB_CK(h, launch_recheck(nd, wk, h->dp.p, h->groups, tx, d_rec, sl, pr, h->ctr.p, h->recheck_part.p, rgrid,
-                                     h->bar.p + 1, h->bar2_count, h->st2)); launches += 2;
-            RMB_CK(h, cudaEventRecord(h->ev_join, h->st2));
+            const bool dev_publish = !draws && n_tx > 0 && h->fuse_finish;
             RMB_CK(h, cudaEventRecord(h->ev[3], h->st));
-            RMB_CK(h, launch_order_buckets(pr, h->ctr.p, n_tx, h->seg.p, h->key_alt.p, h->val.p, h->st)); launches += 2;
-            RMB_CK(h, cudaStreamWaitEvent(h->st, h->ev_join, 0));
-            // deterministic reception: the emit kernel's last block stores the counters into the pinned host copy
-            const bool dev_publish = !draws && n_tx > 0;
-            if (!draws) { RMB_CK(h, launch_emit_sinr(nd, h->dp.p, d_rec, n_tx, pr, h->val.p, pa, -1, false, h->ctr.p, h->h_ctr.p, h->st)); launches += 1; }
+            if (!draws && h->fuse_finish && n_tx <= 0) {
+                // nothing on the air: no launch (and no barrier arrivals to account for)
+            } else if (!draws && h->fuse_finish) {
+                // deterministic reception: guard-band recheck, ordering and output rows in one cooperative kernel,
+                // whose last block stores the counters into the pinned host copy
+                const int fgrid = finish_grid();
+                RMB_CK(h, launch_finish(wk, h->dp.p, h->groups, tx, d_rec, sl, pr, pa, n_tx, h->seg.p, h->key_alt.p, h->recheck_part.p,
+                                        h->ctr.p, h->h_ctr.p, fgrid, h->bar.p + 2, h->st));
+                launches += 1;
+            } else {
+                // guard-band receivers: exact sums on a side stream, overlapped with the ordering
+                RMB_CK(h, cudaEventRecord(h->ev_fork, h->st));
+                RMB_CK(h, cudaStreamWaitEvent(h->st2, h->ev_fork, 0));
+                const int rgrid = recheck_grid();
+                h->bar2_count += (unsigned)rgrid;
+                RMB_CK(h, launch_recheck(nd, wk, h->dp.p, h->groups, tx, d_rec, sl, pr, h->ctr.p, h->recheck_part.p, rgrid,
+                                         h->bar.p + 1, h->bar2_count, h->st2)); launches += 2;
+                RMB_CK(h, cudaEventRecord(h->ev_join, h->st2));
+                RMB_CK(h, launch_order_buckets(pr, h->ctr.p, n_tx, h->seg.p, h->key_alt.p, h->val.p, h->st)); launches += 2;
+                RMB_CK(h, cudaStreamWaitEvent(h->st, h->ev_join, 0));
+                if (!draws) { RMB_CK(h, launch_emit_sinr(nd, h->dp.p, d_rec, n_tx, pr, h->val.p, pa, -1, false, h->ctr.p, nullptr, h->st)); launches += 1; }
+            }
             RMB_CK(h, cudaEventRecord(h->ev[4], h->st));
             if (h->async_mode && attempt == 0 && !draws) {
                 // enqueue only: the counters travel to the host behind the tick, finish_pending looks at them

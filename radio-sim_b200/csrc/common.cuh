@@ -78,13 +78,25 @@ __device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned *p)
     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
+constexpr unsigned long long kBarrierWaitNs = 5ull * 1000 * 1000 * 1000;
 __device__ __forceinline__ void grid_barrier(unsigned *bar, unsigned target)
 {
     __syncthreads();
     if (threadIdx.x == 0) {
         __threadfence();
         atomicAdd(bar, 1u);
-        while ((int)(ld_acquire_gpu(bar) - target) < 0) { }
+        // a barrier that never completes (host and device disagreeing about the arrival count) must not hang
+        // the GPU: after kBarrierWaitNs the kernel traps and the host sees a launch failure
+        unsigned spins = 0;
+        unsigned long long t0 = 0;
+        while ((int)(ld_acquire_gpu(bar) - target) < 0) {
+            if ((++spins & 0xfffu) == 0) {
+                unsigned long long now;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+                if (t0 == 0) t0 = now;
+                else if (now - t0 > kBarrierWaitNs) __trap();
+            }
+        }
         __threadfence();
     }
     __syncthreads();

@@ -68,20 +68,22 @@ int sweep_plan(int mode, bool planar, int variant, int n_work, int n_tx_bucket, 
 // The sweep's fused epilogue (128-thread variants): the last tx-split block of an rx block resolves its receivers
 // (exact decisions, pair records) and the last rx block scans the per-packet counts -- see resolve_body.cuh.
 struct SlotArrays; struct PairRecs;
-int sweep_spin_first_rx_block(int mode, bool planar, int variant, int n_work, int splits);
+struct SweepSplits { int s1, s2, rb_taper, block_rx; bool can_fuse; };
+SweepSplits sweep_splits(int mode, bool planar, int variant, int n_work, int n_tx_bucket, int s1, int taper);
 
 // ---- exact resolve of the near candidates + guard-band recheck --------------------------------
 struct SlotArrays {
     int K;
     int *slots;                       // [n_work*K] bucket position j of the candidate (resolve sorts them ascending)
     int *cnt;                         // [n_work] candidates found (may exceed K => retry)
-    float *far_part;                  // [splits][n_work] fp32 partial far-field interference sums [mW]
-    int splits;
+    float *far_part;                  // [max splits][n_work] fp32 partial far-field interference sums [mW]
+    int splits, splits2, w_taper;     // receivers < w_taper were swept in `splits` tx splits, the others in `splits2`
     double *prx, *lin, *sinr;         // [n_work*K] exact values per candidate
     uint8_t *flags;                   // [n_work*K] kHeard | kDecodable
     int *hcnt;                        // [n_work] heard pairs of the receiver
     double *itot;                     // [n_work] total in-band power [mW]
     int *recheck;                     // receivers inside the SINR guard band
+    int *recheck_cnt;                 // [entry of recheck] partial sums stored so far (zeroed when the entry is appended)
     int *recheck2;                    // of those, the ones the tree sum cannot decide (sequential redo)
     int *first;                       // [n_work] first pair record of the receiver (its heard slots follow in slot order)
 };
@@ -102,7 +104,7 @@ struct SweepFuse {
     int *rx_done, *rx_pass;           // [rx blocks] splits finished / resolve passes claimed (zero on entry)
     int rb_spin;                      // rx blocks >= rb_spin: the last R finishers share the resolve passes
 };
-cudaError_t launch_sweep(int mode, bool planar, int variant, int n_work, int splits, const SweepArgs &a, const SweepFuse &fuse,
+cudaError_t launch_sweep(int mode, bool planar, int variant, int n_work, SweepSplits splits, const SweepArgs &a, const SweepFuse &fuse,
                          cudaStream_t st);
 // also turns the per-packet heard counts into segment offsets (seg[t] = first pair of packet t, exclusive scan
 // of pr.tx_cnt; largest bucket -> ctr->max_bucket): done by the last block to finish
@@ -117,6 +119,15 @@ int recheck_grid();
 cudaError_t launch_recheck(const NodeArrays &nd, const WorkArrays &wk, const DevParams *dp, Groups groups, TxTiles tx,
                            const rmb_tx_record *rec, SlotArrays sl, PairRecs pr, Counters *ctr, double *part, int grid,
                            unsigned *bar, unsigned bar_target, cudaStream_t st);
+
+struct PairArrays;
+// everything behind the sweep of a deterministic-reception tick in one cooperative kernel (finish.cu): guard-band
+// recheck, bucket placement, per-packet ranking and the output rows.  bar: a counter that is ZERO at launch.
+// part: >= n_work + grid doubles; items: >= record capacity
+int finish_grid();
+cudaError_t launch_finish(const WorkArrays &wk, const DevParams *dp, Groups groups, TxTiles tx, const rmb_tx_record *rec,
+                          SlotArrays sl, PairRecs pr, PairArrays pa, int n_tx, const int *seg, unsigned long long *items,
+                          double *part, Counters *ctr, Counters *host_ctr, int grid, unsigned *bar, cudaStream_t st);
 
 // ---- emission: compaction, (tx,rx) ordering, stochastic rule, outputs -------------------------
 struct PairArrays {

@@ -69,38 +69,6 @@ cudaError_t launch_node_info(const WorkArrays &wk, SlotArrays sl, float *node_rs
 //   tier 2: for those (practically only constructed test cases) the ADDITION is redone strictly
 //           sequentially in arrival order, bit-identical to the Java/C loop, pipelined over
 //           double-buffered chunks (one adder thread, 31 warps evaluating the next chunk).
-__device__ __forceinline__ double exact_lin(const DevParams *dp, const rmb_tx_record &r, int self, double X, double Y, double Z)
-{
-    // itot + 0.0 == itot: skipping the source is the same as adding zero
-    if (r.src == self) return 0.0;
-    return xm::dbm_to_mw(rx_power_dbm(dp, r.power_dbm, xm::distance(r.x, r.y, r.z, X, Y, Z)));
-}
-
-// writes the receiver's total and the SINR / flags of its heard slots and pair records; returns
-// true if some decision is closer to the threshold than tol_rel (relative uncertainty of itot) allows
-__device__ bool apply_itot(const DevParams *dp, SlotArrays sl, PairRecs pr, int w, double itot, double tol_rel)
-{
-    bool close = false;
-    const int c = min(sl.cnt[w], sl.K);
-    const size_t base = (size_t)w * sl.K;
-    sl.itot[w] = itot;
-    int h = 0;                                   // the receiver's records follow first[w] in slot order (heard slots only)
-    for (int s = 0; s < c; ++s) {
-        if (!(sl.flags[base + s] & kHeard)) continue;
-        const double lin = sl.lin[base + s];
-        const double sinr = sinr_db(sl.prx[base + s], itot, lin);
-        const double ioth = itot - lin;
-        const double tol_db = ioth > 0.0 ? 4.342944819032518 * tol_rel * (itot / ioth) + 1e-12 : 0.0;
-        if (fabs(sinr - dp->sinr_threshold_db) <= tol_db) close = true;
-        const uint8_t f = kHeard | (sinr >= dp->sinr_threshold_db ? kDecodable : 0);
-        sl.sinr[base + s] = sinr; sl.flags[base + s] = f;
-        const long long ri = (long long)sl.first[w] + h;
-        if (ri < pr.cap) { pr.sinr[ri] = sinr; pr.flags[ri] = f; }
-        ++h;
-    }
-    return close;
-}
-
 constexpr int kRecheckThreads = 1024;          // tier 2 (sequential sum)
 constexpr int kTreeThreads = 256;              // tier 1: work unit = (flagged receiver, part of its bucket)
 constexpr int kTreeMaxParts = 64;

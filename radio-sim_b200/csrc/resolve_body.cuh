@@ -101,10 +101,11 @@ __device__ __forceinline__ void resolve_receiver(int w, const WorkArrays &wk, co
         // far field: the sweep's per-split partial sums, added in split order (deterministic)
         // (eight loads in flight at a time; a missing split adds +0.0, which changes nothing)
         double far = 0.0;
-        for (int s0 = 0; s0 < sl.splits; s0 += 8) {
+        const int nsplit = w < sl.w_taper ? sl.splits : sl.splits2;
+        for (int s0 = 0; s0 < nsplit; s0 += 8) {
             float v[8];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) v[k] = s0 + k < sl.splits ? __ldcg(&sl.far_part[(size_t)(s0 + k) * wk.n_work + w]) : 0.f;
+            for (int k = 0; k < 8; ++k) v[k] = s0 + k < nsplit ? __ldcg(&sl.far_part[(size_t)(s0 + k) * wk.n_work + w]) : 0.f;
 #pragma unroll
             for (int k = 0; k < 8; ++k) far = xm::add(far, (double)v[k]);
         }
@@ -212,9 +213,46 @@ __device__ __forceinline__ void resolve_receiver(int w, const WorkArrays &wk, co
         bool guard = false;
         for (int s = 0; s < c; ++s) guard |= (sl.flags[base + s] & kGuard) != 0;
         sl.itot[w] = itot;
-        if (guard && sl.cnt[w] <= K) sl.recheck[atomicAdd(&ctr->n_recheck, 1)] = w;
+        if (guard && sl.cnt[w] <= K) {
+            const int e = atomicAdd(&ctr->n_recheck, 1);
+            sl.recheck[e] = w; sl.recheck_cnt[e] = 0;
+        }
     }
     sl.hcnt[w] = nh;
 }
+
+// ---- guard-band recheck helpers (resolve.cu, finish.cu) ----------------------------------------
+__device__ __forceinline__ double exact_lin(const DevParams *dp, const rmb_tx_record &r, int self, double X, double Y, double Z)
+{
+    // itot + 0.0 == itot: skipping the source is the same as adding zero
+    if (r.src == self) return 0.0;
+    return xm::dbm_to_mw(rx_power_dbm(dp, r.power_dbm, xm::distance(r.x, r.y, r.z, X, Y, Z)));
+}
+
+// writes the receiver's total and the SINR / flags of its heard slots and pair records; returns
+// true if some decision is closer to the threshold than tol_rel (relative uncertainty of itot) allows
+__device__ __forceinline__ bool apply_itot(const DevParams *dp, SlotArrays sl, PairRecs pr, int w, double itot, double tol_rel)
+{
+    bool close = false;
+    const int c = min(sl.cnt[w], sl.K);
+    const size_t base = (size_t)w * sl.K;
+    sl.itot[w] = itot;
+    int h = 0;                                   // the receiver's records follow first[w] in slot order (heard slots only)
+    for (int s = 0; s < c; ++s) {
+        if (!(sl.flags[base + s] & kHeard)) continue;
+        const double lin = sl.lin[base + s];
+        const double sinr = sinr_db(sl.prx[base + s], itot, lin);
+        const double ioth = itot - lin;
+        const double tol_db = ioth > 0.0 ? 4.342944819032518 * tol_rel * (itot / ioth) + 1e-12 : 0.0;
+        if (fabs(sinr - dp->sinr_threshold_db) <= tol_db) close = true;
+        const uint8_t f = kHeard | (sinr >= dp->sinr_threshold_db ? kDecodable : 0);
+        sl.sinr[base + s] = sinr; sl.flags[base + s] = f;
+        const long long ri = (long long)sl.first[w] + h;
+        if (ri < pr.cap) { pr.sinr[ri] = sinr; pr.flags[ri] = f; }
+        ++h;
+    }
+    return close;
+}
+
 
 }  // namespace rmb

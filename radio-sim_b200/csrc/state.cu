@@ -325,7 +325,7 @@ prepare_all_kernel(NodeArrays nd, const DevParams *dp, const Geom *geom, Groups 
         for (int i = gtid; i < aux.n_work / 4; i += gsz) c4[i] = make_int4(0, 0, 0, 0);
         for (int i = gtid; i <= n_tx; i += gsz) aux.tx_cnt[i] = 0;
         for (int i = gtid; i < aux.n_rx_done; i += gsz) aux.rx_done[i] = 0;
-        if (gtid == 0) *ctr = Counters{};
+        if (gtid == 0) { *ctr = Counters{}; aux.bar[2] = 0u; }      // bar[2]: the barrier counter of finish.cu, zero at its launch
     }
     __syncthreads();
 

@@ -77,7 +77,7 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 128 && R == 4) ? 9 : 1)
 sweep_kernel(const float *__restrict__ fx, const float *__restrict__ fy, const float *__restrict__ fz,
              Groups groups, TxTiles tx, const float *__restrict__ theta, const float *__restrict__ theta_min_g,
              float neg_h, float *__restrict__ far_part, int *__restrict__ cnt, int *__restrict__ slots,
-             int K, int n_work, int S, SweepFuse fuse)
+             int K, int n_work, int S1, int S2, int rb_taper, SweepFuse fuse)
 {
     // one stage buffer, carved
     __shared__ __align__(16) float s_stage[(PLANAR ? 4 : 5) * kStage];
@@ -86,7 +86,13 @@ sweep_kernel(const float *__restrict__ fx, const float *__restrict__ fy, const f
 
     // block = (rx block, tx split), splits of one rx block adjacent: receivers complete progressively
     // over the launch, so the fused exact resolve runs in the shadow of the other blocks' sweeps
-    const int rb = blockIdx.x / S, split = blockIdx.x - rb * S;
+    // The last rx blocks of the launch (rb >= rb_taper, about its final wave) are cut into S2 > S1 splits: shorter
+    // blocks where the launch runs out of work, so the SMs go idle closer together.
+    const int n1 = rb_taper * S1;
+    const bool tapered = (int)blockIdx.x >= n1;
+    const int S = tapered ? S2 : S1;
+    const int bb = tapered ? (int)blockIdx.x - n1 : (int)blockIdx.x;
+    const int rb = (tapered ? rb_taper : 0) + bb / S, split = bb % S;
     const int w0 = (rb * THREADS + threadIdx.x) * R;
     // the block's receivers all belong to one channel group (groups are padded to 1024)
     const int wb = rb * THREADS * R;
@@ -313,19 +319,25 @@ int sweep_plan(int mode, bool planar, int variant, int n_work, int n_tx_bucket, 
     return min(max_s, max(best, n_tx_bucket / kTargetSplitTx));
 }
 
-// first rx block of the launch's final wave (with a margin), where the finishers of an rx block share the resolve
-// passes; -1: the variant cannot fuse the resolve (launch_resolve does it)
-int sweep_spin_first_rx_block(int mode, bool planar, int variant, int n_work, int splits)
+// The launch's final wave (with a margin): rx blocks >= rb_taper are cut into s2 = taper * s1 splits (shorter blocks
+// where the work runs out), and -- when the variant fuses the resolve -- the last finishers of such an rx block
+// share its resolve passes.  n_tx_bucket bounds s2 (every split keeps >= 128 transmissions).
+SweepSplits sweep_splits(int mode, bool planar, int variant, int n_work, int n_tx_bucket, int s1, int taper)
 {
     const SweepVariant v = pick(mode, planar, variant);
-    if (v.threads != 128) return -1;
     const int sms = device_sms(), occ = variant_occupancy(v);
     const int nb = n_work / (v.R * v.threads);
-    const int tail = (int)ceil(1.25 * sms * occ / max(1, splits));
-    return max(0, nb - tail);
+    const int tail = (int)ceil(1.25 * sms * occ / max(1, s1));
+    SweepSplits sp;
+    sp.s1 = max(1, s1);
+    sp.s2 = max(sp.s1, min(min(128, sp.s1 * max(1, taper)), max(1, n_tx_bucket / 128)));
+    sp.rb_taper = max(0, nb - tail);
+    sp.block_rx = v.R * v.threads;
+    sp.can_fuse = v.threads == 128;
+    return sp;
 }
 
-cudaError_t launch_sweep(int mode, bool planar, int variant, int n_work, int splits, const SweepArgs &a, const SweepFuse &fuse,
+cudaError_t launch_sweep(int mode, bool planar, int variant, int n_work, SweepSplits splits, const SweepArgs &a, const SweepFuse &fuse,
                          cudaStream_t st)
 {
     if (n_work <= 0) return cudaSuccess;
@@ -333,11 +345,13 @@ cudaError_t launch_sweep(int mode, bool planar, int variant, int n_work, int spl
     SweepArgs b = a;
     SweepFuse f = fuse;
     if (v.threads != 128) f.enabled = 0;
-    int nw = n_work, S = max(1, splits);
+    int nw = n_work, S1 = max(1, splits.s1), S2 = max(1, splits.s2), rbt = splits.rb_taper;
+    const int nb = n_work / (v.R * v.threads);
+    rbt = max(0, min(rbt, nb));
     void *args[] = {(void *)&b.fx, (void *)&b.fy, (void *)&b.fz, (void *)&b.groups, (void *)&b.tx, (void *)&b.theta,
                     (void *)&b.theta_min_g, (void *)&b.neg_h, (void *)&b.far_part, (void *)&b.cnt, (void *)&b.slots,
-                    (void *)&b.K, (void *)&nw, (void *)&S, (void *)&f};
-    const long long blocks = (long long)(n_work / (v.R * v.threads)) * S;
+                    (void *)&b.K, (void *)&nw, (void *)&S1, (void *)&S2, (void *)&rbt, (void *)&f};
+    const long long blocks = (long long)rbt * S1 + (long long)(nb - rbt) * S2;
     if (blocks > 0x7fffffffll) return cudaErrorInvalidConfiguration;
     return cudaLaunchKernel(v.fn, dim3((unsigned)blocks), dim3((unsigned)v.threads), args, 0, st);
 }

@@ -35,7 +35,9 @@ def run_case(rsb, orc, x, y, z, ch, src, power=None, pkt_channel=None, enabled=N
     return r, ref
 
 
-@pytest.mark.parametrize("variant", [0, 2, 3, 4, 5, 6, 7, 8])
+# sweep variants, then tuning bits: 0x10000 stand-alone resolve kernel, 0x20000 / 0x80000 final-wave split multiplier 1 / 4,
+# 0x100000 separate recheck / ordering / emit kernels instead of the one finish kernel
+@pytest.mark.parametrize("variant", [0, 2, 3, 4, 5, 6, 7, 8, 0x10000, 0x20000, 0x80000, 0x100000, 0x110000])
 def test_config2_1k_nodes_50_tx(rsb, orc, variant):
     x, y, z, ch = random_deployment(1, 1000, 1000.0)
     r, _ = run_case(rsb, orc, x, y, z, ch, pick_sources(1, 1000, 50), variant=variant)
@@ -46,6 +48,15 @@ def test_dense_all_hear_all_grows_slots(rsb, orc):
     x, y, z, ch = random_deployment(2, 600, 60.0)
     r, _ = run_case(rsb, orc, x, y, z, ch, pick_sources(2, 600, 40))
     assert r.near_slots >= 32
+
+
+@pytest.mark.parametrize("n,tuning", [(50, 0), (300, 0), (900, 0), (1500, 0), (300, 0x100000)])
+def test_every_bucket_ranking_path(rsb, orc, n, tuning):
+    """All nodes within hearing distance: a packet's bucket holds ~n pairs -- one warp (<= 64), counting in a block
+    (<= 512), bitonic sort in a block (<= 2048) in finish.cu."""
+    x, y, z, ch = random_deployment(20 + n, n, 40.0)
+    r, _ = run_case(rsb, orc, x, y, z, ch, pick_sources(n, n, 12), variant=tuning)
+    assert r.n_pairs >= 12 * (n - 12)
 
 
 def test_three_dimensional(rsb, orc):
