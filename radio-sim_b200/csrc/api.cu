@@ -14,6 +14,7 @@
 #include <unistd.h>
 #include <string>
 #include <vector>
+#include <vector>
 
 using namespace rmb;
 
@@ -92,7 +93,8 @@ struct rmb_handle {
 
     // slots
     int K = 8;
-    DevBuf<int> slots, cnt, hcnt, hoff, recheck, recheck2, recheck_cnt; DevBuf<float> far_part; SweepSplits splits{1, 1, 0, 512, false}; int forced_splits = 0, taper = 2;
+    DevBuf<unsigned long long> trace;      // debug: per-block time stamps of the sweep (RMB_SWEEP_TRACE=<file>)
+    DevBuf<int> slots, cnt, hcnt, hoff, recheck, recheck2, recheck_cnt; DevBuf<float> far_part; SweepSplits splits{1, 1, 0, 0, 512, false}; int forced_splits = 0, taper = 2, fine8 = 4;
     DevBuf<double> sl_prx, sl_lin, sl_sinr, itot; DevBuf<uint8_t> sl_flags;
 
     // pairs
@@ -550,6 +552,7 @@ extern "C" int rmb_set_tuning(rmb_handle *h, int32_t sweep_variant, int32_t near
     h->forced_splits = (sweep_variant >> 8) & 0xff;
     h->fuse_resolve = ((sweep_variant >> 16) & 1) == 0;
     h->fuse_finish = ((sweep_variant >> 20) & 1) == 0;
+    h->fine8 = ((sweep_variant >> 21) & 7) ? ((sweep_variant >> 21) & 7) : 4;       // bits 21..23: eighths of a wave resolved in 32-receiver passes (7: none)
     h->taper = ((sweep_variant >> 17) & 7) ? ((sweep_variant >> 17) & 7) : 2;      // bits 17..19: split multiplier of the final wave
     if (near_slots > 0 && near_slots != h->K) { h->K = near_slots; return ensure_slots(h); }
     return RMB_OK;
@@ -725,7 +728,7 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
         const int variant = h->sweep_variant ? h->sweep_variant : 1;
         const int n_tx_bucket = n_tx / std::max(1, h->groups.ngroups);
         h->splits = sweep_splits(mode, h->planar, variant, h->n_work, n_tx_bucket,
-                                 sweep_plan(mode, h->planar, variant, h->n_work, n_tx_bucket, h->forced_splits), h->taper);
+                                 sweep_plan(mode, h->planar, variant, h->n_work, n_tx_bucket, h->forced_splits), h->taper, h->fine8);
         RMB_CK(h, h->far_part.ensure((size_t)h->splits.s2 * (size_t)std::max(h->n_work, 1)));
         RMB_CK(h, h->stg_f.ensure(std::max(n_tx, 1))); RMB_CK(h, h->stg_theta.ensure(std::max(n_tx, 1))); RMB_CK(h, h->stg_gid.ensure(std::max(n_tx, 1)));
         if (h->key.cap == 0 && (rc = ensure_pairs(h, std::min<long long>(h->cfg.max_pairs, std::max(2ll * h->n_work, 1024ll))))) return rc;
@@ -768,11 +771,24 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
             PairRecs pr = pair_recs(h);
             PairArrays pa = pair_arrays(h);
             SweepFuse fuse{};
-            fuse.rb_spin = h->splits.rb_taper;
+            fuse.rb_spin = h->splits.rb_taper; fuse.rb_fine = h->splits.rb_fine;
             fuse.enabled = (h->fuse_resolve && h->splits.can_fuse) ? 1 : 0;
             fuse.wk = wk; fuse.dp = h->dp.p; fuse.rec = d_rec; fuse.sl = sl; fuse.pr = pr; fuse.ctr = h->ctr.p;
             fuse.n_tx = n_tx; fuse.seg = h->seg.p; fuse.rx_done = h->rx_done.p; fuse.rx_pass = h->rx_done.p + (h->n_work / 32 + 1);
+            static const char *trace_path = getenv("RMB_SWEEP_TRACE");
+            const size_t trace_blocks = (size_t)h->splits.rb_taper * h->splits.s1 +
+                                        (size_t)(h->n_work / h->splits.block_rx - h->splits.rb_taper) * h->splits.s2;
+            if (trace_path) { RMB_CK(h, h->trace.ensure(12 * trace_blocks + 12)); fuse.trace = h->trace.p; }
             RMB_CK(h, launch_sweep(mode, h->planar, variant, h->n_work, h->splits, a, fuse, h->st));
+            if (trace_path) {
+                std::vector<unsigned long long> tr(12 * trace_blocks);
+                RMB_CK(h, cudaMemcpyAsync(tr.data(), h->trace.p, tr.size() * 8, cudaMemcpyDeviceToHost, h->st));
+                RMB_CK(h, cudaStreamSynchronize(h->st));
+                if (FILE *f = fopen(trace_path, "wb")) {
+                    const int hdr[4] = {h->splits.s1, h->splits.s2, h->splits.rb_taper, h->n_work / h->splits.block_rx};
+                    fwrite(hdr, sizeof(int), 4, f); fwrite(tr.data(), 8, tr.size(), f); fclose(f);
+                }
+            }
             ++launches; ++sweeps;
             RMB_CK(h, cudaEventRecord(h->ev[2], h->st));
             if (!fuse.enabled) {

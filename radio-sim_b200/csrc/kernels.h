@@ -68,8 +68,8 @@ int sweep_plan(int mode, bool planar, int variant, int n_work, int n_tx_bucket, 
 // The sweep's fused epilogue (128-thread variants): the last tx-split block of an rx block resolves its receivers
 // (exact decisions, pair records) and the last rx block scans the per-packet counts -- see resolve_body.cuh.
 struct SlotArrays; struct PairRecs;
-struct SweepSplits { int s1, s2, rb_taper, block_rx; bool can_fuse; };
-SweepSplits sweep_splits(int mode, bool planar, int variant, int n_work, int n_tx_bucket, int s1, int taper);
+struct SweepSplits { int s1, s2, rb_taper, rb_fine, block_rx; bool can_fuse; };
+SweepSplits sweep_splits(int mode, bool planar, int variant, int n_work, int n_tx_bucket, int s1, int taper, int fine8);
 
 // ---- exact resolve of the near candidates + guard-band recheck --------------------------------
 struct SlotArrays {
@@ -101,8 +101,10 @@ struct SweepFuse {
     int enabled;
     WorkArrays wk; const DevParams *dp; const rmb_tx_record *rec; SlotArrays sl; PairRecs pr; Counters *ctr;
     int n_tx; int *seg;
+    unsigned long long *trace;        // debug (RMB_SWEEP_TRACE): [block][12] start / sweep done / block done [ns], smid | passes << 16, stamps of the last pass
     int *rx_done, *rx_pass;           // [rx blocks] splits finished / resolve passes claimed (zero on entry)
-    int rb_spin;                      // rx blocks >= rb_spin: the last R finishers share the resolve passes
+    int rb_spin;                      // rx blocks >= rb_spin: the last finishers of an rx block wait for its last split and share the passes
+    int rb_fine;                      // rx blocks >= rb_fine (>= rb_spin): passes of 32 receivers instead of 128
 };
 cudaError_t launch_sweep(int mode, bool planar, int variant, int n_work, SweepSplits splits, const SweepArgs &a, const SweepFuse &fuse,
                          cudaStream_t st);

@@ -19,13 +19,13 @@ resolve_kernel(NodeArrays nd, WorkArrays wk, const DevParams *dp, TxTiles tx, co
 {
     __shared__ int s_last;
     const int w = w_first + blockIdx.x * blockDim.x + threadIdx.x;       // n_work is a multiple of 1024: no partial warps
-    resolve_receiver<false>(w, wk, dp, tx, rec, sl, pr, ctr);
+    resolve_receiver<false>(w, true, wk, dp, tx, rec, sl, pr, ctr);
 
     // the last block to finish turns the per-packet counts into segment offsets
     // (barrier, then ONE fence + arrival by thread 0: the release pattern of a grid-wide semaphore)
     __syncthreads();
-    // (resolve_done counts groups of 128 receivers: the sweep's fused epilogue resolves the others)
-    if (threadIdx.x == 0) { __threadfence(); s_last = atomicAdd(&ctr->resolve_done, 1u) + 1u == (unsigned)(wk.n_work / 128); }
+    // (resolve_done counts receivers: the sweep's fused epilogue resolves the others)
+    if (threadIdx.x == 0) { __threadfence(); s_last = atomicAdd(&ctr->resolve_done, 128u) + 128u == (unsigned)wk.n_work; }
     __syncthreads();
     if (s_last) { __threadfence(); scan_tx_counts(pr.tx_cnt, n_tx, seg, ctr); }
 }

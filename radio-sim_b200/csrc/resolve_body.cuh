@@ -81,33 +81,43 @@ __device__ __forceinline__ void scan_tx_counts(const int *tx_cnt, int n_tx, int 
     if (tid == 0) { seg[n_tx] = s_w[0] + s_w[1] + s_w[2] + s_w[3]; ctr->max_bucket = max(max(s_m[0], s_m[1]), max(s_m[2], s_m[3])); }
 }
 
-// One warp = 32 consecutive receivers in work order; `w` is this lane's receiver.  All 32 lanes must call.
+// One warp = up to 32 consecutive receivers in work order: lane l stands for receiver w = w_lane0 + l and owns it
+// iff `active` (the active lanes are the first ones).  All 32 lanes must call and all of them evaluate candidates,
+// so a warp that owns only 8 receivers gets through its pooled candidates four times sooner -- what the sweep's
+// epilogue wants at the end of the launch, where latency and not throughput is what counts.
 // fresh: the candidate slots, counters and far sums were written by OTHER blocks of the running kernel
 // (fused epilogue) and are read past the L1.
 template <bool FRESH>
-__device__ __forceinline__ void resolve_receiver(int w, const WorkArrays &wk, const DevParams *dp, const TxTiles &tx,
-                                                 const rmb_tx_record *rec, const SlotArrays &sl, const PairRecs &pr, Counters *ctr)
+__device__ __forceinline__ void resolve_receiver(int w, bool active, const WorkArrays &wk, const DevParams *dp, const TxTiles &tx,
+                                                 const rmb_tx_record *rec, const SlotArrays &sl, const PairRecs &pr, Counters *ctr,
+                                                 unsigned long long *dbg = nullptr)
 {
     const int lane = threadIdx.x & 31;
     const int K = sl.K;
-    const int p = wk.perm[w];
+    if (dbg && threadIdx.x == 0) dbg[0] = global_timer_ns();
+    const int p = active ? wk.perm[w] : -1;
     const size_t base = (size_t)w * K;
     int c = 0;
     double itot = dp->n0_mw;
     if (p >= 0) {
+        // (the first eight slots are fetched before anyone knows how many are valid: independent of the count and
+        // of the far sums, so the three round trips overlap)
+        int sv[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) sv[k] = k < K ? __ldcg(&sl.slots[base + k]) : INT_MAX;
         const int found = FRESH ? __ldcg(&sl.cnt[w]) : sl.cnt[w];
         if (found > K) atomicMax(&ctr->max_near, found);      // slot overflow: the host grows K and redoes the sweep
         c = min(found, K);
         // far field: the sweep's per-split partial sums, added in split order (deterministic)
-        // (eight loads in flight at a time; a missing split adds +0.0, which changes nothing)
+        // (sixteen loads in flight at a time; a missing split adds +0.0, which changes nothing)
         double far = 0.0;
         const int nsplit = w < sl.w_taper ? sl.splits : sl.splits2;
-        for (int s0 = 0; s0 < nsplit; s0 += 8) {
-            float v[8];
+        for (int s0 = 0; s0 < nsplit; s0 += 16) {
+            float v[16];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) v[k] = s0 + k < nsplit ? __ldcg(&sl.far_part[(size_t)(s0 + k) * wk.n_work + w]) : 0.f;
+            for (int k = 0; k < 16; ++k) v[k] = s0 + k < nsplit ? __ldcg(&sl.far_part[(size_t)(s0 + k) * wk.n_work + w]) : 0.f;
 #pragma unroll
-            for (int k = 0; k < 8; ++k) far = xm::add(far, (double)v[k]);
+            for (int k = 0; k < 16; ++k) far = xm::add(far, (double)v[k]);
         }
         itot = xm::add(itot, far);
         // the sweep appends near candidates in arbitrary order: sort by bucket position (= arrival order)
@@ -115,7 +125,7 @@ __device__ __forceinline__ void resolve_receiver(int w, const WorkArrays &wk, co
             // the common case in registers: independent loads, odd-even transposition network, one write back
             int v[8];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) v[k] = k < c ? __ldcg(&sl.slots[base + k]) : INT_MAX;
+            for (int k = 0; k < 8; ++k) v[k] = k < c ? sv[k] : INT_MAX;
 #pragma unroll
             for (int round = 0; round < 8; ++round)
 #pragma unroll
@@ -137,6 +147,7 @@ __device__ __forceinline__ void resolve_receiver(int w, const WorkArrays &wk, co
     const int total = __shfl_sync(0xffffffffu, incl, 31);
     const size_t wbase = (size_t)(w - lane) * K;
     __syncwarp();
+    if (dbg && threadIdx.x == 0) dbg[1] = global_timer_ns();
 
     // pass 1 (pooled): link budget of every candidate
     for (int i0 = 0; i0 < total; i0 += 32) {
@@ -161,6 +172,7 @@ __device__ __forceinline__ void resolve_receiver(int w, const WorkArrays &wk, co
     }
     __syncwarp();
 
+    if (dbg && threadIdx.x == 0) dbg[2] = global_timer_ns();
     // per receiver: total in-band power, near terms added in arrival order
     int nh = 0;
     for (int s = 0; s < c; ++s) {
@@ -177,8 +189,9 @@ __device__ __forceinline__ void resolve_receiver(int w, const WorkArrays &wk, co
     unsigned long long rbase = 0;
     if (lane == 0 && wtotal) rbase = atomicAdd(&ctr->heard, (unsigned long long)wtotal);
     rbase = __shfl_sync(0xffffffffu, rbase, 0);
-    sl.first[w] = (int)rbase + hincl - nh;
+    if (active) sl.first[w] = (int)rbase + hincl - nh;
 
+    if (dbg && threadIdx.x == 0) { dbg[3] = global_timer_ns(); dbg[5] = (unsigned long long)total; }
     // pass 2 (pooled): SINR of every heard candidate, pair record
     int running = 0;
     for (int i0 = 0; i0 < total; i0 += 32) {
@@ -218,7 +231,7 @@ __device__ __forceinline__ void resolve_receiver(int w, const WorkArrays &wk, co
             sl.recheck[e] = w; sl.recheck_cnt[e] = 0;
         }
     }
-    sl.hcnt[w] = nh;
+    if (active) sl.hcnt[w] = nh;
 }
 
 // ---- guard-band recheck helpers (resolve.cu, finish.cu) ----------------------------------------

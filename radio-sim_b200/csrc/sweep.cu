@@ -88,6 +88,7 @@ sweep_kernel(const float *__restrict__ fx, const float *__restrict__ fy, const f
     // over the launch, so the fused exact resolve runs in the shadow of the other blocks' sweeps
     // The last rx blocks of the launch (rb >= rb_taper, about its final wave) are cut into S2 > S1 splits: shorter
     // blocks where the launch runs out of work, so the SMs go idle closer together.
+    if (fuse.trace && threadIdx.x == 0) fuse.trace[12 * (size_t)blockIdx.x] = global_timer_ns();
     const int n1 = rb_taper * S1;
     const bool tapered = (int)blockIdx.x >= n1;
     const int S = tapered ? S2 : S1;
@@ -202,21 +203,32 @@ sweep_kernel(const float *__restrict__ fx, const float *__restrict__ fy, const f
     float *out = far_part + (size_t)split * n_work + w0;
 #pragma unroll
     for (int r = 0; r < R; ++r) out[r] = sum[r];
+    if (fuse.trace && threadIdx.x == 0) {
+        unsigned smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        fuse.trace[12 * (size_t)blockIdx.x + 1] = global_timer_ns();
+        fuse.trace[12 * (size_t)blockIdx.x + 2] = 0ull;
+        fuse.trace[12 * (size_t)blockIdx.x + 3] = smid;
+        fuse.trace[12 * (size_t)blockIdx.x + 10] = 0ull;
+    }
 
     // ---- fused epilogue: the exact decisions of the rx block's receivers (resolve_body.cuh) are taken by the
     // sweep blocks themselves -- double-precision, latency-bound work on pipes the sweep leaves idle, hidden behind
     // the other resident blocks instead of being a kernel of its own after the sweep.  The LAST split of an rx
     // block to finish does it, in R passes of 128 receivers claimed through a per-rx-block counter.  In the
-    // launch's final wave (rb >= rb_spin; nothing is waiting for a block slot there) the R-1 finishers before the
-    // last one wait for it and share the passes, so that the end of the launch is ONE pass deep, not R.
+    // launch's final wave (rb >= rb_spin; nothing is waiting for a block slot there) what counts is how soon the
+    // last receiver is resolved, not throughput: the passes are 32 receivers there (8 per warp, all 32 lanes
+    // evaluating their pooled candidates), and the 4R - 1 finishers before the last one wait for it and share them.
     if (THREADS == 128 && fuse.enabled) {
         __shared__ int s_role, s_q, s_flag;
+        const bool fine = rb >= fuse.rb_fine;
+        const int npass = fine ? R * (THREADS / 32) : R, pass_rx = fine ? 32 : THREADS;
         __syncthreads();
         if (threadIdx.x == 0) {
             __threadfence();
             const int k = atomicAdd(&fuse.rx_done[rb], 1);
             int role = k == S - 1;
-            if (!role && rb >= fuse.rb_spin && k >= S - R) {
+            if (!role && rb >= fuse.rb_spin && k >= S - npass) {
                 const unsigned *done = reinterpret_cast<const unsigned *>(&fuse.rx_done[rb]);
                 const unsigned long long t0 = global_timer_ns();
                 while (ld_acquire_gpu(done) < (unsigned)S && global_timer_ns() - t0 < 500000ull) __nanosleep(200);
@@ -232,15 +244,26 @@ sweep_kernel(const float *__restrict__ fx, const float *__restrict__ fy, const f
                 __syncthreads();
                 const int q = s_q;
                 __syncthreads();
-                if (q >= R) break;
-                resolve_receiver<true>(wb + q * THREADS + (int)threadIdx.x, fuse.wk, fuse.dp, tx, fuse.rec, fuse.sl, fuse.pr, fuse.ctr);
-                // the last group of 128 receivers of the launch turns the per-packet heard counts into segment offsets
+                if (q >= npass) break;
+                if (fuse.trace && threadIdx.x == 0) fuse.trace[12 * (size_t)blockIdx.x + 3] += 1ull << 16;
+                const int lane = threadIdx.x & 31, wv = threadIdx.x >> 5;
+                const int w = fine ? wb + q * 32 + wv * 8 + lane : wb + q * THREADS + (int)threadIdx.x;
+                resolve_receiver<true>(w, !fine || lane < 8, fuse.wk, fuse.dp, tx, fuse.rec, fuse.sl, fuse.pr, fuse.ctr,
+                                       fuse.trace ? fuse.trace + 12 * (size_t)blockIdx.x + 4 : nullptr);
+                if (fuse.trace && threadIdx.x == 0) fuse.trace[12 * (size_t)blockIdx.x + 8] = global_timer_ns();
+                // the last group of receivers of the launch turns the per-packet heard counts into segment offsets
                 __syncthreads();
-                if (threadIdx.x == 0) { __threadfence(); s_flag = atomicAdd(&fuse.ctr->resolve_done, 1u) + 1u == (unsigned)(n_work / 128); }
+                if (threadIdx.x == 0) { __threadfence(); s_flag = atomicAdd(&fuse.ctr->resolve_done, (unsigned)pass_rx) + (unsigned)pass_rx == (unsigned)n_work; }
                 __syncthreads();
-                if (s_flag) { __threadfence(); scan_tx_counts(fuse.pr.tx_cnt, fuse.n_tx, fuse.seg, fuse.ctr); }
+                if (s_flag) {
+                    __threadfence();
+                    if (fuse.trace && threadIdx.x == 0) fuse.trace[12 * (size_t)blockIdx.x + 10] = global_timer_ns();
+                    scan_tx_counts(fuse.pr.tx_cnt, fuse.n_tx, fuse.seg, fuse.ctr);
+                    if (fuse.trace && threadIdx.x == 0) fuse.trace[12 * (size_t)blockIdx.x + 11] = global_timer_ns();
+                }
             }
         }
+        if (fuse.trace && threadIdx.x == 0) fuse.trace[12 * (size_t)blockIdx.x + 2] = global_timer_ns();
     }
 }
 
@@ -321,8 +344,9 @@ int sweep_plan(int mode, bool planar, int variant, int n_work, int n_tx_bucket, 
 
 // The launch's final wave (with a margin): rx blocks >= rb_taper are cut into s2 = taper * s1 splits (shorter blocks
 // where the work runs out), and -- when the variant fuses the resolve -- the last finishers of such an rx block
-// share its resolve passes.  n_tx_bucket bounds s2 (every split keeps >= 128 transmissions).
-SweepSplits sweep_splits(int mode, bool planar, int variant, int n_work, int n_tx_bucket, int s1, int taper)
+// share its resolve passes; in the last fine8/8 of a wave (rx blocks >= rb_fine) the passes are 32 receivers wide.
+// n_tx_bucket bounds s2 (every split keeps >= 128 transmissions).
+SweepSplits sweep_splits(int mode, bool planar, int variant, int n_work, int n_tx_bucket, int s1, int taper, int fine8)
 {
     const SweepVariant v = pick(mode, planar, variant);
     const int sms = device_sms(), occ = variant_occupancy(v);
@@ -332,6 +356,7 @@ SweepSplits sweep_splits(int mode, bool planar, int variant, int n_work, int n_t
     sp.s1 = max(1, s1);
     sp.s2 = max(sp.s1, min(min(128, sp.s1 * max(1, taper)), max(1, n_tx_bucket / 128)));
     sp.rb_taper = max(0, nb - tail);
+    sp.rb_fine = fine8 >= 7 ? nb : max(sp.rb_taper, nb - (int)ceil(0.125 * fine8 * sms * occ / max(1, sp.s2)));
     sp.block_rx = v.R * v.threads;
     sp.can_fuse = v.threads == 128;
     return sp;
