@@ -215,6 +215,8 @@ def run_ours(args):
         exchange()
         return med.tick_records(n_rec, rec_all.data_ptr(), copy=False)
 
+    align_token = torch.zeros(1, device=dev)
+
     def timed(fn, steps, sampler=None):
         times, walls, res, sweep_ms, launches = [], [], None, [], 0
         for _ in range(steps):
@@ -226,6 +228,11 @@ def run_ours(args):
             if sampler:
                 sampler.active = True
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            if G > 1 and fn is step_resident:
+                # (device-timed leg only) the ranks leave the host barrier microseconds apart; a collective enqueued (not waited for) right
+                # before the start event lines the streams up on the device, so that one rank's host jitter is not
+                # timed as another rank's wait for its records
+                dist.all_reduce(align_token)
             t0 = time.perf_counter()
             e0.record(stream)
             res = fn()
@@ -289,8 +296,9 @@ def run_ours(args):
                            "transmitters": N_TX, "parallelism": f"receivers sharded x{G}",
                            "exchange": "none" if G == 1 else ("peer-memory stores + flags (rmb_peer_push)" if p2p else "NCCL all-gather"),
                            "l2": "flushed (256 MiB write) before every timed step",
-                           "timing": "CUDA events on the stream the library and NCCL run on, per step, summed, max over ranks; "
-                                     "e2e: host wall clock around the public C-ABI call with host buffers"},
+                           "timing": "CUDA events on the stream the library and NCCL run on, per step, summed, max over ranks"
+                                     + ("" if G == 1 else " (an NCCL all-reduce enqueued right before the start event lines the ranks up on the device)")
+                                     + "; e2e: host wall clock around the public C-ABI call with host buffers"},
                 "clocks": clocks,
                 "e2e": {"value": decisions * args.steps / t_e2e, "unit": UNIT, "ms_per_step": 1e3 * t_e2e / args.steps,
                         "h2d_bytes_per_step": int(4 * (src.size if G == 1 else tpad)),
@@ -373,6 +381,8 @@ def run_c5(args):
         mine[:m.size] = m
         return src, mine, tpad
 
+    align_token = torch.zeros(1, device=dev)
+
     def timed(kind, steps, sampler=None):
         times, dec, pairs, sweep_ms, launches = [], 0, 0, [], 0
         for _ in range(steps):
@@ -388,6 +398,8 @@ def run_c5(args):
             if sampler:
                 sampler.active = True
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            if G > 1 and kind == "resident":
+                dist.all_reduce(align_token)            # line the ranks' streams up on the device (see run_ours)
             t0 = time.perf_counter()
             e0.record(stream)
             if kind == "resident":

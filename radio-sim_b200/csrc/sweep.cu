@@ -354,9 +354,17 @@ SweepSplits sweep_splits(int mode, bool planar, int variant, int n_work, int n_t
     const int tail = (int)ceil(1.25 * sms * occ / max(1, s1));
     SweepSplits sp;
     sp.s1 = max(1, s1);
-    sp.s2 = max(sp.s1, min(min(128, sp.s1 * max(1, taper)), max(1, n_tx_bucket / 128)));
+    // a launch of fewer than three waves is "final wave" almost everywhere (16 channel groups of 625 transmissions
+    // each: 1.5 waves of 8 us blocks): cutting its blocks further only multiplies the per-block overhead
+    const bool deep = (long long)nb * sp.s1 >= 3ll * sms * occ;
+    sp.s2 = deep ? max(sp.s1, min(min(128, sp.s1 * max(1, taper)), max(1, n_tx_bucket / 128))) : sp.s1;
     sp.rb_taper = max(0, nb - tail);
-    sp.rb_fine = fine8 >= 7 ? nb : max(sp.rb_taper, nb - (int)ceil(0.125 * fine8 * sms * occ / max(1, sp.s2)));
+    // the narrow passes trade throughput for latency: at most the last sixteenth of the receivers takes them, and
+    // only when an rx block has as many finishers (tx splits) as narrow passes to share -- with two splits per
+    // rx block (16 channel groups of 625 transmissions) they would run eight deep instead (C5: +44 us)
+    const int fine_blocks = min((int)ceil(0.125 * fine8 * sms * occ / max(1, sp.s2)), nb / 16);
+    const bool can_share = sp.s2 >= v.R * (v.threads / 32);
+    sp.rb_fine = (fine8 >= 7 || !can_share) ? nb : max(sp.rb_taper, nb - fine_blocks);
     sp.block_rx = v.R * v.threads;
     sp.can_fuse = v.threads == 128;
     return sp;
