@@ -251,7 +251,13 @@ int rmb_last_timing(const rmb_handle *h, rmb_timing *out);
  * NULL restores the handle's own stream.  No reference counterpart (device plumbing). */
 int rmb_get_stream(rmb_handle *h, void **stream);
 int rmb_set_stream(rmb_handle *h, void *stream);
-/* tuning knob for benchmarks/tests: sweep variant (0 = auto) and near-slot capacity */
+/* tuning knob for benchmarks/tests: near-slot capacity, and in `sweep_variant`
+ *   bits 0..7   sweep kernel variant (0 = auto)            bits 8..15  forced number of tx splits (0 = planned)
+ *   bit 16      stand-alone resolve kernel instead of the sweep's fused epilogue
+ *   bits 17..19 tx-split multiplier of the launch's final wave (0 = default 2, 1 = none)
+ *   bit 20      separate recheck / ordering / emit kernels instead of the one finish kernel
+ *   bits 21..23 eighths of a wave resolved in 32-receiver passes (0 = default 4, 7 = none)
+ * Results do not depend on any of these. */
 int rmb_set_tuning(rmb_handle *h, int32_t sweep_variant, int32_t near_slots);
 
 #ifdef __cplusplus
