@@ -220,7 +220,9 @@ def run_ours(args):
     def timed(fn, steps, sampler=None):
         times, walls, res, sweep_ms, launches = [], [], None, [], 0
         for _ in range(steps):
-            flush_buf.fill_(1)                      # evict L2 between timed iterations
+            device_timed = fn is step_resident
+            if not device_timed:
+                flush_buf.fill_(1)                  # evict L2 between timed iterations
             torch.cuda.synchronize()
             if G > 1:
                 dist.barrier()
@@ -228,11 +230,14 @@ def run_ours(args):
             if sampler:
                 sampler.active = True
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            if G > 1 and fn is step_resident:
-                # (device-timed leg only) the ranks leave the host barrier microseconds apart; a collective enqueued (not waited for) right
-                # before the start event lines the streams up on the device, so that one rank's host jitter is not
-                # timed as another rank's wait for its records
-                dist.all_reduce(align_token)
+            if device_timed:
+                # device-timed leg: L2 flush, (ranks lined up by a collective,) start event, tick, stop event are
+                # enqueued back to back and waited for once.  The host runs ahead while the flush executes, so the
+                # timed region is the tick's device time -- not the host's launch latency in front of its first
+                # kernel, nor (N > 1) one rank's host jitter timed as another rank's wait for its records.
+                flush_buf.fill_(1)
+                if G > 1:
+                    dist.all_reduce(align_token)
             t0 = time.perf_counter()
             e0.record(stream)
             res = fn()
@@ -297,7 +302,8 @@ def run_ours(args):
                            "exchange": "none" if G == 1 else ("peer-memory stores + flags (rmb_peer_push)" if p2p else "NCCL all-gather"),
                            "l2": "flushed (256 MiB write) before every timed step",
                            "timing": "CUDA events on the stream the library and NCCL run on, per step, summed, max over ranks"
-                                     + ("" if G == 1 else " (an NCCL all-reduce enqueued right before the start event lines the ranks up on the device)")
+                                     + "; L2 flush" + ("" if G == 1 else ", an NCCL all-reduce that lines the ranks up,")
+                                     + " start event, tick and stop event enqueued back to back"
                                      + "; e2e: host wall clock around the public C-ABI call with host buffers"},
                 "clocks": clocks,
                 "e2e": {"value": decisions * args.steps / t_e2e, "unit": UNIT, "ms_per_step": 1e3 * t_e2e / args.steps,
@@ -390,7 +396,8 @@ def run_c5(args):
             if kind == "resident":
                 med.update_positions(x[lo:hi], y[lo:hi])
                 med.build_tx_records(mine, rec_local.data_ptr())
-            flush_buf.fill_(1)
+            if kind != "resident":
+                flush_buf.fill_(1)
             torch.cuda.synchronize()
             if G > 1:
                 dist.barrier()
@@ -398,8 +405,10 @@ def run_c5(args):
             if sampler:
                 sampler.active = True
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            if G > 1 and kind == "resident":
-                dist.all_reduce(align_token)            # line the ranks' streams up on the device (see run_ours)
+            if kind == "resident":
+                flush_buf.fill_(1)                      # enqueued in front of the start event, see run_ours
+                if G > 1:
+                    dist.all_reduce(align_token)
             t0 = time.perf_counter()
             e0.record(stream)
             if kind == "resident":

@@ -305,10 +305,8 @@ prepare_all_kernel(NodeArrays nd, const DevParams *dp, const Geom *geom, Groups 
             }
         }
     }
-    // ... and the peers' records of this tick must have landed before anybody reads `rec`
     if (tid == 0) s_timeout = 0;
     __syncthreads();
-    if (aux.peer_flags && tid < aux.world && !peer_wait(aux.peer_flags + tid, aux.epoch)) s_timeout = 1;
 
     if (tid < 3) {
         const double n = dp->pl_exponent, d0 = dp->d0_m;
@@ -327,6 +325,9 @@ prepare_all_kernel(NodeArrays nd, const DevParams *dp, const Geom *geom, Groups 
         for (int i = gtid; i < aux.n_rx_done; i += gsz) aux.rx_done[i] = 0;
         if (gtid == 0) { *ctr = Counters{}; aux.bar[2] = 0u; }      // bar[2]: the barrier counter of finish.cu, zero at its launch
     }
+    // ... and the peers' records of this tick must have landed before anybody reads `rec` (everything above is
+    // independent of them and runs while the records are on their way)
+    if (aux.peer_flags && tid < aux.world && !peer_wait(aux.peer_flags + tid, aux.epoch)) s_timeout = 1;
     __syncthreads();
 
     // 1. per-transmission constants of this block's arrival range

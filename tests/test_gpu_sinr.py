@@ -209,6 +209,25 @@ def test_position_and_radio_updates(rsb, orc):
         compare(r, ref)
 
 
+def test_mobility_over_many_dense_updates(rsb, orc):
+    """BASELINE configs[4] in small: every node moves every tick, fresh sources per tick.  The library re-sorts its
+    work order only on every 8th dense update; the steps here are large (nodes cross the whole area), so a stale
+    order is as bad as it gets -- results must not depend on it."""
+    n = 4000
+    x, y, z, ch = random_deployment(12, n, 700.0, channels=16)
+    rng = np.random.default_rng(12)
+    with rsb.Medium("sinr", f64_values=True) as m:
+        m.set_nodes(x, y, z, channel=ch)
+        for tick in range(11):
+            step = 0.5 if tick % 3 else 300.0
+            x = np.clip(x + rng.uniform(-step, step, n), 0.0, 700.0)
+            y = np.clip(y + rng.uniform(-step, step, n), 0.0, 700.0)
+            m.update_positions(x, y)
+            src = pick_sources(100 + tick, n, 160)
+            ref = orc.tick(orc.params(orc.MODEL_SINR), orc.NodeSet(x, y, None, channel=ch), orc.make_packets(src, 0.0, ch[src]))
+            compare(m.tick(src), ref)
+
+
 def test_enqueued_tick_equals_the_synchronous_one(rsb, orc):
     """rmb_tick_enqueue + rmb_tick_finish + rmb_fetch: same lists as rmb_tick; an enqueued tick whose
     near-slot capacity is exceeded is redone when it is settled."""
