@@ -93,11 +93,16 @@ __device__ __forceinline__ void warp_bucket(const PairRecs &pr, const PairArrays
         r[k] = 0;
     }
     __syncwarp();
+    // (the rx index -- the items' high word -- alone orders a bucket: 32-bit compares)
+    const unsigned *sk = reinterpret_cast<const unsigned *>(sw) + 1;
+    unsigned vk[PER];
+#pragma unroll
+    for (int k = 0; k < PER; ++k) vk[k] = (unsigned)(v[k] >> 32);
 #pragma unroll 4
     for (int j = 0; j < nb; ++j) {
-        const unsigned long long x = sw[j];
+        const unsigned x = sk[2 * j];
 #pragma unroll
-        for (int k = 0; k < PER; ++k) r[k] += x < v[k];
+        for (int k = 0; k < PER; ++k) r[k] += x < vk[k];
     }
     const bool failed = pa.tx_failed[t] != 0;
 #pragma unroll
@@ -220,11 +225,13 @@ finish_kernel(WorkArrays wk, const DevParams *dp, Groups groups, TxTiles tx, con
             if (nb <= kCountRankMax) {
                 for (int i = threadIdx.x; i < nb; i += kFinThreads) s_items[i] = __ldcg(&items[b0 + i]);
                 __syncthreads();
+                const unsigned *sk = reinterpret_cast<const unsigned *>(s_items) + 1;     // high words: the rx indices
                 for (int i = threadIdx.x; i < nb; i += kFinThreads) {
                     const unsigned long long mine = s_items[i];
+                    const unsigned mk = (unsigned)(mine >> 32);
                     int rank = 0;
 #pragma unroll 8
-                    for (int j = 0; j < nb; ++j) rank += s_items[j] < mine;
+                    for (int j = 0; j < nb; ++j) rank += sk[2 * j] < mk;
                     emit_row(pr, pa, t, failed, mine, (long long)b0 + rank, n);
                 }
             } else {
