@@ -86,3 +86,30 @@ def test_config4_1m_nodes_10k_tx_properties(rsb, orc):
     assert np.array_equal(a.outcome[sel], ref["outcome"]) and np.array_equal(a.rssi_dbm_f64[sel], ref["rssi_dbm"])
     fin = np.isfinite(ref["sinr_db"])
     assert np.abs(a.sinr_db_f64[sel][fin] - ref["sinr_db"][fin]).max() < SINR_TOL_DB
+
+
+def test_renumbering_the_nodes_only_renumbers_the_lists_300k(rsb):
+    """Size-independent property (no oracle): the same deployment with its nodes renumbered gives the same pairs,
+    outcomes and exact link budgets under the renumbering; SINR within the documented tolerance (the fp32 far sums
+    see the receivers in another work order only where Morton keys tie)."""
+    rng = np.random.default_rng(7)
+    n, t, side = 300_000, 3_000, 5477.0
+    x, y = rng.uniform(0, side, n), rng.uniform(0, side, n)
+    ch = (11 + rng.integers(0, 2, n)).astype(np.int32)
+    src = rng.permutation(n)[:t].astype(np.int32)
+    perm = rng.permutation(n)                                  # new index i holds old node perm[i]
+    inv = np.empty(n, dtype=np.int64); inv[perm] = np.arange(n)
+    with rsb.Medium("sinr", f64_values=True) as m:
+        m.set_nodes(x, y, channel=ch)
+        a = m.tick(src)
+    with rsb.Medium("sinr", f64_values=True) as m:
+        m.set_nodes(x[perm], y[perm], channel=ch[perm])
+        b = m.tick(inv[src].astype(np.int32))
+    assert a.n_pairs == b.n_pairs > 100_000 and a.n_decisions == b.n_decisions
+    order = np.lexsort((perm[b.rx], b.tx))
+    assert np.array_equal(b.tx[order], a.tx) and np.array_equal(perm[b.rx][order], a.rx)
+    assert np.array_equal(b.outcome[order], a.outcome)
+    assert np.array_equal(b.rssi_dbm_f64[order], a.rssi_dbm_f64)
+    fin = np.isfinite(a.sinr_db_f64)
+    assert np.array_equal(fin, np.isfinite(b.sinr_db_f64[order]))
+    assert np.abs(b.sinr_db_f64[order][fin] - a.sinr_db_f64[fin]).max() < SINR_TOL_DB
