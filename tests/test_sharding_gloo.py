@@ -1,4 +1,4 @@
-"""CPU, world_size 2 over gloo: the multi-GPU host logic (receiver shards, tx-record exchange plan,
+"""CPU, world_size 2 and 3 over gloo: the multi-GPU host logic (receiver shards, tx-record exchange plan,
 result merge).  Each rank evaluates ITS receivers with the oracle standing in for the GPU shard
 (this is a test: the oracle is the checker of the merge logic), all-gathers its list, merges, and
 must reproduce the unsharded tick exactly."""
@@ -53,11 +53,12 @@ def _worker(rank, world, port, q):
     dist.destroy_process_group()
 
 
-def test_two_rank_sharded_tick_merges_to_the_global_order():
+@pytest.mark.parametrize("world", [2, 3])
+def test_sharded_tick_merges_to_the_global_order(world):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    port = 29500 + os.getpid() % 2000
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    port = 29500 + (os.getpid() + 7 * world) % 2000
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
     for p in procs:
         p.start()
     ok, npairs, counts, tpad = q.get(timeout=120)
