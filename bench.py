@@ -250,7 +250,7 @@ def run_ours(args):
             if sampler:
                 sampler.active = False
             tm = med.timing()
-            sweep_ms.append(tm["ms_sweep"]); launches += tm["kernel_launches"] + (1 if G > 1 else 0)
+            sweep_ms.append(tm["ms_sweep"]); launches += tm["kernel_launches"]        # (the exchange is inside the preparation kernel; NCCL's kernels are not ours)
         return times, walls, res, sweep_ms, launches
 
     med.build_tx_records(mine_padded, rec_local.data_ptr())
