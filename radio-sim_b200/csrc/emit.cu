@@ -102,7 +102,7 @@ __global__ void __launch_bounds__(128) bucket_sort_kernel(PairRecs pr, const Cou
                                                           const unsigned long long *items, unsigned *order)
 {
     __shared__ unsigned long long s[kBucketSortMax];
-    if ((long long)ctr->heard > pr.cap || ctr->max_bucket > kBucketSortMax) return;   // host: redo / radix-sort fallback
+    if (ctr->heard == 0 || (long long)ctr->heard > pr.cap || ctr->max_bucket > kBucketSortMax) return;   // nothing heard (seg may be stale: no receiver, no resolve) / host: redo / radix-sort fallback
     const int t = blockIdx.x;
     const int b0 = seg[t], n = seg[t + 1] - b0;
     if (n <= 0) return;

@@ -207,7 +207,8 @@ finish_kernel(WorkArrays wk, const DevParams *dp, Groups groups, TxTiles tx, con
 
     // ---- 3: rank every packet's bucket by rx, write its rows -----------------------------------------
     EmitCount n{0, 0};
-    if (!stand_down && __ldcg(&ctr->max_bucket) <= kBucketSortMax) {
+    // (m == 0: nothing was heard -- with no enabled receiver at all the sweep did not even run and `seg` is stale)
+    if (m > 0 && __ldcg(&ctr->max_bucket) <= kBucketSortMax) {
         // buckets of up to kWarpBucket pairs: a warp each
         unsigned long long *sw = s_items + warp * kWarpBucket;
         for (int t = blockIdx.x * kFinWarps + warp; t < n_tx; t += gridDim.x * kFinWarps) {

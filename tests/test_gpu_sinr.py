@@ -108,6 +108,24 @@ def test_empty_and_tiny(rsb, orc):
     run_case(rsb, orc, x, y, z, ch, np.array([0, 1, 2], dtype=np.int32))
 
 
+def test_no_enabled_receiver_at_all(rsb, orc):
+    """Every radio disabled: no sweep, no resolve, hence no segment offsets for the tick -- the tail of the tick must
+    not walk stale ones.  Enabling the radios afterwards gives the ordinary tick."""
+    x, y, z, ch = random_deployment(14, 800, 150.0)
+    src = pick_sources(14, 800, 20)
+    off = np.zeros(800, dtype=np.uint8)
+    with rsb.Medium("sinr", f64_values=True) as m:
+        m.set_nodes(x, y, z, channel=ch)
+        first = m.tick(src)                                   # leaves segment offsets of a busy tick behind
+        assert first.n_pairs > 1000
+        m.update_radio(enabled=off)
+        r = m.tick(src)
+        assert r.n_pairs == 0 and r.n_delivered == 0 and r.n_interfered == 0 and r.n_decisions == 0
+        m.update_radio(enabled=np.ones(800, dtype=np.uint8))
+        compare(m.tick(src), orc.tick(orc.params(orc.MODEL_SINR), orc.NodeSet(x, y, z, channel=ch), orc.make_packets(src, 0.0, ch[src])))
+    run_case(rsb, orc, x, y, z, ch, src, enabled=off)         # and from a fresh handle, against the oracle
+
+
 def test_guard_band_forces_exact_recheck(rsb, orc):
     """Place an interferer so that one receiver's SINR sits on the 4 dB threshold: the decision must
     come from the exact double path and agree with the oracle on both sides of the threshold."""
