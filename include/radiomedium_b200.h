@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define RMB_ABI_VERSION 1
+#define RMB_ABI_VERSION 2
 
 typedef struct rmb_handle rmb_handle;
 
@@ -81,7 +81,26 @@ typedef struct rmb_config {
     int64_t max_pairs;            /* cap on heard pairs per tick, 0 = default (64 Mi)    */
     int32_t rx_base;              /* multi-GPU: global index of this shard's first node  */
     int32_t n_shards;             /* multi-GPU: number of receiver shards (0/1 = unsharded) */
+    int32_t half_duplex;          /* 0 = the reference: only node == source is excluded as a receiver
+                                     (UDGMRadioMedium.java:100), a node that is itself on the air still receives.
+                                     1 = spec flag (all media): a node that is the source of ANY packet of the tick
+                                     passes no receiver filter in that tick and reports the noise floor            */
+    int32_t reserved;             /* 0                                                   */
 } rmb_config;
+
+/* Limits (exceeding one is an error return, never a wrong result):
+ *   - at most 64 distinct wireless channels among the ENABLED receivers of a handle (RMB_ERR_UNSUPPORTED from
+ *     rmb_set_nodes / rmb_update_radio); packets may use any channel;
+ *   - max_pairs <= 2^31 - 1 (row and segment offsets are int32; rmb_create rejects more with RMB_ERR_INVALID);
+ *   - reference media (NULL/UDGM/UDGM_CONSTANT/N2N): n_tx * ceil(n / 256) < 2^31 per tick (RMB_ERR_CAPACITY);
+ *   - SINR: per-receiver near-candidate slots grow on demand (x2) up to 3e9 slots per handle; a tick in which
+ *     every receiver hears thousands of packets fails with RMB_ERR_CAPACITY instead;
+ *   - N2N needs the source's integer id, which a tx record does not carry: RMB_MODEL_N2N with n_shards > 1 is
+ *     rejected by rmb_create (RMB_ERR_UNSUPPORTED);
+ *   - stochastic reception (any rx/tx probability strictly between 0 and 1) on sharded receivers needs the
+ *     rmb_tick_draws_begin/_end pair; any other tick entry point returns RMB_ERR_UNSUPPORTED for such a tick,
+ *     also when the probability arrives in a record built by another shard;
+ *   - at most 16 handles exchange records with rmb_peer_* (RMB_ERR_INVALID). */
 
 /* One active transmission as the device sees it (RadioPacket.java:46-52 plus the
  * source's Position.java:37-39 and Transciever.txProbability).  48 bytes; this is the
@@ -242,6 +261,9 @@ int rmb_peer_exchange_tick_enqueue(rmb_handle *h, int32_t slots, const void *d_r
  * of the last tick per local node [dBm] (noise floor when idle), and 1 if the node heard
  * at least one frame. NULL outputs are skipped. */
 int rmb_node_info(rmb_handle *h, float *rssi_dbm, uint8_t *receiving);
+/* the same in double: what `node-info.rssi` carries (a JSON double, net/JSONClientConnection.java:337) and what
+ * the parity tests compare with the oracle's sequential sum */
+int rmb_node_info_f64(rmb_handle *h, double *rssi_dbm, uint8_t *receiving);
 
 int rmb_last_timing(const rmb_handle *h, rmb_timing *out);
 /* CUDA stream the handle's kernels and copies run on (a cudaStream_t passed as void*).

@@ -126,9 +126,13 @@ static void emit(sink *s, int32_t tx, int32_t rx, double rssi, double sinr, int3
     s->needed++;
 }
 
-/* receiver filter shared by all four Java media (UDGMRadioMedium.java:100-102 etc.) */
-static int passes_filter(const orc_nodes *nd, int32_t node, const orc_packet *pk)
+/* receiver filter shared by all four Java media (UDGMRadioMedium.java:100-102 etc.).
+ * txing (NULL unless orc_params.half_duplex): nodes that are the source of some packet of this tick.  The
+ * reference excludes only node == source, so a node that is itself on the air still "receives"; with the
+ * half_duplex spec flag (SURVEY.md 8(a) "open" row) such a node passes no filter during the tick. */
+static int passes_filter(const orc_nodes *nd, int32_t node, const orc_packet *pk, const uint8_t *txing)
 {
+    if (txing && txing[node]) return 0;
     return node != pk->src && nd->enabled[node] && nd->channel[node] == pk->channel;
 }
 
@@ -136,7 +140,7 @@ static int passes_filter(const orc_nodes *nd, int32_t node, const orc_packet *pk
 /* UDGMRadioMedium.transmit (java:83-116) and N2NRadioMedium.transmit (java:40-72):
  * identical control flow, different probability functions. */
 static void stochastic_transmit(const orc_params *p, const orc_nodes *nd, const orc_packet *pk, int32_t t,
-                                ustream *us, sink *sk, uint8_t *tx_failed, uint64_t *decisions)
+                                ustream *us, sink *sk, uint8_t *tx_failed, uint64_t *decisions, const uint8_t *txing)
 {
     double txSuccess = (p->model == ORC_MODEL_UDGM)
         ? p->success_ratio_rx * nd->txprob[pk->src]      /* java:63-65 -- uses the Rx ratio (sic) */
@@ -146,7 +150,7 @@ static void stochastic_transmit(const orc_params *p, const orc_nodes *nd, const 
     if (tx_failed) tx_failed[t] = (uint8_t)interference;
     double rssi = pk->power_dbm;
     for (int32_t node = 0; node < nd->n; node++) {
-        if (!passes_filter(nd, node, pk)) continue;
+        if (!passes_filter(nd, node, pk, txing)) continue;
         (*decisions)++;
         double rxSuccess = (p->model == ORC_MODEL_UDGM)
             ? orc_udgm_rx_probability(p, nd, pk->src, node)
@@ -163,11 +167,11 @@ static void stochastic_transmit(const orc_params *p, const orc_nodes *nd, const 
 
 /* UDGMConstantLossRadioMedium.transmit (java:16-36): strict '<', immediate delivery */
 static void constant_transmit(const orc_params *p, const orc_nodes *nd, const orc_packet *pk, int32_t t,
-                              sink *sk, uint64_t *decisions)
+                              sink *sk, uint64_t *decisions, const uint8_t *txing)
 {
     double rssi = pk->power_dbm;
     for (int32_t node = 0; node < nd->n; node++) {
-        if (!passes_filter(nd, node, pk)) continue;
+        if (!passes_filter(nd, node, pk, txing)) continue;
         (*decisions)++;
         double distance = node_distance(nd, pk->src, node);
         if (distance < p->constant_range) emit(sk, t, node, rssi, NAN, ORC_DELIVERED);
@@ -175,11 +179,12 @@ static void constant_transmit(const orc_params *p, const orc_nodes *nd, const or
 }
 
 /* NullRadioMedium.transmit (java:48-77) */
-static void null_transmit(const orc_nodes *nd, const orc_packet *pk, int32_t t, sink *sk, uint64_t *decisions)
+static void null_transmit(const orc_nodes *nd, const orc_packet *pk, int32_t t, sink *sk, uint64_t *decisions,
+                          const uint8_t *txing)
 {
     double rssi = pk->power_dbm;
     for (int32_t node = 0; node < nd->n; node++) {
-        if (!passes_filter(nd, node, pk)) continue;
+        if (!passes_filter(nd, node, pk, txing)) continue;
         (*decisions)++;
         emit(sk, t, node, rssi, NAN, ORC_DELIVERED);
     }
@@ -225,14 +230,14 @@ static void cv_push(candvec *c, cand x)
 }
 
 static void sinr_receiver(const orc_params *p, const orc_nodes *nd, const orc_packet *pk, int32_t T,
-                          int32_t r, double n0, candvec *cv, double *total_dbm, uint64_t *decisions)
+                          int32_t r, double n0, candvec *cv, double *total_dbm, uint64_t *decisions, const uint8_t *txing)
 {
     if (!nd->enabled[r]) { if (total_dbm) total_dbm[r] = p->noise_floor_dbm; return; }
     size_t first = cv->n;
     double itot = n0;
     uint64_t dec = 0;
     for (int32_t t = 0; t < T; t++) {
-        if (!passes_filter(nd, r, &pk[t])) continue;
+        if (!passes_filter(nd, r, &pk[t], txing)) continue;
         dec++;
         double d = node_distance(nd, pk[t].src, r);
         double prx = orc_sinr_rx_power_dbm(p, pk[t].power_dbm, d);
@@ -256,7 +261,7 @@ static void sinr_receiver(const orc_params *p, const orc_nodes *nd, const orc_pa
 
 typedef struct {
     const orc_params *p; const orc_nodes *nd; const orc_packet *pk; int32_t T; double n0;
-    candvec *cvs; uint64_t *decs; double *total_dbm; int nchunk; int next;
+    candvec *cvs; uint64_t *decs; double *total_dbm; int nchunk; int next; const uint8_t *txing;
 } sinr_job;
 
 /* receivers are independent given the tick's packets: chunks of the node array are handed to
@@ -269,21 +274,21 @@ static void *sinr_worker(void *arg)
         if (c >= j->nchunk) break;
         int32_t lo = (int32_t)((int64_t)j->nd->n * c / j->nchunk), hi = (int32_t)((int64_t)j->nd->n * (c + 1) / j->nchunk);
         for (int32_t r = lo; r < hi; r++)
-            sinr_receiver(j->p, j->nd, j->pk, j->T, r, j->n0, &j->cvs[c], j->total_dbm, &j->decs[c]);
+            sinr_receiver(j->p, j->nd, j->pk, j->T, r, j->n0, &j->cvs[c], j->total_dbm, &j->decs[c], j->txing);
     }
     return NULL;
 }
 
 static void sinr_tick(const orc_params *p, const orc_nodes *nd, const orc_packet *pk, int32_t T,
                       ustream *us, sink *sk, uint8_t *tx_failed, double *total_dbm, int threads,
-                      uint64_t *decisions)
+                      uint64_t *decisions, const uint8_t *txing)
 {
     double n0 = orc_dbm_to_mw(p->noise_floor_dbm);
     int nchunk = threads > 1 ? threads * 8 : 1;
     if (nchunk > nd->n) nchunk = nd->n > 0 ? nd->n : 1;
     candvec *cvs = (candvec *)calloc((size_t)nchunk, sizeof(candvec));
     uint64_t *decs = (uint64_t *)calloc((size_t)nchunk, sizeof(uint64_t));
-    sinr_job job = { p, nd, pk, T, n0, cvs, decs, total_dbm, nchunk, 0 };
+    sinr_job job = { p, nd, pk, T, n0, cvs, decs, total_dbm, nchunk, 0, txing };
     int nthr = threads > 1 ? threads : 1;
     if (nthr == 1) {
         sinr_worker(&job);
@@ -330,22 +335,28 @@ void orc_tick(const orc_params *p, const orc_nodes *nodes, const orc_packet *pac
     ustream us = { uniforms, uniforms ? n_uniforms : 0, 0, 0 };
     sink sk = { out, out ? cap : 0, 0, 0 };
     uint64_t decisions = 0;
+    uint8_t *txing = NULL;
+    if (p->half_duplex) {
+        txing = (uint8_t *)calloc((size_t)(nodes->n > 0 ? nodes->n : 1), 1);
+        for (int32_t t = 0; t < T; t++) if (packets[t].src >= 0 && packets[t].src < nodes->n) txing[packets[t].src] = 1;
+    }
     if (p->model == ORC_MODEL_SINR) {
-        sinr_tick(p, nodes, packets, T, &us, &sk, tx_failed, total_dbm, threads, &decisions);
+        sinr_tick(p, nodes, packets, T, &us, &sk, tx_failed, total_dbm, threads, &decisions, txing);
     } else {
         for (int32_t t = 0; t < T; t++) {
             switch (p->model) {
             case ORC_MODEL_NULL:
                 if (tx_failed) tx_failed[t] = 0;
-                null_transmit(nodes, &packets[t], t, &sk, &decisions); break;
+                null_transmit(nodes, &packets[t], t, &sk, &decisions, txing); break;
             case ORC_MODEL_UDGM_CONSTANT:
                 if (tx_failed) tx_failed[t] = 0;
-                constant_transmit(p, nodes, &packets[t], t, &sk, &decisions); break;
+                constant_transmit(p, nodes, &packets[t], t, &sk, &decisions, txing); break;
             default:
-                stochastic_transmit(p, nodes, &packets[t], t, &us, &sk, tx_failed, &decisions); break;
+                stochastic_transmit(p, nodes, &packets[t], t, &us, &sk, tx_failed, &decisions, txing); break;
             }
         }
     }
+    free(txing);
     if (stats) {
         stats->n_pairs = sk.n;
         stats->n_needed = sk.needed;

@@ -84,6 +84,10 @@ typedef struct {
     double  sensitivity_dbm;       /* -95.0                                    */
     double  sinr_threshold_db;     /* 4.0                                      */
     double  noise_floor_dbm;       /* -100.0 == AbstractRadioMedium.baseRSSI   */
+    /* spec flag, all media (SURVEY.md 8(a) "open" row).  0 = the reference's behaviour: only node == source is
+     * excluded (UDGMRadioMedium.java:100), a node that is itself transmitting still receives.  1: a node that is
+     * the source of ANY packet of the tick passes no receiver filter during that tick (one transceiver). */
+    int32_t half_duplex;
 } orc_params;
 
 void orc_params_default(orc_params *p, int32_t model);

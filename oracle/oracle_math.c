@@ -2,6 +2,18 @@
  * oracle_math.c -- TEST INFRASTRUCTURE ONLY.
  * fdlibm-style log / log10 / exp in strict IEEE double arithmetic.
  * Build: gcc -O2 -ffp-contract=off (see oracle/Makefile).
+ *
+ * The algorithms, evaluation order and coefficient tables follow fdlibm's e_log.c, e_log10.c and e_exp.c
+ * (third-party, not part of the reference), whose notice is preserved here as it requires:
+ *
+ * ====================================================
+ * Copyright (C) 1993 by Sun Microsystems, Inc. All rights reserved.
+ *
+ * Developed at SunSoft, a Sun Microsystems, Inc. business.
+ * Permission to use, copy, modify, and distribute this
+ * software is freely granted, provided that this notice
+ * is preserved.
+ * ====================================================
  */
 #include "oracle_math.h"
 #include <stdint.h>

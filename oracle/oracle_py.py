@@ -30,7 +30,7 @@ class Params(C.Structure):
                 ("matrix", C.POINTER(C.c_double)), ("matrix_n", C.c_int32),
                 ("pl0_db", C.c_double), ("pl_exponent", C.c_double), ("d0_m", C.c_double),
                 ("sensitivity_dbm", C.c_double), ("sinr_threshold_db", C.c_double),
-                ("noise_floor_dbm", C.c_double)]
+                ("noise_floor_dbm", C.c_double), ("half_duplex", C.c_int32)]
 
 
 class Nodes(C.Structure):

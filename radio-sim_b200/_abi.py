@@ -22,7 +22,7 @@ FLAG_COMPACT = 2
 SYMBOLS = ("rmb_version", "rmb_config_default", "rmb_create", "rmb_destroy", "rmb_last_error",
            "rmb_set_nodes", "rmb_set_matrix", "rmb_update_positions", "rmb_update_radio", "rmb_tick",
            "rmb_build_tx_records", "rmb_tick_records", "rmb_tick_resident", "rmb_fetch",
-           "rmb_node_info", "rmb_last_timing", "rmb_set_tuning", "rmb_get_stream", "rmb_set_stream",
+           "rmb_node_info", "rmb_node_info_f64", "rmb_last_timing", "rmb_set_tuning", "rmb_get_stream", "rmb_set_stream",
            "rmb_peer_export", "rmb_peer_open", "rmb_peer_push", "rmb_peer_push_records", "rmb_tick_peers",
            "rmb_tick_peers_resident", "rmb_tick_enqueue", "rmb_tick_finish", "rmb_tick_peers_enqueue", "rmb_peer_exchange_tick_enqueue", "rmb_tick_draws_begin", "rmb_tick_draws_end",
            "rmb_tick_peers_draws_begin")
@@ -35,7 +35,8 @@ class Config(C.Structure):
                 ("pl0_db", C.c_double), ("pl_exponent", C.c_double), ("d0_m", C.c_double),
                 ("sensitivity_dbm", C.c_double), ("sinr_threshold_db", C.c_double),
                 ("noise_floor_dbm", C.c_double), ("max_pairs", C.c_int64),
-                ("rx_base", C.c_int32), ("n_shards", C.c_int32)]
+                ("rx_base", C.c_int32), ("n_shards", C.c_int32),
+                ("half_duplex", C.c_int32), ("reserved", C.c_int32)]
 
 
 class TxRecord(C.Structure):
@@ -94,6 +95,7 @@ def load():
     L.rmb_tick_resident.argtypes = [H, C.c_int32, C.c_void_p, C.POINTER(Result)]
     L.rmb_fetch.argtypes = [H, C.POINTER(Result)]
     L.rmb_node_info.argtypes = [H, pf, pu8]
+    L.rmb_node_info_f64.argtypes = [H, pd, pu8]
     L.rmb_last_timing.argtypes = [H, C.POINTER(Timing)]
     L.rmb_set_tuning.argtypes = [H, C.c_int32, C.c_int32]
     L.rmb_peer_export.argtypes = [H, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]

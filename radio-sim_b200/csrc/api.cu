@@ -14,7 +14,6 @@
 #include <unistd.h>
 #include <string>
 #include <vector>
-#include <vector>
 
 using namespace rmb;
 
@@ -82,7 +81,8 @@ struct rmb_handle {
     Groups groups{};
     DevBuf<DevParams> dp; DevBuf<Geom> geom; DevBuf<unsigned long long> geom_scratch;
     DevBuf<Counters> ctr; PinBuf<Counters> h_ctr;
-    DevBuf<float> node_rssi; DevBuf<uint8_t> node_recv;
+    DevBuf<float> node_rssi; DevBuf<double> node_rssi64; DevBuf<uint8_t> node_recv;
+    DevBuf<int> tx_epoch, hd_cnt; int hd_epoch = 0;      // half duplex (rmb_config.half_duplex): see PrepareAux
 
     // per tick: tx side
     DevBuf<int> pk_src, pk_channel; DevBuf<double> pk_power; PinBuf<char> pk_stage;
@@ -163,6 +163,7 @@ WorkArrays work_arrays(rmb_handle *h)
 {
     WorkArrays w; w.n_work = h->n_work; w.perm = h->perm.p; w.fx = h->fx.p; w.fy = h->fy.p; w.fz = h->fz.p;
     w.x64 = h->wx.p; w.y64 = h->wy.p; w.z64 = h->wz.p; w.rxp = h->wrxp.p;
+    w.tx_epoch = h->cfg.half_duplex ? h->tx_epoch.p : nullptr; w.hd_epoch = h->hd_epoch;
     return w;
 }
 TxTiles tx_tiles(rmb_handle *h)
@@ -264,9 +265,16 @@ static int build_work_order(rmb_handle *h)
     if (rc) return rc;
     // idle nodes report the noise floor (AbstractRadioMedium.java:38,45-52)
     std::vector<float> idle((size_t)std::max(n, 1), (float)h->cfg.noise_floor_dbm);
-    RMB_CK(h, h->node_rssi.ensure(std::max(n, 1))); RMB_CK(h, h->node_recv.ensure(std::max(n, 1)));
+    std::vector<double> idle64((size_t)std::max(n, 1), h->cfg.noise_floor_dbm);
+    RMB_CK(h, h->node_rssi.ensure(std::max(n, 1))); RMB_CK(h, h->node_rssi64.ensure(std::max(n, 1))); RMB_CK(h, h->node_recv.ensure(std::max(n, 1)));
     RMB_CK(h, cudaMemcpy(h->node_rssi.p, idle.data(), idle.size() * sizeof(float), cudaMemcpyHostToDevice));
+    RMB_CK(h, cudaMemcpy(h->node_rssi64.p, idle64.data(), idle64.size() * sizeof(double), cudaMemcpyHostToDevice));
     RMB_CK(h, cudaMemset(h->node_recv.p, 0, std::max(n, 1)));
+    if (h->cfg.half_duplex) {
+        // stamps of earlier ticks never equal a later epoch, so a grown array only has to start from zero
+        if ((size_t)nn > h->tx_epoch.cap) { RMB_CK(h, h->tx_epoch.ensure(nn)); RMB_CK(h, cudaMemset(h->tx_epoch.p, 0, h->tx_epoch.cap * sizeof(int))); }
+        if (!h->hd_cnt.p) RMB_CK(h, h->hd_cnt.ensure(2 * kMaxGroups, true));
+    }
     return RMB_OK;
 }
 
@@ -339,6 +347,10 @@ int rmb_create(const rmb_config *cfg, rmb_handle **out)
     if (cfg->struct_size != (int32_t)sizeof(rmb_config)) { g_create_error = "rmb_config.struct_size mismatch"; return RMB_ERR_INVALID; }
     if (cfg->model < RMB_MODEL_NULL || cfg->model > RMB_MODEL_SINR) { g_create_error = "unknown model"; return RMB_ERR_INVALID; }
     if (cfg->model == RMB_MODEL_SINR && !(cfg->pl_exponent > 0.0 && cfg->d0_m > 0.0)) { g_create_error = "pl_exponent and d0_m must be > 0"; return RMB_ERR_INVALID; }
+    // row and segment offsets are int32 (seg, tx_first, draw scans; the record index rides in 32 bits of an ordering item)
+    if (cfg->max_pairs > (int64_t)INT32_MAX) { g_create_error = "max_pairs must not exceed 2^31 - 1"; return RMB_ERR_INVALID; }
+    // N2N looks the SOURCE's integer id up in the node table, and a tx record does not carry it across shards
+    if (cfg->model == RMB_MODEL_N2N && cfg->n_shards > 1) { g_create_error = "RMB_MODEL_N2N does not support sharded receivers (n_shards > 1)"; return RMB_ERR_UNSUPPORTED; }
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev <= 0) {
@@ -370,7 +382,7 @@ int rmb_create(const rmb_config *cfg, rmb_handle **out)
     dp.model = cfg->model; dp.success_ratio_rx = cfg->success_ratio_rx; dp.transmission_range = cfg->transmission_range;
     dp.constant_range = cfg->constant_range; dp.pl0_db = cfg->pl0_db; dp.pl_exponent = cfg->pl_exponent; dp.d0_m = cfg->d0_m;
     dp.sensitivity_dbm = cfg->sensitivity_dbm; dp.sinr_threshold_db = cfg->sinr_threshold_db;
-    dp.noise_floor_dbm = cfg->noise_floor_dbm; dp.rx_base = cfg->rx_base;
+    dp.noise_floor_dbm = cfg->noise_floor_dbm; dp.rx_base = cfg->rx_base; dp.half_duplex = cfg->half_duplex ? 1 : 0;
     if ((e = cudaMemcpy(h->dp.p, &dp, sizeof(dp), cudaMemcpyHostToDevice)) != cudaSuccess) return bail(e, "cudaMemcpy");
     if ((e = launch_init_params(h->dp.p, h->st)) != cudaSuccess) return bail(e, "init_params");
     if ((e = cudaStreamSynchronize(h->st)) != cudaSuccess) return bail(e, "init_params sync");
@@ -388,7 +400,7 @@ int rmb_destroy(rmb_handle *h)
     h->x.release(); h->y.release(); h->z.release(); h->txpower.release(); h->rxprob.release(); h->txprob.release();
     h->matrix.release(); h->channel.release(); h->id_int.release(); h->enabled.release(); h->perm.release(); h->wx.release(); h->wy.release(); h->wz.release(); h->wrxp.release(); h->gid.release(); h->ro_key.release(); h->ro_key_alt.release(); h->ro_val.release(); h->ro_val_alt.release(); h->ro_tmp.release();
     h->fx.release(); h->fy.release(); h->fz.release(); h->dp.release(); h->geom.release(); h->geom_scratch.release();
-    h->ctr.release(); h->h_ctr.release(); h->node_rssi.release(); h->node_recv.release(); h->pk_src.release();
+    h->ctr.release(); h->h_ctr.release(); h->node_rssi.release(); h->node_rssi64.release(); h->tx_epoch.release(); h->hd_cnt.release(); h->node_recv.release(); h->pk_src.release();
     h->pk_channel.release(); h->pk_power.release(); h->pk_stage.release(); h->rec.release(); h->txf.release(); h->stg_f.release(); h->stg_theta.release(); h->stg_gid.release(); h->blk_cnt.release(); h->blk_thmin.release(); h->bar.release(); h->recheck_part.release(); h->rx_done.release();
     h->theta.release(); h->theta_min_g.release(); h->arrival.release(); h->goff.release(); h->gcount.release();
     h->uniforms.release(); h->slots.release(); h->cnt.release(); h->hcnt.release(); h->hoff.release();
@@ -558,21 +570,34 @@ extern "C" int rmb_set_tuning(rmb_handle *h, int32_t sweep_variant, int32_t near
     return RMB_OK;
 }
 
-extern "C" int rmb_node_info(rmb_handle *h, float *rssi_dbm, uint8_t *receiving)
+static int node_info_locked(rmb_handle *h, float *rssi_dbm, double *rssi_dbm64, uint8_t *receiving)
 {
-    if (!h) return RMB_ERR_INVALID;
-    std::lock_guard<std::mutex> lk(h->mu);
     RMB_SETTLE(h);
     if (!h->have_nodes) return h->fail(RMB_ERR_STATE, "rmb_node_info before rmb_set_nodes");
     RMB_CK(h, cudaSetDevice(h->cfg.device));
     if (h->node_info_dirty) {
-        RMB_CK(h, launch_node_info(work_arrays(h), slot_arrays(h), h->node_rssi.p, h->node_recv.p, h->st));
+        RMB_CK(h, launch_node_info(work_arrays(h), slot_arrays(h), h->node_rssi.p, h->node_rssi64.p, h->node_recv.p, h->st));
         h->node_info_dirty = false;
     }
     RMB_CK(h, cudaStreamSynchronize(h->st));
     if (rssi_dbm && h->n) RMB_CK(h, cudaMemcpy(rssi_dbm, h->node_rssi.p, (size_t)h->n * sizeof(float), cudaMemcpyDeviceToHost));
+    if (rssi_dbm64 && h->n) RMB_CK(h, cudaMemcpy(rssi_dbm64, h->node_rssi64.p, (size_t)h->n * sizeof(double), cudaMemcpyDeviceToHost));
     if (receiving && h->n) RMB_CK(h, cudaMemcpy(receiving, h->node_recv.p, (size_t)h->n, cudaMemcpyDeviceToHost));
     return RMB_OK;
+}
+
+extern "C" int rmb_node_info(rmb_handle *h, float *rssi_dbm, uint8_t *receiving)
+{
+    if (!h) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    return node_info_locked(h, rssi_dbm, nullptr, receiving);
+}
+
+extern "C" int rmb_node_info_f64(rmb_handle *h, double *rssi_dbm, uint8_t *receiving)
+{
+    if (!h) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    return node_info_locked(h, nullptr, rssi_dbm, receiving);
 }
 
 extern "C" int rmb_get_stream(rmb_handle *h, void **stream)
@@ -664,6 +689,9 @@ static int publish(rmb_handle *h, int n_tx, long long m, bool draws, int launche
 }
 
 static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const double *uniforms, size_t n_uniforms);
+static const char *const kNeedsDrawsMsg =
+    "a tx record carries a transmission probability strictly between 0 and 1 but this handle evaluates the tick "
+    "without draws (its own nodes are all deterministic): sharded receivers need rmb_tick_draws_begin / rmb_tick_draws_end";
 
 // An enqueued tick is settled the first time the host needs anything from the handle: wait for it, look at the
 // counters, and in the rare case a capacity was exceeded (or a packet's bucket needs the radix-sort path) redo the
@@ -675,6 +703,7 @@ static int finish_pending(rmb_handle *h)
     RMB_CK(h, cudaStreamSynchronize(h->st));
     const Counters c = *h->h_ctr.p;
     if (c.peer_timeout) return h->fail(RMB_ERR_PEER, "peer exchange: a rank's tx records did not arrive (no rmb_peer_push on that rank?)");
+    if (c.needs_draws) return h->fail(RMB_ERR_UNSUPPORTED, kNeedsDrawsMsg);
     const bool redo = c.max_near > h->K || (long long)c.heard > (long long)h->key.cap || c.max_bucket > kBucketSortMax;
     if (redo) {
         const bool am = h->async_mode;
@@ -694,8 +723,10 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
 {
     int rc;
     int launches = 0, sweeps = 0;
+    if (h->cfg.half_duplex) ++h->hd_epoch;            // every evaluation stamps its own sources (a redo stamps them again)
     const NodeArrays nd = node_arrays(h);
     const WorkArrays wk = work_arrays(h);
+    const int *hd_ep = h->cfg.half_duplex ? h->tx_epoch.p : nullptr;
     // a shard takes the stochastic path whenever the split API is used: a packet's source may sit on another shard
     const bool draws = h->maybe_draws || h->split_counts != nullptr;
     if (draws && h->cfg.n_shards > 1 && !h->split_counts)
@@ -734,10 +765,11 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
         if (h->key.cap == 0 && (rc = ensure_pairs(h, std::min<long long>(h->cfg.max_pairs, std::max(2ll * h->n_work, 1024ll))))) return rc;
         TxStage stg{h->stg_f.p, h->stg_theta.p, h->stg_gid.p};
         const int pgrid = prepare_grid(n_tx);
-        h->bar_count += (unsigned)pgrid;
         PrepareAux aux{};
+        aux.stochastic = draws ? 1 : 0;
+        if (h->cfg.half_duplex) { aux.tx_epoch = h->tx_epoch.p; aux.hd_epoch = h->hd_epoch; aux.hd_cnt = h->hd_cnt.p; aux.node_gid = h->gid.p; }
         aux.cnt = h->cnt.p; aux.n_work = h->n_work; aux.tx_cnt = h->tx_cnt.p; aux.tx_failed = h->tx_failed.p; aux.tx_base = h->tx_base.p;
-        aux.blk_cnt = h->blk_cnt.p; aux.blk_thmin = h->blk_thmin.p; aux.bar = h->bar.p; aux.bar_target = h->bar_count;
+        aux.blk_cnt = h->blk_cnt.p; aux.blk_thmin = h->blk_thmin.p; aux.bar = h->bar.p; aux.bar_target = h->bar_count + (unsigned)pgrid;
         aux.rx_done = h->rx_done.p; aux.n_rx_done = 2 * (h->n_work / 32 + 1);
         aux.peer_flags = h->wait_flags; aux.world = h->wait_world; aux.epoch = h->wait_epoch;
         if (h->fused_push) {
@@ -746,6 +778,7 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
             for (int r = 0; r < h->peer.world; ++r) aux.push_peer[r] = h->peer.peer[r];
         }
         RMB_CK(h, launch_prepare(nd, h->dp.p, h->geom.p, h->groups, n_tx, d_rec, stg, tx, h->theta.p, h->theta_min_g.p, h->ctr.p, aux, pgrid, h->st));
+        h->bar_count += (unsigned)pgrid;      // only a launch that went out has arrivals: host and device targets stay in step
         launches += 1;
         RMB_CK(h, cudaEventRecord(h->ev[1], h->st));
         // The whole tick is enqueued without a host round trip: the kernels downstream of the resolve read
@@ -834,6 +867,7 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
             else if ((rc = read_counters(h))) return rc;
             const Counters c = *h->h_ctr.p;
             if (c.peer_timeout) return h->fail(RMB_ERR_PEER, "peer exchange: a rank's tx records did not arrive (no rmb_peer_push on that rank?)");
+            if (c.needs_draws) return h->fail(RMB_ERR_UNSUPPORTED, kNeedsDrawsMsg);
             const bool slots_short = c.max_near > h->K, recs_short = (long long)c.heard > (long long)h->key.cap;
             if (!slots_short && !recs_short) { fallback = c.max_bucket > kBucketSortMax; break; }
             if (attempt > 5) return h->fail(RMB_ERR_CAPACITY, "near-slot / pair-record capacity could not be established");
@@ -888,17 +922,19 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
         RMB_CK(h, h->blkcnt.ensure(nb + 2)); RMB_CK(h, h->scan_tmp.ensure(nb / 1024 + 8));
         RMB_CK(h, cudaMemsetAsync(h->node_recv.p, 0, std::max(h->n, 1), h->st));
         RMB_CK(h, cudaEventRecord(h->ev[1], h->st));
-        RMB_CK(h, launch_refmedia_count(nd, h->dp.p, h->matrix.p, h->matrix_n, n_tx, d_rec, h->blkcnt.p, h->ctr.p, h->st));
+        RMB_CK(h, launch_refmedia_mark(nd, h->dp.p, n_tx, d_rec, h->cfg.half_duplex ? h->tx_epoch.p : nullptr, h->hd_epoch, h->st));
+        RMB_CK(h, launch_refmedia_count(nd, h->dp.p, h->matrix.p, h->matrix_n, n_tx, d_rec, h->blkcnt.p, h->ctr.p, draws, hd_ep, h->hd_epoch, h->st));
         ++launches; ++sweeps;
         RMB_CK(h, cudaEventRecord(h->ev[2], h->st));
         if ((rc = read_counters(h))) return rc;
+        if (h->h_ctr.p->needs_draws) return h->fail(RMB_ERR_UNSUPPORTED, kNeedsDrawsMsg);
         m = (long long)h->h_ctr.p->heard;
         if ((rc = ensure_pairs(h, m))) return rc;
         RMB_CK(h, cudaEventRecord(h->ev[3], h->st));
         if (m > 0) {
             RMB_CK(h, launch_exclusive_scan(h->blkcnt.p, h->blkcnt.p, (int)nb, h->scan_tmp.p, nullptr, h->st)); launches += 3;
             RMB_CK(h, launch_refmedia_scatter(nd, h->dp.p, h->matrix.p, h->matrix_n, n_tx, d_rec, h->blkcnt.p, pair_arrays(h),
-                                              h->node_recv.p, h->st));
+                                              h->node_recv.p, hd_ep, h->hd_epoch, h->st));
             ++launches;
         }
     }

@@ -18,6 +18,7 @@ struct DevParams {
     double n0_mw;                     // dbm_to_mw(noise_floor) computed on device once
     double sinr_guard_db;             // |sinr - threshold| below this => exact recheck
     int    rx_base;
+    int    half_duplex;               // rmb_config.half_duplex
 };
 
 // bounding box / fast-path geometry, written by geom_kernel after every position update
@@ -62,7 +63,7 @@ struct Counters {
     unsigned resolve_done;            // blocks of the resolve kernel that have finished (the last one scans tx_cnt)
     unsigned recheck_done;            // work units of the guard-band recheck that have finished
     unsigned emit_done;               // blocks of the emit kernel that have finished (the last one publishes the counters)
-    unsigned pad;
+    int needs_draws;                  // a record carries 0 < p_tx < 1 but the tick runs on the deterministic path
 };
 
 // slot flags
@@ -149,6 +150,10 @@ struct PrepareAux {
     // buffer, raise the flags, then wait -- one kernel does the "all-gather" and the preparation that consumes it
     const rmb_tx_record *push_local; int push_slots, push_rank; size_t push_off; unsigned *push_done;
     char *push_peer[kMaxPeers];
+    int stochastic;                   // the tick takes the draw path (records with 0 < p_tx < 1 are fine)
+    // half duplex (rmb_config.half_duplex): tx_epoch[node] = hd_epoch for every local source of this tick,
+    // hd_cnt[parity][group] = distinct local sources per receiver group; tx_epoch == nullptr: off
+    int *tx_epoch; int hd_epoch; int *hd_cnt; const int *node_gid;
 };
 
 // SM count of the current device (queried once per device: this sits on the tick's launch path)

@@ -6,6 +6,18 @@
 // (__dadd_rn / __dmul_rn / __ddiv_rn), which nvcc never fuses, so the result is the same
 // bit pattern any IEEE-754 machine produces for the same sequence.  tests/ compare these
 // device functions bit-for-bit with the CPU oracle.
+//
+// The algorithms, evaluation order and coefficient tables follow fdlibm's e_log.c, e_log10.c and e_exp.c
+// (third-party, not part of the reference), whose notice is preserved here as it requires:
+//
+// ====================================================
+// Copyright (C) 1993 by Sun Microsystems, Inc. All rights reserved.
+//
+// Developed at SunSoft, a Sun Microsystems, Inc. business.
+// Permission to use, copy, modify, and distribute this
+// software is freely granted, provided that this notice
+// is preserved.
+// ====================================================
 #pragma once
 #include <cstdint>
 

@@ -20,6 +20,7 @@ struct WorkArrays {
     int *perm;                        // work slot -> local node index, -1 = padding
     float *fx, *fy, *fz;              // centred fp32 copy used by the sweep
     double *x64, *y64, *z64, *rxp;    // exact coordinates and rxProbability in work order (resolve / recheck)
+    const int *tx_epoch; int hd_epoch; // half duplex: node p is on the air in this tick iff tx_epoch[p] == hd_epoch (nullptr: off)
 };
 
 // ---- K4: state maintenance ----------------------------------------------------------------
@@ -114,7 +115,7 @@ cudaError_t launch_resolve(const NodeArrays &nd, const WorkArrays &wk, const Dev
                            const rmb_tx_record *rec, SlotArrays sl, PairRecs pr, Counters *ctr, int n_tx, int *seg,
                            int w_first, cudaStream_t st);   // receivers [w_first, n_work) (a multiple of 128)
 // per-node RSSI (total in-band power, dBm) and receiving flag from the work-order results of the last tick
-cudaError_t launch_node_info(const WorkArrays &wk, SlotArrays sl, float *node_rssi, uint8_t *node_recv, cudaStream_t st);
+cudaError_t launch_node_info(const WorkArrays &wk, SlotArrays sl, float *node_rssi, double *node_rssi64, uint8_t *node_recv, cudaStream_t st);
 // part: >= n_work + grid doubles of scratch; cooperative launch of `grid` (= recheck_grid()) blocks with its
 // own barrier counter
 int recheck_grid();
@@ -183,11 +184,15 @@ cudaError_t launch_emit_draw_finish(const DevParams *dp, const rmb_tx_record *re
                                     cudaStream_t st);   // order: records in original packet arrival order (null = as stored)
 
 // ---- K2: the reference media (Null / UDGM / UDGMConstantLoss / N2N), exact double --------------
+// tx_epoch / hd_epoch: half duplex (nullptr: off) -- launch_refmedia_mark stamps the tick's local sources first
+cudaError_t launch_refmedia_mark(const NodeArrays &nd, const DevParams *dp, int n_tx, const rmb_tx_record *rec,
+                                 int *tx_epoch, int hd_epoch, cudaStream_t st);
 cudaError_t launch_refmedia_count(const NodeArrays &nd, const DevParams *dp, const double *matrix, int matrix_n,
-                                  int n_tx, const rmb_tx_record *rec, int *blkcnt, Counters *ctr, cudaStream_t st);
+                                  int n_tx, const rmb_tx_record *rec, int *blkcnt, Counters *ctr, bool stochastic,
+                                  const int *tx_epoch, int hd_epoch, cudaStream_t st);
 cudaError_t launch_refmedia_scatter(const NodeArrays &nd, const DevParams *dp, const double *matrix, int matrix_n,
                                     int n_tx, const rmb_tx_record *rec, const int *blkoff, PairArrays pa,
-                                    uint8_t *node_recv, cudaStream_t st);
+                                    uint8_t *node_recv, const int *tx_epoch, int hd_epoch, cudaStream_t st);
 int refmedia_blocks_per_tx(int n);
 
 }  // namespace rmb

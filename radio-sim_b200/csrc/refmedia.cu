@@ -19,9 +19,11 @@ int refmedia_blocks_per_tx(int n) { return (n + kRefThreads - 1) / kRefThreads; 
 
 // returns the reception probability p (> 0 => heard), and whether the filter passed
 __device__ __forceinline__ double ref_probability(const NodeArrays &nd, const DevParams *dp, const double *matrix,
-                                                  int matrix_n, const rmb_tx_record &r, int node, bool &filter)
+                                                  int matrix_n, const rmb_tx_record &r, int node, bool &filter,
+                                                  const int *tx_epoch, int hd_epoch)
 {
     filter = (dp->rx_base + node) != r.src && nd.enabled[node] && nd.channel[node] == r.channel;
+    if (tx_epoch && tx_epoch[node] == hd_epoch) filter = false;       // half duplex: the node is on the air itself
     if (!filter) return 0.0;
     switch (dp->model) {
     case RMB_MODEL_NULL:
@@ -54,14 +56,19 @@ __device__ __forceinline__ double ref_probability(const NodeArrays &nd, const De
 
 __global__ void __launch_bounds__(kRefThreads)
 refmedia_count_kernel(NodeArrays nd, const DevParams *dp, const double *matrix, int matrix_n, int nblk,
-                      const rmb_tx_record *rec, int *blkcnt, Counters *ctr)
+                      const rmb_tx_record *rec, int *blkcnt, Counters *ctr, int stochastic, const int *tx_epoch, int hd_epoch)
 {
     __shared__ int s_h[kRefThreads / 32], s_f[kRefThreads / 32];
     const int t = blockIdx.x / nblk, b = blockIdx.x % nblk;
     const int node = b * kRefThreads + threadIdx.x;
     const rmb_tx_record r = rec[t];
     bool filter = false, heard = false;
-    if (node < nd.n && r.src >= 0) heard = ref_probability(nd, dp, matrix, matrix_n, r, node, filter) > 0.0;
+    if (node < nd.n && r.src >= 0) heard = ref_probability(nd, dp, matrix, matrix_n, r, node, filter, tx_epoch, hd_epoch) > 0.0;
+    if (b == 0 && threadIdx.x == 0 && r.src >= 0 && !stochastic) {
+        // a record whose tx rule needs a draw must not be evaluated on the deterministic path (see prepare_all_kernel)
+        const double pt = dp->model == RMB_MODEL_UDGM ? dp->success_ratio_rx * r.txprob : dp->model == RMB_MODEL_N2N ? r.txprob : 1.0;
+        if (pt > 0.0 && pt < 1.0) ctr->needs_draws = 1;
+    }
     const unsigned bh = __ballot_sync(0xffffffffu, heard), bf = __ballot_sync(0xffffffffu, filter);
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     if (lane == 0) { s_h[wid] = __popc(bh); s_f[wid] = __popc(bf); }
@@ -77,7 +84,8 @@ refmedia_count_kernel(NodeArrays nd, const DevParams *dp, const double *matrix, 
 
 __global__ void __launch_bounds__(kRefThreads)
 refmedia_scatter_kernel(NodeArrays nd, const DevParams *dp, const double *matrix, int matrix_n, int nblk,
-                        const rmb_tx_record *rec, const int *blkoff, PairArrays pa, uint8_t *node_recv)
+                        const rmb_tx_record *rec, const int *blkoff, PairArrays pa, uint8_t *node_recv,
+                        const int *tx_epoch, int hd_epoch)
 {
     __shared__ int s_w[kRefThreads / 32];
     const int t = blockIdx.x / nblk, b = blockIdx.x % nblk;
@@ -85,7 +93,7 @@ refmedia_scatter_kernel(NodeArrays nd, const DevParams *dp, const double *matrix
     const rmb_tx_record r = rec[t];
     bool filter = false;
     double p = 0.0;
-    if (node < nd.n && r.src >= 0) p = ref_probability(nd, dp, matrix, matrix_n, r, node, filter);
+    if (node < nd.n && r.src >= 0) p = ref_probability(nd, dp, matrix, matrix_n, r, node, filter, tx_epoch, hd_epoch);
     const bool heard = p > 0.0;
     const unsigned bh = __ballot_sync(0xffffffffu, heard);
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -104,22 +112,42 @@ refmedia_scatter_kernel(NodeArrays nd, const DevParams *dp, const double *matrix
     }
 }
 
+// half duplex: stamp the tick's local sources (the count / scatter kernels then drop them as receivers)
+__global__ void refmedia_mark_kernel(NodeArrays nd, const DevParams *dp, int n_tx, const rmb_tx_record *rec, int *tx_epoch, int hd_epoch)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_tx) return;
+    const int s = rec[t].src - dp->rx_base;
+    if (rec[t].src >= 0 && s >= 0 && s < nd.n) tx_epoch[s] = hd_epoch;
+}
+
+cudaError_t launch_refmedia_mark(const NodeArrays &nd, const DevParams *dp, int n_tx, const rmb_tx_record *rec,
+                                 int *tx_epoch, int hd_epoch, cudaStream_t st)
+{
+    if (n_tx <= 0 || !tx_epoch) return cudaSuccess;
+    refmedia_mark_kernel<<<(n_tx + 255) / 256, 256, 0, st>>>(nd, dp, n_tx, rec, tx_epoch, hd_epoch);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_refmedia_count(const NodeArrays &nd, const DevParams *dp, const double *matrix, int matrix_n,
-                                  int n_tx, const rmb_tx_record *rec, int *blkcnt, Counters *ctr, cudaStream_t st)
+                                  int n_tx, const rmb_tx_record *rec, int *blkcnt, Counters *ctr, bool stochastic,
+                                  const int *tx_epoch, int hd_epoch, cudaStream_t st)
 {
     const int nblk = refmedia_blocks_per_tx(nd.n);
     if (n_tx <= 0 || nblk <= 0) return cudaSuccess;
-    refmedia_count_kernel<<<(unsigned)((long long)nblk * n_tx), kRefThreads, 0, st>>>(nd, dp, matrix, matrix_n, nblk, rec, blkcnt, ctr);
+    refmedia_count_kernel<<<(unsigned)((long long)nblk * n_tx), kRefThreads, 0, st>>>(nd, dp, matrix, matrix_n, nblk, rec, blkcnt, ctr,
+                                                                                     stochastic ? 1 : 0, tx_epoch, hd_epoch);
     return cudaGetLastError();
 }
 
 cudaError_t launch_refmedia_scatter(const NodeArrays &nd, const DevParams *dp, const double *matrix, int matrix_n,
                                     int n_tx, const rmb_tx_record *rec, const int *blkoff, PairArrays pa,
-                                    uint8_t *node_recv, cudaStream_t st)
+                                    uint8_t *node_recv, const int *tx_epoch, int hd_epoch, cudaStream_t st)
 {
     const int nblk = refmedia_blocks_per_tx(nd.n);
     if (n_tx <= 0 || nblk <= 0) return cudaSuccess;
-    refmedia_scatter_kernel<<<(unsigned)((long long)nblk * n_tx), kRefThreads, 0, st>>>(nd, dp, matrix, matrix_n, nblk, rec, blkoff, pa, node_recv);
+    refmedia_scatter_kernel<<<(unsigned)((long long)nblk * n_tx), kRefThreads, 0, st>>>(nd, dp, matrix, matrix_n, nblk, rec, blkoff, pa, node_recv,
+                                                                                       tx_epoch, hd_epoch);
     return cudaGetLastError();
 }
 

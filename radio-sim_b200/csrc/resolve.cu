@@ -42,20 +42,22 @@ cudaError_t launch_resolve(const NodeArrays &nd, const WorkArrays &wk, const Dev
 
 // Transciever.getRSSI / getReceivingState for the per-tick node-info (Transciever.java:52-78,
 // JSONClientConnection.java:331-341), produced on demand from the work-order results.
-__global__ void node_info_kernel(WorkArrays wk, SlotArrays sl, float *node_rssi, uint8_t *node_recv)
+__global__ void node_info_kernel(WorkArrays wk, SlotArrays sl, float *node_rssi, double *node_rssi64, uint8_t *node_recv)
 {
     const int w = blockIdx.x * blockDim.x + threadIdx.x;
     if (w >= wk.n_work) return;
     const int p = wk.perm[w];
     if (p < 0) return;
-    node_rssi[p] = (float)xm::mw_to_dbm(sl.itot[w]);
+    const double v = xm::mw_to_dbm(sl.itot[w]);
+    node_rssi[p] = (float)v;
+    node_rssi64[p] = v;
     node_recv[p] = sl.hcnt[w] > 0;
 }
 
-cudaError_t launch_node_info(const WorkArrays &wk, SlotArrays sl, float *node_rssi, uint8_t *node_recv, cudaStream_t st)
+cudaError_t launch_node_info(const WorkArrays &wk, SlotArrays sl, float *node_rssi, double *node_rssi64, uint8_t *node_recv, cudaStream_t st)
 {
     if (wk.n_work <= 0) return cudaSuccess;
-    node_info_kernel<<<(wk.n_work + 255) / 256, 256, 0, st>>>(wk, sl, node_rssi, node_recv);
+    node_info_kernel<<<(wk.n_work + 255) / 256, 256, 0, st>>>(wk, sl, node_rssi, node_rssi64, node_recv);
     return cudaGetLastError();
 }
 

@@ -166,6 +166,7 @@ __device__ __forceinline__ void resolve_receiver(int w, bool active, const WorkA
                 prx = rx_power_dbm(dp, r.power_dbm, d);
                 lin = xm::dbm_to_mw(prx);
                 if (prx >= dp->sensitivity_dbm && wk.rxp[wo] > 0.0) f = kHeard;
+                if (wk.tx_epoch && wk.tx_epoch[po] == wk.hd_epoch) f = 0;     // half duplex: the receiver is on the air itself
             }
             sl.prx[q] = prx; sl.lin[q] = lin; sl.flags[q] = f;
         }
@@ -225,6 +226,7 @@ __device__ __forceinline__ void resolve_receiver(int w, bool active, const WorkA
     if (p >= 0) {
         bool guard = false;
         for (int s = 0; s < c; ++s) guard |= (sl.flags[base + s] & kGuard) != 0;
+        if (wk.tx_epoch && wk.tx_epoch[p] == wk.hd_epoch) itot = dp->n0_mw;     // half duplex: a node on the air reports the noise floor
         sl.itot[w] = itot;
         if (guard && sl.cnt[w] <= K) {
             const int e = atomicAdd(&ctr->n_recheck, 1);

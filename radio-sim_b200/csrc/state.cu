@@ -281,7 +281,7 @@ prepare_all_kernel(NodeArrays nd, const DevParams *dp, const Geom *geom, Groups 
     __shared__ int s_cnt[kMaxGroups], s_base[kMaxGroups], s_goff[kMaxGroups + 1], s_thmin[kMaxGroups];
     __shared__ int s_wcnt[kWarps][kMaxGroups];
     __shared__ unsigned long long s_dec;
-    __shared__ int s_timeout;
+    __shared__ int s_timeout, s_needs;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int ng = groups.ngroups;
 
@@ -305,7 +305,7 @@ prepare_all_kernel(NodeArrays nd, const DevParams *dp, const Geom *geom, Groups 
             }
         }
     }
-    if (tid == 0) s_timeout = 0;
+    if (tid == 0) { s_timeout = 0; s_needs = 0; }
     __syncthreads();
 
     if (tid < 3) {
@@ -359,10 +359,22 @@ prepare_all_kernel(NodeArrays nd, const DevParams *dp, const Geom *geom, Groups 
                 // decisions of this packet: every enabled co-channel receiver except its own source
                 const int s = r.src - dp->rx_base;
                 const int self = (s >= 0 && s < nd.n && nd.enabled[s] && nd.channel[s] == r.channel) ? 1 : 0;
-                decisions += (unsigned long long)(groups.n_rx[g] - self);
+                if (!aux.tx_epoch) decisions += (unsigned long long)(groups.n_rx[g] - self);
+            }
+            // a record with a tx probability strictly inside (0, 1) needs a draw: the deterministic path must not
+            // evaluate it (the host turns this into an error; a shard cannot see it in its own node table)
+            if (r.src >= 0 && !aux.stochastic) { const double pt = tx_success_p(dp, r); if (pt > 0.0 && pt < 1.0) s_needs = 1; }
+            // half duplex: stamp the local sources of this tick and count them per receiver group (each node once)
+            if (aux.tx_epoch && r.src >= 0) {
+                const int s = r.src - dp->rx_base;
+                if (s >= 0 && s < nd.n && atomicExch(&aux.tx_epoch[s], aux.hd_epoch) != aux.hd_epoch) {
+                    const int gg = aux.node_gid[s];
+                    if (gg >= 0) atomicAdd(&aux.hd_cnt[(aux.hd_epoch & 1) * kMaxGroups + gg], 1);
+                }
             }
         }
     }
+    if (aux.tx_epoch && blockIdx.x == 0 && tid < kMaxGroups) aux.hd_cnt[((aux.hd_epoch + 1) & 1) * kMaxGroups + tid] = 0;   // the next tick's
     for (int o = 16; o > 0; o >>= 1) decisions += __shfl_xor_sync(0xffffffffu, decisions, o);
     if (lane == 0 && decisions) atomicAdd(&s_dec, decisions);
     __syncthreads();
@@ -391,6 +403,17 @@ prepare_all_kernel(NodeArrays nd, const DevParams *dp, const Geom *geom, Groups 
             if (blockIdx.x == 0) { theta_min_g[g] = __int_as_float(thm); tx.gcount[g] = total; }
         }
     }
+    if (aux.tx_epoch) {
+        // half duplex: a packet is evaluated by the enabled co-channel receivers that are not on the air themselves
+        // (its own source is one of the transmitting nodes, if it sits in the group at all)
+        unsigned long long dec = 0;
+        for (int t = t_begin + tid; t < t_end; t += kPrepThreads) {
+            const int g = stg.gid[t];
+            if (g >= 0) dec += (unsigned long long)(groups.n_rx[g] - __ldcg(&aux.hd_cnt[(aux.hd_epoch & 1) * kMaxGroups + g]));
+        }
+        for (int o = 16; o > 0; o >>= 1) dec += __shfl_xor_sync(0xffffffffu, dec, o);
+        if (lane == 0 && dec) atomicAdd(&s_dec, dec);
+    }
     __syncthreads();
     if (tid == 0) {
         int cursor = 0;
@@ -398,6 +421,7 @@ prepare_all_kernel(NodeArrays nd, const DevParams *dp, const Geom *geom, Groups 
         s_goff[ng] = cursor;
         if (s_dec) atomicAdd(&ctr->decisions, s_dec);
         if (s_timeout) ctr->peer_timeout = 1;
+        if (s_needs) ctr->needs_draws = 1;
     }
     __syncthreads();
     if (blockIdx.x == 0) {

@@ -1,26 +1,88 @@
 /*
- * CudaRadioMedium -- the reference-side adapter: a RadioMedium (RadioMedium.java:35-45) whose
- * link computation runs in librmb200.so on a B200.  SOURCE ONLY: this image has no JDK, so this
- * file is not compiled or tested here; the C-ABI underneath is (tests/, through ctypes).
+ * CudaRadioMedium -- the reference-side adapter: a RadioMedium (RadioMedium.java:35-45) whose link computation
+ * runs in librmb200.so on a B200.  Goes to radio-medium/java/se/sics/emul8/radiomedium/ together with
+ * events/BulkReceptionEvent.java and the edits of java/reference-edits.patch (INTEGRATION.md section 3).
  *
- * Binding: Panama FFM (java.lang.foreign, JDK 22+), no JNI glue.  transmit() only enqueues (and
- * raises the two transmission events immediately, as every reference medium does:
- * UDGMRadioMedium.java:97); flush(time) -- called from Simulator.emulatorTimeStepDone before
- * processAllEvents (Simulator.java:155-161, see INTEGRATION.md) -- evaluates the whole tick with
- * one rmb_tick and replays the heard pairs as generateReceptionEvents calls in the reference's
- * own order.
+ * NOT COMPILED HERE: this image has no JDK.  What is checked instead (tests/test_java_binding.py): every method
+ * called on a reference class exists in the reference source with that name and arity, every struct offset below
+ * equals offsetof() of include/radiomedium_b200.h under gcc, every downcall descriptor has the arity of the C
+ * prototype, and reference-edits.patch applies to the reference tree.  radio-sim_b200/simulator.py holds the
+ * same adapter logic in Python, and that one runs against the GPU in tests/test_gpu_replay.py.
+ *
+ * Binding: Panama FFM (java.lang.foreign, JDK 22+), no JNI glue.
+ *
+ * Behaviour (each point is the reference's, file:line given):
+ *  - transmit() only queues the packet.  flush() -- FIRST statement of Simulator.emulatorTimeStepDone, i.e.
+ *    before `currentTime = stepTime` (Simulator.java:155-157), so that event start times clamp against the same
+ *    currentTime a reference medium saw in transmit() (Simulator.java:323-326,339-342) -- evaluates all queued
+ *    packets with ONE rmb_tick and hands the result over per packet in arrival order: the packet's two
+ *    transmission events, then its reception events in node-array order (UDGMRadioMedium.java:97-114).
+ *  - udgm-constant delivers at once and raises no events (UDGMConstantLossRadioMedium.java:16-36).
+ *  - RSSI values are the exact doubles (RMB_FLAG_F64_VALUES): the reference media hand on packet.getTransmitPower()
+ *    unchanged (UDGMRadioMedium.java:95), a float column would turn -3.3 into -3.2999999523.
+ *  - Stochastic reception draws from simulator.getRandom() (Simulator.java:94) in the reference's order.  The tick
+ *    consumes host-supplied uniforms and reports how many (rmb_result.n_uniforms_used); a serialised copy of the
+ *    generator supplies them and the real one is then advanced by exactly that many nextDouble() calls.
+ *  - Node state: a new Node[] from simulator.getNodes() (copy-on-write registry, Simulator.java:249-310) is a full
+ *    re-upload; node-config-set mutates nodes in place (net/SimulatorJSONHandler.java:105-143), which reaches the
+ *    device through nodeConfigChanging(node) (the one-line hook of the patch) or, without the hook, through a
+ *    per-tick scan of all nodes against a shadow copy (Options.scanNodes, default on).
+ *  - getBaseRSSI(node) (Transciever.java:52-61) is the reference's constant unless Options.rssiInBand, then the
+ *    node's total in-band power of the last evaluated tick from rmb_node_info_f64 (what CC2420 CCA thresholds).
  */
 package se.sics.emul8.radiomedium;
 
-import java.lang.foreign.*;
+import java.io.ByteArrayInputStream;
+import java.io.ByteArrayOutputStream;
+import java.io.ObjectInputStream;
+import java.io.ObjectOutputStream;
+import java.lang.foreign.Arena;
+import java.lang.foreign.FunctionDescriptor;
+import java.lang.foreign.Linker;
+import java.lang.foreign.MemorySegment;
+import java.lang.foreign.SymbolLookup;
 import java.lang.invoke.MethodHandle;
 import java.util.ArrayList;
-import static java.lang.foreign.ValueLayout.*;
+import java.util.IdentityHashMap;
+import java.util.Random;
+
+import static java.lang.foreign.ValueLayout.ADDRESS;
+import static java.lang.foreign.ValueLayout.JAVA_BYTE;
+import static java.lang.foreign.ValueLayout.JAVA_DOUBLE;
+import static java.lang.foreign.ValueLayout.JAVA_INT;
+import static java.lang.foreign.ValueLayout.JAVA_LONG;
 
 public class CudaRadioMedium extends AbstractRadioMedium {
 
+    /* enum rmb_model */
     public static final int MODEL_NULL = 0, MODEL_UDGM = 1, MODEL_UDGM_CONSTANT = 2, MODEL_N2N = 3, MODEL_SINR = 4;
+    /* enum rmb_outcome, rmb_flags, rmb_status */
     private static final int DELIVERED = 2;
+    private static final int FLAG_F64_VALUES = 1, FLAG_COMPACT = 2;
+    private static final int RMB_OK = 0, RMB_ERR_UNIFORMS = -5;
+
+    /* struct rmb_config: offsetof() of the field named after the prefix, sizeof() for _SIZE */
+    private static final long CFG_SIZE = 120, CFG_MODEL = 4, CFG_DEVICE = 8, CFG_FLAGS = 12,
+            CFG_SUCCESS_RATIO_TX = 16, CFG_SUCCESS_RATIO_RX = 24, CFG_TRANSMISSION_RANGE = 32, CFG_CONSTANT_RANGE = 40,
+            CFG_PL0_DB = 48, CFG_PL_EXPONENT = 56, CFG_D0_M = 64, CFG_SENSITIVITY_DBM = 72, CFG_SINR_THRESHOLD_DB = 80,
+            CFG_NOISE_FLOOR_DBM = 88, CFG_HALF_DUPLEX = 112;
+    /* struct rmb_result */
+    private static final long RES_SIZE = 128, RES_N_PAIRS = 0, RES_N_UNIFORMS_USED = 32, RES_N_TX = 48, RES_RX = 64,
+            RES_OUTCOME = 88, RES_RSSI_DBM_F64 = 96, RES_TX_FAILED = 112, RES_TX_FIRST = 120;
+
+    /** Parameters of the medium (`configuration-set`, net/SimulatorJSONHandler.java:170-216); NaN = library default. */
+    public static class Options {
+        public int device = 0;
+        public double successRatioTx = Double.NaN, successRatioRx = Double.NaN;       /* UDGMRadioMedium.java:17-18 */
+        public double transmissionRange = Double.NaN;                                 /* UDGMRadioMedium.java:23 */
+        public double constantRange = Double.NaN;                                     /* UDGMConstantLossRadioMedium.java:8 */
+        public double pl0Db = Double.NaN, plExponent = Double.NaN, d0M = Double.NaN;
+        public double sensitivityDbm = Double.NaN, sinrThresholdDb = Double.NaN;
+        public boolean halfDuplex = false;       /* false = the reference: only node == source excluded (UDGMRadioMedium.java:100) */
+        public boolean rssiInBand = false;       /* getBaseRSSI = total in-band power of the last tick instead of baseRSSI */
+        public boolean scanNodes = true;         /* diff all nodes against the shadow copy every tick (no handler hook needed) */
+        public boolean bulkEvents = true;        /* Simulator.generateReceptionEventsBulk instead of one call per heard pair */
+    }
 
     private static final Linker LINKER = Linker.nativeLinker();
     private static final SymbolLookup LIB = SymbolLookup.libraryLookup(
@@ -36,32 +98,87 @@ public class CudaRadioMedium extends AbstractRadioMedium {
     private static final MethodHandle LAST_ERROR = fn("rmb_last_error", FunctionDescriptor.of(ADDRESS, ADDRESS));
     private static final MethodHandle SET_NODES = fn("rmb_set_nodes", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT,
             ADDRESS, ADDRESS, ADDRESS, ADDRESS, ADDRESS, ADDRESS, ADDRESS, ADDRESS, ADDRESS));
+    private static final MethodHandle SET_MATRIX = fn("rmb_set_matrix", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT, ADDRESS));
+    private static final MethodHandle UPDATE_POSITIONS = fn("rmb_update_positions", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT,
+            ADDRESS, ADDRESS, ADDRESS, ADDRESS));
+    private static final MethodHandle UPDATE_RADIO = fn("rmb_update_radio", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT,
+            ADDRESS, ADDRESS, ADDRESS, ADDRESS, ADDRESS, ADDRESS));
     private static final MethodHandle TICK = fn("rmb_tick", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT,
             ADDRESS, ADDRESS, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS));
+    private static final MethodHandle NODE_INFO_F64 = fn("rmb_node_info_f64", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
 
-    /* struct rmb_config (include/radiomedium_b200.h): 4 x int32, 10 x double, int64, 2 x int32 = 112 bytes */
-    private static final long CFG_SIZE = 112, CFG_MODEL = 4, CFG_PL0 = 48, CFG_EXPONENT = 56, CFG_SENS = 72, CFG_THR = 80;
-    /* struct rmb_result: 6 x int64, 2 x int32, 9 pointers = 128 bytes */
-    private static final long RES_SIZE = 128, RES_NPAIRS = 0, RES_TX = 56, RES_RX = 64, RES_RSSI = 72, RES_OUTCOME = 88;
-
+    private final int model;
+    private final Options options;
     private final Arena arena = Arena.ofShared();
     private final MemorySegment handle;
     private final ArrayList<RadioPacket> pending = new ArrayList<>();
+
+    /* the node table as last uploaded: array identity, index of every node, shadow copy of what the device holds */
     private Node[] registered = new Node[0];
+    private final IdentityHashMap<Node, Integer> indexOf = new IdentityHashMap<>();
+    private double[] sx = new double[0], sy = sx, sz = sx, sPower = sx, sRxp = sx, sTxp = sx;
+    private int[] sChannel = new int[0];
+    private byte[] sEnabled = new byte[0];
+    private int[] dirty = new int[16];
+    private int nDirty = 0;
+    private boolean[] isDirty = new boolean[0];
+    private boolean mayDraw = false;
+
+    /* node-info of the last evaluated tick (Options.rssiInBand) */
+    private double[] nodeRssi = new double[0];
+    private byte[] nodeReceiving = new byte[0];
+    private boolean nodeInfoValid = false;
 
     public CudaRadioMedium(int model) {
+        this(model, new Options());
+    }
+
+    public CudaRadioMedium(int model, Options o) {
+        this.model = model;
+        this.options = o;
         try {
             MemorySegment cfg = arena.allocate(CFG_SIZE, 8);
             CONFIG_DEFAULT.invoke(cfg, model);
+            cfg.set(JAVA_INT, CFG_DEVICE, o.device);
+            cfg.set(JAVA_INT, CFG_FLAGS, FLAG_F64_VALUES | FLAG_COMPACT);
+            cfg.set(JAVA_INT, CFG_HALF_DUPLEX, o.halfDuplex ? 1 : 0);
+            setIfGiven(cfg, CFG_SUCCESS_RATIO_TX, o.successRatioTx);
+            setIfGiven(cfg, CFG_SUCCESS_RATIO_RX, o.successRatioRx);
+            setIfGiven(cfg, CFG_TRANSMISSION_RANGE, o.transmissionRange);
+            setIfGiven(cfg, CFG_CONSTANT_RANGE, o.constantRange);
+            setIfGiven(cfg, CFG_PL0_DB, o.pl0Db);
+            setIfGiven(cfg, CFG_PL_EXPONENT, o.plExponent);
+            setIfGiven(cfg, CFG_D0_M, o.d0M);
+            setIfGiven(cfg, CFG_SENSITIVITY_DBM, o.sensitivityDbm);
+            setIfGiven(cfg, CFG_SINR_THRESHOLD_DB, o.sinrThresholdDb);
+            cfg.set(JAVA_DOUBLE, CFG_NOISE_FLOOR_DBM, baseRSSI);                      /* AbstractRadioMedium.java:38 */
             MemorySegment out = arena.allocate(ADDRESS);
             int rc = (int) CREATE.invoke(cfg, out);
-            if (rc != 0) {
-                MemorySegment msg = (MemorySegment) LAST_ERROR.invoke(MemorySegment.NULL);
-                throw new IllegalStateException("rmb_create: " + msg.reinterpret(256).getString(0));   // no CPU fallback
+            if (rc != RMB_OK) {
+                throw new IllegalStateException("rmb_create: " + errorText(MemorySegment.NULL));     /* no CPU fallback */
             }
             handle = out.get(ADDRESS, 0);
+        } catch (RuntimeException e) {
+            throw e;
         } catch (Throwable t) {
             throw new IllegalStateException(t);
+        }
+    }
+
+    private static void setIfGiven(MemorySegment cfg, long offset, double v) {
+        if (!Double.isNaN(v)) {
+            cfg.set(JAVA_DOUBLE, offset, v);
+        }
+    }
+
+    private static String errorText(MemorySegment h) throws Throwable {
+        MemorySegment msg = (MemorySegment) LAST_ERROR.invoke(h);
+        return msg.reinterpret(512).getString(0);
+    }
+
+    private void check(int rc, String what) throws Throwable {
+        if (rc != RMB_OK) {
+            throw new IllegalStateException(what + " rc=" + rc + ": " + errorText(handle));
         }
     }
 
@@ -70,38 +187,131 @@ public class CudaRadioMedium extends AbstractRadioMedium {
         return "B200 medium";
     }
 
+    /** N2NRadioMedium.setN2NMatrix (N2NRadioMedium.java:20-22): rows = source id - 1, columns = destination id - 1. */
+    public synchronized void setN2NMatrix(double[][] m) {
+        try (Arena a = Arena.ofConfined()) {
+            int n = m.length;
+            MemorySegment flat = a.allocate(JAVA_DOUBLE, (long) Math.max(1, n * n));
+            for (int i = 0; i < n; i++) {
+                MemorySegment.copy(m[i], 0, flat, JAVA_DOUBLE, (long) i * n * 8, n);
+            }
+            check((int) SET_MATRIX.invoke(handle, n, flat), "rmb_set_matrix");
+        } catch (RuntimeException e) {
+            throw e;
+        } catch (Throwable t) {
+            throw new IllegalStateException(t);
+        }
+    }
+
     /* RadioMedium.transmit: called from any client reader thread (net/SimulatorJSONHandler.java:93) */
     @Override
     public synchronized void transmit(RadioPacket packet) {
-        simulator.generateTransmissionEvents(packet);
+        if (simulator == null) {
+            return;                                                     /* NullRadioMedium.java:50-53 */
+        }
         pending.add(packet);
     }
 
-    /* End-of-tick hook: evaluate every transmission of the tick at once. */
-    public synchronized void flush(long time) {
-        if (pending.isEmpty()) return;
+    /**
+     * Hook for net/SimulatorJSONHandler.java:105 (node-config-set), called BEFORE the handler mutates the node:
+     * packets already transmitted in this tick are evaluated against the state they were sent under (the reference
+     * evaluates inside transmit()), then the node is marked for re-reading at the next evaluation.
+     */
+    public synchronized void nodeConfigChanging(Node node) {
+        flush(0L);
+        Integer i = indexOf.get(node);
+        if (i != null) {
+            markDirty(i);
+        }
+    }
+
+    private void markDirty(int i) {
+        if (isDirty[i]) {
+            return;
+        }
+        isDirty[i] = true;
+        if (nDirty == dirty.length) {
+            dirty = java.util.Arrays.copyOf(dirty, 2 * nDirty);
+        }
+        dirty[nDirty++] = i;
+    }
+
+    /** End-of-tick hook: evaluate every transmission queued since the last evaluation. */
+    public synchronized void flush(long stepTime) {
+        if (pending.isEmpty() || simulator == null) {
+            pending.clear();
+            return;
+        }
         try (Arena tick = Arena.ofConfined()) {
             Node[] nodes = simulator.getNodes();
-            if (nodes != registered) upload(nodes);           // copy-on-write array: identity change == registry change
-            int t = pending.size();
-            MemorySegment src = tick.allocate(JAVA_INT, t), power = tick.allocate(JAVA_DOUBLE, t), chan = tick.allocate(JAVA_INT, t);
-            for (int i = 0; i < t; i++) {
-                RadioPacket p = pending.get(i);
-                src.setAtIndex(JAVA_INT, i, indexOf(nodes, p.getSource()));
-                power.setAtIndex(JAVA_DOUBLE, i, p.getTxpower());
-                chan.setAtIndex(JAVA_INT, i, p.getWirelessChannel());
+            if (nodes != registered) {
+                upload(nodes);                    /* copy-on-write registry: a new array is a registry change */
+            } else {
+                pushChanges(nodes, tick);
             }
-            /* uniforms: the tick may consume at most t + t*n draws; fill lazily in production */
+            /* packets whose source left the registry meanwhile cannot be evaluated (and would not be heard from) */
+            int t = 0;
+            RadioPacket[] packets = new RadioPacket[pending.size()];
+            int[] src = new int[packets.length], chan = new int[packets.length];
+            double[] power = new double[packets.length];
+            for (RadioPacket p : pending) {
+                Integer i = indexOf.get(p.getSource());
+                if (i == null) {
+                    continue;
+                }
+                packets[t] = p;
+                src[t] = i;
+                power[t] = p.getTransmitPower();                        /* RadioPacket.java:49,77: snapshot / override */
+                chan[t] = p.getWirelessChannel();                       /* RadioPacket.java:50,85 */
+                t++;
+            }
+            pending.clear();
+            if (t == 0) {
+                return;
+            }
+            MemorySegment mSrc = tick.allocate(JAVA_INT, t), mPower = tick.allocate(JAVA_DOUBLE, t), mChan = tick.allocate(JAVA_INT, t);
+            MemorySegment.copy(src, 0, mSrc, JAVA_INT, 0, t);
+            MemorySegment.copy(power, 0, mPower, JAVA_DOUBLE, 0, t);
+            MemorySegment.copy(chan, 0, mChan, JAVA_INT, 0, t);
             MemorySegment res = tick.allocate(RES_SIZE, 8);
-            int rc = (int) TICK.invoke(handle, t, src, power, chan, MemorySegment.NULL, 0L, res);
-            if (rc != 0) throw new IllegalStateException("rmb_tick rc=" + rc);
-            long n = res.get(JAVA_LONG, RES_NPAIRS);
-            MemorySegment tx = res.get(ADDRESS, RES_TX).reinterpret(4 * n), rx = res.get(ADDRESS, RES_RX).reinterpret(4 * n);
-            MemorySegment rssi = res.get(ADDRESS, RES_RSSI).reinterpret(4 * n), out = res.get(ADDRESS, RES_OUTCOME).reinterpret(n);
-            for (long i = 0; i < n; i++) {
-                simulator.generateReceptionEvents(pending.get(tx.getAtIndex(JAVA_INT, i)), nodes[rx.getAtIndex(JAVA_INT, i)],
-                        rssi.getAtIndex(JAVA_FLOAT, i), out.get(JAVA_BYTE, i) == DELIVERED);
+
+            /* deterministic tick: one call.  With draws: the first call (no uniforms; missing draws read as 0.0 =
+             * "success", which maximises the number of later draws) tells how many uniforms the tick can consume at
+             * most; a copy of the simulator's generator supplies that many, and the real generator is advanced by
+             * the number actually consumed -- the sequence the reference's media would have left behind. */
+            int rc = (int) TICK.invoke(handle, t, mSrc, mPower, mChan, MemorySegment.NULL, 0L, res);
+            if (rc == RMB_ERR_UNIFORMS) {
+                long bound = res.get(JAVA_LONG, RES_N_UNIFORMS_USED);
+                Random real = simulator.getRandom();
+                Random probe = copyOf(real);
+                MemorySegment u = tick.allocate(JAVA_DOUBLE, Math.max(1L, bound));
+                for (long k = 0; k < bound; k++) {
+                    u.setAtIndex(JAVA_DOUBLE, k, probe.nextDouble());
+                }
+                rc = (int) TICK.invoke(handle, t, mSrc, mPower, mChan, u, bound, res);
+                check(rc, "rmb_tick");
+                long used = res.get(JAVA_LONG, RES_N_UNIFORMS_USED);
+                for (long k = 0; k < used; k++) {
+                    real.nextDouble();
+                }
+            } else {
+                check(rc, "rmb_tick");
             }
+
+            int n = (int) res.get(JAVA_LONG, RES_N_PAIRS);
+            int[] txFirst = new int[t + 1], rx = new int[n];
+            double[] rssi = new double[n];
+            byte[] outcome = new byte[n];
+            MemorySegment.copy(res.get(ADDRESS, RES_TX_FIRST).reinterpret(4L * (t + 1)), JAVA_INT, 0, txFirst, 0, t + 1);
+            if (n > 0) {
+                MemorySegment.copy(res.get(ADDRESS, RES_RX).reinterpret(4L * n), JAVA_INT, 0, rx, 0, n);
+                MemorySegment.copy(res.get(ADDRESS, RES_RSSI_DBM_F64).reinterpret(8L * n), JAVA_DOUBLE, 0, rssi, 0, n);
+                MemorySegment.copy(res.get(ADDRESS, RES_OUTCOME).reinterpret(n), JAVA_BYTE, 0, outcome, 0, n);
+            }
+            nodeInfoValid = false;
+            deliver(packets, t, txFirst, nodes, rx, rssi, outcome);
+        } catch (RuntimeException e) {
+            throw e;
         } catch (Throwable e) {
             throw new IllegalStateException(e);
         } finally {
@@ -109,35 +319,178 @@ public class CudaRadioMedium extends AbstractRadioMedium {
         }
     }
 
-    private static int indexOf(Node[] nodes, Node n) {
-        for (int i = 0; i < nodes.length; i++) if (nodes[i] == n) return i;
-        return -1;
-    }
-
-    /* Node[] (AoS objects) -> the SoA arrays of rmb_set_nodes */
-    private void upload(Node[] nodes) throws Throwable {
-        try (Arena a = Arena.ofConfined()) {
-            int n = nodes.length;
-            MemorySegment x = a.allocate(JAVA_DOUBLE, n), y = a.allocate(JAVA_DOUBLE, n), z = a.allocate(JAVA_DOUBLE, n);
-            MemorySegment pw = a.allocate(JAVA_DOUBLE, n), rxp = a.allocate(JAVA_DOUBLE, n), txp = a.allocate(JAVA_DOUBLE, n);
-            MemorySegment ch = a.allocate(JAVA_INT, n), id = a.allocate(JAVA_INT, n), en = a.allocate(JAVA_BYTE, n);
-            for (int i = 0; i < n; i++) {
-                Position p = nodes[i].getPosition();
-                Transciever r = nodes[i].getRadio();
-                x.setAtIndex(JAVA_DOUBLE, i, p.x); y.setAtIndex(JAVA_DOUBLE, i, p.y); z.setAtIndex(JAVA_DOUBLE, i, p.z);
-                pw.setAtIndex(JAVA_DOUBLE, i, r.getTxpower());
-                rxp.setAtIndex(JAVA_DOUBLE, i, r.getRxProbability()); txp.setAtIndex(JAVA_DOUBLE, i, r.getTxProbability());
-                ch.setAtIndex(JAVA_INT, i, r.getWirelessChannel()); id.setAtIndex(JAVA_INT, i, nodes[i].getIdAsInteger());
-                en.set(JAVA_BYTE, i, (byte) (r.isEnabled() ? 1 : 0));
+    /* the reference's call sequence, packet by packet (UDGMRadioMedium.java:97-114) */
+    private void deliver(RadioPacket[] packets, int t, int[] txFirst, Node[] nodes, int[] rx, double[] rssi, byte[] outcome) {
+        if (model == MODEL_UDGM_CONSTANT) {
+            for (int k = 0; k < t; k++) {                               /* UDGMConstantLossRadioMedium.java:30-32 */
+                for (int i = txFirst[k]; i < txFirst[k + 1]; i++) {
+                    simulator.deliverRadioPacket(packets[k], nodes[rx[i]], rssi[i]);
+                }
             }
-            int rc = (int) SET_NODES.invoke(handle, n, x, y, z, pw, ch, en, rxp, txp, id);
-            if (rc != 0) throw new IllegalStateException("rmb_set_nodes rc=" + rc);
-            registered = nodes;
+        } else if (options.bulkEvents) {
+            simulator.generateReceptionEventsBulk(packets, t, txFirst, nodes, rx, rssi, outcome);
+        } else {
+            for (int k = 0; k < t; k++) {
+                simulator.generateTransmissionEvents(packets[k]);
+                for (int i = txFirst[k]; i < txFirst[k + 1]; i++) {
+                    simulator.generateReceptionEvents(packets[k], nodes[rx[i]], rssi[i], outcome[i] == DELIVERED);
+                }
+            }
         }
     }
 
-    public void close() throws Throwable {
-        DESTROY.invoke(handle);
-        arena.close();
+    /* java.util.Random is Serializable: a deserialised copy continues the same sequence */
+    private static Random copyOf(Random r) throws Exception {
+        ByteArrayOutputStream bytes = new ByteArrayOutputStream();
+        try (ObjectOutputStream out = new ObjectOutputStream(bytes)) {
+            out.writeObject(r);
+        }
+        try (ObjectInputStream in = new ObjectInputStream(new ByteArrayInputStream(bytes.toByteArray()))) {
+            return (Random) in.readObject();
+        }
+    }
+
+    /* Node[] (objects) -> the SoA arrays of rmb_set_nodes; also the shadow copy and the node -> index map */
+    private void upload(Node[] nodes) throws Throwable {
+        int n = nodes.length;
+        sx = new double[n]; sy = new double[n]; sz = new double[n];
+        sPower = new double[n]; sRxp = new double[n]; sTxp = new double[n];
+        sChannel = new int[n]; sEnabled = new byte[n];
+        int[] id = new int[n];
+        isDirty = new boolean[n];
+        nDirty = 0;
+        indexOf.clear();
+        for (int i = 0; i < n; i++) {
+            readNode(nodes[i], i);
+            id[i] = nodes[i].getIdAsInteger();                          /* Node.java:65-67 (N2N rows/columns) */
+            indexOf.put(nodes[i], i);
+        }
+        try (Arena a = Arena.ofConfined()) {
+            long c = Math.max(1, n);
+            MemorySegment x = a.allocate(JAVA_DOUBLE, c), y = a.allocate(JAVA_DOUBLE, c), z = a.allocate(JAVA_DOUBLE, c);
+            MemorySegment pw = a.allocate(JAVA_DOUBLE, c), rxp = a.allocate(JAVA_DOUBLE, c), txp = a.allocate(JAVA_DOUBLE, c);
+            MemorySegment ch = a.allocate(JAVA_INT, c), ids = a.allocate(JAVA_INT, c), en = a.allocate(JAVA_BYTE, c);
+            MemorySegment.copy(sx, 0, x, JAVA_DOUBLE, 0, n); MemorySegment.copy(sy, 0, y, JAVA_DOUBLE, 0, n);
+            MemorySegment.copy(sz, 0, z, JAVA_DOUBLE, 0, n); MemorySegment.copy(sPower, 0, pw, JAVA_DOUBLE, 0, n);
+            MemorySegment.copy(sRxp, 0, rxp, JAVA_DOUBLE, 0, n); MemorySegment.copy(sTxp, 0, txp, JAVA_DOUBLE, 0, n);
+            MemorySegment.copy(sChannel, 0, ch, JAVA_INT, 0, n); MemorySegment.copy(id, 0, ids, JAVA_INT, 0, n);
+            MemorySegment.copy(sEnabled, 0, en, JAVA_BYTE, 0, n);
+            check((int) SET_NODES.invoke(handle, n, x, y, z, pw, ch, en, rxp, txp, ids), "rmb_set_nodes");
+        }
+        registered = nodes;
+        nodeInfoValid = false;
+    }
+
+    /* one node's fields into the shadow arrays; true if anything the device holds changed */
+    private boolean readNode(Node node, int i) {
+        Position p = node.getPosition();                                /* Position.java:37-39: public doubles */
+        Transciever r = node.getRadio();
+        double x = p.x, y = p.y, z = p.z, pw = r.getTransmitPower(), rxp = r.getRxProbability(), txp = r.getTxProbability();
+        int ch = r.getWirelessChannel();
+        byte en = (byte) (r.isEnabled() ? 1 : 0);
+        boolean moved = x != sx[i] || y != sy[i] || z != sz[i];
+        boolean radio = pw != sPower[i] || rxp != sRxp[i] || txp != sTxp[i] || ch != sChannel[i] || en != sEnabled[i];
+        sx[i] = x; sy[i] = y; sz[i] = z; sPower[i] = pw; sRxp[i] = rxp; sTxp[i] = txp; sChannel[i] = ch; sEnabled[i] = en;
+        return moved || radio;
+    }
+
+    /* in-place changes of registered nodes -> rmb_update_positions / rmb_update_radio for exactly those indices */
+    private void pushChanges(Node[] nodes, Arena tick) throws Throwable {
+        if (options.scanNodes) {
+            for (int i = 0; i < nodes.length; i++) {
+                if (!isDirty[i] && readNode(nodes[i], i)) {
+                    markDirty(i);
+                }
+            }
+        }
+        if (nDirty == 0) {
+            return;
+        }
+        int c = nDirty;
+        MemorySegment idx = tick.allocate(JAVA_INT, c), x = tick.allocate(JAVA_DOUBLE, c), y = tick.allocate(JAVA_DOUBLE, c),
+                z = tick.allocate(JAVA_DOUBLE, c), pw = tick.allocate(JAVA_DOUBLE, c), rxp = tick.allocate(JAVA_DOUBLE, c),
+                txp = tick.allocate(JAVA_DOUBLE, c), ch = tick.allocate(JAVA_INT, c), en = tick.allocate(JAVA_BYTE, c);
+        for (int k = 0; k < c; k++) {
+            int i = dirty[k];
+            readNode(nodes[i], i);
+            isDirty[i] = false;
+            idx.setAtIndex(JAVA_INT, k, i);
+            x.setAtIndex(JAVA_DOUBLE, k, sx[i]); y.setAtIndex(JAVA_DOUBLE, k, sy[i]); z.setAtIndex(JAVA_DOUBLE, k, sz[i]);
+            pw.setAtIndex(JAVA_DOUBLE, k, sPower[i]); rxp.setAtIndex(JAVA_DOUBLE, k, sRxp[i]); txp.setAtIndex(JAVA_DOUBLE, k, sTxp[i]);
+            ch.setAtIndex(JAVA_INT, k, sChannel[i]); en.set(JAVA_BYTE, k, sEnabled[i]);
+        }
+        nDirty = 0;
+        check((int) UPDATE_POSITIONS.invoke(handle, c, idx, x, y, z), "rmb_update_positions");
+        check((int) UPDATE_RADIO.invoke(handle, c, idx, pw, ch, en, rxp, txp), "rmb_update_radio");
+        nodeInfoValid = false;
+    }
+
+    /* Transciever.getRSSI falls back to this while the node is not receiving (Transciever.java:52-61) */
+    @Override
+    public synchronized double getBaseRSSI(Node node) {
+        if (!options.rssiInBand) {
+            return baseRSSI;                                            /* AbstractRadioMedium.java:45-48 */
+        }
+        Integer i = indexOf.get(node);
+        if (i == null || !refreshNodeInfo() || i >= nodeRssi.length) {
+            return baseRSSI;
+        }
+        return nodeRssi[i];
+    }
+
+    /**
+     * The idle RSSI of every node for the per-tick node-info (net/JSONClientConnection.java:326-353), index ==
+     * node-array index: total in-band power of the last evaluated tick in dBm (noise floor where nothing was on
+     * the air).  null when Options.rssiInBand is off or `nodes` is not the array the device holds -- the caller
+     * then uses Transciever.getRSSI() as the reference does.  The array is shared, not a copy: read only.
+     */
+    public synchronized double[] nodeRssiForTimeStep(Node[] nodes) {
+        if (!options.rssiInBand || nodes != registered || !refreshNodeInfo()) {
+            return null;
+        }
+        return nodeRssi;
+    }
+
+    /** 1 where the node heard at least one frame in the last evaluated tick (same indexing); null if unknown. */
+    public synchronized byte[] nodeHeardForTimeStep(Node[] nodes) {
+        if (nodes != registered || !refreshNodeInfo()) {
+            return null;
+        }
+        return nodeReceiving;
+    }
+
+    private boolean refreshNodeInfo() {
+        if (nodeInfoValid) {
+            return true;
+        }
+        int n = registered.length;
+        if (n == 0) {
+            return false;
+        }
+        try (Arena a = Arena.ofConfined()) {
+            MemorySegment r = a.allocate(JAVA_DOUBLE, n), f = a.allocate(JAVA_BYTE, n);
+            int rc = (int) NODE_INFO_F64.invoke(handle, r, f);
+            if (rc != RMB_OK) {
+                return false;
+            }
+            nodeRssi = new double[n];
+            nodeReceiving = new byte[n];
+            MemorySegment.copy(r, JAVA_DOUBLE, 0, nodeRssi, 0, n);
+            MemorySegment.copy(f, JAVA_BYTE, 0, nodeReceiving, 0, n);
+            nodeInfoValid = true;
+            return true;
+        } catch (Throwable t) {
+            return false;
+        }
+    }
+
+    public synchronized void close() {
+        try {
+            DESTROY.invoke(handle);
+        } catch (Throwable t) {
+            throw new IllegalStateException(t);
+        } finally {
+            arena.close();
+        }
     }
 }

@@ -270,6 +270,13 @@ class Medium:
         self._ck(self._lib.rmb_node_info(self._h, _ptr(rssi, C.c_float), _ptr(recv, C.c_uint8)))
         return rssi[:self.n], recv[:self.n]
 
+    def node_info_f64(self):
+        """The same with the total in-band power in double (what node-info.rssi carries)."""
+        rssi = np.zeros(max(self.n, 1), dtype=np.float64)
+        recv = np.zeros(max(self.n, 1), dtype=np.uint8)
+        self._ck(self._lib.rmb_node_info_f64(self._h, _ptr(rssi, C.c_double), _ptr(recv, C.c_uint8)))
+        return rssi[:self.n], recv[:self.n]
+
     def timing(self):
         t = A.Timing()
         self._ck(self._lib.rmb_last_timing(self._h, C.byref(t)))

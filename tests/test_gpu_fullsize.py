@@ -113,3 +113,110 @@ def test_renumbering_the_nodes_only_renumbers_the_lists_300k(rsb):
     fin = np.isfinite(a.sinr_db_f64)
     assert np.array_equal(fin, np.isfinite(b.sinr_db_f64[order]))
     assert np.abs(b.sinr_db_f64[order][fin] - a.sinr_db_f64[fin]).max() < SINR_TOL_DB
+
+
+# ---- every receiver of the full-size configurations, pair for pair --------------------------------------------
+# Deployments from java.util.Random (tools/workloads.py).  The oracle runs on the box's host threads (1e10
+# decisions: 15-30 s on 16 threads); its lists are also pinned by digest in tests/golden/fullsize_hashes.json
+# (generated by the oracle on another machine: tests/golden/make_fullsize_hashes.py).
+GUARD_DB = 1.5e-3            # DevParams.sinr_guard_db (csrc/state.cu init_params_kernel)
+
+
+def _digest(tx, rx, outcome):
+    import hashlib
+    h = hashlib.sha256()
+    h.update(np.ascontiguousarray(tx, dtype="<i4").tobytes())
+    h.update(np.ascontiguousarray(rx, dtype="<i4").tobytes())
+    h.update(np.ascontiguousarray(outcome, dtype="u1").tobytes())
+    return h.hexdigest()
+
+
+def _golden():
+    import json, os
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "fullsize_hashes.json")) as f:
+        return json.load(f)
+
+
+def _full_compare(r, ref, key):
+    """lists bit-exact vs the oracle run here AND vs the committed digest; SINR error of every heard pair below a
+    third of the guard band (what makes the guard-band recheck sound)."""
+    compare(r, ref)
+    g = _golden()[key]
+    assert r.n_pairs == g["n_pairs"] and r.n_decisions == g["n_decisions"] and r.n_delivered == g["n_delivered"]
+    assert _digest(r.tx, r.rx, r.outcome) == g["sha256"]
+    p = ref["pairs"]
+    fin = np.isfinite(p["sinr_db"])
+    err = np.abs(r.sinr_db_f64[fin] - p["sinr_db"][fin]).max()
+    assert err < GUARD_DB / 3, err
+    return float(err)
+
+
+@pytest.mark.parametrize("grid", [False, True], ids=["random", "grid"])
+def test_config4_every_receiver_against_the_oracle(rsb, orc, grid):
+    import workloads as W
+    dep = W.deployment("c4", grid=grid)
+    with rsb.Medium("sinr", f64_values=True) as m:
+        m.set_nodes(dep["x"], dep["y"])
+        r = m.tick(dep["src"])
+        rssi, recv = m.node_info_f64()
+    ref = orc.tick(orc.params(orc.MODEL_SINR), orc.NodeSet(dep["x"], dep["y"]), orc.make_packets(dep["src"], 0.0, 26),
+                   threads=16, cap=6_000_000, want_total=True)
+    assert ref["status"] == 0 and ref["n_pairs"] > 1_000_000
+    err = _full_compare(r, ref, "c4-grid" if grid else "c4")
+    # per-node total in-band power (far fp32 sum + exact near terms) against the sequential double sum, ALL receivers
+    tot_err = np.abs(rssi - ref["total_dbm"]).max()
+    assert tot_err < GUARD_DB / 3, tot_err
+    heard = np.zeros(dep["n"], dtype=bool); heard[ref["pairs"]["rx"]] = True
+    assert np.array_equal(recv.astype(bool), heard)
+    print(f"\nC4 {'grid' if grid else 'random'}: max |SINR err| {err:.3e} dB, max |total power err| {tot_err:.3e} dB, "
+          f"recheck {r.n_recheck}")
+
+
+def test_config5_1m_nodes_16_channels_three_mobility_ticks_against_the_oracle(rsb, orc):
+    import workloads as W
+    dep = W.deployment("c5")
+    with rsb.Medium("sinr", f64_values=True) as m:
+        m.set_nodes(dep["x"], dep["y"], channel=dep["channel"])
+        for k in (1, 2, 3):
+            src = W.c5_tick(dep, k)
+            m.update_positions(dep["x"], dep["y"])
+            r = m.tick(src)
+            ref = orc.tick(orc.params(orc.MODEL_SINR), orc.NodeSet(dep["x"], dep["y"], channel=dep["channel"]),
+                           orc.make_packets(src, 0.0, dep["channel"][src]), threads=16, cap=6_000_000)
+            assert r.n_decisions == ref["n_decisions"] > 6.2e8
+            _full_compare(r, ref, f"c5-tick{k}")
+
+
+@pytest.mark.parametrize("name", ["c2", "c3"])
+def test_config2_and_3_java_random_deployments(rsb, orc, name):
+    import workloads as W
+    dep = W.deployment(name)
+    with rsb.Medium("sinr", f64_values=True) as m:
+        m.set_nodes(dep["x"], dep["y"])
+        r = m.tick(dep["src"])
+    ref = orc.tick(orc.params(orc.MODEL_SINR), orc.NodeSet(dep["x"], dep["y"]), orc.make_packets(dep["src"], 0.0, 26),
+                   threads=16, cap=6_000_000)
+    _full_compare(r, ref, name)
+
+
+def test_far_sum_error_on_a_100_km_deployment(rsb, orc):
+    """D_near grows with the extent of the deployment (fp32 geometry error of the centred copy): 100 km square,
+    200 k nodes clustered in towns so that there ARE heard pairs, 2 000 transmitters.  Same bound as above."""
+    rng = np.random.default_rng(11)
+    n, t = 200_000, 2_000
+    towns = rng.uniform(0, 100_000.0, (400, 2))
+    k = rng.integers(0, 400, n)
+    x = np.clip(towns[k, 0] + rng.normal(0, 150.0, n), 0, 100_000.0)
+    y = np.clip(towns[k, 1] + rng.normal(0, 150.0, n), 0, 100_000.0)
+    src = rng.permutation(n)[:t].astype(np.int32)
+    with rsb.Medium("sinr", f64_values=True) as m:
+        m.set_nodes(x, y)
+        r = m.tick(src)
+        rssi, _ = m.node_info_f64()
+    ref = orc.tick(orc.params(orc.MODEL_SINR), orc.NodeSet(x, y), orc.make_packets(src, 0.0, 26), threads=16,
+                   cap=6_000_000, want_total=True)
+    assert ref["n_pairs"] > 10_000
+    compare(r, ref)
+    fin = np.isfinite(ref["pairs"]["sinr_db"])
+    assert np.abs(r.sinr_db_f64[fin] - ref["pairs"]["sinr_db"][fin]).max() < GUARD_DB / 3
+    assert np.abs(rssi - ref["total_dbm"]).max() < GUARD_DB / 3

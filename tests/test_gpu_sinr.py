@@ -1,7 +1,7 @@
 """-m gpu: the SINR medium (K1 sweep + exact resolve) against the CPU oracle, through the C-ABI."""
 import numpy as np
 import pytest
-from helpers import random_deployment, pick_sources, compare
+from helpers import random_deployment, pick_sources, compare, SINR_TOL_DB
 
 pytestmark = pytest.mark.gpu
 
@@ -282,3 +282,63 @@ def test_compact_result_form(rsb, orc, model):
     assert np.array_equal(b.tx_column(), a.tx) and np.array_equal(b.rx, a.rx)
     assert np.array_equal(b.outcome, a.outcome) and np.array_equal(b.rssi_dbm, a.rssi_dbm)
     assert np.array_equal(b.tx_failed, a.tx_failed)
+
+
+def test_half_duplex_flag_against_the_oracle(rsb, orc):
+    """rmb_config.half_duplex (SURVEY 8(a) open row): a node that is the source of any packet of the tick passes no
+    receiver filter, reports the noise floor, and the decision count drops accordingly; default = the reference."""
+    x, y, z, ch = random_deployment(61, 4000, 500.0, channels=2)
+    src = pick_sources(61, 4000, 120)
+    src[5] = src[4]                                        # one node with two packets in the tick
+    for hd in (0, 1):
+        with rsb.Medium("sinr", f64_values=True, half_duplex=hd) as m:
+            m.set_nodes(x, y, z, channel=ch)
+            r = m.tick(src)
+            r2 = m.tick(src[:60])                          # the stamps of the previous tick must not leak
+            rssi, _ = m.node_info_f64()
+        p = orc.params(orc.MODEL_SINR, half_duplex=hd)
+        ref = orc.tick(p, orc.NodeSet(x, y, z, channel=ch), orc.make_packets(src, 0.0, ch[src]))
+        ref2 = orc.tick(p, orc.NodeSet(x, y, z, channel=ch), orc.make_packets(src[:60], 0.0, ch[src[:60]]), want_total=True)
+        compare(r, ref)
+        compare(r2, ref2)
+        assert np.abs(rssi - ref2["total_dbm"]).max() < SINR_TOL_DB
+        if hd:
+            assert not np.isin(r.rx, src).any()
+            assert np.all(rssi[src[:60]] == -100.0) and rssi[src[100]] > -100.0
+    for model in ("udgm", "null", "udgm-constant"):
+        with rsb.Medium(model, f64_values=True, half_duplex=1) as m:
+            m.set_nodes(x, y, z, channel=ch)
+            r = m.tick(src)
+        ref = orc.tick(orc.params({"udgm": 1, "null": 0, "udgm-constant": 2}[model], half_duplex=1),
+                       orc.NodeSet(x, y, z, channel=ch), orc.make_packets(src, 0.0, ch[src]))
+        compare(r, ref)
+
+
+def test_limits_are_errors_not_wrong_results(rsb):
+    """max_pairs beyond int32, N2N on sharded receivers, and a foreign record with 0 < txprob < 1 on a
+    shard whose own nodes are deterministic."""
+    import ctypes as C
+    from radio_sim_b200 import _abi as A
+    with pytest.raises(rsb.MediumError) as e:
+        rsb.Medium("sinr", max_pairs=1 << 31)
+    assert e.value.code == A.ERR_INVALID
+    with pytest.raises(rsb.MediumError) as e:
+        rsb.Medium("n2n", n_shards=2)
+    assert e.value.code == A.ERR_UNSUPPORTED
+    import torch
+    x, y, z, ch = random_deployment(62, 2000, 300.0)
+    for model in ("sinr", "udgm"):
+        with rsb.Medium(model, rx_base=0, n_shards=2) as m:
+            m.set_nodes(x[:1000], y[:1000])
+            recs = torch.zeros(4 * 48, dtype=torch.uint8, device="cuda")
+            m.build_tx_records(np.array([3, 10, 20, 30], dtype=np.int32), recs.data_ptr())
+            r = np.frombuffer(recs.cpu().numpy().tobytes(), dtype=[("x", "f8"), ("y", "f8"), ("z", "f8"), ("p", "f8"), ("txprob", "f8"),
+                                                             ("ch", "i4"), ("src", "i4")]).copy()
+            r["src"][3] = 1500; r["x"][3] = x[1500]; r["y"][3] = y[1500]; r["txprob"][3] = 0.5     # as another shard built it
+            recs.copy_(torch.from_numpy(np.frombuffer(r.tobytes(), dtype=np.uint8).copy()))
+            with pytest.raises(rsb.MediumError) as e:
+                m.tick_records(4, recs.data_ptr())
+            assert e.value.code == A.ERR_UNSUPPORTED
+            r["txprob"][3] = 1.0
+            recs.copy_(torch.from_numpy(np.frombuffer(r.tobytes(), dtype=np.uint8).copy()))
+            assert m.tick_records(4, recs.data_ptr()).n_tx == 4
