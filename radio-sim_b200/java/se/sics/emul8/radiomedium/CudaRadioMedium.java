@@ -187,8 +187,8 @@ public class CudaRadioMedium extends AbstractRadioMedium {
         return "B200 medium";
     }
 
-    /** N2NRadioMedium.setN2NMatrix (N2NRadioMedium.java:20-22): rows = source id - 1, columns = destination id - 1. */
-    public synchronized void setN2NMatrix(double[][] m) {
+    /** N2NRadioMedium.setMatrix (N2NRadioMedium.java:20-22): rows = source id - 1, columns = destination id - 1. */
+    public synchronized void setMatrix(double[][] m) {
         try (Arena a = Arena.ofConfined()) {
             int n = m.length;
             MemorySegment flat = a.allocate(JAVA_DOUBLE, (long) Math.max(1, n * n));
@@ -383,15 +383,16 @@ public class CudaRadioMedium extends AbstractRadioMedium {
 
     /* one node's fields into the shadow arrays; true if anything the device holds changed */
     private boolean readNode(Node node, int i) {
-        Position p = node.getPosition();                                /* Position.java:37-39: public doubles */
-        Transciever r = node.getRadio();
-        double x = p.x, y = p.y, z = p.z, pw = r.getTransmitPower(), rxp = r.getRxProbability(), txp = r.getTxProbability();
-        int ch = r.getWirelessChannel();
-        byte en = (byte) (r.isEnabled() ? 1 : 0);
+        Position pos = node.getPosition();                              /* Position.java:37-39: public doubles */
+        Transciever radio = node.getRadio();
+        double x = pos.x, y = pos.y, z = pos.z;
+        double pw = radio.getTransmitPower(), rxp = radio.getRxProbability(), txp = radio.getTxProbability();
+        int ch = radio.getWirelessChannel();
+        byte en = (byte) (radio.isEnabled() ? 1 : 0);
         boolean moved = x != sx[i] || y != sy[i] || z != sz[i];
-        boolean radio = pw != sPower[i] || rxp != sRxp[i] || txp != sTxp[i] || ch != sChannel[i] || en != sEnabled[i];
+        boolean retuned = pw != sPower[i] || rxp != sRxp[i] || txp != sTxp[i] || ch != sChannel[i] || en != sEnabled[i];
         sx[i] = x; sy[i] = y; sz[i] = z; sPower[i] = pw; sRxp[i] = rxp; sTxp[i] = txp; sChannel[i] = ch; sEnabled[i] = en;
-        return moved || radio;
+        return moved || retuned;
     }
 
     /* in-place changes of registered nodes -> rmb_update_positions / rmb_update_radio for exactly those indices */
@@ -468,15 +469,15 @@ public class CudaRadioMedium extends AbstractRadioMedium {
             return false;
         }
         try (Arena a = Arena.ofConfined()) {
-            MemorySegment r = a.allocate(JAVA_DOUBLE, n), f = a.allocate(JAVA_BYTE, n);
-            int rc = (int) NODE_INFO_F64.invoke(handle, r, f);
+            MemorySegment power = a.allocate(JAVA_DOUBLE, n), heard = a.allocate(JAVA_BYTE, n);
+            int rc = (int) NODE_INFO_F64.invoke(handle, power, heard);
             if (rc != RMB_OK) {
                 return false;
             }
             nodeRssi = new double[n];
             nodeReceiving = new byte[n];
-            MemorySegment.copy(r, JAVA_DOUBLE, 0, nodeRssi, 0, n);
-            MemorySegment.copy(f, JAVA_BYTE, 0, nodeReceiving, 0, n);
+            MemorySegment.copy(power, JAVA_DOUBLE, 0, nodeRssi, 0, n);
+            MemorySegment.copy(heard, JAVA_BYTE, 0, nodeReceiving, 0, n);
             nodeInfoValid = true;
             return true;
         } catch (Throwable t) {

@@ -159,12 +159,12 @@ public class GenGolden {
         for (int i = 0; i < n; i++) {
             Node node = sim.addNode(Integer.toString(i + 1), null);
             node.getPosition().set(x[i], y[i]);
-            Transciever r = node.getRadio();
-            r.setTransmitPower(power[i]);
-            r.setWirelessChannel(channel[i]);
-            r.setEnabled(enabled[i]);
-            r.setRxProbability(rxprob[i]);
-            r.setTxProbability(txprob[i]);
+            Transciever radio = node.getRadio();
+            radio.setTransmitPower(power[i]);
+            radio.setWirelessChannel(channel[i]);
+            radio.setEnabled(enabled[i]);
+            radio.setRxProbability(rxprob[i]);
+            radio.setTxProbability(txprob[i]);
         }
         sim.indexNodes();
         Node[] nodes = sim.getNodes();

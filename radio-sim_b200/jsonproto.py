@@ -10,6 +10,12 @@ import json
 
 from .simulator import RadioPacket, CudaRadioMedium
 
+# propagation-option -> model.  The reference knows n2n-link / udgm / nullrm (net/SimulatorJSONHandler.java:179-214);
+# reference-edits.patch adds the "-b200" names that select the CUDA medium there.  In this harness every option is
+# served by the CUDA medium (there is no other), so both spellings are accepted.
+OPTIONS = {"n2n-link": "n2n", "udgm": "udgm", "nullrm": "null", "udgm-constant": "udgm-constant",
+           "n2n-link-b200": "n2n", "udgm-b200": "udgm", "nullrm-b200": "null", "udgm-constant-b200": "udgm-constant",
+           "sinr-b200": "sinr"}
 WELCOME = {"radio-simulator": {"name": "RSIM 0.1", "api-version": "0.6"}, "status": "OK"}        # net/Server.java:60-66
 
 
@@ -74,8 +80,14 @@ class JSONClientConnection:
         return True
 
     def emulate_to_time(self, nodes, time, time_id):               # :326-353: node-info of the client's own nodes
-        infos = [{"node-id": nd.id, "rssi": nd.radio.get_rssi(), "receiving": nd.radio.get_receiving_state(),
-                  "wireless-channel": nd.radio.wireless_channel} for nd in nodes if nd.client is self]
+        # reference-edits.patch: with the B200 medium the idle RSSI of all nodes is ONE read of the device buffers
+        # (index == node-array index); the reference's rule stays -- the receiving RSSI while receiving, else this
+        medium = nodes[0].simulator.radio_medium if nodes else None
+        device_rssi = medium.node_rssi_for_time_step(nodes) if hasattr(medium, "node_rssi_for_time_step") else None
+        infos = [{"node-id": nd.id,
+                  "rssi": float(device_rssi[i]) if device_rssi is not None and nd.radio.receiving_packet is None else nd.radio.get_rssi(),
+                  "receiving": nd.radio.get_receiving_state(),
+                  "wireless-channel": nd.radio.wireless_channel} for i, nd in enumerate(nodes) if nd.client is self]
         self.send({"command": "time-step", "id": time_id, "parameters": {"time": time, "node-info": infos}})
 
     def set_time(self, time, time_id):                             # :360-366
@@ -106,8 +118,7 @@ class SimulatorJSONHandler:
 
     def __init__(self, simulator, medium_factory=None):
         self.simulator = simulator
-        self.medium_factory = medium_factory or (lambda option, params: CudaRadioMedium(
-            {"n2n-link": "n2n", "udgm": "udgm", "nullrm": "null", "udgm-constant": "udgm-constant", "sinr-b200": "sinr"}[option]))
+        self.medium_factory = medium_factory or (lambda option, params: CudaRadioMedium(OPTIONS[option]))
 
     @staticmethod
     def _reply(msg_id, **extra):                                   # createReplyObject, :256-263
@@ -171,6 +182,10 @@ class SimulatorJSONHandler:
                 medium.transmit(packet)
         elif command == "node-config-set":                         # :105-153
             p = msg["parameters"]
+            # reference-edits.patch: packets already transmitted in this tick are evaluated against the node state
+            # they were sent under (the reference evaluates inside transmit()); None = the node does not exist yet
+            if hasattr(sim.radio_medium, "node_config_changing"):
+                sim.radio_medium.node_config_changing(sim.get_node(_node_id(p["node-id"])))
             node = sim.add_node(_node_id(p["node-id"]), client)
             pos = p.get("position")
             if isinstance(pos, list):
@@ -189,7 +204,6 @@ class SimulatorJSONHandler:
                 node.radio.tx_probability = float(p["tx-loss"])
             if isinstance(p.get("radio-state"), str):
                 node.radio.is_enabled = p["radio-state"] != "disabled"
-            sim._state_changed()
             if mid >= 0:
                 info = {"node-id": node.id, "rssi": node.radio.get_rssi(), "receiving": node.radio.get_receiving_state(),
                         "wireless-channel": node.radio.wireless_channel}
@@ -203,7 +217,7 @@ class SimulatorJSONHandler:
                 p = msg["parameters"]
                 option = p.get("propagation-option")
                 if option is not None:
-                    if option == "n2n-link":
+                    if option in ("n2n-link", "n2n-link-b200"):
                         vec = p.get("matrix-data")
                         if not isinstance(vec, list) or not vec:
                             reply = self._error(mid, "command-error", "no matrix specified")
@@ -213,7 +227,7 @@ class SimulatorJSONHandler:
                             medium = self.medium_factory(option, p)
                             medium.set_matrix([float(v) for v in vec])
                             sim.set_radio_medium(medium)
-                    elif option in ("udgm", "udgm-constant", "sinr-b200"):
+                    elif option in ("udgm", "udgm-constant", "sinr-b200", "udgm-b200", "udgm-constant-b200", "nullrm-b200"):
                         sim.set_radio_medium(self.medium_factory(option, p))
                     elif option == "nullrm":
                         if sim.radio_medium is None:               # "the null radio medium is the default" (Main.java:66)

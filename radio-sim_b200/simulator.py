@@ -12,6 +12,7 @@ import heapq
 
 import numpy as np
 
+from .javarandom import JavaRandom
 from .medium import Medium
 
 LISTENING, TRANSMITTING, RECEIVING, DISABLED = 0, 1, 2, 3          # Transciever.java:7-10
@@ -123,23 +124,40 @@ class AbstractRadioMedium:
 
 
 class CudaRadioMedium(AbstractRadioMedium):
-    """The adapter of INTEGRATION.md (java/.../CudaRadioMedium.java is the same thing in Java): transmit()
-    enqueues the packet and raises the two transmission events at once, as every reference medium does
-    (UDGMRadioMedium.java:97); flush(), called when the tick's emulators are done, evaluates all queued
-    packets with ONE rmb_tick and replays the heard pairs as generateReceptionEvents calls in the
-    reference's own order (packets in arrival order, receivers in node-array order).
+    """The adapter of INTEGRATION.md -- java/se/sics/emul8/radiomedium/CudaRadioMedium.java is the same logic in Java,
+    statement for statement, and this is the copy that runs (tests/test_gpu_replay.py).
 
-    model 'udgm-constant' delivers at once instead (UDGMConstantLossRadioMedium.java:16-36: no events)."""
+    transmit() only queues.  flush(), the FIRST thing Simulator.emulatorTimeStepDone does (before `currentTime =
+    stepTime`, Simulator.java:155-157), evaluates all queued packets with ONE rmb_tick and hands the result over
+    packet by packet in arrival order: the packet's two transmission events, then its reception events in
+    node-array order -- the reference's own call sequence (UDGMRadioMedium.java:97-114), so equal-time events are
+    queued in the reference's insertion order.  'udgm-constant' delivers at once and raises no events
+    (UDGMConstantLossRadioMedium.java:16-36).
 
-    def __init__(self, model="udgm", uniforms=None, device=0, **params):
+    Node state reaches the device incrementally: a new node list (copy-on-write registry) is a full rmb_set_nodes;
+    in-place changes (node-config-set) go through rmb_update_positions / rmb_update_radio for exactly the changed
+    indices, found by node_config_changing() (the hook the JSON handler calls BEFORE it mutates a node: packets
+    already queued are evaluated against the state they were sent under, as the reference does inside transmit())
+    or by a per-tick scan against the shadow copy (scan_nodes, default on, for callers without the hook).
+
+    Stochastic reception draws from simulator.get_random() (Simulator.java:94) in the reference's order: the tick
+    consumes host-supplied uniforms and reports how many; a look-ahead of the generator supplies them and the
+    generator is then advanced by exactly n_uniforms_used (`uniforms=` overrides the source for tests)."""
+
+    def __init__(self, model="udgm", uniforms=None, device=0, rssi_in_band=False, scan_nodes=True, bulk_events=True, **params):
         super().__init__()
         self.model = model
-        self.medium = Medium(model, device=device, f64_values=True, **params)
+        self.medium = Medium(model, device=device, f64_values=True, compact=True, **params)
+        self.base_rssi = float(self.medium.cfg.noise_floor_dbm)
         self.pending = []
-        self.uniforms = uniforms           # callable(n) -> n doubles standing in for simulator.getRandom().nextDouble()
-        self._registered = None            # node objects as last uploaded (identity == array index)
-        self._dirty = True
-        self.ticks = 0
+        self.uniforms = uniforms           # optional JavaRandom-like object (peek_doubles / skip_doubles) instead of simulator.get_random()
+        self.rssi_in_band, self.scan_nodes, self.bulk_events = rssi_in_band, scan_nodes, bulk_events
+        self._registered = None            # the node list as last uploaded (identity == registry version)
+        self._index = {}                   # id(node) -> array index
+        self._shadow = None                # what the device holds: dict of numpy arrays
+        self._dirty = set()
+        self._node_info = None
+        self.ticks = self.uploads = self.updates = 0
 
     def get_name(self):
         return "cuda-" + self.model
@@ -147,60 +165,126 @@ class CudaRadioMedium(AbstractRadioMedium):
     def close(self):
         self.medium.close()
 
-    def node_state_changed(self):
-        """node-config-set / addNode / removeNode happened: the SoA copy is re-uploaded before the next tick."""
-        self._dirty = True
-
-    def set_matrix(self, matrix):                                  # N2NRadioMedium.java:20-22
+    def set_matrix(self, matrix):                                  # N2NRadioMedium.setMatrix, N2NRadioMedium.java:20-22
         self.medium.set_matrix(matrix)
 
-    def _upload(self):
-        nodes = self.simulator.get_nodes()
-        n = len(nodes)
-        a = lambda f, dt: np.array([f(nd) for nd in nodes], dtype=dt) if n else np.zeros(0, dtype=dt)
-        self.medium.set_nodes(a(lambda nd: nd.position.x, np.float64), a(lambda nd: nd.position.y, np.float64),
-                              a(lambda nd: nd.position.z, np.float64),
-                              txpower_dbm=a(lambda nd: nd.radio.txpower, np.float64),
-                              channel=a(lambda nd: nd.radio.wireless_channel, np.int32),
-                              enabled=a(lambda nd: 1 if nd.radio.is_enabled else 0, np.uint8),
-                              rxprob=a(lambda nd: nd.radio.rx_probability, np.float64),
-                              txprob=a(lambda nd: nd.radio.tx_probability, np.float64),
-                              id_int=a(lambda nd: nd.get_id_as_integer(), np.int32))
-        self._registered = list(nodes)
-        self._dirty = False
+    # -- node table ------------------------------------------------------------------------------------------------
+    _FIELDS = (("x", np.float64, lambda nd: nd.position.x), ("y", np.float64, lambda nd: nd.position.y),
+               ("z", np.float64, lambda nd: nd.position.z), ("txpower", np.float64, lambda nd: nd.radio.txpower),
+               ("rxprob", np.float64, lambda nd: nd.radio.rx_probability), ("txprob", np.float64, lambda nd: nd.radio.tx_probability),
+               ("channel", np.int32, lambda nd: nd.radio.wireless_channel), ("enabled", np.uint8, lambda nd: 1 if nd.radio.is_enabled else 0))
 
+    def _read(self, nodes):
+        n = len(nodes)
+        return {k: (np.array([g(nd) for nd in nodes], dtype=dt) if n else np.zeros(0, dtype=dt)) for k, dt, g in self._FIELDS}
+
+    def _upload(self, nodes):
+        s = self._read(nodes)
+        ids = np.array([nd.get_id_as_integer() for nd in nodes], dtype=np.int32)          # Node.java:65-67 (N2N)
+        self.medium.set_nodes(s["x"], s["y"], s["z"], txpower_dbm=s["txpower"], channel=s["channel"], enabled=s["enabled"],
+                              rxprob=s["rxprob"], txprob=s["txprob"], id_int=ids)
+        self._registered, self._shadow = nodes, s
+        self._index = {id(nd): i for i, nd in enumerate(nodes)}
+        self._dirty.clear()
+        self._node_info = None
+        self.uploads += 1
+
+    def _push_changes(self, nodes):
+        if self.scan_nodes and nodes:
+            now = self._read(nodes)
+            changed = np.zeros(len(nodes), dtype=bool)
+            for k in now:
+                changed |= now[k] != self._shadow[k]
+            self._dirty.update(int(i) for i in np.nonzero(changed)[0])
+        if not self._dirty:
+            return
+        idx = np.array(sorted(self._dirty), dtype=np.int32)
+        sub = self._read([nodes[i] for i in idx])
+        for k in sub:
+            self._shadow[k][idx] = sub[k]
+        self.medium.update_positions(sub["x"], sub["y"], sub["z"], idx=idx)
+        self.medium.update_radio(idx=idx, txpower_dbm=sub["txpower"], channel=sub["channel"], enabled=sub["enabled"],
+                                 rxprob=sub["rxprob"], txprob=sub["txprob"])
+        self._dirty.clear()
+        self._node_info = None
+        self.updates += 1
+
+    def node_config_changing(self, node):
+        """Hook of net/SimulatorJSONHandler.java:105 (node-config-set), BEFORE the node is mutated or created."""
+        self.flush()
+        if node is not None and id(node) in self._index:
+            self._dirty.add(self._index[id(node)])
+
+    def node_state_changed(self):
+        """Compatibility with callers that only know `something changed`: the next flush re-reads every node."""
+        if self._registered is not None:
+            self._dirty.update(range(len(self._registered)))
+
+    # -- the tick --------------------------------------------------------------------------------------------------
     def transmit(self, packet):
-        if self.model != "udgm-constant":
-            self.simulator.generate_transmission_events(packet)
+        if self.simulator is None:
+            return                                                 # NullRadioMedium.java:50-53
         self.pending.append(packet)
 
-    def flush(self):
-        """End of tick (hook before Simulator.processAllEvents, Simulator.java:155-161)."""
+    def flush(self, step_time=0):
         packets, self.pending = self.pending, []
-        if not packets:
+        if not packets or self.simulator is None:
             return 0
-        if self._dirty or self._registered is None:
-            self._upload()
-        index = {id(nd): i for i, nd in enumerate(self._registered)}
-        keep = [p for p in packets if id(p.node) in index]          # a source removed meanwhile cannot transmit
+        nodes = self.simulator.get_nodes()
+        if nodes is not self._registered:
+            self._upload(nodes)                                    # copy-on-write registry: a new list is a registry change
+        else:
+            self._push_changes(nodes)
+        keep = [p for p in packets if id(p.node) in self._index]   # a source that left the registry cannot be evaluated
         if not keep:
             return 0
-        src = np.array([index[id(p.node)] for p in keep], dtype=np.int32)
-        power = np.array([p.txpower for p in keep], dtype=np.float64)
-        channel = np.array([p.channel for p in keep], dtype=np.int32)
-        u = None
-        if self.uniforms is not None:
-            u = np.asarray(self.uniforms(len(keep) * (len(self._registered) + 1)), dtype=np.float64)
-        r = self.medium.tick(src, power, channel, uniforms=u)
+        src = np.array([self._index[id(p.node)] for p in keep], dtype=np.int32)
+        power = np.array([p.txpower for p in keep], dtype=np.float64)            # RadioPacket.java:49,77: snapshot / override
+        channel = np.array([p.channel for p in keep], dtype=np.int32)            # RadioPacket.java:50,85
+        # deterministic tick: one call.  With draws: the first call (no uniforms; a missing draw reads as 0.0 = success,
+        # which maximises the number of later draws) tells how many uniforms the tick can consume at most; the
+        # generator's look-ahead supplies them and the generator is advanced by the number actually consumed.
+        r = self.medium.tick(src, power, channel, allow_short_uniforms=True)
+        if r.status != 0:
+            rnd = self.uniforms if self.uniforms is not None else self.simulator.get_random()
+            r = self.medium.tick(src, power, channel, uniforms=rnd.peek_doubles(r.n_uniforms_used))
+            rnd.skip_doubles(r.n_uniforms_used)
         self.ticks += 1
+        self._node_info = None
         sim = self.simulator
-        for t, rx, rssi, outcome in zip(r.tx, r.rx, r.rssi_dbm_f64, r.outcome):
-            packet, dest = keep[t], self._registered[rx]
-            if self.model == "udgm-constant":
-                sim.deliver_radio_packet(packet, dest, float(rssi))
-            else:
-                sim.generate_reception_events(packet, dest, float(rssi), outcome == 2)
+        if self.model == "udgm-constant":
+            for t, p in enumerate(keep):                           # UDGMConstantLossRadioMedium.java:30-32
+                for i in range(r.tx_first[t], r.tx_first[t + 1]):
+                    sim.deliver_radio_packet(p, nodes[r.rx[i]], float(r.rssi_dbm_f64[i]))
+        elif self.bulk_events:
+            sim.generate_reception_events_bulk(keep, len(keep), r.tx_first, nodes, r.rx, r.rssi_dbm_f64, r.outcome)
+        else:
+            for t, p in enumerate(keep):
+                sim.generate_transmission_events(p)
+                for i in range(r.tx_first[t], r.tx_first[t + 1]):
+                    sim.generate_reception_events(p, nodes[r.rx[i]], float(r.rssi_dbm_f64[i]), r.outcome[i] == 2)
         return int(r.n_pairs)
+
+    # -- node-info from the device buffers (8(f)2) -----------------------------------------------------------------------
+    def _refresh_node_info(self):
+        if self._node_info is None and self._registered:
+            self._node_info = self.medium.node_info_f64()
+        return self._node_info
+
+    def get_base_rssi(self, node):                                 # Transciever.getRSSI falls back to this (Transciever.java:52-61)
+        if not self.rssi_in_band:
+            return self.base_rssi                                  # AbstractRadioMedium.java:45-48
+        i = self._index.get(id(node))
+        info = self._refresh_node_info()
+        return self.base_rssi if i is None or info is None or i >= len(info[0]) else float(info[0][i])
+
+    def node_rssi_for_time_step(self, nodes):
+        """Idle RSSI of every node for the per-tick node-info (net/JSONClientConnection.java:326-353), index == node
+        array index: total in-band power of the last evaluated tick; None = use Transciever.get_rssi() as the reference."""
+        if not self.rssi_in_band or nodes is not self._registered:
+            return None
+        info = self._refresh_node_info()
+        return None if info is None else info[0]
 
     def node_info(self):
         """Total in-band power and 'heard something' per node for the last tick (rmb_node_info)."""
@@ -215,9 +299,10 @@ class Simulator:
     in an order that depends on its bucket layout; here they pop in insertion order.  Parity with the reference
     is therefore defined on the SET of messages per tick, as SURVEY.md 8(f) notes."""
 
-    TIME_STEP_OK = 1
+    TIME_STEP_OK = 0                                               # Simulator.java:61
 
-    def __init__(self):
+    def __init__(self, random=None):
+        self.random = random if random is not None else JavaRandom(0)          # Simulator.java:64,83-89 (`new Random()` there)
         self.nodes, self.node_table = [], {}
         self.emulators, self.event_listeners = [], []
         self.radio_medium = None
@@ -247,7 +332,6 @@ class Simulator:
         node.client = client
         self.node_table[node.id] = node
         self.nodes = self.nodes + [node]                           # copy-on-write, util/ArrayUtils.java:48-79
-        self._state_changed()
         return node
 
     def remove_node(self, node_id):
@@ -257,13 +341,10 @@ class Simulator:
         self.nodes = [n for n in self.nodes if n is not node]
         if node.client is not None and not any(n.client is node.client for n in self.nodes):
             self.emulators = [e for e in self.emulators if e is not node.client]
-        self._state_changed()
         return node
 
-    def _state_changed(self):
-        m = self.radio_medium
-        if m is not None and hasattr(m, "node_state_changed"):
-            m.node_state_changed()
+    def get_random(self):                                          # Simulator.java:94
+        return self.random
 
     def set_radio_medium(self, medium):                            # Simulator.java:234-239
         if medium is not None:
@@ -285,6 +366,30 @@ class Simulator:
             if do_deliver:
                 self.deliver_radio_packet(packet, destination, rssi)
         self._add_event(t0 + packet.get_packet_air_time(), end)
+
+    def generate_reception_events_bulk(self, packets, n_packets, tx_first, nodes, rx, rssi, outcome):
+        """reference-edits.patch `Simulator.generateReceptionEventsBulk` + events/BulkReceptionEvent.java: per packet the
+        two transmission events, then ONE start and ONE end event covering rows tx_first[t] .. tx_first[t+1]."""
+        for t in range(n_packets):
+            packet = packets[t]
+            self.generate_transmission_events(packet)
+            lo, hi = int(tx_first[t]), int(tx_first[t + 1])
+            if hi <= lo:
+                continue
+            t0 = max(packet.time, self.current_time)
+
+            def start(packet=packet, lo=lo, hi=hi):
+                for i in range(lo, hi):
+                    nodes[rx[i]].radio.set_receiving(packet, float(rssi[i]))
+
+            def end(packet=packet, lo=lo, hi=hi):
+                for i in range(lo, hi):
+                    dest = nodes[rx[i]]
+                    dest.radio.clear_receiving()
+                    if outcome[i] == 2:
+                        self.deliver_radio_packet(packet, dest, float(rssi[i]))
+            self._add_event(t0, start)
+            self._add_event(t0 + packet.get_packet_air_time(), end)
 
     def generate_transmission_events(self, packet):
         t0 = max(packet.time, self.current_time)                   # Simulator.java:339-342
@@ -329,7 +434,7 @@ class Simulator:
         # of the step are processed
         m = self.radio_medium
         if m is not None and hasattr(m, "flush"):
-            m.flush()
+            m.flush(self.step_time_value)
         self.current_time = self.step_time_value                   # Simulator.java:156-157
         self.waiting_for_time_id = -1
         self.process_all_events(self.current_time)

@@ -11,24 +11,31 @@ MODELS = {"null": orc.MODEL_NULL, "udgm": orc.MODEL_UDGM, "udgm-constant": orc.M
 
 
 class OracleRadioMedium(AbstractRadioMedium):
-    def __init__(self, model="udgm", **params):
+    """eager=True is the REFERENCE's behaviour for its own media: every transmit() is evaluated at once, on its own,
+    against the node state of that moment, with the draws taken from simulator.get_random() -- the batched CUDA adapter
+    must reproduce it message for message.  eager=False (the only meaningful mode for the SINR medium, which
+    evaluates the tick's packets jointly) batches like the adapter does."""
+
+    def __init__(self, model="udgm", eager=None, **params):
         super().__init__()
         self.model, self.params, self.pending, self.matrix = model, params, [], None
+        self.eager = (model != "sinr") if eager is None else eager
 
     def set_matrix(self, matrix):
         m = np.asarray(matrix, dtype=np.float64)
         n = int(round(m.size ** 0.5))
         self.matrix = m.reshape(n, n)
 
-    def node_state_changed(self):
-        pass
+    def node_config_changing(self, node):
+        if not self.eager:
+            self.flush()
 
     def transmit(self, packet):
-        if self.model != "udgm-constant":
-            self.simulator.generate_transmission_events(packet)
         self.pending.append(packet)
+        if self.eager:
+            self.flush()
 
-    def flush(self):
+    def flush(self, step_time=0):
         packets, self.pending = self.pending, []
         nodes = self.simulator.get_nodes()
         index = {id(nd): i for i, nd in enumerate(nodes)}
@@ -47,10 +54,19 @@ class OracleRadioMedium(AbstractRadioMedium):
             kw["matrix"] = self.matrix
         pk = orc.make_packets(np.array([index[id(p.node)] for p in keep], dtype=np.int32),
                               np.array([p.txpower for p in keep]), np.array([p.channel for p in keep], dtype=np.int32))
-        pairs = orc.tick(orc.params(MODELS[self.model], **kw), ns, pk)["pairs"]
-        for t, rx, rssi, outcome in zip(pairs["tx"], pairs["rx"], pairs["rssi_dbm"], pairs["outcome"]):
-            if self.model == "udgm-constant":
-                self.simulator.deliver_radio_packet(keep[t], nodes[rx], float(rssi))
-            else:
-                self.simulator.generate_reception_events(keep[t], nodes[rx], float(rssi), outcome == 2)
+        rnd = self.simulator.get_random()
+        res = orc.tick(orc.params(MODELS[self.model], **kw), ns, pk, uniforms=rnd.peek_doubles(len(keep) * (len(nodes) + 1)))
+        rnd.skip_doubles(res["n_uniforms_used"])
+        pairs = res["pairs"]
+        k = 0
+        for t, p in enumerate(keep):                               # the reference's call order (UDGMRadioMedium.java:97-114)
+            if self.model != "udgm-constant":
+                self.simulator.generate_transmission_events(p)
+            while k < len(pairs) and pairs["tx"][k] == t:
+                rx, rssi, outcome = pairs["rx"][k], float(pairs["rssi_dbm"][k]), pairs["outcome"][k]
+                if self.model == "udgm-constant":
+                    self.simulator.deliver_radio_packet(p, nodes[rx], rssi)
+                else:
+                    self.simulator.generate_reception_events(p, nodes[rx], rssi, outcome == 2)
+                k += 1
         return len(pairs)

@@ -1,5 +1,6 @@
 """Command streams of the JSON radio protocol for the replay tests (what an emulator and a time controller send;
 cf. the reference's test/TestEmulator.java:91-125 and test/TestClient.java)."""
+from radio_sim_b200.javarandom import JavaRandom
 from radio_sim_b200.simulator import Simulator
 from radio_sim_b200.jsonproto import SimulatorJSONHandler, JSONClientConnection
 
@@ -7,8 +8,8 @@ from radio_sim_b200.jsonproto import SimulatorJSONHandler, JSONClientConnection
 class Session:
     """One simulator + one controller + `n_emulators` emulator connections, all in memory."""
 
-    def __init__(self, medium_factory, n_emulators=1):
-        self.sim = Simulator()
+    def __init__(self, medium_factory, n_emulators=1, seed=42):
+        self.sim = Simulator(JavaRandom(seed))                     # Simulator(Random r), Simulator.java:87-89
         self.handler = SimulatorJSONHandler(self.sim, medium_factory)
         self.ctrl = JSONClientConnection("controller")
         self.emus = [JSONClientConnection(f"emulator{i}") for i in range(n_emulators)]

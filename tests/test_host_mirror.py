@@ -155,3 +155,141 @@ def test_framing_round_trip():
     raw = b"RSIM 0.1\r\n" + jsonproto.encode(msgs[0]) + b"\r\n\r\n" + jsonproto.encode(msgs[1], use_length=True) + jsonproto.encode(msgs[0])
     assert jsonproto.decode_stream(raw) == [msgs[0], msgs[1], msgs[0]]
     assert jsonproto.WELCOME["radio-simulator"]["api-version"] == "0.6"
+
+
+# ---- round 2: java.util.Random port, bulk event hand-off, the adapter's host logic without a GPU -------------------
+def test_java_random_port_matches_the_jdk_algorithm(orc):
+    import ctypes as C
+    from radio_sim_b200.javarandom import JavaRandom
+    assert [JavaRandom(42).next_double() for _ in range(1)] + list(JavaRandom(42).peek_doubles(3)[1:]) == KAT["jrandom"]["next_double"]
+    r = JavaRandom(12345)
+    a = r.peek_doubles(5000)
+    assert np.array_equal(a, orc.jrandom_doubles(12345, 5000))           # the oracle's C port (oracle/medium_oracle.c)
+    r.skip_doubles(1234)
+    assert r.next_double() == a[1234] and np.array_equal(r.next_doubles(10), a[1235:1245])
+    st = orc.JRandomState()
+    orc.lib().orc_jrandom_init(C.byref(st), 7)
+    r = JavaRandom(7)
+    for b in [10, 16, 1_000_000, 3, (1 << 30) + 5, 1] * 40:
+        assert r.next_int(b) == orc.lib().orc_jrandom_next_int_bound(C.byref(st), b)
+    picks = JavaRandom(3).sample_distinct(1000, 200)
+    assert len(set(picks.tolist())) == 200 and picks.min() >= 0 and picks.max() < 1000
+
+
+def test_bulk_event_hand_off_equals_one_event_pair_per_heard_pair():
+    """Simulator.generate_reception_events_bulk (reference-edits.patch + BulkReceptionEvent.java) against the
+    reference's per-pair calls (Simulator.java:321-350): same messages in the same order, same transceiver states."""
+    def run(bulk):
+        sim = Simulator()
+        emu = jsonproto.JSONClientConnection("emu")
+        nodes = [sim.add_node(i + 1, emu) for i in range(6)]
+        sim.current_time = 50
+        packets = [RadioPacket(nodes[0], 0, "0102030405"), RadioPacket(nodes[3], 200, "01"), RadioPacket(nodes[5], 60, "0102")]
+        tx_first, rx = [0, 3, 3, 5], [1, 2, 4, 0, 2]
+        rssi, outcome = [-1.0, -2.0, -3.0, -4.0, -5.0], [2, 1, 2, 2, 2]
+        nl = sim.get_nodes()
+        if bulk:
+            sim.generate_reception_events_bulk(packets, 3, tx_first, nl, rx, rssi, outcome)
+        else:
+            for t, p in enumerate(packets):
+                sim.generate_transmission_events(p)
+                for i in range(tx_first[t], tx_first[t + 1]):
+                    sim.generate_reception_events(p, nl[rx[i]], rssi[i], outcome[i] == 2)
+        states = []
+        for t in (51, 61, 130, 201, 1000):
+            sim.process_all_events(t)
+            states.append([(n.radio.get_receiving_state(), n.radio.get_rssi()) for n in nl])
+        return emu.sent, states
+    assert run(True) == run(False)
+    sent, states = run(True)
+    assert len(sent) == 4 and all(m["command"] == "receive" for m in sent)             # delivered rows only (outcome 2)
+    assert states[0][1][0] == RECEIVING and states[0][0][0] == TRANSMITTING            # clamp to current_time = 50
+
+
+class _FakeMedium:
+    """Stands in for radio_sim_b200.medium.Medium so that the adapter's HOST logic runs without a GPU: records the
+    calls and answers a tick with 'every other node hears every packet' (plus one draw per pair when asked)."""
+
+    def __init__(self, *a, **kw):
+        import types
+        self.cfg = types.SimpleNamespace(noise_floor_dbm=-100.0)
+        self.calls, self.n, self.need_draws = [], 0, False
+
+    def set_nodes(self, x, y, z=None, **kw):
+        self.n = len(x)
+        self.calls.append(("set_nodes", self.n))
+
+    def update_positions(self, x, y, z=None, idx=None):
+        self.calls.append(("update_positions", idx.tolist(), list(x)))
+
+    def update_radio(self, idx=None, **kw):
+        self.calls.append(("update_radio", idx.tolist(), kw["channel"].tolist()))
+
+    def tick(self, src, power, channel, uniforms=None, allow_short_uniforms=False):
+        import types
+        t = len(src)
+        rx = np.concatenate([np.delete(np.arange(self.n), s) for s in src]).astype(np.int32)
+        first = np.arange(t + 1, dtype=np.int32) * (self.n - 1)
+        need = len(rx) if self.need_draws else 0
+        short = need and (uniforms is None or len(uniforms) < need)
+        self.calls.append(("tick", src.tolist(), None if uniforms is None else len(uniforms)))
+        used = need if short else need // 2                        # "consumes" half of the upper bound
+        return types.SimpleNamespace(status=-5 if short else 0, n_uniforms_used=used, n_pairs=len(rx), rx=rx, tx_first=first,
+                                     rssi_dbm_f64=np.repeat(power, self.n - 1), outcome=np.full(len(rx), 2, np.uint8))
+
+    def node_info_f64(self):
+        return np.full(self.n, -90.0), np.zeros(self.n, np.uint8)
+
+    def close(self):
+        pass
+
+
+def test_adapter_host_logic_without_a_gpu(monkeypatch):
+    from radio_sim_b200 import simulator as S
+    from radio_sim_b200.javarandom import JavaRandom
+    monkeypatch.setattr(S, "Medium", _FakeMedium)
+    sim = Simulator(JavaRandom(5))
+    emu = jsonproto.JSONClientConnection("emu")
+    handler = jsonproto.SimulatorJSONHandler(sim, lambda o, p: S.CudaRadioMedium("udgm", rssi_in_band=True))
+    handler.handle_message(emu, {"command": "configuration-set", "id": 1, "parameters": {"propagation-option": "udgm-b200"}})
+    med = sim.radio_medium
+    for i in range(4):
+        handler.handle_message(emu, {"command": "node-config-set", "parameters": {"node-id": i + 1, "position": [10.0 * i, 0.0]}})
+    tx = lambda nid, t: handler.handle_message(emu, {"command": "transmit", "node-id": nid, "time": t, "packet-data": "01"})
+    tx(1, 0)
+    assert med.medium.calls == []                                  # transmit() only queues
+    sim.step_time(1000, 7)
+    handler.handle_message(emu, {"reply": "OK", "id": sim.waiting_for_time_id})
+    assert med.medium.calls == [("set_nodes", 4), ("tick", [0], None)]
+    assert len([m for m in emu.sent if m.get("command") == "receive"]) == 3
+    # an in-place change of a registered node: incremental update of exactly that index, no re-upload; and the packet
+    # queued BEFORE the change is evaluated before it (node_config_changing flushes)
+    tx(2, 1000)
+    handler.handle_message(emu, {"command": "node-config-set", "parameters": {"node-id": 3, "wireless-channel": 11, "position": [5.0, 5.0]}})
+    tx(4, 1001)
+    sim.step_time(2000, 8)
+    handler.handle_message(emu, {"reply": "OK", "id": sim.waiting_for_time_id})
+    assert med.medium.calls[2:] == [("tick", [1], None), ("update_positions", [2], [5.0]), ("update_radio", [2], [11]), ("tick", [3], None)]
+    assert med.uploads == 1 and med.updates == 1
+    # draws: first call without uniforms (-5) tells the upper bound, the look-ahead supplies it, the generator advances
+    # by what the tick consumed
+    med.medium.need_draws = True
+    before = sim.get_random().seed
+    tx(1, 2000)
+    sim.step_time(3000, 9)
+    handler.handle_message(emu, {"reply": "OK", "id": sim.waiting_for_time_id})
+    assert med.medium.calls[-2:] == [("tick", [0], None), ("tick", [0], 3)]
+    probe = JavaRandom(0); probe.seed = before; probe.skip_doubles(1)          # the fake consumed 3 // 2 = 1 draw
+    assert sim.get_random().seed == probe.seed
+    # a node removed while its packet is queued: the packet is dropped, the others are evaluated (ADVICE r1)
+    med.medium.need_draws = False
+    tx(2, 3000); tx(1, 3001)
+    sim.remove_node("2")
+    sim.step_time(4000, 10)
+    handler.handle_message(emu, {"reply": "OK", "id": sim.waiting_for_time_id})
+    assert med.medium.calls[-2:] == [("set_nodes", 3), ("tick", [0], None)]
+    # node-info of the next time-step comes from the device buffers for idle nodes (rssi_in_band)
+    step = [m for m in emu.sent if m.get("command") == "time-step"][-1]
+    sim.step_time(5000, 11)
+    step = [m for m in emu.sent if m.get("command") == "time-step"][-1]
+    assert [ni["rssi"] for ni in step["parameters"]["node-info"]] == [-90.0, -90.0, -90.0]
