@@ -255,6 +255,11 @@ int rmb_tick_peers_draws_begin(rmb_handle *h, int32_t *d_counts_out);   /* rmb_t
  * Needs one GPU per handle: the preparation kernel is a cooperative launch, and two cooperative kernels do not
  * run side by side on one device (handles sharing a GPU use rmb_peer_push + rmb_tick_peers). */
 int rmb_peer_exchange_tick_enqueue(rmb_handle *h, int32_t slots, const void *d_records);
+/* Device-side rendezvous of all ranks' streams: a one-warp kernel that raises this rank's barrier flag in every
+ * peer's buffer and waits for all of theirs (no host synchronisation, no collective).  Every rank must call it the
+ * same number of times.  What a caller puts on the stream behind it starts within an NVLink round trip on all
+ * GPUs -- bench.py lines the ranks up with it in front of the start event.  Asynchronous. */
+int rmb_peer_barrier_enqueue(rmb_handle *h);
 
 /* Replaces Transciever.getRSSI / RadioMedium.getBaseRSSI for the per-tick node-info
  * (Transciever.java:52-61, net/JSONClientConnection.java:331-341): total in-band power

@@ -59,7 +59,7 @@ struct rmb_handle {
     cudaStream_t own_st = nullptr;                 // created by rmb_create; st == own_st unless rmb_set_stream
     cudaStream_t st = nullptr, st2 = nullptr;      // st2: guard-band recheck, overlapped with the pair ordering
     cudaEvent_t ev[6] = {}, ev_fork = nullptr, ev_join = nullptr;
-    rmb_timing timing{}; bool timing_pending = false;
+    rmb_timing timing{}; bool timing_pending = false, timing_by_events = true;
 
     // host mirrors of the radio state (work order + stochastic detection are host-built)
     int n = 0;
@@ -111,6 +111,7 @@ struct rmb_handle {
     struct Peer {
         int world = 0, rank = 0, max_slots = 0, slots = 0;
         unsigned epoch = 0;               // ticks pushed so far (flags carry this value)
+        unsigned barrier_epoch = 0;       // rmb_peer_barrier_enqueue calls so far (second flag row)
         bool pushed = false;              // a push is waiting for its tick
         char *buf = nullptr;              // this handle's gather buffer: flags, then 2 x world x max_slots records
         char *peer[kMaxPeers] = {};       // every rank's buffer as mapped here (peer[rank] == buf)
@@ -135,6 +136,8 @@ struct rmb_handle {
     int sweep_variant = 0;
     bool fuse_resolve = true;          // rmb_set_tuning bit 16 turns the fused epilogue off (stand-alone resolve kernel)
     bool fuse_finish = true;           // rmb_set_tuning bit 20: separate recheck / ordering / emit kernels instead of finish.cu
+    bool kernel_events = false;        // rmb_set_tuning bit 24: CUDA events BETWEEN the tick's kernels (per-kernel durations by
+                                       // event; the launches are then serialised, no programmatic dependent launch)
     bool have_nodes = false;
 
     int fail(int code, const std::string &m) { err = m; return code; }
@@ -564,6 +567,7 @@ extern "C" int rmb_set_tuning(rmb_handle *h, int32_t sweep_variant, int32_t near
     h->forced_splits = (sweep_variant >> 8) & 0xff;
     h->fuse_resolve = ((sweep_variant >> 16) & 1) == 0;
     h->fuse_finish = ((sweep_variant >> 20) & 1) == 0;
+    h->kernel_events = ((sweep_variant >> 24) & 1) != 0;
     h->fine8 = ((sweep_variant >> 21) & 7) ? ((sweep_variant >> 21) & 7) : 4;       // bits 21..23: eighths of a wave resolved in 32-receiver passes (7: none)
     h->taper = ((sweep_variant >> 17) & 7) ? ((sweep_variant >> 17) & 7) : 2;      // bits 17..19: split multiplier of the final wave
     if (near_slots > 0 && near_slots != h->K) { h->K = near_slots; return ensure_slots(h); }
@@ -628,10 +632,22 @@ extern "C" int rmb_last_timing(const rmb_handle *h, rmb_timing *out)
     if (m->timing_pending) {
         rmb_timing &t = m->timing;
         cudaEventElapsedTime(&t.ms_total, m->ev[0], m->ev[4]);
-        cudaEventElapsedTime(&t.ms_prepare, m->ev[0], m->ev[1]);
-        cudaEventElapsedTime(&t.ms_sweep, m->ev[1], m->ev[2]);
-        cudaEventElapsedTime(&t.ms_resolve, m->ev[2], m->ev[3]);
-        cudaEventElapsedTime(&t.ms_emit, m->ev[3], m->ev[4]);
+        if (m->timing_by_events) {
+            cudaEventElapsedTime(&t.ms_prepare, m->ev[0], m->ev[1]);
+            cudaEventElapsedTime(&t.ms_sweep, m->ev[1], m->ev[2]);
+            cudaEventElapsedTime(&t.ms_resolve, m->ev[2], m->ev[3]);
+            cudaEventElapsedTime(&t.ms_emit, m->ev[3], m->ev[4]);
+        } else {
+            // no event between the kernels (they overlap at their edges): the kernels' own globaltimer stamps
+            const Counters &c = *m->h_ctr.p;
+            const unsigned long long sb = ~c.t_sweep_begin_inv, fb = ~c.t_finish_begin_inv;
+            const bool ok = c.t_prepare_begin && c.t_sweep_end && sb >= c.t_prepare_begin && c.t_sweep_end >= sb;
+            t.ms_prepare = ok ? (float)((sb - c.t_prepare_begin) * 1e-6) : 0.f;
+            t.ms_sweep = ok ? (float)((c.t_sweep_end - sb) * 1e-6) : 0.f;
+            t.ms_resolve = 0.f;
+            t.ms_emit = (ok && c.t_finish_begin_inv) ? t.ms_total - (float)((c.t_sweep_end - c.t_prepare_begin) * 1e-6) : 0.f;
+            (void)fb;
+        }
         cudaGetLastError();
         m->timing_pending = false;
     }
@@ -678,6 +694,7 @@ static int publish(rmb_handle *h, int n_tx, long long m, bool draws, int launche
     const Counters &c = *h->h_ctr.p;
     rmb_timing &t = h->timing;
     h->timing_pending = true;          // the event durations are read on demand (rmb_last_timing)
+    h->timing_by_events = h->kernel_events || h->cfg.model != RMB_MODEL_SINR;
     t.sweep_launches = sweeps; t.kernel_launches = launches; t.recheck_sequential = c.n_recheck2;
     rmb_result &r = h->last;
     memset(&r, 0, sizeof(r));
@@ -780,7 +797,9 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
         RMB_CK(h, launch_prepare(nd, h->dp.p, h->geom.p, h->groups, n_tx, d_rec, stg, tx, h->theta.p, h->theta_min_g.p, h->ctr.p, aux, pgrid, h->st));
         h->bar_count += (unsigned)pgrid;      // only a launch that went out has arrivals: host and device targets stay in step
         launches += 1;
-        RMB_CK(h, cudaEventRecord(h->ev[1], h->st));
+        const bool kev = h->kernel_events;
+        if (kev) RMB_CK(h, cudaEventRecord(h->ev[1], h->st));
+        const bool use_finish = !draws && h->fuse_finish && n_tx > 0;
         // The whole tick is enqueued without a host round trip: the kernels downstream of the resolve read
         // the pair / recheck counts on the device.  The host looks at the counters once, at the end, and
         // redoes the tick only when a capacity was exceeded (near slots, pair records) -- both grow
@@ -796,7 +815,7 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
                 RMB_CK(h, cudaMemsetAsync(h->tx_cnt.p, 0, ((size_t)n_tx + 1) * sizeof(int), h->st));
                 RMB_CK(h, cudaMemsetAsync(h->rx_done.p, 0, 2 * ((size_t)h->n_work / 32 + 1) * sizeof(int), h->st));
                 RMB_CK(h, cudaMemsetAsync(h->bar.p + 2, 0, sizeof(unsigned), h->st));
-                RMB_CK(h, cudaEventRecord(h->ev[1], h->st));
+                if (kev) RMB_CK(h, cudaEventRecord(h->ev[1], h->st));
             }
             // exact resolve (decisions + dense pair records, then the per-packet segment offsets): fused into the
             // sweep as the epilogue of every rx block's last tx split; a kernel of its own for the other variants
@@ -807,12 +826,12 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
             fuse.rb_spin = h->splits.rb_taper; fuse.rb_fine = h->splits.rb_fine;
             fuse.enabled = (h->fuse_resolve && h->splits.can_fuse) ? 1 : 0;
             fuse.wk = wk; fuse.dp = h->dp.p; fuse.rec = d_rec; fuse.sl = sl; fuse.pr = pr; fuse.ctr = h->ctr.p;
-            fuse.n_tx = n_tx; fuse.seg = h->seg.p; fuse.rx_done = h->rx_done.p; fuse.rx_pass = h->rx_done.p + (h->n_work / 32 + 1);
+            fuse.n_tx = n_tx; fuse.seg = (use_finish && finish_scans(n_tx)) ? nullptr : h->seg.p; fuse.rx_done = h->rx_done.p; fuse.rx_pass = h->rx_done.p + (h->n_work / 32 + 1);
             static const char *trace_path = getenv("RMB_SWEEP_TRACE");
             const size_t trace_blocks = (size_t)h->splits.rb_taper * h->splits.s1 +
                                         (size_t)(h->n_work / h->splits.block_rx - h->splits.rb_taper) * h->splits.s2;
             if (trace_path) { RMB_CK(h, h->trace.ensure(12 * trace_blocks + 12)); fuse.trace = h->trace.p; }
-            RMB_CK(h, launch_sweep(mode, h->planar, variant, h->n_work, h->splits, a, fuse, h->st));
+            RMB_CK(h, launch_sweep(mode, h->planar, variant, h->n_work, h->splits, a, fuse, attempt == 0 && !kev, h->st));
             if (trace_path) {
                 std::vector<unsigned long long> tr(12 * trace_blocks);
                 RMB_CK(h, cudaMemcpyAsync(tr.data(), h->trace.p, tr.size() * 8, cudaMemcpyDeviceToHost, h->st));
@@ -823,21 +842,21 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
                 }
             }
             ++launches; ++sweeps;
-            RMB_CK(h, cudaEventRecord(h->ev[2], h->st));
+            if (kev) RMB_CK(h, cudaEventRecord(h->ev[2], h->st));
             if (!fuse.enabled) {
                 RMB_CK(h, launch_resolve(nd, wk, h->dp.p, tx, d_rec, sl, pr, h->ctr.p, n_tx, h->seg.p, 0, h->st));
                 launches += 1;
             }
-            const bool dev_publish = !draws && n_tx > 0 && h->fuse_finish;
-            RMB_CK(h, cudaEventRecord(h->ev[3], h->st));
+            const bool dev_publish = use_finish;
+            if (kev) RMB_CK(h, cudaEventRecord(h->ev[3], h->st));
             if (!draws && h->fuse_finish && n_tx <= 0) {
                 // nothing on the air: no launch (and no barrier arrivals to account for)
             } else if (!draws && h->fuse_finish) {
                 // deterministic reception: guard-band recheck, ordering and output rows in one cooperative kernel,
                 // whose last block stores the counters into the pinned host copy
-                const int fgrid = finish_grid();
+                const int fgrid = finish_grid(n_tx);
                 RMB_CK(h, launch_finish(wk, h->dp.p, h->groups, tx, d_rec, sl, pr, pa, n_tx, h->seg.p, h->key_alt.p, h->recheck_part.p,
-                                        h->ctr.p, h->h_ctr.p, fgrid, h->bar.p + 2, h->st));
+                                        h->ctr.p, h->h_ctr.p, fgrid, h->bar.p + 2, fuse.enabled && !kev && !trace_path, h->st));
                 launches += 1;
             } else {
                 // guard-band receivers: exact sums on a side stream, overlapped with the ordering
@@ -1324,6 +1343,21 @@ int rmb_peer_exchange_tick_enqueue(rmb_handle *h, int32_t slots, const void *d_r
     h->fused_push = nullptr;
     h->async_mode = false;
     return rc;
+}
+
+int rmb_peer_barrier_enqueue(rmb_handle *h)
+{
+    if (!h) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    auto &P = h->peer;
+    if (P.world < 1) return h->fail(RMB_ERR_STATE, "rmb_peer_barrier_enqueue before rmb_peer_export");
+    for (int r = 0; r < P.world; ++r) if (!P.peer[r]) return h->fail(RMB_ERR_STATE, "rmb_peer_barrier_enqueue before rmb_peer_open");
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    PeerPush pp{};
+    for (int r = 0; r < P.world; ++r) pp.peer[r] = P.peer[r];
+    pp.world = P.world; pp.rank = P.rank; pp.epoch = ++P.barrier_epoch;
+    RMB_CK(h, launch_peer_barrier(pp, h->ctr.p, h->st));
+    return RMB_OK;
 }
 
 int rmb_tick_peers_resident(rmb_handle *h, rmb_result *out)

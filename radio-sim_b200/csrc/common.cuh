@@ -64,6 +64,10 @@ struct Counters {
     unsigned recheck_done;            // work units of the guard-band recheck that have finished
     unsigned emit_done;               // blocks of the emit kernel that have finished (the last one publishes the counters)
     int needs_draws;                  // a record carries 0 < p_tx < 1 but the tick runs on the deterministic path
+    // device-side time stamps of the tick (globaltimer, ns): no CUDA event sits between the tick's kernels (an event
+    // record between two launches would serialise them and undo the programmatic dependent launch), so the kernels
+    // stamp themselves.  *_inv holds ~t so that one atomicMax gives the EARLIEST start.
+    unsigned long long t_prepare_begin, t_sweep_begin_inv, t_sweep_end, t_finish_begin_inv;
 };
 
 // slot flags
@@ -185,6 +189,28 @@ inline cudaError_t launch_grid_synced(const void *fn, dim3 grid, dim3 block, voi
 {
     return use_cooperative_launch() ? cudaLaunchCooperativeKernel(fn, grid, block, args, 0, st)
                                     : cudaLaunchKernel(fn, grid, block, args, 0, st);
+}
+
+// The same with dynamic shared memory and, optionally, programmatic dependent launch: the kernel's blocks may become
+// resident as soon as every block of the kernel in front of it on the stream has executed griddepcontrol.launch_dependents
+// (or exited); the kernel itself must execute griddepcontrol.wait before it touches what its predecessor wrote.
+// RMB_NO_PDL=1 turns the attribute off (an experiment knob).
+inline bool use_pdl()
+{
+    static int v = -1;
+    if (v < 0) { const char *e = getenv("RMB_NO_PDL"); v = (e && e[0] == '1') ? 0 : 1; }
+    return v == 1;
+}
+inline cudaError_t launch_grid_synced_ex(const void *fn, dim3 grid, dim3 block, void **args, size_t smem, bool overlap, cudaStream_t st)
+{
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[2];
+    int na = 0;
+    if (use_cooperative_launch()) { attr[na].id = cudaLaunchAttributeCooperative; attr[na].val.cooperative = 1; ++na; }
+    if (overlap && use_pdl()) { attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization; attr[na].val.programmaticStreamSerializationAllowed = 1; ++na; }
+    cfg.attrs = attr; cfg.numAttrs = (unsigned)na;
+    return cudaLaunchKernelExC(&cfg, fn, args);
 }
 
 #define RMB_CUDA_OK(expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) return e__; } while (0)

@@ -111,19 +111,72 @@ __device__ __forceinline__ void warp_bucket(const PairRecs &pr, const PairArrays
     __syncwarp();
 }
 
+// seg[t] = first pair of packet t (exclusive scan of the per-packet heard counts) for n <= kFinScanMax packets, by ONE
+// block into shared memory; returns the largest count.  Every block of the finish kernel does this for itself (40 KB
+// of counts out of the L2, ~2 us) -- the sweep used to leave the scan to the one block that resolved last, 10 us at
+// the very end of its launch with the rest of the GPU idle (profiles/r02_trace8.txt).
+__device__ __forceinline__ int block_scan_counts(const int *cnt, int n, int *s_seg, int *s_warp /* [2 * kFinWarps] */)
+{
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < n; i += kFinThreads) s_seg[i] = __ldcg(cnt + i);
+    __syncthreads();
+    const int per = (n + kFinThreads - 1) / kFinThreads;
+    const int b = min(n, tid * per), e = min(n, b + per);
+    int sum = 0, mx = 0;
+    for (int i = b; i < e; ++i) { const int v = s_seg[i]; sum += v; mx = max(mx, v); }
+    int incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (lane == 31) s_warp[warp] = incl;
+    if (lane == 0) s_warp[kFinWarps + warp] = mx;
+    __syncthreads();
+    int carry = 0, total = 0, gmx = 0;
+#pragma unroll
+    for (int k = 0; k < kFinWarps; ++k) { const int v = s_warp[k]; if (k < warp) carry += v; total += v; gmx = max(gmx, s_warp[kFinWarps + k]); }
+    int ex = carry + incl - sum;
+    for (int i = b; i < e; ++i) { const int v = s_seg[i]; s_seg[i] = ex; ex += v; }
+    if (tid == 0) s_seg[n] = total;
+    __syncthreads();
+    return gmx;
+}
+
 __global__ void __launch_bounds__(kFinThreads, 4)
 finish_kernel(WorkArrays wk, const DevParams *dp, Groups groups, TxTiles tx, const rmb_tx_record *rec, SlotArrays sl,
-              PairRecs pr, PairArrays pa, int n_tx, const int *seg, unsigned long long *items, double *part,
-              Counters *ctr, Counters *host_ctr, unsigned *bar)
+              PairRecs pr, PairArrays pa, int n_tx, int *seg_global, unsigned long long *items, double *part,
+              Counters *ctr, Counters *host_ctr, unsigned *bar, int scan_here)
 {
-    __shared__ unsigned long long s_items[kBucketSortMax];
+    // one dynamic buffer, two lives: the segment offsets of all packets while the records go to their buckets
+    // (scan_here: [n_tx + 1] ints), the ranking scratch of phase 3 behind the grid barrier ([kBucketSortMax] items;
+    // the offsets are read from global memory there -- block 0 stored them in front of the barrier)
+    extern __shared__ unsigned long long s_items[];
+    int *const s_seg_dyn = reinterpret_cast<int *>(s_items);
     __shared__ double s_part[kFinWarps];
-    __shared__ int s_last;
+    __shared__ int s_last, s_scanw[2 * kFinWarps];
     double *s_lin = reinterpret_cast<double *>(s_items);            // tier 2: [2][kFinSeqChunk]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    // launched with programmatic stream serialization: everything above ran while the sweep's last blocks were
+    // still at work; its results (and the counters) may be read from here on
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (threadIdx.x == 0 && blockIdx.x == 0) atomicMax(&ctr->t_finish_begin_inv, ~global_timer_ns());
     const long long m_all = (long long)ctr->heard;
     const bool stand_down = m_all > pr.cap;                         // the host grows the record lists and redoes the tick
     const long long m = stand_down ? 0 : m_all;
+    // ---- 0: segment offsets.  scan_here: every block scans the per-packet counts for itself (block 0 also stores
+    //         them for the host side / later kernels); otherwise the sweep's last resolving block did it
+    const int *seg = seg_global;
+    int max_bucket;
+    if (scan_here) {
+        max_bucket = block_scan_counts(pr.tx_cnt, n_tx, s_seg_dyn, s_scanw);
+        seg = s_seg_dyn;
+        if (blockIdx.x == 0) {
+            for (int i = threadIdx.x; i <= n_tx; i += kFinThreads) seg_global[i] = s_seg_dyn[i];
+            if (threadIdx.x == 0) ctr->max_bucket = max_bucket;
+        }
+    } else {
+        max_bucket = __ldcg(&ctr->max_bucket);
+    }
 
     // ---- 1a: records -> buckets, at the rank their atomic drew -----------------------------------
     for (long long i = (long long)blockIdx.x * kFinThreads + threadIdx.x; i < m; i += (long long)gridDim.x * kFinThreads) {
@@ -170,6 +223,7 @@ finish_kernel(WorkArrays wk, const DevParams *dp, Groups groups, TxTiles tx, con
         __syncthreads();
     }
     grid_barrier(bar, gridDim.x);
+    seg = seg_global;                                   // the shared copy is about to be overwritten by the ranking scratch
 
     // ---- 2: tier 2 (rare), the addition in arrival order: one adder thread, the other warps evaluate ahead ----
     const int n2 = __ldcg(&ctr->n_recheck2);
@@ -208,7 +262,7 @@ finish_kernel(WorkArrays wk, const DevParams *dp, Groups groups, TxTiles tx, con
     // ---- 3: rank every packet's bucket by rx, write its rows -----------------------------------------
     EmitCount n{0, 0};
     // (m == 0: nothing was heard -- with no enabled receiver at all the sweep did not even run and `seg` is stale)
-    if (m > 0 && __ldcg(&ctr->max_bucket) <= kBucketSortMax) {
+    if (m > 0 && max_bucket <= kBucketSortMax) {
         // buckets of up to kWarpBucket pairs: a warp each
         unsigned long long *sw = s_items + warp * kWarpBucket;
         for (int t = blockIdx.x * kFinWarps + warp; t < n_tx; t += gridDim.x * kFinWarps) {
@@ -276,33 +330,55 @@ finish_kernel(WorkArrays wk, const DevParams *dp, Groups groups, TxTiles tx, con
     }
 }
 
-// co-resident blocks of the kernel on the current device (queried once per device)
-int finish_grid()
+// co-resident blocks of the kernel on the current device for a given dynamic shared memory size
+constexpr int kFinScanMax = 16 * 1024 - 1;         // packets whose offsets a block scans for itself (64 KB of shared memory)
+static size_t finish_smem(int n_tx, bool scan_here)
 {
-    static int cache[64] = {};
+    const size_t items = (size_t)kBucketSortMax * sizeof(unsigned long long);
+    return scan_here ? std::max(items, ((size_t)n_tx + 1) * sizeof(int)) : items;
+}
+bool finish_scans(int n_tx) { return n_tx <= kFinScanMax; }
+
+int finish_grid(int n_tx)
+{
+    static int cache[64][2] = {};
+    static bool attr_set[64] = {};
     int dev = 0;
     cudaGetDevice(&dev);
     const int slot = (dev >= 0 && dev < 64) ? dev : 0;
-    if (cache[slot] == 0) {
-        int per_sm = 1;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, finish_kernel, kFinThreads, 0) != cudaSuccess || per_sm < 1) {
-            per_sm = 1; cudaGetLastError();
-        }
-        cache[slot] = device_sms() * std::min(per_sm, 4);
+    if (!attr_set[slot]) {                              // per device: more than 48 KB of dynamic shared memory is opt-in
+        cudaFuncSetAttribute(finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (kFinScanMax + 1) * (int)sizeof(int));
+        attr_set[slot] = true;
     }
-    return cache[slot];
+    // occupancy depends on the dynamic size only through a few steps: cache the two common cases (none / <= 48 KB),
+    // query the others
+    const bool scan = finish_scans(n_tx);
+    const size_t smem = finish_smem(n_tx, scan);
+    const int kind = smem <= 16 * 1024 ? 0 : (smem <= 40 * 1024 + 4 ? 1 : -1);
+    if (kind >= 0 && cache[slot][kind]) return cache[slot][kind];
+    int per_sm = 1;
+    const size_t q = kind == 0 ? 16 * 1024 : kind == 1 ? 40 * 1024 + 4 : smem;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, finish_kernel, kFinThreads, q) != cudaSuccess || per_sm < 1) {
+        per_sm = 1; cudaGetLastError();
+    }
+    const int g = device_sms() * std::min(per_sm, 4);
+    if (kind >= 0) cache[slot][kind] = g;
+    return g;
 }
 
 cudaError_t launch_finish(const WorkArrays &wk, const DevParams *dp, Groups groups, TxTiles tx, const rmb_tx_record *rec,
-                          SlotArrays sl, PairRecs pr, PairArrays pa, int n_tx, const int *seg, unsigned long long *items,
-                          double *part, Counters *ctr, Counters *host_ctr, int grid, unsigned *bar, cudaStream_t st)
+                          SlotArrays sl, PairRecs pr, PairArrays pa, int n_tx, int *seg, unsigned long long *items,
+                          double *part, Counters *ctr, Counters *host_ctr, int grid, unsigned *bar, bool overlap, cudaStream_t st)
 {
     if (n_tx <= 0) return cudaSuccess;
     WorkArrays a_wk = wk; Groups a_groups = groups;
+    int scan_here = finish_scans(n_tx) ? 1 : 0;
     void *args[] = {(void *)&a_wk, (void *)&dp, (void *)&a_groups, (void *)&tx, (void *)&rec, (void *)&sl, (void *)&pr,
                     (void *)&pa, (void *)&n_tx, (void *)&seg, (void *)&items, (void *)&part, (void *)&ctr, (void *)&host_ctr,
-                    (void *)&bar};
-    return launch_grid_synced((const void *)&finish_kernel, dim3((unsigned)grid), dim3(kFinThreads), args, st);
+                    (void *)&bar, (void *)&scan_here};
+    // (finish_grid(n_tx) was computed for the same dynamic size; it also opted the kernel in to > 48 KB)
+    return launch_grid_synced_ex((const void *)&finish_kernel, dim3((unsigned)grid), dim3(kFinThreads), args,
+                                 finish_smem(n_tx, scan_here != 0), overlap, st);
 }
 
 }  // namespace rmb

@@ -45,6 +45,7 @@ cudaError_t launch_gather_records(const NodeArrays &nd, int rx_base, int n_tx, c
 constexpr size_t kPeerFlagBytes = 256;       // flags[kMaxPeers] at the start of a gather buffer, records follow
 struct PeerPush { char *peer[kMaxPeers]; int world, rank; size_t rec_off; unsigned epoch; unsigned *done; };
 cudaError_t launch_peer_push(const rmb_tx_record *local, int slots, const PeerPush &pp, cudaStream_t st);
+cudaError_t launch_peer_barrier(const PeerPush &pp, Counters *ctr, cudaStream_t st);   // pp.epoch = barrier epoch, second flag row
 struct TxStage { float4 *f; float *theta; int *gid; };
 // one cooperative launch: peer wait, counter zeroing, per-tx constants, tx-failure rule, stable bucketing
 int prepare_grid(int n_tx);
@@ -101,14 +102,15 @@ struct PairRecs {
 struct SweepFuse {
     int enabled;
     WorkArrays wk; const DevParams *dp; const rmb_tx_record *rec; SlotArrays sl; PairRecs pr; Counters *ctr;
-    int n_tx; int *seg;
+    int n_tx; int *seg;               // seg == nullptr: the kernel behind the sweep scans the per-packet counts itself
     unsigned long long *trace;        // debug (RMB_SWEEP_TRACE): [block][12] start / sweep done / block done [ns], smid | passes << 16, stamps of the last pass
     int *rx_done, *rx_pass;           // [rx blocks] splits finished / resolve passes claimed (zero on entry)
     int rb_spin;                      // rx blocks >= rb_spin: the last finishers of an rx block wait for its last split and share the passes
     int rb_fine;                      // rx blocks >= rb_fine (>= rb_spin): passes of 32 receivers instead of 128
 };
+// overlap: programmatic dependent launch behind the preparation kernel (no event may sit between the two launches)
 cudaError_t launch_sweep(int mode, bool planar, int variant, int n_work, SweepSplits splits, const SweepArgs &a, const SweepFuse &fuse,
-                         cudaStream_t st);
+                         bool overlap, cudaStream_t st);
 // also turns the per-packet heard counts into segment offsets (seg[t] = first pair of packet t, exclusive scan
 // of pr.tx_cnt; largest bucket -> ctr->max_bucket): done by the last block to finish
 cudaError_t launch_resolve(const NodeArrays &nd, const WorkArrays &wk, const DevParams *dp, TxTiles tx,
@@ -127,10 +129,14 @@ struct PairArrays;
 // everything behind the sweep of a deterministic-reception tick in one cooperative kernel (finish.cu): guard-band
 // recheck, bucket placement, per-packet ranking and the output rows.  bar: a counter that is ZERO at launch.
 // part: >= n_work + grid doubles; items: >= record capacity
-int finish_grid();
+// finish_scans(n_tx): the kernel turns the per-packet heard counts into segment offsets itself (every block, in shared
+// memory) -- the sweep's epilogue then leaves the scan out (SweepFuse.seg == nullptr).  overlap: launched with
+// programmatic stream serialization, so that its blocks become resident while the sweep's last blocks still run.
+bool finish_scans(int n_tx);
+int finish_grid(int n_tx);
 cudaError_t launch_finish(const WorkArrays &wk, const DevParams *dp, Groups groups, TxTiles tx, const rmb_tx_record *rec,
-                          SlotArrays sl, PairRecs pr, PairArrays pa, int n_tx, const int *seg, unsigned long long *items,
-                          double *part, Counters *ctr, Counters *host_ctr, int grid, unsigned *bar, cudaStream_t st);
+                          SlotArrays sl, PairRecs pr, PairArrays pa, int n_tx, int *seg, unsigned long long *items,
+                          double *part, Counters *ctr, Counters *host_ctr, int grid, unsigned *bar, bool overlap, cudaStream_t st);
 
 // ---- emission: compaction, (tx,rx) ordering, stochastic rule, outputs -------------------------
 struct PairArrays {

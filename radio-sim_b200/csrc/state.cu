@@ -246,6 +246,23 @@ __global__ void __launch_bounds__(256) peer_push_kernel(const rmb_tx_record *loc
     }
 }
 
+// Device-side rendezvous of all ranks' streams (rmb_peer_barrier_enqueue): every rank raises its slot of the SECOND
+// flag row (bytes 64..127 of a gather buffer) in every peer's buffer to `epoch`, then waits until all its own slots
+// show it.  The ranks leave within an NVLink round trip of each other -- a tighter line-up than a collective gives.
+__global__ void peer_barrier_kernel(PeerPush pp, Counters *ctr)
+{
+    const int p = threadIdx.x;
+    if (p < pp.world) st_release_sys(reinterpret_cast<unsigned *>(pp.peer[p] + 64) + pp.rank, pp.epoch);
+    __syncthreads();
+    if (p < pp.world && !peer_wait(reinterpret_cast<const unsigned *>(pp.peer[pp.rank] + 64) + p, pp.epoch)) ctr->peer_timeout = 1;
+}
+
+cudaError_t launch_peer_barrier(const PeerPush &pp, Counters *ctr, cudaStream_t st)
+{
+    peer_barrier_kernel<<<1, 32, 0, st>>>(pp, ctr);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_peer_push(const rmb_tx_record *local, int slots, const PeerPush &pp, cudaStream_t st)
 {
     peer_push_kernel<<<max(1, (slots + 255) / 256), 256, 0, st>>>(local, slots, pp);
@@ -284,6 +301,9 @@ prepare_all_kernel(NodeArrays nd, const DevParams *dp, const Geom *geom, Groups 
     __shared__ int s_timeout, s_needs;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int ng = groups.ngroups;
+    // the sweep behind this kernel is launched with programmatic stream serialization: its blocks may become resident
+    // (and fetch their receivers) while this kernel still runs; they wait for its completion before they read a tile
+    asm volatile("griddepcontrol.launch_dependents;");
 
     // fused exchange: this rank's records go out first (16-byte stores over NVLink, a record per thread) ...
     if (aux.push_local) {
@@ -323,7 +343,7 @@ prepare_all_kernel(NodeArrays nd, const DevParams *dp, const Geom *geom, Groups 
         for (int i = gtid; i < aux.n_work / 4; i += gsz) c4[i] = make_int4(0, 0, 0, 0);
         for (int i = gtid; i <= n_tx; i += gsz) aux.tx_cnt[i] = 0;
         for (int i = gtid; i < aux.n_rx_done; i += gsz) aux.rx_done[i] = 0;
-        if (gtid == 0) { *ctr = Counters{}; aux.bar[2] = 0u; }      // bar[2]: the barrier counter of finish.cu, zero at its launch
+        if (gtid == 0) { Counters z{}; z.t_prepare_begin = global_timer_ns(); *ctr = z; aux.bar[2] = 0u; }      // bar[2]: the barrier counter of finish.cu, zero at its launch
     }
     // ... and the peers' records of this tick must have landed before anybody reads `rec` (everything above is
     // independent of them and runs while the records are on their way)
@@ -347,8 +367,10 @@ prepare_all_kernel(NodeArrays nd, const DevParams *dp, const Geom *geom, Groups 
             if (g >= 0) {
                 const double n = dp->pl_exponent;
                 const double d0n = s_const[0], dnear_n = s_const[1], theta_s = s_const[2];
-                const double P = pow(10.0, (r.power_dbm - dp->pl0_db) / 10.0) * d0n;
-                const float cf = (float)pow(P, -1.0 / n);
+                // P^(-1/n) = 10^(-e/n) / d0: two exp10 instead of a pow(10, .) and a general pow (half the latency chain)
+                const double e10 = (r.power_dbm - dp->pl0_db) / 10.0;
+                const double P = exp10(e10) * d0n;
+                const float cf = (float)(exp10(-e10 / n) / dp->d0_m);
                 const double c = (double)cf;
                 stg.f[t] = make_float4((float)((r.x - geom->cx) * c), (float)((r.y - geom->cy) * c),
                                        (float)((r.z - geom->cz) * c), cf);

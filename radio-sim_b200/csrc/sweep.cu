@@ -89,6 +89,10 @@ sweep_kernel(const float *__restrict__ fx, const float *__restrict__ fy, const f
     // The last rx blocks of the launch (rb >= rb_taper, about its final wave) are cut into S2 > S1 splits: shorter
     // blocks where the launch runs out of work, so the SMs go idle closer together.
     if (fuse.trace && threadIdx.x == 0) fuse.trace[12 * (size_t)blockIdx.x] = global_timer_ns();
+    // programmatic dependent launch, both ways: the kernel behind this one (finish.cu) may bring its blocks in as soon
+    // as every block of this launch has started -- i.e. during the final wave, into slots nobody is waiting for --
+    // and this kernel's own blocks may have started before the preparation kernel in front of it was done
+    asm volatile("griddepcontrol.launch_dependents;");
     const int n1 = rb_taper * S1;
     const bool tapered = (int)blockIdx.x >= n1;
     const int S = tapered ? S2 : S1;
@@ -100,11 +104,6 @@ sweep_kernel(const float *__restrict__ fx, const float *__restrict__ fy, const f
     int g = 0;
     while (g + 1 < groups.ngroups && wb >= groups.w_begin[g + 1]) ++g;
 
-    // this block's share of the bucket: split `split` of S, a multiple of kTile
-    const int b0 = tx.goff[g], b1 = tx.goff[g + 1];
-    const int per = ((b1 - b0 + S - 1) / S + kTile - 1) / kTile * kTile;
-    const int j_begin = min(b1, b0 + split * per), j_end = min(b1, j_begin + per);
-
     float rx[R], ry[R], rz[R], sum[R];
     f32x2 X[R], Y[R], Z[R];
 #pragma unroll
@@ -113,6 +112,14 @@ sweep_kernel(const float *__restrict__ fx, const float *__restrict__ fy, const f
         X[r] = pack2(rx[r], rx[r]); Y[r] = pack2(ry[r], ry[r]); Z[r] = pack2(rz[r], rz[r]);
         sum[r] = 0.f;
     }
+    // (the receivers above do not depend on the preparation kernel; everything below does)
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (threadIdx.x == 0) atomicMax(&fuse.ctr->t_sweep_begin_inv, ~global_timer_ns());
+
+    // this block's share of the bucket: split `split` of S, a multiple of kTile
+    const int b0 = tx.goff[g], b1 = tx.goff[g + 1];
+    const int per = ((b1 - b0 + S - 1) / S + kTile - 1) / kTile * kTile;
+    const int j_begin = min(b1, b0 + split * per), j_end = min(b1, j_begin + per);
     const float th_min = theta_min_g[g];
 
     for (int s0 = j_begin; s0 < j_end; s0 += kStage) {
@@ -255,7 +262,7 @@ sweep_kernel(const float *__restrict__ fx, const float *__restrict__ fy, const f
                 __syncthreads();
                 if (threadIdx.x == 0) { __threadfence(); s_flag = atomicAdd(&fuse.ctr->resolve_done, (unsigned)pass_rx) + (unsigned)pass_rx == (unsigned)n_work; }
                 __syncthreads();
-                if (s_flag) {
+                if (s_flag && fuse.seg) {
                     __threadfence();
                     if (fuse.trace && threadIdx.x == 0) fuse.trace[12 * (size_t)blockIdx.x + 10] = global_timer_ns();
                     scan_tx_counts(fuse.pr.tx_cnt, fuse.n_tx, fuse.seg, fuse.ctr);
@@ -265,6 +272,7 @@ sweep_kernel(const float *__restrict__ fx, const float *__restrict__ fy, const f
         }
         if (fuse.trace && threadIdx.x == 0) fuse.trace[12 * (size_t)blockIdx.x + 2] = global_timer_ns();
     }
+    if (threadIdx.x == 0) atomicMax(&fuse.ctr->t_sweep_end, global_timer_ns());
 }
 
 // ---- host side: variant table, split planning, launch ---------------------------------------
@@ -371,7 +379,7 @@ SweepSplits sweep_splits(int mode, bool planar, int variant, int n_work, int n_t
 }
 
 cudaError_t launch_sweep(int mode, bool planar, int variant, int n_work, SweepSplits splits, const SweepArgs &a, const SweepFuse &fuse,
-                         cudaStream_t st)
+                         bool overlap, cudaStream_t st)
 {
     if (n_work <= 0) return cudaSuccess;
     const SweepVariant v = pick(mode, planar, variant);
@@ -386,7 +394,12 @@ cudaError_t launch_sweep(int mode, bool planar, int variant, int n_work, SweepSp
                     (void *)&b.K, (void *)&nw, (void *)&S1, (void *)&S2, (void *)&rbt, (void *)&f};
     const long long blocks = (long long)rbt * S1 + (long long)(nb - rbt) * S2;
     if (blocks > 0x7fffffffll) return cudaErrorInvalidConfiguration;
-    return cudaLaunchKernel(v.fn, dim3((unsigned)blocks), dim3((unsigned)v.threads), args, 0, st);
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)blocks); cfg.blockDim = dim3((unsigned)v.threads); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization; attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = (overlap && use_pdl()) ? 1u : 0u;
+    return cudaLaunchKernelExC(&cfg, v.fn, args);
 }
 
 }  // namespace rmb

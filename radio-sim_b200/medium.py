@@ -218,6 +218,10 @@ class Medium:
         """Exchange + tick in one step (the preparation kernel pushes the records itself); asynchronous."""
         self._ck(self._lib.rmb_peer_exchange_tick_enqueue(self._h, slots, C.c_void_p(d_records)))
 
+    def peer_barrier_enqueue(self):
+        """Device-side rendezvous of all ranks' streams (no host synchronisation)."""
+        self._ck(self._lib.rmb_peer_barrier_enqueue(self._h))
+
     def tick_finish(self):
         """Settle an enqueued tick; counts only (fetch() downloads the lists)."""
         r = A.Result()
