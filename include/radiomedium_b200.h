@@ -270,6 +270,43 @@ int rmb_node_info(rmb_handle *h, float *rssi_dbm, uint8_t *receiving);
  * the parity tests compare with the oracle's sequential sum */
 int rmb_node_info_f64(rmb_handle *h, double *rssi_dbm, uint8_t *receiving);
 
+/* ---- several GPUs behind one object ---------------------------------------------------------------------------
+ * For a caller that lives in ONE process and thinks in whole node arrays and whole packet lists -- the reference's
+ * Simulator with its one RadioMedium (Simulator.java:155-165, 234-239).  A group owns one handle per device
+ * (receivers in contiguous node-index blocks, rmb_config.rx_base / n_shards filled in), maps the handles' exchange
+ * buffers onto each other and runs the shards' calls on one host worker thread per device, so that kernels and
+ * device-to-host copies of all GPUs overlap.  Every call below is the whole-array form of the handle call of the
+ * same name.
+ *   rmb_group_create   cfg: as for rmb_create (device / rx_base / n_shards are overwritten); devices NULL = 0..n-1
+ *                      (the same device may appear twice: development on a one-GPU box); max_tx_per_tick sizes the
+ *                      exchange buffers (a tick with more packets from one shard returns RMB_ERR_CAPACITY).
+ *   rmb_group_tick     results[r] = shard r's lists (r = 0..n_devices-1, handle-owned pinned memory as for rmb_tick).
+ *                      Row order inside a shard: gathered record position, then node index; record position
+ *                      p = r * slots + i is packet packet_of[p] of the caller's list (-1 = padding).  Shards own
+ *                      increasing node blocks, so packet t's rows in the reference's order are shard 0's rows of t,
+ *                      then shard 1's, ...  (*slots_out, packet_of[n_devices * max_tx_per_tick] may be NULL for
+ *                      n_devices == 1, where position == packet).  uniforms: as for rmb_tick, used by a group of ONE
+ *                      device (RMB_ERR_UNIFORMS tells how many a tick needs); on several devices stochastic reception
+ *                      needs the draws API of the handles (rmb_group_shard) and returns RMB_ERR_UNSUPPORTED here. */
+typedef struct rmb_group rmb_group;
+int         rmb_group_create(const rmb_config *cfg, int32_t n_devices, const int32_t *devices, int32_t max_tx_per_tick, rmb_group **out);
+int         rmb_group_destroy(rmb_group *g);
+const char *rmb_group_last_error(const rmb_group *g);      /* g may be NULL: last create error */
+int32_t     rmb_group_size(const rmb_group *g);
+int         rmb_group_shard(const rmb_group *g, int32_t r, rmb_handle **handle, int32_t *first_node, int32_t *n_nodes);
+int rmb_group_set_nodes(rmb_group *g, int32_t n, const double *x, const double *y, const double *z,
+                        const double *txpower_dbm, const int32_t *channel, const uint8_t *enabled,
+                        const double *rxprob, const double *txprob, const int32_t *id_int);
+int rmb_group_update_positions(rmb_group *g, int32_t count, const int32_t *idx, const double *x, const double *y, const double *z);
+int rmb_group_update_radio(rmb_group *g, int32_t count, const int32_t *idx, const double *txpower_dbm, const int32_t *channel,
+                           const uint8_t *enabled, const double *rxprob, const double *txprob);
+int rmb_group_tick(rmb_group *g, int32_t n_tx, const int32_t *src, const double *power_dbm, const int32_t *channel,
+                   const double *uniforms, size_t n_uniforms, rmb_result *results, int32_t *slots_out, int32_t *packet_of);
+int rmb_group_node_info_f64(rmb_group *g, double *rssi_dbm, uint8_t *receiving);
+/* Moves a shard: the global index of the handle's first node (rmb_config.rx_base) for the node table that the next
+ * rmb_set_nodes uploads.  What rmb_group_set_nodes uses when the node count, and with it the partition, changes. */
+int rmb_set_shard_base(rmb_handle *h, int32_t rx_base);
+
 int rmb_last_timing(const rmb_handle *h, rmb_timing *out);
 /* CUDA stream the handle's kernels and copies run on (a cudaStream_t passed as void*).
  * rmb_set_stream makes the handle use the caller's stream instead of its own, so that work the

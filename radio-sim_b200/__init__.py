@@ -7,8 +7,8 @@ hyphen is not importable; radio_sim_b200/ is a shim pointing here).
 """
 from ._abi import (MODEL_NULL, MODEL_UDGM, MODEL_UDGM_CONSTANT, MODEL_N2N, MODEL_SINR,
                    NOT_HEARD, INTERFERED, DELIVERED, LIB_PATH, SYMBOLS, load)
-from .medium import Medium, MediumError, TickResult
+from .medium import Medium, MediumError, TickResult, Group, GroupResult
 
-__all__ = ["Medium", "MediumError", "TickResult", "load", "LIB_PATH", "SYMBOLS",
+__all__ = ["Medium", "MediumError", "TickResult", "Group", "GroupResult", "load", "LIB_PATH", "SYMBOLS",
            "MODEL_NULL", "MODEL_UDGM", "MODEL_UDGM_CONSTANT", "MODEL_N2N", "MODEL_SINR",
            "NOT_HEARD", "INTERFERED", "DELIVERED"]

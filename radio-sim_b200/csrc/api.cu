@@ -25,7 +25,9 @@ template <class T> struct DevBuf {
     T *p = nullptr; size_t cap = 0;
     cudaError_t ensure(size_t need, bool zero = false) {
         if (need <= cap) return cudaSuccess;
-        size_t ncap = std::max(need, cap + cap / 2);
+        // a quarter of headroom: per-tick sizes (heard pairs, packets) wander by a few per cent from tick to tick, and
+        // a re-allocation costs milliseconds
+        size_t ncap = std::max(need + need / 4, cap + cap / 2);
         if (p) { cudaFree(p); p = nullptr; cap = 0; }
         cudaError_t e = cudaMalloc((void **)&p, std::max<size_t>(ncap, 1) * sizeof(T));
         if (e != cudaSuccess) return e;
@@ -40,7 +42,7 @@ template <class T> struct PinBuf {
     T *p = nullptr; size_t cap = 0;
     cudaError_t ensure(size_t need) {
         if (need <= cap) return cudaSuccess;
-        size_t ncap = std::max(need, cap + cap / 2);
+        size_t ncap = std::max(need + need / 4, cap + cap / 2);      // pinning pages is slow: 17 ms for the lists of a C4 tick
         if (p) { cudaFreeHost(p); p = nullptr; cap = 0; }
         cudaError_t e = cudaMallocHost((void **)&p, std::max<size_t>(ncap, 1) * sizeof(T));
         if (e != cudaSuccess) return e;
@@ -66,7 +68,8 @@ struct rmb_handle {
     std::vector<int> h_channel; std::vector<uint8_t> h_enabled;
     std::vector<double> h_txpower, h_rxprob, h_txprob;
     bool maybe_draws = false;
-    bool planar = true;
+    bool planar = true; double planar_z = 0.0;      // all nodes share one z (2-D sweep) and which
+    cudaEvent_t ev_h2d = nullptr;                   // "the caller's arrays have been read" (dense position updates)
 
     // device state
     DevBuf<double> x, y, z, txpower, rxprob, txprob, matrix;
@@ -292,20 +295,27 @@ static void update_draw_flag(rmb_handle *h)
     h->maybe_draws = d;
 }
 
-// bounding box -> centre / planarity, then the fp32 work-order copy
-static int refresh_geometry(rmb_handle *h, bool reorder)
+// bounding box -> centre / planarity, then the fp32 work-order copy.
+// planar_known: 1 / 0 = the caller knows whether all z are equal (it saw them on the host), so nothing is read back
+// and nothing waits -- the kernels stay queued behind the upload; -1 = read the device's verdict (one round trip).
+static int refresh_geometry(rmb_handle *h, bool reorder, int planar_known = -1)
 {
     NodeArrays nd = node_arrays(h);
     RMB_CK(h, launch_geom(nd, h->geom_scratch.p, h->geom.p, h->st));
-    Geom g;
-    RMB_CK(h, cudaMemcpyAsync(&g, h->geom.p, sizeof(Geom), cudaMemcpyDeviceToHost, h->st));
+    Geom g{};
+    if (planar_known < 0) RMB_CK(h, cudaMemcpyAsync(&g, h->geom.p, sizeof(Geom), cudaMemcpyDeviceToHost, h->st));
     if (reorder) {
         ReorderScratch sc{h->ro_key.p, h->ro_key_alt.p, h->ro_val.p, h->ro_val_alt.p, h->ro_tmp.p, h->ro_tmp.cap};
         RMB_CK(h, launch_reorder(nd, h->gid.p, h->geom.p, h->groups, h->n_work, sc, h->perm.p, h->st));
     }
     RMB_CK(h, launch_regather(nd, work_arrays(h), h->geom.p, h->st));
-    RMB_CK(h, cudaStreamSynchronize(h->st));
-    h->planar = g.planar != 0;
+    if (planar_known < 0) {
+        RMB_CK(h, cudaStreamSynchronize(h->st));
+        h->planar = g.planar != 0;
+        h->planar_z = g.zmin;
+    } else {
+        h->planar = planar_known != 0;
+    }
     return RMB_OK;
 }
 
@@ -371,6 +381,7 @@ int rmb_create(const rmb_config *cfg, rmb_handle **out)
     h->st = h->own_st;
     if ((e = cudaStreamCreateWithFlags(&h->st2, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
     for (auto &ev : h->ev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) return bail(e, "cudaEventCreate");
+    if ((e = cudaEventCreateWithFlags(&h->ev_h2d, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
     if ((e = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming)) != cudaSuccess ||
         (e = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
     if ((e = h->dp.ensure(1)) != cudaSuccess || (e = h->geom.ensure(1)) != cudaSuccess ||
@@ -419,6 +430,7 @@ int rmb_destroy(rmb_handle *h)
     h->rec_sinr.release(); h->rec_flags.release(); h->rec_rank.release(); h->tx_cnt.release(); h->first.release();
     for (auto &ev : h->ev) if (ev) cudaEventDestroy(ev);
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    if (h->ev_h2d) cudaEventDestroy(h->ev_h2d);
     if (h->ev_join) cudaEventDestroy(h->ev_join);
     for (int r = 0; r < kMaxPeers; ++r) if (h->peer.ipc[r] && h->peer.peer[r]) cudaIpcCloseMemHandle(h->peer.peer[r]);
     if (h->peer.buf) cudaFree(h->peer.buf);
@@ -460,6 +472,19 @@ int rmb_set_nodes(rmb_handle *h, int32_t n, const double *x, const double *y, co
     return RMB_OK;
 }
 
+int rmb_set_shard_base(rmb_handle *h, int32_t rx_base)
+{
+    if (!h) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    RMB_SETTLE(h);
+    if (rx_base < 0) return h->fail(RMB_ERR_INVALID, "rmb_set_shard_base: negative index");
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    h->cfg.rx_base = rx_base;
+    RMB_CK(h, cudaMemcpy(&h->dp.p->rx_base, &rx_base, sizeof(int), cudaMemcpyHostToDevice));
+    h->have_nodes = false;                 // the node table that follows is the one that counts
+    return RMB_OK;
+}
+
 int rmb_set_matrix(rmb_handle *h, int32_t n, const double *matrix)
 {
     if (!h) return RMB_ERR_INVALID;
@@ -488,6 +513,7 @@ extern "C" int rmb_update_positions(rmb_handle *h, int32_t count, const int32_t 
     if (count < 0 || (count > 0 && (!x || !y))) return h->fail(RMB_ERR_INVALID, "rmb_update_positions: bad arguments");
     RMB_CK(h, cudaSetDevice(h->cfg.device));
     if (count == 0) return RMB_OK;
+    int planar_known = -1;
     if (!idx) {
         if (count != h->n) return h->fail(RMB_ERR_INVALID, "dense position update needs count == n");
         const size_t b = (size_t)count * sizeof(double);
@@ -495,6 +521,11 @@ extern "C" int rmb_update_positions(rmb_handle *h, int32_t count, const int32_t 
         RMB_CK(h, cudaMemcpyAsync(h->y.p, y, b, cudaMemcpyHostToDevice, h->st));
         if (z) RMB_CK(h, cudaMemcpyAsync(h->z.p, z, b, cudaMemcpyHostToDevice, h->st));
         else   RMB_CK(h, cudaMemsetAsync(h->z.p, 0, b, h->st));       // Position.set(x, y) zeroes z (Position.java:44-46)
+        RMB_CK(h, cudaEventRecord(h->ev_h2d, h->st));
+        // planarity is decided here, from the caller's z, so that no device round trip sits on the per-tick path
+        planar_known = 1;
+        h->planar_z = z ? z[0] : 0.0;
+        if (z) for (int i = 1; i < count; ++i) if (z[i] != z[0]) { planar_known = 0; break; }
     } else {
         for (int i = 0; i < count; ++i)
             if (idx[i] < 0 || idx[i] >= h->n) return h->fail(RMB_ERR_INVALID, "rmb_update_positions: node index out of range");
@@ -514,7 +545,13 @@ extern "C" int rmb_update_positions(rmb_handle *h, int32_t count, const int32_t 
     // well enough, and the re-sort (radix sort of all receivers) costs as much as the upload itself.
     constexpr int kReorderEvery = 8;
     const bool reorder = idx == nullptr && (h->dense_updates++ % kReorderEvery) == 0;
-    return refresh_geometry(h, reorder);
+    if (idx && h->planar && (z ? false : h->planar_z == 0.0)) planar_known = 1;     // sparse Position.set(x, y) on a z = 0 plane
+    const int rc = refresh_geometry(h, reorder, planar_known);
+    if (rc) return rc;
+    // the caller may reuse its arrays on return: wait for the upload (not for the kernels queued behind it)
+    if (!idx) RMB_CK(h, cudaEventSynchronize(h->ev_h2d));
+    else if (planar_known >= 0) RMB_CK(h, cudaStreamSynchronize(h->st));           // staged copies of idx / x / y / z
+    return RMB_OK;
 }
 
 extern "C" int rmb_update_radio(rmb_handle *h, int32_t count, const int32_t *idx, const double *txpower_dbm,
@@ -773,8 +810,8 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
         TxTiles tx = tx_tiles(h);
         const int mode = sweep_mode_for_exponent(h->cfg.pl_exponent);
         // default: 4 receivers per thread, 128 threads (the fastest variant at every shard size once the blocks are short)
-        const int variant = h->sweep_variant ? h->sweep_variant : 1;
         const int n_tx_bucket = n_tx / std::max(1, h->groups.ngroups);
+        const int variant = h->sweep_variant ? h->sweep_variant : sweep_auto_variant(mode, h->planar, h->n_work, n_tx_bucket);
         h->splits = sweep_splits(mode, h->planar, variant, h->n_work, n_tx_bucket,
                                  sweep_plan(mode, h->planar, variant, h->n_work, n_tx_bucket, h->forced_splits), h->taper, h->fine8);
         RMB_CK(h, h->far_part.ensure((size_t)h->splits.s2 * (size_t)std::max(h->n_work, 1)));
@@ -831,7 +868,11 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
             const size_t trace_blocks = (size_t)h->splits.rb_taper * h->splits.s1 +
                                         (size_t)(h->n_work / h->splits.block_rx - h->splits.rb_taper) * h->splits.s2;
             if (trace_path) { RMB_CK(h, h->trace.ensure(12 * trace_blocks + 12)); fuse.trace = h->trace.p; }
-            RMB_CK(h, launch_sweep(mode, h->planar, variant, h->n_work, h->splits, a, fuse, attempt == 0 && !kev, h->st));
+            // programmatic dependent launch behind the preparation kernel: worth ~3 us on a launch that is several waves
+            // deep, but a single-wave launch (16 channel groups on a 1/8 shard) ran 30 us LONGER with it (measured,
+            // tools/c5_shard_probe.py with RMB_PDL=0/1), so only deep launches take it
+            const bool deep = h->splits.s2 > h->splits.s1;
+            RMB_CK(h, launch_sweep(mode, h->planar, variant, h->n_work, h->splits, a, fuse, attempt == 0 && !kev && deep, h->st));
             if (trace_path) {
                 std::vector<unsigned long long> tr(12 * trace_blocks);
                 RMB_CK(h, cudaMemcpyAsync(tr.data(), h->trace.p, tr.size() * 8, cudaMemcpyDeviceToHost, h->st));

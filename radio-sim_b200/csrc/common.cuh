@@ -195,12 +195,13 @@ inline cudaError_t launch_grid_synced(const void *fn, dim3 grid, dim3 block, voi
 // resident as soon as every block of the kernel in front of it on the stream has executed griddepcontrol.launch_dependents
 // (or exited); the kernel itself must execute griddepcontrol.wait before it touches what its predecessor wrote.
 // RMB_NO_PDL=1 turns the attribute off (an experiment knob).
-inline bool use_pdl()
+inline int pdl_mode()          // RMB_PDL: 0 off, 1 sweep behind the preparation kernel only (default), 2 also finish behind the sweep
 {
     static int v = -1;
-    if (v < 0) { const char *e = getenv("RMB_NO_PDL"); v = (e && e[0] == '1') ? 0 : 1; }
-    return v == 1;
+    if (v < 0) { const char *e = getenv("RMB_PDL"); v = (e && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 1; }
+    return v;
 }
+inline bool use_pdl() { return pdl_mode() >= 1; }
 inline cudaError_t launch_grid_synced_ex(const void *fn, dim3 grid, dim3 block, void **args, size_t smem, bool overlap, cudaStream_t st)
 {
     cudaLaunchConfig_t cfg{};
@@ -208,7 +209,7 @@ inline cudaError_t launch_grid_synced_ex(const void *fn, dim3 grid, dim3 block, 
     cudaLaunchAttribute attr[2];
     int na = 0;
     if (use_cooperative_launch()) { attr[na].id = cudaLaunchAttributeCooperative; attr[na].val.cooperative = 1; ++na; }
-    if (overlap && use_pdl()) { attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization; attr[na].val.programmaticStreamSerializationAllowed = 1; ++na; }
+    if (overlap && pdl_mode() >= 2) { attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization; attr[na].val.programmaticStreamSerializationAllowed = 1; ++na; }
     cfg.attrs = attr; cfg.numAttrs = (unsigned)na;
     return cudaLaunchKernelExC(&cfg, fn, args);
 }

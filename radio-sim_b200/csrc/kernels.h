@@ -65,6 +65,7 @@ struct SweepArgs {
     int K;
 };
 int sweep_mode_for_exponent(double n);
+int sweep_auto_variant(int mode, bool planar, int n_work, int n_tx_bucket);     // variant for a tick of this shape (shallow launches: shorter rx blocks)
 // number of tx splits (grid.y) for a bucket of about n_tx_bucket transmissions; forced_splits > 0 overrides
 int sweep_plan(int mode, bool planar, int variant, int n_work, int n_tx_bucket, int forced_splits);
 // The sweep's fused epilogue (128-thread variants): the last tx-split block of an rx block resolves its receivers

@@ -73,7 +73,7 @@ __device__ __forceinline__ f32x2 accumulate2(f32x2 d2, f32x2 acc, float neg_h)
 constexpr int kStage = 1024;          // tx per shared-memory stage (SoA: c, -x', -y', -z', theta)
 
 template <int MODE, bool PLANAR, int R, int THREADS>
-__global__ void __launch_bounds__(THREADS, (THREADS == 128 && R == 4) ? 9 : 1)
+__global__ void __launch_bounds__(THREADS, (THREADS == 128 && R <= 4) ? 9 : 1)
 sweep_kernel(const float *__restrict__ fx, const float *__restrict__ fy, const float *__restrict__ fz,
              Groups groups, TxTiles tx, const float *__restrict__ theta, const float *__restrict__ theta_min_g,
              float neg_h, float *__restrict__ far_part, int *__restrict__ cnt, int *__restrict__ slots,
@@ -290,6 +290,7 @@ static SweepVariant variant_of(int variant)
     case 6:  return RMB_V(1, 32);
     case 7:  return RMB_V(2, 128);
     case 8:  return RMB_V(4, 256);
+    case 9:  return RMB_V(1, 128);
     default: return RMB_V(4, 128);
     }
 #undef RMB_V
@@ -314,6 +315,21 @@ static int variant_occupancy(const SweepVariant &v)
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, v.fn, v.threads, 0) != cudaSuccess || o < 1) { o = 1; cudaGetLastError(); }
     if (n < 64) { fn[n] = v.fn; occ[n] = o; ++n; }
     return o;
+}
+
+int sweep_plan(int mode, bool planar, int variant, int n_work, int n_tx_bucket, int forced_splits);
+// Which variant a tick takes when the caller did not force one: 4 receivers per thread (the fewest shared-memory loads
+// per pair) unless that launch would be shallow -- under ~3 waves of blocks the tick's time is the latency chain of the
+// fused resolve (one rx block = R passes of 128 receivers by its last finisher), not the arithmetic, and blocks of
+// 2 x 128 receivers halve it.  Measured (tools/c5_shard_probe.py, tools/shard_probe.py): 16 channels on a 1/8 shard
+// 135 -> 119 us, on one GPU 312 -> 308 us; C4 on a 1/8 shard (3.5 waves) 413 us with R = 4, 419 with R = 2.
+int sweep_auto_variant(int mode, bool planar, int n_work, int n_tx_bucket)
+{
+    const SweepVariant v4 = pick(mode, planar, 1);
+    const double slots = (double)device_sms() * variant_occupancy(v4);
+    const int s = sweep_plan(mode, planar, 1, n_work, n_tx_bucket, 0);
+    const double waves = (double)(n_work / (v4.R * v4.threads)) * s / slots;
+    return waves < 3.25 ? 7 : 1;
 }
 
 int sweep_mode_for_exponent(double n)

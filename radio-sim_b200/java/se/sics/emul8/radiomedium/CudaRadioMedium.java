@@ -9,7 +9,9 @@
  * prototype, and reference-edits.patch applies to the reference tree.  radio-sim_b200/simulator.py holds the
  * same adapter logic in Python, and that one runs against the GPU in tests/test_gpu_replay.py.
  *
- * Binding: Panama FFM (java.lang.foreign, JDK 22+), no JNI glue.
+ * Binding: Panama FFM (java.lang.foreign, JDK 22+), no JNI glue.  The adapter binds the rmb_group_* entry points: one
+ * or several GPUs behind the same calls (Options.devices; receivers in contiguous node-index blocks, one handle and
+ * one host worker thread per device inside the library), so a single JVM drives all GPUs of a box.
  *
  * Behaviour (each point is the reference's, file:line given):
  *  - transmit() only queues the packet.  flush() -- FIRST statement of Simulator.emulatorTimeStepDone, i.e.
@@ -72,7 +74,8 @@ public class CudaRadioMedium extends AbstractRadioMedium {
 
     /** Parameters of the medium (`configuration-set`, net/SimulatorJSONHandler.java:170-216); NaN = library default. */
     public static class Options {
-        public int device = 0;
+        public int[] devices = { 0 };            /* CUDA device ordinals; several = receivers sharded over them */
+        public int maxTxPerTick = 16384;         /* sizes the exchange buffers between the devices */
         public double successRatioTx = Double.NaN, successRatioRx = Double.NaN;       /* UDGMRadioMedium.java:17-18 */
         public double transmissionRange = Double.NaN;                                 /* UDGMRadioMedium.java:23 */
         public double constantRange = Double.NaN;                                     /* UDGMConstantLossRadioMedium.java:8 */
@@ -93,24 +96,26 @@ public class CudaRadioMedium extends AbstractRadioMedium {
     }
 
     private static final MethodHandle CONFIG_DEFAULT = fn("rmb_config_default", FunctionDescriptor.ofVoid(ADDRESS, JAVA_INT));
-    private static final MethodHandle CREATE = fn("rmb_create", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS));
-    private static final MethodHandle DESTROY = fn("rmb_destroy", FunctionDescriptor.of(JAVA_INT, ADDRESS));
-    private static final MethodHandle LAST_ERROR = fn("rmb_last_error", FunctionDescriptor.of(ADDRESS, ADDRESS));
-    private static final MethodHandle SET_NODES = fn("rmb_set_nodes", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT,
+    private static final MethodHandle GROUP_CREATE = fn("rmb_group_create", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT, ADDRESS, JAVA_INT, ADDRESS));
+    private static final MethodHandle GROUP_DESTROY = fn("rmb_group_destroy", FunctionDescriptor.of(JAVA_INT, ADDRESS));
+    private static final MethodHandle GROUP_LAST_ERROR = fn("rmb_group_last_error", FunctionDescriptor.of(ADDRESS, ADDRESS));
+    private static final MethodHandle GROUP_SHARD = fn("rmb_group_shard", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
+    private static final MethodHandle GROUP_SET_NODES = fn("rmb_group_set_nodes", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT,
             ADDRESS, ADDRESS, ADDRESS, ADDRESS, ADDRESS, ADDRESS, ADDRESS, ADDRESS, ADDRESS));
     private static final MethodHandle SET_MATRIX = fn("rmb_set_matrix", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT, ADDRESS));
-    private static final MethodHandle UPDATE_POSITIONS = fn("rmb_update_positions", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT,
+    private static final MethodHandle GROUP_UPDATE_POSITIONS = fn("rmb_group_update_positions", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT,
             ADDRESS, ADDRESS, ADDRESS, ADDRESS));
-    private static final MethodHandle UPDATE_RADIO = fn("rmb_update_radio", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT,
+    private static final MethodHandle GROUP_UPDATE_RADIO = fn("rmb_group_update_radio", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT,
             ADDRESS, ADDRESS, ADDRESS, ADDRESS, ADDRESS, ADDRESS));
-    private static final MethodHandle TICK = fn("rmb_tick", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT,
-            ADDRESS, ADDRESS, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS));
-    private static final MethodHandle NODE_INFO_F64 = fn("rmb_node_info_f64", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
+    private static final MethodHandle GROUP_TICK = fn("rmb_group_tick", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT,
+            ADDRESS, ADDRESS, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS, ADDRESS, ADDRESS));
+    private static final MethodHandle GROUP_NODE_INFO_F64 = fn("rmb_group_node_info_f64", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
 
     private final int model;
     private final Options options;
     private final Arena arena = Arena.ofShared();
-    private final MemorySegment handle;
+    private final MemorySegment handle;              /* rmb_group* */
+    private final int world;                         /* devices in the group */
     private final ArrayList<RadioPacket> pending = new ArrayList<>();
 
     /* the node table as last uploaded: array identity, index of every node, shadow copy of what the device holds */
@@ -139,7 +144,6 @@ public class CudaRadioMedium extends AbstractRadioMedium {
         try {
             MemorySegment cfg = arena.allocate(CFG_SIZE, 8);
             CONFIG_DEFAULT.invoke(cfg, model);
-            cfg.set(JAVA_INT, CFG_DEVICE, o.device);
             cfg.set(JAVA_INT, CFG_FLAGS, FLAG_F64_VALUES | FLAG_COMPACT);
             cfg.set(JAVA_INT, CFG_HALF_DUPLEX, o.halfDuplex ? 1 : 0);
             setIfGiven(cfg, CFG_SUCCESS_RATIO_TX, o.successRatioTx);
@@ -152,10 +156,13 @@ public class CudaRadioMedium extends AbstractRadioMedium {
             setIfGiven(cfg, CFG_SENSITIVITY_DBM, o.sensitivityDbm);
             setIfGiven(cfg, CFG_SINR_THRESHOLD_DB, o.sinrThresholdDb);
             cfg.set(JAVA_DOUBLE, CFG_NOISE_FLOOR_DBM, baseRSSI);                      /* AbstractRadioMedium.java:38 */
+            world = o.devices.length;
+            MemorySegment devs = arena.allocate(JAVA_INT, world);
+            MemorySegment.copy(o.devices, 0, devs, JAVA_INT, 0, world);
             MemorySegment out = arena.allocate(ADDRESS);
-            int rc = (int) CREATE.invoke(cfg, out);
+            int rc = (int) GROUP_CREATE.invoke(cfg, world, devs, o.maxTxPerTick, out);
             if (rc != RMB_OK) {
-                throw new IllegalStateException("rmb_create: " + errorText(MemorySegment.NULL));     /* no CPU fallback */
+                throw new IllegalStateException("rmb_group_create: " + errorText(MemorySegment.NULL));     /* no CPU fallback */
             }
             handle = out.get(ADDRESS, 0);
         } catch (RuntimeException e) {
@@ -172,7 +179,7 @@ public class CudaRadioMedium extends AbstractRadioMedium {
     }
 
     private static String errorText(MemorySegment h) throws Throwable {
-        MemorySegment msg = (MemorySegment) LAST_ERROR.invoke(h);
+        MemorySegment msg = (MemorySegment) GROUP_LAST_ERROR.invoke(h);
         return msg.reinterpret(512).getString(0);
     }
 
@@ -195,7 +202,10 @@ public class CudaRadioMedium extends AbstractRadioMedium {
             for (int i = 0; i < n; i++) {
                 MemorySegment.copy(m[i], 0, flat, JAVA_DOUBLE, (long) i * n * 8, n);
             }
-            check((int) SET_MATRIX.invoke(handle, n, flat), "rmb_set_matrix");
+            /* the matrix medium lives on ONE device (rmb_create refuses RMB_MODEL_N2N with n_shards > 1) */
+            MemorySegment shard = a.allocate(ADDRESS);
+            check((int) GROUP_SHARD.invoke(handle, 0, shard, MemorySegment.NULL, MemorySegment.NULL), "rmb_group_shard");
+            check((int) SET_MATRIX.invoke(shard.get(ADDRESS, 0), n, flat), "rmb_set_matrix");
         } catch (RuntimeException e) {
             throw e;
         } catch (Throwable t) {
@@ -273,13 +283,15 @@ public class CudaRadioMedium extends AbstractRadioMedium {
             MemorySegment.copy(src, 0, mSrc, JAVA_INT, 0, t);
             MemorySegment.copy(power, 0, mPower, JAVA_DOUBLE, 0, t);
             MemorySegment.copy(chan, 0, mChan, JAVA_INT, 0, t);
-            MemorySegment res = tick.allocate(RES_SIZE, 8);
+            MemorySegment res = tick.allocate(RES_SIZE * world, 8);                 /* rmb_result[world] */
+            MemorySegment slotsOut = tick.allocate(JAVA_INT), packetOf = tick.allocate(JAVA_INT, (long) world * Math.max(options.maxTxPerTick, t));
 
-            /* deterministic tick: one call.  With draws: the first call (no uniforms; missing draws read as 0.0 =
-             * "success", which maximises the number of later draws) tells how many uniforms the tick can consume at
-             * most; a copy of the simulator's generator supplies that many, and the real generator is advanced by
-             * the number actually consumed -- the sequence the reference's media would have left behind. */
-            int rc = (int) TICK.invoke(handle, t, mSrc, mPower, mChan, MemorySegment.NULL, 0L, res);
+            /* deterministic tick: one call.  With draws (one device only: the draw order is global): the first call (no
+             * uniforms; missing draws read as 0.0 = "success", which maximises the number of later draws) tells how
+             * many uniforms the tick can consume at most; a copy of the simulator's generator supplies that many, and
+             * the real generator is advanced by the number actually consumed -- the sequence the reference's media
+             * would have left behind. */
+            int rc = (int) GROUP_TICK.invoke(handle, t, mSrc, mPower, mChan, MemorySegment.NULL, 0L, res, slotsOut, packetOf);
             if (rc == RMB_ERR_UNIFORMS) {
                 long bound = res.get(JAVA_LONG, RES_N_UNIFORMS_USED);
                 Random real = simulator.getRandom();
@@ -288,28 +300,45 @@ public class CudaRadioMedium extends AbstractRadioMedium {
                 for (long k = 0; k < bound; k++) {
                     u.setAtIndex(JAVA_DOUBLE, k, probe.nextDouble());
                 }
-                rc = (int) TICK.invoke(handle, t, mSrc, mPower, mChan, u, bound, res);
-                check(rc, "rmb_tick");
+                rc = (int) GROUP_TICK.invoke(handle, t, mSrc, mPower, mChan, u, bound, res, slotsOut, packetOf);
+                check(rc, "rmb_group_tick");
                 long used = res.get(JAVA_LONG, RES_N_UNIFORMS_USED);
                 for (long k = 0; k < used; k++) {
                     real.nextDouble();
                 }
             } else {
-                check(rc, "rmb_tick");
+                check(rc, "rmb_group_tick");
             }
 
-            int n = (int) res.get(JAVA_LONG, RES_N_PAIRS);
-            int[] txFirst = new int[t + 1], rx = new int[n];
-            double[] rssi = new double[n];
-            byte[] outcome = new byte[n];
-            MemorySegment.copy(res.get(ADDRESS, RES_TX_FIRST).reinterpret(4L * (t + 1)), JAVA_INT, 0, txFirst, 0, t + 1);
-            if (n > 0) {
-                MemorySegment.copy(res.get(ADDRESS, RES_RX).reinterpret(4L * n), JAVA_INT, 0, rx, 0, n);
-                MemorySegment.copy(res.get(ADDRESS, RES_RSSI_DBM_F64).reinterpret(8L * n), JAVA_DOUBLE, 0, rssi, 0, n);
-                MemorySegment.copy(res.get(ADDRESS, RES_OUTCOME).reinterpret(n), JAVA_BYTE, 0, outcome, 0, n);
+            /* packet k sits at gathered record position position[k] of every shard's lists */
+            int slots = slotsOut.get(JAVA_INT, 0);
+            int positions = world * slots;
+            int[] position = new int[t];
+            for (int p = 0; p < positions; p++) {
+                int k = packetOf.getAtIndex(JAVA_INT, p);
+                if (k >= 0) {
+                    position[k] = p;
+                }
+            }
+            int[][] txFirst = new int[world][], rx = new int[world][];
+            double[][] rssi = new double[world][];
+            byte[][] outcome = new byte[world][];
+            for (int s = 0; s < world; s++) {
+                MemorySegment r = res.asSlice(RES_SIZE * s, RES_SIZE);
+                int n = (int) r.get(JAVA_LONG, RES_N_PAIRS);
+                txFirst[s] = new int[positions + 1];
+                rx[s] = new int[n];
+                rssi[s] = new double[n];
+                outcome[s] = new byte[n];
+                MemorySegment.copy(r.get(ADDRESS, RES_TX_FIRST).reinterpret(4L * (positions + 1)), JAVA_INT, 0, txFirst[s], 0, positions + 1);
+                if (n > 0) {
+                    MemorySegment.copy(r.get(ADDRESS, RES_RX).reinterpret(4L * n), JAVA_INT, 0, rx[s], 0, n);
+                    MemorySegment.copy(r.get(ADDRESS, RES_RSSI_DBM_F64).reinterpret(8L * n), JAVA_DOUBLE, 0, rssi[s], 0, n);
+                    MemorySegment.copy(r.get(ADDRESS, RES_OUTCOME).reinterpret(n), JAVA_BYTE, 0, outcome[s], 0, n);
+                }
             }
             nodeInfoValid = false;
-            deliver(packets, t, txFirst, nodes, rx, rssi, outcome);
+            deliver(packets, t, position, txFirst, nodes, rx, rssi, outcome);
         } catch (RuntimeException e) {
             throw e;
         } catch (Throwable e) {
@@ -319,21 +348,27 @@ public class CudaRadioMedium extends AbstractRadioMedium {
         }
     }
 
-    /* the reference's call sequence, packet by packet (UDGMRadioMedium.java:97-114) */
-    private void deliver(RadioPacket[] packets, int t, int[] txFirst, Node[] nodes, int[] rx, double[] rssi, byte[] outcome) {
+    /* the reference's call sequence, packet by packet (UDGMRadioMedium.java:97-114); the rows of packet k are rows
+     * txFirst[s][position[k]] .. txFirst[s][position[k] + 1] of shard s, shards in node order */
+    private void deliver(RadioPacket[] packets, int t, int[] position, int[][] txFirst, Node[] nodes, int[][] rx, double[][] rssi,
+            byte[][] outcome) {
         if (model == MODEL_UDGM_CONSTANT) {
             for (int k = 0; k < t; k++) {                               /* UDGMConstantLossRadioMedium.java:30-32 */
-                for (int i = txFirst[k]; i < txFirst[k + 1]; i++) {
-                    simulator.deliverRadioPacket(packets[k], nodes[rx[i]], rssi[i]);
+                for (int s = 0; s < world; s++) {
+                    for (int i = txFirst[s][position[k]]; i < txFirst[s][position[k] + 1]; i++) {
+                        simulator.deliverRadioPacket(packets[k], nodes[rx[s][i]], rssi[s][i]);
+                    }
                 }
             }
         } else if (options.bulkEvents) {
-            simulator.generateReceptionEventsBulk(packets, t, txFirst, nodes, rx, rssi, outcome);
+            simulator.generateReceptionEventsBulk(packets, t, position, world, txFirst, nodes, rx, rssi, outcome);
         } else {
             for (int k = 0; k < t; k++) {
                 simulator.generateTransmissionEvents(packets[k]);
-                for (int i = txFirst[k]; i < txFirst[k + 1]; i++) {
-                    simulator.generateReceptionEvents(packets[k], nodes[rx[i]], rssi[i], outcome[i] == DELIVERED);
+                for (int s = 0; s < world; s++) {
+                    for (int i = txFirst[s][position[k]]; i < txFirst[s][position[k] + 1]; i++) {
+                        simulator.generateReceptionEvents(packets[k], nodes[rx[s][i]], rssi[s][i], outcome[s][i] == DELIVERED);
+                    }
                 }
             }
         }
@@ -350,7 +385,7 @@ public class CudaRadioMedium extends AbstractRadioMedium {
         }
     }
 
-    /* Node[] (objects) -> the SoA arrays of rmb_set_nodes; also the shadow copy and the node -> index map */
+    /* Node[] (objects) -> the SoA arrays of rmb_group_set_nodes; also the shadow copy and the node -> index map */
     private void upload(Node[] nodes) throws Throwable {
         int n = nodes.length;
         sx = new double[n]; sy = new double[n]; sz = new double[n];
@@ -375,7 +410,7 @@ public class CudaRadioMedium extends AbstractRadioMedium {
             MemorySegment.copy(sRxp, 0, rxp, JAVA_DOUBLE, 0, n); MemorySegment.copy(sTxp, 0, txp, JAVA_DOUBLE, 0, n);
             MemorySegment.copy(sChannel, 0, ch, JAVA_INT, 0, n); MemorySegment.copy(id, 0, ids, JAVA_INT, 0, n);
             MemorySegment.copy(sEnabled, 0, en, JAVA_BYTE, 0, n);
-            check((int) SET_NODES.invoke(handle, n, x, y, z, pw, ch, en, rxp, txp, ids), "rmb_set_nodes");
+            check((int) GROUP_SET_NODES.invoke(handle, n, x, y, z, pw, ch, en, rxp, txp, ids), "rmb_group_set_nodes");
         }
         registered = nodes;
         nodeInfoValid = false;
@@ -395,7 +430,7 @@ public class CudaRadioMedium extends AbstractRadioMedium {
         return moved || retuned;
     }
 
-    /* in-place changes of registered nodes -> rmb_update_positions / rmb_update_radio for exactly those indices */
+    /* in-place changes of registered nodes -> rmb_group_update_positions / _radio for exactly those indices */
     private void pushChanges(Node[] nodes, Arena tick) throws Throwable {
         if (options.scanNodes) {
             for (int i = 0; i < nodes.length; i++) {
@@ -421,8 +456,8 @@ public class CudaRadioMedium extends AbstractRadioMedium {
             ch.setAtIndex(JAVA_INT, k, sChannel[i]); en.set(JAVA_BYTE, k, sEnabled[i]);
         }
         nDirty = 0;
-        check((int) UPDATE_POSITIONS.invoke(handle, c, idx, x, y, z), "rmb_update_positions");
-        check((int) UPDATE_RADIO.invoke(handle, c, idx, pw, ch, en, rxp, txp), "rmb_update_radio");
+        check((int) GROUP_UPDATE_POSITIONS.invoke(handle, c, idx, x, y, z), "rmb_group_update_positions");
+        check((int) GROUP_UPDATE_RADIO.invoke(handle, c, idx, pw, ch, en, rxp, txp), "rmb_group_update_radio");
         nodeInfoValid = false;
     }
 
@@ -470,7 +505,7 @@ public class CudaRadioMedium extends AbstractRadioMedium {
         }
         try (Arena a = Arena.ofConfined()) {
             MemorySegment power = a.allocate(JAVA_DOUBLE, n), heard = a.allocate(JAVA_BYTE, n);
-            int rc = (int) NODE_INFO_F64.invoke(handle, power, heard);
+            int rc = (int) GROUP_NODE_INFO_F64.invoke(handle, power, heard);
             if (rc != RMB_OK) {
                 return false;
             }
@@ -487,7 +522,7 @@ public class CudaRadioMedium extends AbstractRadioMedium {
 
     public synchronized void close() {
         try {
-            DESTROY.invoke(handle);
+            GROUP_DESTROY.invoke(handle);
         } catch (Throwable t) {
             throw new IllegalStateException(t);
         } finally {

@@ -298,3 +298,122 @@ class Medium:
 
     def set_tuning(self, sweep_variant=0, near_slots=0):
         self._ck(self._lib.rmb_set_tuning(self._h, sweep_variant, near_slots))
+
+
+class GroupResult:
+    """One tick of a `Group`: the shards' lists (`parts`, rank order) and the merged view in the reference's call
+    order -- packets in arrival order, receivers in node-array order."""
+
+    def __init__(self, parts, slots, packet_of):
+        self.parts, self.slots, self.packet_of = parts, slots, packet_of
+        self.n_pairs = sum(p.n_pairs for p in parts)
+        self.n_decisions = sum(p.n_decisions for p in parts)
+        self.n_delivered = sum(p.n_delivered for p in parts)
+
+    def merged(self):
+        """-> dict(tx, rx, outcome, rssi_dbm): tx = index into the caller's packet list.  (The adapter does not need
+        this copy: it walks the shards per packet through tx_first.)"""
+        cols = {k: np.concatenate([np.asarray(getattr(p, k)) for p in self.parts]) for k in ("rx", "outcome", "rssi_dbm")}
+        pos = np.concatenate([p.tx_column() for p in self.parts])
+        tx = self.packet_of[pos] if pos.size else pos.astype(np.int32)
+        order = np.lexsort((cols["rx"], tx))
+        out = {k: v[order] for k, v in cols.items()}
+        out["tx"] = tx[order].astype(np.int32)
+        return out
+
+
+class Group:
+    """rmb_group_*: several GPUs behind one object (one process, one worker thread per device inside the library)."""
+
+    def __init__(self, model="sinr", devices=(0,), max_tx_per_tick=16384, f64_values=False, compact=False, **params):
+        self._lib = A.load()
+        cfg = A.Config()
+        self._lib.rmb_config_default(C.byref(cfg), Medium.MODELS[model] if isinstance(model, str) else int(model))
+        if f64_values:
+            cfg.flags |= A.FLAG_F64_VALUES
+        if compact:
+            cfg.flags |= A.FLAG_COMPACT
+        for k, v in params.items():
+            if not hasattr(cfg, k):
+                raise AttributeError(f"unknown medium parameter {k}")
+            setattr(cfg, k, v)
+        self._f64, self.world, self.max_tx = bool(f64_values), len(devices), int(max_tx_per_tick)
+        dv = np.asarray(devices, dtype=np.int32)
+        self._g = C.c_void_p()
+        rc = self._lib.rmb_group_create(C.byref(cfg), self.world, _ptr(dv, C.c_int32), self.max_tx, C.byref(self._g))
+        if rc != A.OK:
+            self._g = None
+            raise MediumError(rc, self._lib.rmb_group_last_error(None).decode())
+        self.n = 0
+
+    def close(self):
+        if getattr(self, "_g", None):
+            self._lib.rmb_group_destroy(self._g)
+            self._g = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc != A.OK:
+            raise MediumError(rc, self._lib.rmb_group_last_error(self._g).decode())
+
+    def set_nodes(self, x, y, z=None, txpower_dbm=None, channel=None, enabled=None, rxprob=None, txprob=None, id_int=None):
+        x = _arr(x, np.float64)
+        n = x.shape[0]
+        y, z = _arr(y, np.float64, n), _arr(z, np.float64, n)
+        txpower_dbm, rxprob, txprob = _arr(txpower_dbm, np.float64, n), _arr(rxprob, np.float64, n), _arr(txprob, np.float64, n)
+        channel, id_int, enabled = _arr(channel, np.int32, n), _arr(id_int, np.int32, n), _arr(enabled, np.uint8, n)
+        self._ck(self._lib.rmb_group_set_nodes(self._g, n, _ptr(x, C.c_double), _ptr(y, C.c_double), _ptr(z, C.c_double),
+                                               _ptr(txpower_dbm, C.c_double), _ptr(channel, C.c_int32), _ptr(enabled, C.c_uint8),
+                                               _ptr(rxprob, C.c_double), _ptr(txprob, C.c_double), _ptr(id_int, C.c_int32)))
+        self.n = n
+
+    def update_positions(self, x, y, z=None, idx=None):
+        x = _arr(x, np.float64)
+        c = x.shape[0]
+        y, z, idx = _arr(y, np.float64, c), _arr(z, np.float64, c), _arr(idx, np.int32, c)
+        self._ck(self._lib.rmb_group_update_positions(self._g, c, _ptr(idx, C.c_int32), _ptr(x, C.c_double), _ptr(y, C.c_double),
+                                                      _ptr(z, C.c_double)))
+
+    def update_radio(self, idx, txpower_dbm=None, channel=None, enabled=None, rxprob=None, txprob=None):
+        idx = _arr(idx, np.int32)
+        c = idx.shape[0]
+        txpower_dbm, rxprob, txprob = _arr(txpower_dbm, np.float64, c), _arr(rxprob, np.float64, c), _arr(txprob, np.float64, c)
+        channel, enabled = _arr(channel, np.int32, c), _arr(enabled, np.uint8, c)
+        self._ck(self._lib.rmb_group_update_radio(self._g, c, _ptr(idx, C.c_int32), _ptr(txpower_dbm, C.c_double), _ptr(channel, C.c_int32),
+                                                  _ptr(enabled, C.c_uint8), _ptr(rxprob, C.c_double), _ptr(txprob, C.c_double)))
+
+    def tick(self, src, power_dbm=None, channel=None, uniforms=None, copy=True, allow_short_uniforms=False):
+        src = _arr(src, np.int32)
+        t = src.shape[0]
+        power_dbm, channel = _arr(power_dbm, np.float64, t), _arr(channel, np.int32, t)
+        uniforms = _arr(uniforms, np.float64)
+        res = (A.Result * self.world)()
+        slots = C.c_int32(0)
+        packet_of = np.full(self.world * max(self.max_tx, t, 1), -1, dtype=np.int32)
+        rc = self._lib.rmb_group_tick(self._g, t, _ptr(src, C.c_int32), _ptr(power_dbm, C.c_double), _ptr(channel, C.c_int32),
+                                      _ptr(uniforms, C.c_double), 0 if uniforms is None else uniforms.shape[0],
+                                      res, C.byref(slots), _ptr(packet_of, C.c_int32))
+        if not (allow_short_uniforms and rc == A.ERR_UNIFORMS):
+            self._ck(rc)
+        parts = [TickResult(res[r], self._f64, copy) for r in range(self.world)]
+        out = GroupResult(parts, slots.value, packet_of[:self.world * slots.value])
+        out.status = rc
+        out.n_uniforms_used = sum(p.n_uniforms_used for p in parts)
+        return out
+
+    def node_info_f64(self):
+        rssi = np.zeros(max(self.n, 1), dtype=np.float64)
+        recv = np.zeros(max(self.n, 1), dtype=np.uint8)
+        self._ck(self._lib.rmb_group_node_info_f64(self._g, _ptr(rssi, C.c_double), _ptr(recv, C.c_uint8)))
+        return rssi[:self.n], recv[:self.n]

@@ -13,7 +13,7 @@ import heapq
 import numpy as np
 
 from .javarandom import JavaRandom
-from .medium import Medium
+from .medium import Group
 
 LISTENING, TRANSMITTING, RECEIVING, DISABLED = 0, 1, 2, 3          # Transciever.java:7-10
 
@@ -144,11 +144,13 @@ class CudaRadioMedium(AbstractRadioMedium):
     consumes host-supplied uniforms and reports how many; a look-ahead of the generator supplies them and the
     generator is then advanced by exactly n_uniforms_used (`uniforms=` overrides the source for tests)."""
 
-    def __init__(self, model="udgm", uniforms=None, device=0, rssi_in_band=False, scan_nodes=True, bulk_events=True, **params):
+    def __init__(self, model="udgm", uniforms=None, devices=(0,), max_tx_per_tick=16384, rssi_in_band=False, scan_nodes=True,
+                 bulk_events=True, **params):
         super().__init__()
         self.model = model
-        self.medium = Medium(model, device=device, f64_values=True, compact=True, **params)
-        self.base_rssi = float(self.medium.cfg.noise_floor_dbm)
+        # rmb_group_*: one or several GPUs behind the same calls (receivers in contiguous node blocks, one handle each)
+        self.medium = Group(model, devices=tuple(devices), max_tx_per_tick=max_tx_per_tick, f64_values=True, compact=True, **params)
+        self.base_rssi = float(params.get("noise_floor_dbm", self.base_rssi))
         self.pending = []
         self.uniforms = uniforms           # optional JavaRandom-like object (peek_doubles / skip_doubles) instead of simulator.get_random()
         self.rssi_in_band, self.scan_nodes, self.bulk_events = rssi_in_band, scan_nodes, bulk_events
@@ -244,25 +246,34 @@ class CudaRadioMedium(AbstractRadioMedium):
         # deterministic tick: one call.  With draws: the first call (no uniforms; a missing draw reads as 0.0 = success,
         # which maximises the number of later draws) tells how many uniforms the tick can consume at most; the
         # generator's look-ahead supplies them and the generator is advanced by the number actually consumed.
-        r = self.medium.tick(src, power, channel, allow_short_uniforms=True)
+        r = self.medium.tick(src, power, channel, allow_short_uniforms=True, copy=False)
         if r.status != 0:
             rnd = self.uniforms if self.uniforms is not None else self.simulator.get_random()
-            r = self.medium.tick(src, power, channel, uniforms=rnd.peek_doubles(r.n_uniforms_used))
+            r = self.medium.tick(src, power, channel, uniforms=rnd.peek_doubles(r.n_uniforms_used), copy=False)
             rnd.skip_doubles(r.n_uniforms_used)
         self.ticks += 1
         self._node_info = None
         sim = self.simulator
+        # packet t sits at gathered record position position[t] of every shard's lists; its rows in the reference's
+        # order are shard 0's rows of that position, then shard 1's, ... (shards own increasing node blocks)
+        position = np.empty(len(keep), dtype=np.int64)
+        filled = np.flatnonzero(r.packet_of >= 0)
+        position[r.packet_of[filled]] = filled
+        tx_first = [p.tx_first for p in r.parts]
+        rx, rssi, outcome = [p.rx for p in r.parts], [p.rssi_dbm_f64 for p in r.parts], [p.outcome for p in r.parts]
         if self.model == "udgm-constant":
             for t, p in enumerate(keep):                           # UDGMConstantLossRadioMedium.java:30-32
-                for i in range(r.tx_first[t], r.tx_first[t + 1]):
-                    sim.deliver_radio_packet(p, nodes[r.rx[i]], float(r.rssi_dbm_f64[i]))
+                for s in range(len(r.parts)):
+                    for i in range(tx_first[s][position[t]], tx_first[s][position[t] + 1]):
+                        sim.deliver_radio_packet(p, nodes[rx[s][i]], float(rssi[s][i]))
         elif self.bulk_events:
-            sim.generate_reception_events_bulk(keep, len(keep), r.tx_first, nodes, r.rx, r.rssi_dbm_f64, r.outcome)
+            sim.generate_reception_events_bulk(keep, len(keep), position, len(r.parts), tx_first, nodes, rx, rssi, outcome)
         else:
             for t, p in enumerate(keep):
                 sim.generate_transmission_events(p)
-                for i in range(r.tx_first[t], r.tx_first[t + 1]):
-                    sim.generate_reception_events(p, nodes[r.rx[i]], float(r.rssi_dbm_f64[i]), r.outcome[i] == 2)
+                for s in range(len(r.parts)):
+                    for i in range(tx_first[s][position[t]], tx_first[s][position[t] + 1]):
+                        sim.generate_reception_events(p, nodes[rx[s][i]], float(rssi[s][i]), outcome[s][i] == 2)
         return int(r.n_pairs)
 
     # -- node-info from the device buffers (8(f)2) -----------------------------------------------------------------------
@@ -287,8 +298,8 @@ class CudaRadioMedium(AbstractRadioMedium):
         return None if info is None else info[0]
 
     def node_info(self):
-        """Total in-band power and 'heard something' per node for the last tick (rmb_node_info)."""
-        return self.medium.node_info()
+        """Total in-band power and 'heard something' per node for the last tick (rmb_group_node_info_f64)."""
+        return self.medium.node_info_f64()
 
 
 class Simulator:
@@ -367,29 +378,31 @@ class Simulator:
                 self.deliver_radio_packet(packet, destination, rssi)
         self._add_event(t0 + packet.get_packet_air_time(), end)
 
-    def generate_reception_events_bulk(self, packets, n_packets, tx_first, nodes, rx, rssi, outcome):
-        """reference-edits.patch `Simulator.generateReceptionEventsBulk` + events/BulkReceptionEvent.java: per packet the
-        two transmission events, then ONE start and ONE end event covering rows tx_first[t] .. tx_first[t+1]."""
+    def generate_reception_events_bulk(self, packets, n_packets, position, n_shards, tx_first, nodes, rx, rssi, outcome):
+        """reference-edits.patch `Simulator.generateReceptionEventsBulk` + events/BulkReceptionEvent.java: per packet, in
+        arrival order, the two transmission events, then per shard ONE start and ONE end event covering the packet's
+        rows tx_first[s][position[t]] .. tx_first[s][position[t] + 1] of that shard's lists (shards in node order)."""
         for t in range(n_packets):
             packet = packets[t]
             self.generate_transmission_events(packet)
-            lo, hi = int(tx_first[t]), int(tx_first[t + 1])
-            if hi <= lo:
-                continue
             t0 = max(packet.time, self.current_time)
+            for s in range(n_shards):
+                lo, hi = int(tx_first[s][position[t]]), int(tx_first[s][position[t] + 1])
+                if hi <= lo:
+                    continue
 
-            def start(packet=packet, lo=lo, hi=hi):
-                for i in range(lo, hi):
-                    nodes[rx[i]].radio.set_receiving(packet, float(rssi[i]))
+                def start(packet=packet, lo=lo, hi=hi, rx=rx[s], rssi=rssi[s]):
+                    for i in range(lo, hi):
+                        nodes[rx[i]].radio.set_receiving(packet, float(rssi[i]))
 
-            def end(packet=packet, lo=lo, hi=hi):
-                for i in range(lo, hi):
-                    dest = nodes[rx[i]]
-                    dest.radio.clear_receiving()
-                    if outcome[i] == 2:
-                        self.deliver_radio_packet(packet, dest, float(rssi[i]))
-            self._add_event(t0, start)
-            self._add_event(t0 + packet.get_packet_air_time(), end)
+                def end(packet=packet, lo=lo, hi=hi, rx=rx[s], rssi=rssi[s], outcome=outcome[s]):
+                    for i in range(lo, hi):
+                        dest = nodes[rx[i]]
+                        dest.radio.clear_receiving()
+                        if outcome[i] == 2:
+                            self.deliver_radio_packet(packet, dest, float(rssi[i]))
+                self._add_event(t0, start)
+                self._add_event(t0 + packet.get_packet_air_time(), end)
 
     def generate_transmission_events(self, packet):
         t0 = max(packet.time, self.current_time)                   # Simulator.java:339-342

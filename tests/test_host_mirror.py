@@ -189,7 +189,12 @@ def test_bulk_event_hand_off_equals_one_event_pair_per_heard_pair():
         rssi, outcome = [-1.0, -2.0, -3.0, -4.0, -5.0], [2, 1, 2, 2, 2]
         nl = sim.get_nodes()
         if bulk:
-            sim.generate_reception_events_bulk(packets, 3, tx_first, nl, rx, rssi, outcome)
+            # the same rows as two shards' lists: nodes 0-2 on the first shard, 3-5 on the second; position == packet
+            first = [[0, 2, 2, 4], [0, 1, 1, 1]]
+            rxs = [[1, 2, 0, 2], [4]]
+            rss = [[-1.0, -2.0, -4.0, -5.0], [-3.0]]
+            outs = [[2, 1, 2, 2], [2]]
+            sim.generate_reception_events_bulk(packets, 3, [0, 1, 2], 2, first, nl, rxs, rss, outs)
         else:
             for t, p in enumerate(packets):
                 sim.generate_transmission_events(p)
@@ -225,7 +230,7 @@ class _FakeMedium:
     def update_radio(self, idx=None, **kw):
         self.calls.append(("update_radio", idx.tolist(), kw["channel"].tolist()))
 
-    def tick(self, src, power, channel, uniforms=None, allow_short_uniforms=False):
+    def tick(self, src, power, channel, uniforms=None, allow_short_uniforms=False, copy=True):
         import types
         t = len(src)
         rx = np.concatenate([np.delete(np.arange(self.n), s) for s in src]).astype(np.int32)
@@ -234,8 +239,9 @@ class _FakeMedium:
         short = need and (uniforms is None or len(uniforms) < need)
         self.calls.append(("tick", src.tolist(), None if uniforms is None else len(uniforms)))
         used = need if short else need // 2                        # "consumes" half of the upper bound
-        return types.SimpleNamespace(status=-5 if short else 0, n_uniforms_used=used, n_pairs=len(rx), rx=rx, tx_first=first,
-                                     rssi_dbm_f64=np.repeat(power, self.n - 1), outcome=np.full(len(rx), 2, np.uint8))
+        part = types.SimpleNamespace(rx=rx, tx_first=first, rssi_dbm_f64=np.repeat(power, self.n - 1), outcome=np.full(len(rx), 2, np.uint8))
+        return types.SimpleNamespace(status=-5 if short else 0, n_uniforms_used=used, n_pairs=len(rx), parts=[part],
+                                     packet_of=np.arange(t, dtype=np.int32))
 
     def node_info_f64(self):
         return np.full(self.n, -90.0), np.zeros(self.n, np.uint8)
@@ -247,7 +253,7 @@ class _FakeMedium:
 def test_adapter_host_logic_without_a_gpu(monkeypatch):
     from radio_sim_b200 import simulator as S
     from radio_sim_b200.javarandom import JavaRandom
-    monkeypatch.setattr(S, "Medium", _FakeMedium)
+    monkeypatch.setattr(S, "Group", _FakeMedium)
     sim = Simulator(JavaRandom(5))
     emu = jsonproto.JSONClientConnection("emu")
     handler = jsonproto.SimulatorJSONHandler(sim, lambda o, p: S.CudaRadioMedium("udgm", rssi_in_band=True))

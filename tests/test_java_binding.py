@@ -213,7 +213,7 @@ def test_adapter_calls_only_what_the_reference_declares():
     must = {("RadioPacket", "getTransmitPower", 0), ("RadioPacket", "getWirelessChannel", 0), ("RadioPacket", "getSource", 0),
             ("Transciever", "getTransmitPower", 0), ("Transciever", "getRxProbability", 0), ("Transciever", "getTxProbability", 0),
             ("Transciever", "isEnabled", 0), ("Node", "getPosition", 0), ("Node", "getRadio", 0), ("Node", "getIdAsInteger", 0),
-            ("Simulator", "getNodes", 0), ("Simulator", "getRandom", 0), ("Simulator", "generateReceptionEventsBulk", 7),
+            ("Simulator", "getNodes", 0), ("Simulator", "getRandom", 0), ("Simulator", "generateReceptionEventsBulk", 9),
             ("Simulator", "generateReceptionEvents", 4), ("Simulator", "generateTransmissionEvents", 1),
             ("Simulator", "deliverRadioPacket", 3)}
     assert must <= set(found), must - set(found)
