@@ -90,7 +90,7 @@ struct rmb_handle {
     // per tick: tx side
     DevBuf<int> pk_src, pk_channel; DevBuf<double> pk_power; PinBuf<char> pk_stage;
     DevBuf<rmb_tx_record> rec;
-    DevBuf<float4> txf, stg_f; DevBuf<float> theta, theta_min_g, stg_theta; DevBuf<int> stg_gid; DevBuf<int> arrival, goff, gcount;
+    DevBuf<float> txf; DevBuf<float4> stg_f; DevBuf<float> theta, theta_min_g, stg_theta; DevBuf<int> stg_gid; DevBuf<int> arrival, goff, gcount;
     DevBuf<int> blk_cnt, blk_thmin; DevBuf<unsigned> bar; unsigned bar_count = 0, bar2_count = 0; DevBuf<double> recheck_part; DevBuf<int> rx_done;   // fused tx preparation (cooperative launch)
     DevBuf<double> uniforms;
 
@@ -174,7 +174,10 @@ WorkArrays work_arrays(rmb_handle *h)
 }
 TxTiles tx_tiles(rmb_handle *h)
 {
-    TxTiles t; t.f = h->txf.p; t.arrival = h->arrival.p; t.goff = h->goff.p; t.gcount = h->gcount.p;
+    TxTiles t;
+    const size_t q = h->txf.cap / 4;                 // four SoA rows in one allocation, each 256-byte aligned
+    t.c = h->txf.p; t.nx = h->txf.p + q; t.ny = h->txf.p + 2 * q; t.nz = h->txf.p + 3 * q;
+    t.arrival = h->arrival.p; t.goff = h->goff.p; t.gcount = h->gcount.p;
     return t;
 }
 SlotArrays slot_arrays(rmb_handle *h)
@@ -805,7 +808,7 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
     bool final_sync = true;           // the SINR path usually synchronises once, inside its attempt loop
     if (h->cfg.model == RMB_MODEL_SINR) {
         const size_t tcap = (size_t)n_tx + (size_t)(h->groups.ngroups + 1) * kTile;
-        RMB_CK(h, h->txf.ensure(tcap)); RMB_CK(h, h->theta.ensure(tcap)); RMB_CK(h, h->arrival.ensure(tcap));
+        RMB_CK(h, h->txf.ensure(4 * ((tcap + 63) / 64 * 64))); RMB_CK(h, h->theta.ensure(tcap)); RMB_CK(h, h->arrival.ensure(tcap));
         RMB_CK(h, h->tx_cnt.ensure((size_t)n_tx + 1));
         TxTiles tx = tx_tiles(h);
         const int mode = sweep_mode_for_exponent(h->cfg.pl_exponent);

@@ -32,7 +32,9 @@ struct Geom {
 
 // per-tick tx side in sweep order (bucketed by channel group, arrival order inside a bucket)
 struct TxTiles {
-    float4 *f;                        // {x', y', z', theta}: scaled centred coords, near threshold
+    // SoA, exactly as a sweep block wants it in shared memory (so that a stage is a handful of 1-D bulk copies):
+    // c = P_t^(-1/n), nx / ny / nz = MINUS the scaled centred coordinates (dx' = c * x_rx + nx)
+    float *c, *nx, *ny, *nz;
     int    *arrival;                  // bucket position -> arrival index t
     int    *goff;                     // [ngroups+1] bucket offsets (multiples of kTile)
     int    *gcount;                   // [ngroups] real tx per bucket

@@ -451,7 +451,7 @@ prepare_all_kernel(NodeArrays nd, const DevParams *dp, const Geom *geom, Groups 
         for (int i = tid; i < ng * kTile; i += kPrepThreads) {           // pad every bucket to a whole tile
             const int g = i / kTile, j = s_goff[g] + s_cnt[g] + i % kTile;
             if (j < s_goff[g + 1]) {
-                tx.f[j] = make_float4(1e18f, 1e18f, 1e18f, 0.f);           // d2' ~ 1e36 -> lin underflows to 0
+                tx.c[j] = 0.f; tx.nx[j] = tx.ny[j] = tx.nz[j] = -1e18f;     // d2' ~ 1e36 -> lin underflows to 0
                 theta[j] = FLT_MAX;
                 tx.arrival[j] = -1;
             }
@@ -476,7 +476,9 @@ prepare_all_kernel(NodeArrays nd, const DevParams *dp, const Geom *geom, Groups 
         __syncthreads();
         if (g >= 0) {
             const int j = s_wcnt[wid][g] + r;
-            tx.f[j] = stg.f[t]; theta[j] = stg.theta[t]; tx.arrival[j] = t;
+            const float4 f = stg.f[t];
+            tx.c[j] = f.w; tx.nx[j] = -f.x; tx.ny[j] = -f.y; tx.nz[j] = -f.z;
+            theta[j] = stg.theta[t]; tx.arrival[j] = t;
         }
         __syncthreads();
     }

@@ -70,7 +70,53 @@ __device__ __forceinline__ f32x2 accumulate2(f32x2 d2, f32x2 acc, float neg_h)
     return add2(acc, pack2(mufu_ex2(__fmul_rn(neg_h, mufu_lg2(a))), mufu_ex2(__fmul_rn(neg_h, mufu_lg2(b)))));
 }
 
-constexpr int kStage = 1024;          // tx per shared-memory stage (SoA: c, -x', -y', -z', theta)
+constexpr int kStage = 1024;          // tx per shared-memory stage (SoA: c, -x', -y', (-z',) theta)
+
+// ---- the tx stage: 1-D bulk copies (TMA, cp.async.bulk) global -> shared, completion on an mbarrier ------------
+// The tiles are regular -- five SoA rows, 16-float granules -- so one elected thread moves a whole stage with five
+// copy instructions and the other threads never touch the data on its way in (no LDG -> register -> STS round trip,
+// no barrier between "loaded" and "stored").  One buffer: a block's share is one stage long in practice (~526
+// transmissions), and two half-size buffers measured slower (2544 vs 2465 us at C4: a second wait + barrier per block).
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, unsigned bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned bytes, unsigned long long *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity)
+{
+    asm volatile("{\n"
+                 ".reg .pred p;\n"
+                 "RMB_WAIT:\n"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+                 "@p bra RMB_DONE;\n"
+                 "bra RMB_WAIT;\n"
+                 "RMB_DONE:\n"
+                 "}" :: "r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+
+// one stage = NF bulk copies fired by one thread, the barrier armed with their byte count.  Deliberately NOT inlined:
+// inlined, its address arithmetic raised the register pressure of the sweep loop (56-register budget) and the loop's
+// running sums went to local memory -- 2513 instead of 2465 us per C4 launch (ptxas: 64 vs 16 bytes of spill stores)
+template <bool PLANAR>
+__device__ __noinline__ void fire_stage(float *s_stage, unsigned long long *bar, const TxTiles &tx, const float *theta, int s0, int ns)
+{
+    const unsigned bytes = (unsigned)ns * 4u;
+    mbar_expect_tx(bar, bytes * (PLANAR ? 4u : 5u));
+    bulk_g2s(s_stage, tx.c + s0, bytes, bar);
+    bulk_g2s(s_stage + kStage, tx.nx + s0, bytes, bar);
+    bulk_g2s(s_stage + 2 * kStage, tx.ny + s0, bytes, bar);
+    bulk_g2s(s_stage + 3 * kStage, theta + s0, bytes, bar);
+    if (!PLANAR) bulk_g2s(s_stage + 4 * kStage, tx.nz + s0, bytes, bar);
+}
 
 template <int MODE, bool PLANAR, int R, int THREADS>
 __global__ void __launch_bounds__(THREADS, (THREADS == 128 && R <= 4) ? 9 : 1)
@@ -79,15 +125,13 @@ sweep_kernel(const float *__restrict__ fx, const float *__restrict__ fy, const f
              float neg_h, float *__restrict__ far_part, int *__restrict__ cnt, int *__restrict__ slots,
              int K, int n_work, int S1, int S2, int rb_taper, SweepFuse fuse)
 {
-    // one stage buffer, carved
-    __shared__ __align__(16) float s_stage[(PLANAR ? 4 : 5) * kStage];
+    // one stage buffer, carved into its SoA rows; one mbarrier
+    constexpr int NF = PLANAR ? 4 : 5;
+    __shared__ __align__(128) float s_stage[NF * kStage];
+    __shared__ __align__(8) unsigned long long s_bar;
     float *const s_c = s_stage, *const s_nx = s_stage + kStage, *const s_ny = s_stage + 2 * kStage,
           *const s_theta = s_stage + 3 * kStage, *const s_nz = s_stage + (PLANAR ? 0 : 4 * kStage);
 
-    // block = (rx block, tx split), splits of one rx block adjacent: receivers complete progressively
-    // over the launch, so the fused exact resolve runs in the shadow of the other blocks' sweeps
-    // The last rx blocks of the launch (rb >= rb_taper, about its final wave) are cut into S2 > S1 splits: shorter
-    // blocks where the launch runs out of work, so the SMs go idle closer together.
     if (fuse.trace && threadIdx.x == 0) fuse.trace[12 * (size_t)blockIdx.x] = global_timer_ns();
     // programmatic dependent launch, both ways: the kernel behind this one (finish.cu) may bring its blocks in as soon
     // as every block of this launch has started -- i.e. during the final wave, into slots nobody is waiting for --
@@ -122,16 +166,17 @@ sweep_kernel(const float *__restrict__ fx, const float *__restrict__ fy, const f
     const int j_begin = min(b1, b0 + split * per), j_end = min(b1, j_begin + per);
     const float th_min = theta_min_g[g];
 
+    if (threadIdx.x == 0) {
+        mbar_init(&s_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    unsigned phase = 0;
     for (int s0 = j_begin; s0 < j_end; s0 += kStage) {
         const int ns = min(kStage, j_end - s0);
-        __syncthreads();
-        for (int i = threadIdx.x; i < ns; i += THREADS) {
-            const float4 t = tx.f[s0 + i];
-            s_c[i] = t.w; s_nx[i] = -t.x; s_ny[i] = -t.y;
-            if (!PLANAR) s_nz[i] = -t.z;
-            s_theta[i] = theta[s0 + i];
-        }
-        __syncthreads();
+        __syncthreads();                  // the barrier is initialised / everybody is done with the previous stage
+        if (threadIdx.x == 0) fire_stage<PLANAR>(s_stage, &s_bar, tx, theta, s0, ns);
+        mbar_wait(&s_bar, phase);
+        phase ^= 1u;
         for (int j = 0; j < ns; j += kTile) {
             f32x2 ps[R];
 #pragma unroll

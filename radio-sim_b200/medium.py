@@ -378,6 +378,18 @@ class Group:
                                                _ptr(rxprob, C.c_double), _ptr(txprob, C.c_double), _ptr(id_int, C.c_int32)))
         self.n = n
 
+    def set_matrix(self, matrix):
+        """N2N: the matrix medium lives on ONE device (rmb_create refuses RMB_MODEL_N2N with n_shards > 1)."""
+        m = np.ascontiguousarray(matrix, dtype=np.float64)
+        n = int(round(m.size ** 0.5))
+        if n * n != m.size:
+            raise ValueError("matrix must be square (flat row-major n*n)")
+        h = C.c_void_p()
+        self._ck(self._lib.rmb_group_shard(self._g, 0, C.byref(h), None, None))
+        rc = self._lib.rmb_set_matrix(h, n, _ptr(m.reshape(-1), C.c_double))
+        if rc != A.OK:
+            raise MediumError(rc, self._lib.rmb_last_error(h).decode())
+
     def update_positions(self, x, y, z=None, idx=None):
         x = _arr(x, np.float64)
         c = x.shape[0]

@@ -246,10 +246,11 @@ class CudaRadioMedium(AbstractRadioMedium):
         # deterministic tick: one call.  With draws: the first call (no uniforms; a missing draw reads as 0.0 = success,
         # which maximises the number of later draws) tells how many uniforms the tick can consume at most; the
         # generator's look-ahead supplies them and the generator is advanced by the number actually consumed.
-        r = self.medium.tick(src, power, channel, allow_short_uniforms=True, copy=False)
+        # (copies, not views of the handles' pinned slabs: the events raised below outlive this tick)
+        r = self.medium.tick(src, power, channel, allow_short_uniforms=True)
         if r.status != 0:
             rnd = self.uniforms if self.uniforms is not None else self.simulator.get_random()
-            r = self.medium.tick(src, power, channel, uniforms=rnd.peek_doubles(r.n_uniforms_used), copy=False)
+            r = self.medium.tick(src, power, channel, uniforms=rnd.peek_doubles(r.n_uniforms_used))
             rnd.skip_doubles(r.n_uniforms_used)
         self.ticks += 1
         self._node_info = None
