@@ -361,7 +361,7 @@ def run_static(args):
         return med.tick_records(p.n_records, rec_all.data_ptr(), copy=False)
 
     def timed(fn, steps, sampler=None, device_timed=True):
-        times, walls, sweep_ms, launches, dec, pairs = [], [], [], 0, 0, 0
+        times, walls, sweep_ms, launches, dec, pairs, phases = [], [], [], 0, 0, 0, []
         for i in range(steps):
             k = i % len(lists)
             torch.cuda.synchronize()
@@ -391,7 +391,11 @@ def run_static(args):
                 sampler.active = False
             tm = med.timing()
             sweep_ms.append(tm["ms_sweep"]); launches += tm["kernel_launches"]
+            phases.append((tm["ms_prepare"], tm["ms_sweep"], tm["ms_emit"], tm["ms_total"], times[-1] * 1e3))
             dec += res.n_decisions; pairs += res.n_pairs
+        if os.environ.get("RMB_BENCH_DEBUG") and device_timed and steps > 3:
+            print(f"[rank {rank}] median ms: prepare(+peer wait) %.4f sweep %.4f rest %.4f total(lib events) %.4f step(events) %.4f" %
+                  tuple(np.median(np.array(phases), axis=0)), file=sys.stderr, flush=True)
         return dict(times=times, walls=walls, sweep_ms=sweep_ms, launches=launches, dec=dec, pairs=pairs, last=res)
 
     sampler = ClockSampler(local, period=0.0003 if N * T < 5e8 else 0.005)

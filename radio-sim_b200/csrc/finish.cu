@@ -112,31 +112,53 @@ __device__ __forceinline__ void warp_bucket(const PairRecs &pr, const PairArrays
 }
 
 // seg[t] = first pair of packet t (exclusive scan of the per-packet heard counts) for n <= kFinScanMax packets, by ONE
-// block into shared memory; returns the largest count.  Every block of the finish kernel does this for itself (40 KB
-// of counts out of the L2, ~2 us) -- the sweep used to leave the scan to the one block that resolved last, 10 us at
-// the very end of its launch with the rest of the GPU idle (profiles/r02_trace8.txt).
+// block into shared memory; returns the largest count.  Every block of the finish kernel does this for itself -- the
+// sweep used to leave the scan to the one block that resolved last, 10 us at the very end of its launch with the rest
+// of the GPU idle (profiles/r02_trace8.txt).  Warp w owns the contiguous segment [w * seg_len, (w + 1) * seg_len):
+// 32 counts per step straight from global memory (coalesced, the next steps' loads already in flight), a shuffle scan,
+// the running carry in a register -- no barrier inside the loop, no bank conflict.  One barrier, then the warps'
+// offsets are added in place (coalesced again).
 __device__ __forceinline__ int block_scan_counts(const int *cnt, int n, int *s_seg, int *s_warp /* [2 * kFinWarps] */)
 {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (int i = tid; i < n; i += kFinThreads) s_seg[i] = __ldcg(cnt + i);
-    __syncthreads();
-    const int per = (n + kFinThreads - 1) / kFinThreads;
-    const int b = min(n, tid * per), e = min(n, b + per);
-    int sum = 0, mx = 0;
-    for (int i = b; i < e; ++i) { const int v = s_seg[i]; sum += v; mx = max(mx, v); }
-    int incl = sum;
+    const int seg_len = ((n + kFinWarps - 1) / kFinWarps + 127) / 128 * 128;
+    const int b = min(n, warp * seg_len), e = min(n, b + seg_len);
+    int carry = 0, mx = 0;
+    // four counts per lane and step (one 16-byte load), five steps' loads in flight: the loop is two L2 round trips
+    // long instead of ten
+#pragma unroll 5
+    for (int i0 = b; i0 < e; i0 += 128) {
+        const int i = i0 + 4 * lane;
+        int4 v = make_int4(0, 0, 0, 0);
+        if (i + 3 < e) v = __ldcg(reinterpret_cast<const int4 *>(cnt + i));
+        else {
+            if (i < e) v.x = __ldcg(cnt + i);
+            if (i + 1 < e) v.y = __ldcg(cnt + i + 1);
+            if (i + 2 < e) v.z = __ldcg(cnt + i + 2);
+        }
+        mx = max(mx, max(max(v.x, v.y), max(v.z, v.w)));
+        const int t = v.x + v.y + v.z + v.w;
+        int incl = t;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
+        for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
+        const int ex = carry + incl - t;
+        if (i + 3 < e) *reinterpret_cast<int4 *>(s_seg + i) = make_int4(ex, ex + v.x, ex + v.x + v.y, ex + v.x + v.y + v.z);
+        else {
+            if (i < e) s_seg[i] = ex;
+            if (i + 1 < e) s_seg[i + 1] = ex + v.x;
+            if (i + 2 < e) s_seg[i + 2] = ex + v.x + v.y;
+        }
+        carry += __shfl_sync(0xffffffffu, incl, 31);
+    }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    if (lane == 31) s_warp[warp] = incl;
-    if (lane == 0) s_warp[kFinWarps + warp] = mx;
+    if (lane == 0) { s_warp[warp] = carry; s_warp[kFinWarps + warp] = mx; }
     __syncthreads();
-    int carry = 0, total = 0, gmx = 0;
+    int off = 0, total = 0, gmx = 0;
 #pragma unroll
-    for (int k = 0; k < kFinWarps; ++k) { const int v = s_warp[k]; if (k < warp) carry += v; total += v; gmx = max(gmx, s_warp[kFinWarps + k]); }
-    int ex = carry + incl - sum;
-    for (int i = b; i < e; ++i) { const int v = s_seg[i]; s_seg[i] = ex; ex += v; }
+    for (int k = 0; k < kFinWarps; ++k) { const int v = s_warp[k]; if (k < warp) off += v; total += v; gmx = max(gmx, s_warp[kFinWarps + k]); }
+    if (off)
+        for (int i = b + lane; i < e; i += 32) s_seg[i] += off;
     if (tid == 0) s_seg[n] = total;
     __syncthreads();
     return gmx;

@@ -109,15 +109,15 @@ __device__ __forceinline__ void resolve_receiver(int w, bool active, const WorkA
         if (found > K) atomicMax(&ctr->max_near, found);      // slot overflow: the host grows K and redoes the sweep
         c = min(found, K);
         // far field: the sweep's per-split partial sums, added in split order (deterministic)
-        // (sixteen loads in flight at a time; a missing split adds +0.0, which changes nothing)
+        // (twenty loads in flight at a time; a missing split adds +0.0, which changes nothing)
         double far = 0.0;
         const int nsplit = w < sl.w_taper ? sl.splits : sl.splits2;
-        for (int s0 = 0; s0 < nsplit; s0 += 16) {
-            float v[16];
+        for (int s0 = 0; s0 < nsplit; s0 += 20) {      // (19 rows, or 38 in the launch's final wave: one or two round trips)
+            float v[20];
 #pragma unroll
-            for (int k = 0; k < 16; ++k) v[k] = s0 + k < nsplit ? __ldcg(&sl.far_part[(size_t)(s0 + k) * wk.n_work + w]) : 0.f;
+            for (int k = 0; k < 20; ++k) v[k] = s0 + k < nsplit ? __ldcg(&sl.far_part[(size_t)(s0 + k) * wk.n_work + w]) : 0.f;
 #pragma unroll
-            for (int k = 0; k < 16; ++k) far = xm::add(far, (double)v[k]);
+            for (int k = 0; k < 20; ++k) far = xm::add(far, (double)v[k]);
         }
         itot = xm::add(itot, far);
         // the sweep appends near candidates in arbitrary order: sort by bucket position (= arrival order)
