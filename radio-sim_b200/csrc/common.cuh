@@ -126,6 +126,12 @@ __device__ __forceinline__ void st_release_sys(unsigned *p, unsigned v)
 {
     asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
 }
+// a flag store BEHIND a __threadfence_system(): the fence has ordered the data, the store itself need not wait for
+// anything -- seven release stores in a row wait for one another's acknowledgement over NVLink, seven of these pipeline
+__device__ __forceinline__ void st_relaxed_sys(unsigned *p, unsigned v)
+{
+    asm volatile("st.relaxed.sys.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
 __device__ __forceinline__ unsigned long long global_timer_ns()
 {
     unsigned long long t;

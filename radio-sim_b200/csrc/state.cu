@@ -241,7 +241,7 @@ __global__ void __launch_bounds__(256) peer_push_kernel(const rmb_tx_record *loc
         if (atomicAdd(pp.done, 1u) == gridDim.x - 1) {
             *pp.done = 0u;
             __threadfence_system();
-            for (int p = 0; p < pp.world; ++p) st_release_sys(reinterpret_cast<unsigned *>(pp.peer[p]) + pp.rank, pp.epoch);
+            for (int p = 0; p < pp.world; ++p) st_relaxed_sys(reinterpret_cast<unsigned *>(pp.peer[p]) + pp.rank, pp.epoch);
         }
     }
 }
@@ -321,7 +321,7 @@ prepare_all_kernel(NodeArrays nd, const DevParams *dp, const Geom *geom, Groups 
             if (atomicAdd(aux.push_done, 1u) == gridDim.x - 1) {
                 *aux.push_done = 0u;
                 __threadfence_system();
-                for (int p = 0; p < aux.world; ++p) st_release_sys(reinterpret_cast<unsigned *>(aux.push_peer[p]) + aux.push_rank, aux.epoch);
+                for (int p = 0; p < aux.world; ++p) st_relaxed_sys(reinterpret_cast<unsigned *>(aux.push_peer[p]) + aux.push_rank, aux.epoch);
             }
         }
     }
