@@ -772,13 +772,13 @@ def run_c1_reference(args):
 
 # ---------------------------------------------------------------------------------------------------------------
 def run_single_process(args):
-    """N handles in ONE process (what one JVM owning N handles does): one host thread per GPU pushes its share of the
-    packet list and runs its shard's tick; the step ends when every shard's result lists are in this process's host
-    memory (rank order == node order, so packet t's rows are the shards' rows of t one after the other -- the merge is
-    a walk over tx_first, no copy).  Reported as e2e."""
+    """N GPUs behind ONE object in ONE process (rmb_group_*: what one JVM with the adapter does): a tick is one call
+    with the whole packet list, inside the library one host worker thread per GPU pushes its share, runs its shard's
+    tick and brings its lists to host memory; the call returns when every shard's lists are there (rank order == node
+    order, so packet t's rows are the shards' rows of t one after the other -- the merge is a walk over tx_first, no
+    copy).  Reported as e2e."""
     import torch
     import radio_sim_b200 as rsb
-    from radio_sim_b200.sharding import shard_bounds, TickPlan, merge_results
     import workloads as W
     G = args.gpus
     if torch.cuda.device_count() < G:
@@ -786,72 +786,34 @@ def run_single_process(args):
     name = args.workload
     dep = W.deployment("c4" if name == "c4-grid" else name, grid=name == "c4-grid")
     N, T = dep["n"], dep["t"]
-    bounds = shard_bounds(N, G)
     lists = source_lists(dep, max(1, min(args.steps, 8)))
-    plans = [TickPlan(s, bounds) for s in lists]
-    tpad_max = max(p.tpad for p in plans)
-    meds = []
-    for r, (lo, hi) in enumerate(bounds):
-        m = rsb.Medium("sinr", device=r, rx_base=lo, n_shards=G, compact=True)
-        m.set_nodes(dep["x"][lo:hi], dep["y"][lo:hi])
-        meds.append(m)
-    if G > 1:
-        blobs = [m.peer_export(G, r, tpad_max) for r, m in enumerate(meds)]
-        for m in meds:
-            m.peer_open(blobs)
-    results = [None] * G
-    go, done = threading.Barrier(G + 1), threading.Barrier(G + 1)
-    state = {"k": 0, "stop": False}
-
-    def worker(r):
-        torch.cuda.set_device(r)
-        while True:
-            go.wait()
-            if state["stop"]:
-                return
-            p = plans[state["k"]]
-            if G == 1:
-                results[r] = meds[r].tick(lists[state["k"]], copy=False)
-            else:
-                meds[r].peer_push(p.local_src[r])
-                results[r] = meds[r].tick_peers(copy=False)
-            done.wait()
-
-    threads = [threading.Thread(target=worker, args=(r,), daemon=True) for r in range(G)]
-    for t in threads:
-        t.start()
+    grp = rsb.Group("sinr", devices=tuple(range(G)), max_tx_per_tick=T, compact=True, **medium_params(args))
+    grp.set_nodes(dep["x"], dep["y"])
     walls, dec, pairs = [], 0, 0
     for i in range(args.warmup + args.steps):
-        state["k"] = i % len(lists)
         for r in range(G):
             torch.cuda.synchronize(r)
         t0 = time.perf_counter()
-        go.wait()
-        done.wait()
+        res = grp.tick(lists[i % len(lists)], copy=False)
         dt = time.perf_counter() - t0
         if i >= args.warmup:
             walls.append(dt)
-            dec += sum(x.n_decisions for x in results); pairs += sum(x.n_pairs for x in results)
-    state["k"] = 0
-    go.wait(); done.wait()
-    parts = [dict(tx=x.tx_column(), rx=x.rx.copy(), outcome=x.outcome.copy()) for x in results]
-    m = merge_results(plans[0], parts) if G > 1 else parts[0]
+            dec += res.n_decisions; pairs += res.n_pairs
+    m = grp.tick(lists[0]).merged()
     d = digest(m["tx"], m["rx"], m["outcome"])
     gold = golden(name)
-    state["stop"] = True
-    go.wait()
-    for mm in meds:
-        mm.close()
+    grp.close()
     line = {"metric": METRIC, "value": dec / sum(walls), "unit": UNIT, "n_gpus": G, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * sum(walls) / len(walls), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32+f64", "data": "synthetic",
-            "config": config_of(args, dep, parallelism=f"receivers sharded x{G}, ONE process, one host thread per GPU",
-                                timing="host wall clock from releasing the worker threads to the last shard's lists in host memory"),
+            "config": config_of(args, dep, parallelism=f"receivers sharded x{G}, ONE process (rmb_group_*), one host worker thread per GPU inside the library",
+                                timing="host wall clock around rmb_group_tick: host packet list in, every shard's lists in host memory out"),
             "e2e": {"value": dec / sum(walls), "unit": UNIT, "ms_per_step": 1e3 * sum(walls) / len(walls),
-                    "h2d_bytes_per_step": int(4 * T), "d2h_bytes_per_step": int(9 * pairs / len(walls) + 5 * G * tpad_max),
+                    "h2d_bytes_per_step": int(4 * T), "d2h_bytes_per_step": int(9 * pairs / len(walls) + 5 * T),
                     "heard_pairs": int(pairs / len(walls))},
             "gpu_launches": 3 * G * args.steps,
-            "verified": {"sha256": d, "golden": None if gold is None else bool(gold["sha256"] == d), "heard_pairs": int(len(m["rx"]))}}
+            "verified": {"sha256": d, "golden": None if gold is None else bool(gold["sha256"] == d), "heard_pairs": int(len(m["rx"])),
+                         "what": "the shards' lists merged in the reference's order vs tests/golden/fullsize_hashes.json"}}
     print(json.dumps(line), flush=True)
 
 

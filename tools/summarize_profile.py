@@ -1,7 +1,8 @@
 """Turn gpurun_out ncu artefacts into the tracked summaries under profiles/.
 
-usage: python tools/summarize_profile.py <tag> <launches.csv> <full.ncu-rep> [kernel-regex]
-writes profiles/<tag>_launches.md, profiles/<tag>_sweep_ncu.md and profiles/sweep_traffic.json
+usage: python tools/summarize_profile.py <tag> <launches.csv> <full.ncu-rep> [workload] [n_gpus]
+       python tools/summarize_profile.py --traffic <workload> <n_gpus> <dram.csv>     (a --metrics dram__bytes_* capture of one sweep launch)
+writes profiles/<tag>_launches.md, profiles/<tag>_sweep_ncu.md and the entry [workload][n_gpus] of profiles/sweep_traffic.json
 """
 import collections, csv, json, os, subprocess, sys
 
@@ -22,6 +23,36 @@ KEYS = ["gpu__time_duration.sum", "sm__cycles_elapsed.avg.per_second", "launch__
         "smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio",
         "smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio",
         "smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio"]
+
+
+WORKLOAD, NGPUS = "c4", "1"
+
+
+def set_traffic(workload, n, value, source):
+    """profiles/sweep_traffic.json: {workload: {n_gpus: dram bytes of ONE sweep launch of one rank}, "_source": {...}}"""
+    path = os.path.join(ROOT, "profiles", "sweep_traffic.json")
+    try:
+        d = json.load(open(path))
+        if "dram_bytes_per_launch" in d:
+            d = {}
+    except Exception:
+        d = {}
+    d.setdefault(workload, {})[str(n)] = value
+    d.setdefault("_source", {})[f"{workload}/{n}"] = source
+    json.dump(d, open(path, "w"), indent=1, sort_keys=True)
+
+
+def traffic_csv(workload, n, path):
+    rows = [r for r in csv.reader(open(path)) if len(r) > 5]
+    hdr = rows[0]
+    ki, mi, ui, vi = hdr.index("Kernel Name"), hdr.index("Metric Name"), hdr.index("Metric Unit"), hdr.index("Metric Value")
+    mult = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    tot = 0.0
+    for r in rows[1:]:
+        if "sweep_kernel" in r[ki] and r[mi].startswith("dram__bytes_"):
+            tot += float(r[vi].replace(",", "")) * mult[r[ui]]
+    set_traffic(workload, n, tot, os.path.basename(path))
+    print(workload, n, tot)
 
 
 def launches(tag, path):
@@ -63,8 +94,8 @@ def full(tag, rep):
             mult = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
             tr = float(d["dram__bytes_read.sum"]) * mult[u["dram__bytes_read.sum"]] + \
                 float(d["dram__bytes_write.sum"]) * mult[u["dram__bytes_write.sum"]]
-            json.dump({"dram_bytes_per_launch": tr, "source": f"profiles/{tag}_sweep_ncu.md"},
-                      open(os.path.join(ROOT, "profiles", "sweep_traffic.json"), "w"))
+            if "sweep_kernel" in name:
+                set_traffic(WORKLOAD, NGPUS, tr, f"profiles/{tag}_sweep_ncu.md")
             out.append(f"| dram read+write per launch | byte | {tr:.0f} |")
         except Exception:
             pass
@@ -73,7 +104,12 @@ def full(tag, rep):
 
 
 if __name__ == "__main__":
+    if sys.argv[1] == "--traffic":
+        traffic_csv(sys.argv[2], sys.argv[3], sys.argv[4])
+        sys.exit(0)
     tag = sys.argv[1]
+    if len(sys.argv) > 5:
+        WORKLOAD, NGPUS = sys.argv[4], sys.argv[5]
     os.makedirs(os.path.join(ROOT, "profiles"), exist_ok=True)
     launches(tag, sys.argv[2])
     if len(sys.argv) > 3:
