@@ -70,6 +70,27 @@ __device__ __forceinline__ f32x2 accumulate2(f32x2 d2, f32x2 acc, float neg_h)
     return add2(acc, pack2(mufu_ex2(__fmul_rn(neg_h, mufu_lg2(a))), mufu_ex2(__fmul_rn(neg_h, mufu_lg2(b)))));
 }
 
+// (d2)^(-3/2) on both lanes WITHOUT the XU pipe: integer seed + two Newton steps in packed fp32.  The sweep is bound by
+// the MUFU (XU) pipe at 16 lanes/SM/clk while the FMA pipe idles a quarter of the time (ncu: XU 90 %, FMA-heavy 68 %),
+// so one pair in eight could take this route: 7 packed FMA-pipe instructions + 4 integer ones for two pairs instead of two
+// MUFU.RSQ -- on paper both pipes then fill up together (-10 %); on the GPU the launch got 5.5 % LONGER (the extra 13 % of
+// issued instructions and the 7-deep dependent chain cost more than the freed XU slots give back), so it is compiled out.  Relative error of q after two steps <= 4.7e-6 (always low), i.e.
+// 1.4e-5 on q^3 for an eighth of the far terms: two orders of magnitude inside the guard band.
+__device__ __forceinline__ f32x2 accumulate2_fma_n3(f32x2 d2, f32x2 acc)
+{
+    float a, b;
+    unpack2(d2, a, b);
+    const f32x2 y0 = pack2(__int_as_float(0x5f3759df - (__float_as_int(a) >> 1)), __int_as_float(0x5f3759df - (__float_as_int(b) >> 1)));
+    const f32x2 nh = mul2(d2, pack2(-0.5f, -0.5f)), c15 = pack2(1.5f, 1.5f);
+    f32x2 y = mul2(y0, fma2(nh, mul2(y0, y0), c15));
+    y = mul2(y, fma2(nh, mul2(y, y), c15));
+    return fma2(mul2(y, y), y, acc);
+}
+
+#ifndef RMB_FMA_RSQRT
+#define RMB_FMA_RSQRT 0      // MEASURED SLOWER (C4, one B200: sweep 2605 us with, 2470 us without): off, kept for the record
+#endif
+constexpr bool kFmaRsqrt = RMB_FMA_RSQRT != 0;
 constexpr int kStage = 1024;          // tx per shared-memory stage (SoA: c, -x', -y', (-z',) theta)
 
 // ---- the tx stage: 1-D bulk copies (TMA, cp.async.bulk) global -> shared, completion on an mbarrier ------------
@@ -198,7 +219,8 @@ sweep_kernel(const float *__restrict__ fx, const float *__restrict__ fy, const f
                     dx = fma2(X[r], c2.y, x2.y); dy = fma2(Y[r], c2.y, y2.y);
                     d2 = fma2(dy, dy, mul2(dx, dx));
                     if (!PLANAR) { f32x2 dz = fma2(Z[r], c2.y, z2.y); d2 = fma2(dz, dz, d2); }
-                    ps[r] = accumulate2<MODE>(d2, ps[r], neg_h);
+                    if (MODE == MODE_N3 && kFmaRsqrt && u == kTile - 4) ps[r] = accumulate2_fma_n3(d2, ps[r]);   // one pair in eight off the XU pipe
+                    else ps[r] = accumulate2<MODE>(d2, ps[r], neg_h);
                 }
             }
             float s[R];

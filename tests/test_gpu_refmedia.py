@@ -25,8 +25,14 @@ def test_known_answers_on_gpu(rsb, c):
                     rxprob=c.get("rxprob"), txprob=c.get("txprob"), txpower_dbm=c.get("txpower"))
         if "matrix" in c:
             m.set_matrix(np.array(c["matrix"], float))
-        r = m.tick(np.array(c["src"], dtype=np.int32), channel=c.get("pkt_channel"))
+        u = None
+        if "seed" in c:
+            from radio_sim_b200.javarandom import JavaRandom
+            u = JavaRandom(c["seed"]).next_doubles(64)               # simulator.getRandom() == new Random(seed)
+        r = m.tick(np.array(c["src"], dtype=np.int32), channel=c.get("pkt_channel"), uniforms=u)
     got = [[int(t), int(x), int(o)] for t, x, o in zip(r.tx, r.rx, r.outcome)]
+    if "draws" in c:
+        assert r.n_uniforms_used == c["draws"]
     assert got == c["expect"], c["why"]
     if "tx_failed" in c:
         assert r.tx_failed.tolist() == c["tx_failed"]
