@@ -375,9 +375,11 @@ def run_static(args):
             if device_timed:
                 line_up()
             else:
+                # host-timed leg: the ranks' HOSTS are released together -- a device-side rendezvous, then each host
+                # waits for its own GPU (a collective's barrier lets the ranks go tens of microseconds apart, and one
+                # rank's late start is every other rank's wait for its records)
+                line_up()
                 torch.cuda.synchronize()
-                if G > 1:
-                    dist.barrier()
             t0 = time.perf_counter()
             e0.record(stream)
             res = fn(k)
@@ -589,13 +591,10 @@ def run_c5(args):
                 sampler.active = True
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             flush_buf.fill_(1)
-            if kind != "e2e":
-                if G > 1:
-                    med.peer_barrier_enqueue()
-            else:
+            if G > 1:
+                med.peer_barrier_enqueue()          # device-side rendezvous (see run_static)
+            if kind == "e2e":
                 torch.cuda.synchronize()
-                if G > 1:
-                    dist.barrier()
             t0 = time.perf_counter()
             e0.record(stream)
             if kind != "e2e":

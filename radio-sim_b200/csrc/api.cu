@@ -109,6 +109,7 @@ struct rmb_handle {
     DevBuf<int> o_tx, o_rx; DevBuf<float> o_rssi, o_sinr; DevBuf<uint8_t> o_outcome; DevBuf<double> o_rssi64, o_sinr64;
     PinBuf<int> ho_tx, ho_rx, ho_first; DevBuf<int> o_first; PinBuf<float> ho_rssi, ho_sinr; PinBuf<uint8_t> ho_outcome, ho_failed;
     PinBuf<double> ho_rssi64, ho_sinr64;
+    DevBuf<char> o_slab; PinBuf<char> ho_slab; bool slab_ready = false;     // finish.cu path: all columns packed, one copy (kernels.h slab_layout)
 
     // multi-GPU exchange over peer memory (rmb_peer_*)
     struct Peer {
@@ -131,7 +132,7 @@ struct rmb_handle {
     // asynchronous tick (rmb_tick_enqueue / rmb_tick_peers_enqueue): enqueued, counters not looked at yet
     bool async_mode = false, pending = false;
     struct Pending { int n_tx = 0; const rmb_tx_record *rec = nullptr; const unsigned *flags = nullptr; unsigned epoch = 0; int world = 0;
-                     int launches = 0, sweeps = 0; } pend;
+                     int launches = 0, sweeps = 0; bool slab = false; } pend;
 
     // last tick
     long long last_pairs = 0; int last_ntx = 0;
@@ -200,6 +201,7 @@ PairArrays pair_arrays(rmb_handle *h)
     int bits = 1;
     while (bits < 31 && (1ll << bits) < (long long)h->cfg.rx_base + h->n + 1) ++bits;
     p.key_shift = bits;
+    p.slab = nullptr; p.slab_flags = h->cfg.flags;
     return p;
 }
 
@@ -428,7 +430,7 @@ int rmb_destroy(rmb_handle *h)
     h->tx_failed.release(); h->cub_tmp.release(); h->o_tx.release(); h->o_rx.release(); h->o_rssi.release();
     h->o_sinr.release(); h->o_outcome.release(); h->o_rssi64.release(); h->o_sinr64.release(); h->ho_tx.release();
     h->ho_rx.release(); h->ho_first.release(); h->o_first.release(); h->ho_rssi.release(); h->ho_sinr.release(); h->ho_outcome.release(); h->ho_failed.release();
-    h->ho_rssi64.release(); h->ho_sinr64.release();
+    h->ho_rssi64.release(); h->ho_sinr64.release(); h->o_slab.release(); h->ho_slab.release();
     h->fb_key.release(); h->fb_key_alt.release(); h->fb_val.release(); h->fb_val_alt.release(); h->rec_prx.release();
     h->rec_sinr.release(); h->rec_flags.release(); h->rec_rank.release(); h->tx_cnt.release(); h->first.release();
     for (auto &ev : h->ev) if (ev) cudaEventDestroy(ev);
@@ -772,6 +774,7 @@ static int finish_pending(rmb_handle *h)
         return rc;
     }
     h->node_info_dirty = true;
+    h->slab_ready = h->pend.slab;
     return publish(h, h->pend.n_tx, (long long)c.heard, false, h->pend.launches, h->pend.sweeps);
 }
 
@@ -792,6 +795,7 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
     if (h->split_counts && h->cfg.model != RMB_MODEL_SINR)
         return h->fail(RMB_ERR_UNSUPPORTED, "rmb_tick_draws_begin exists for the SINR medium only");
     h->split.active = false;
+    h->slab_ready = false;
     RMB_CK(h, h->seg.ensure((size_t)n_tx + 2)); RMB_CK(h, h->tx_base.ensure((size_t)n_tx + 1));
     RMB_CK(h, h->tx_failed.ensure((size_t)n_tx + 1));
     long long nu = 0;
@@ -899,6 +903,8 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
                 // deterministic reception: guard-band recheck, ordering and output rows in one cooperative kernel,
                 // whose last block stores the counters into the pinned host copy
                 const int fgrid = finish_grid(n_tx);
+                RMB_CK(h, h->o_slab.ensure((size_t)slab_layout((long long)h->key.cap, n_tx, h->cfg.flags).total));
+                pa.slab = h->o_slab.p;
                 RMB_CK(h, launch_finish(wk, h->dp.p, h->groups, tx, d_rec, sl, pr, pa, n_tx, h->seg.p, h->key_alt.p, h->recheck_part.p,
                                         h->ctr.p, h->h_ctr.p, fgrid, h->bar.p + 2, fuse.enabled && !kev && !trace_path, h->st));
                 launches += 1;
@@ -921,7 +927,7 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
                 if (!dev_publish) RMB_CK(h, cudaMemcpyAsync(h->h_ctr.p, h->ctr.p, sizeof(Counters), cudaMemcpyDeviceToHost, h->st));
                 h->pending = true;
                 h->pend.n_tx = n_tx; h->pend.rec = d_rec; h->pend.flags = h->wait_flags; h->pend.epoch = h->wait_epoch;
-                h->pend.world = h->wait_world; h->pend.launches = launches; h->pend.sweeps = sweeps;
+                h->pend.world = h->wait_world; h->pend.launches = launches; h->pend.sweeps = sweeps; h->pend.slab = use_finish;
                 memset(&h->last, 0, sizeof(h->last));
                 h->last.n_tx = n_tx; h->last_pairs = 0; h->last_ntx = n_tx;
                 return RMB_OK;
@@ -952,6 +958,7 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
         }
         m = (long long)h->h_ctr.p->heard;
         h->node_info_dirty = true;
+        h->slab_ready = use_finish && !(fallback && m > 0);       // the finish kernel packed the lists (one copy takes them home)
         final_sync = (fallback && m > 0) || draws;
         PairRecs pr = pair_recs(h);
         PairArrays pa = pair_arrays(h);
@@ -984,12 +991,16 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
         if (nb > 0x7fffffffull) return h->fail(RMB_ERR_CAPACITY, "n_tx * n too large for the reference-media path");
         RMB_CK(h, h->blkcnt.ensure(nb + 2)); RMB_CK(h, h->scan_tmp.ensure(nb / 1024 + 8));
         RMB_CK(h, cudaMemsetAsync(h->node_recv.p, 0, std::max(h->n, 1), h->st));
+        // sharded receivers: the peers' records must have landed before anything reads them (the SINR medium's
+        // preparation kernel does this wait itself)
+        if (h->wait_flags) RMB_CK(h, launch_peer_wait(h->wait_flags, h->wait_world, h->wait_epoch, h->ctr.p, h->st));
         RMB_CK(h, cudaEventRecord(h->ev[1], h->st));
         RMB_CK(h, launch_refmedia_mark(nd, h->dp.p, n_tx, d_rec, h->cfg.half_duplex ? h->tx_epoch.p : nullptr, h->hd_epoch, h->st));
         RMB_CK(h, launch_refmedia_count(nd, h->dp.p, h->matrix.p, h->matrix_n, n_tx, d_rec, h->blkcnt.p, h->ctr.p, draws, hd_ep, h->hd_epoch, h->st));
         ++launches; ++sweeps;
         RMB_CK(h, cudaEventRecord(h->ev[2], h->st));
         if ((rc = read_counters(h))) return rc;
+        if (h->h_ctr.p->peer_timeout) return h->fail(RMB_ERR_PEER, "peer exchange: a rank's tx records did not arrive (no rmb_peer_push on that rank?)");
         if (h->h_ctr.p->needs_draws) return h->fail(RMB_ERR_UNSUPPORTED, kNeedsDrawsMsg);
         m = (long long)h->h_ctr.p->heard;
         if ((rc = ensure_pairs(h, m))) return rc;
@@ -1018,6 +1029,22 @@ static int download(rmb_handle *h, rmb_result *out)
     const int nt = h->last_ntx;
     const size_t c = (size_t)std::max<long long>(m, 1);
     const bool f64 = (h->cfg.flags & RMB_FLAG_F64_VALUES) != 0, compact = (h->cfg.flags & RMB_FLAG_COMPACT) != 0;
+    if (h->slab_ready) {
+        // the finish kernel packed every column for exactly m rows: ONE copy, then pointers into the pinned slab
+        const SlabLayout L = slab_layout(m, nt, h->cfg.flags);
+        RMB_CK(h, h->ho_slab.ensure((size_t)L.total));
+        RMB_CK(h, cudaMemcpyAsync(h->ho_slab.p, h->o_slab.p, (size_t)L.total, cudaMemcpyDeviceToHost, h->st));
+        RMB_CK(h, cudaStreamSynchronize(h->st));
+        char *b = h->ho_slab.p;
+        rmb_result &r = h->last;
+        r.rx = (const int32_t *)(b + L.rx); r.rssi_dbm = (const float *)(b + L.rssi); r.outcome = (const uint8_t *)(b + L.outcome);
+        r.tx = compact ? nullptr : (const int32_t *)(b + L.tx); r.sinr_db = compact ? nullptr : (const float *)(b + L.sinr);
+        r.tx_first = compact ? (const int32_t *)(b + L.first) : nullptr;
+        r.rssi_dbm_f64 = f64 ? (const double *)(b + L.rssi64) : nullptr; r.sinr_db_f64 = f64 ? (const double *)(b + L.sinr64) : nullptr;
+        r.tx_failed = (const uint8_t *)(b + L.failed);
+        if (out) *out = r;
+        return RMB_OK;
+    }
     RMB_CK(h, h->ho_rx.ensure(c)); RMB_CK(h, h->ho_rssi.ensure(c));
     RMB_CK(h, h->ho_outcome.ensure(c)); RMB_CK(h, h->ho_failed.ensure((size_t)nt + 1));
     if (!compact) { RMB_CK(h, h->ho_tx.ensure(c)); RMB_CK(h, h->ho_sinr.ensure(c)); }

@@ -38,10 +38,9 @@ __device__ __forceinline__ void emit_row(const PairRecs &pr, const PairArrays &p
     const double rssi = __ldcg(&pr.prx[ri]), sinr = __ldcg(&pr.sinr[ri]);
     const bool cand = (__ldcg(&pr.flags[ri]) & kDecodable) != 0;
     const int outcome = (failed || !cand) ? RMB_INTERFERED : RMB_DELIVERED;
-    pa.o_tx[pos] = t;
+    if (pa.o_tx) { pa.o_tx[pos] = t; pa.o_sinr[pos] = (float)sinr; }       // (the compact slab has neither column)
     pa.o_rx[pos] = (int)(item >> 32);
     pa.o_rssi[pos] = (float)rssi;
-    pa.o_sinr[pos] = (float)sinr;
     if (pa.o_rssi64) { pa.o_rssi64[pos] = rssi; pa.o_sinr64[pos] = sinr; }
     pa.o_outcome[pos] = (uint8_t)outcome;
     n.delivered += outcome == RMB_DELIVERED; n.interfered += outcome != RMB_DELIVERED;
@@ -166,9 +165,10 @@ __device__ __forceinline__ int block_scan_counts(const int *cnt, int n, int *s_s
 
 __global__ void __launch_bounds__(kFinThreads, 4)
 finish_kernel(WorkArrays wk, const DevParams *dp, Groups groups, TxTiles tx, const rmb_tx_record *rec, SlotArrays sl,
-              PairRecs pr, PairArrays pa, int n_tx, int *seg_global, unsigned long long *items, double *part,
+              PairRecs pr, PairArrays pa_in, int n_tx, int *seg_global, unsigned long long *items, double *part,
               Counters *ctr, Counters *host_ctr, unsigned *bar, int scan_here)
 {
+    PairArrays pa = pa_in;
     // one dynamic buffer, two lives: the segment offsets of all packets while the records go to their buckets
     // (scan_here: [n_tx + 1] ints), the ranking scratch of phase 3 behind the grid barrier ([kBucketSortMax] items;
     // the offsets are read from global memory there -- block 0 stored them in front of the barrier)
@@ -185,6 +185,17 @@ finish_kernel(WorkArrays wk, const DevParams *dp, Groups groups, TxTiles tx, con
     const long long m_all = (long long)ctr->heard;
     const bool stand_down = m_all > pr.cap;                         // the host grows the record lists and redoes the tick
     const long long m = stand_down ? 0 : m_all;
+    // the output columns: packed for exactly m rows in the slab (one copy takes them to the host)
+    SlabLayout L{};
+    if (pa.slab) {
+        L = slab_layout(m, n_tx, pa.slab_flags);
+        pa.o_rx = reinterpret_cast<int *>(pa.slab + L.rx); pa.o_rssi = reinterpret_cast<float *>(pa.slab + L.rssi);
+        pa.o_tx = L.tx >= 0 ? reinterpret_cast<int *>(pa.slab + L.tx) : nullptr;
+        pa.o_sinr = L.sinr >= 0 ? reinterpret_cast<float *>(pa.slab + L.sinr) : nullptr;
+        pa.o_rssi64 = L.rssi64 >= 0 ? reinterpret_cast<double *>(pa.slab + L.rssi64) : nullptr;
+        pa.o_sinr64 = L.sinr64 >= 0 ? reinterpret_cast<double *>(pa.slab + L.sinr64) : nullptr;
+        pa.o_outcome = reinterpret_cast<uint8_t *>(pa.slab + L.outcome);
+    }
     // ---- 0: segment offsets.  scan_here: every block scans the per-packet counts for itself (block 0 also stores
     //         them for the host side / later kernels); otherwise the sweep's last resolving block did it
     const int *seg = seg_global;
@@ -282,6 +293,15 @@ finish_kernel(WorkArrays wk, const DevParams *dp, Groups groups, TxTiles tx, con
     }
 
     // ---- 3: rank every packet's bucket by rx, write its rows -----------------------------------------
+    if (pa.slab) {
+        // first row of every packet (== the segment offsets: rows are written at seg[t] + rank) and the tx-failure flags
+        int *first = reinterpret_cast<int *>(pa.slab + L.first);
+        uint8_t *failed = reinterpret_cast<uint8_t *>(pa.slab + L.failed);
+        for (int i = blockIdx.x * kFinThreads + threadIdx.x; i <= n_tx; i += gridDim.x * kFinThreads) {
+            first[i] = m > 0 ? seg[i] : 0;
+            if (i < n_tx) failed[i] = pa.tx_failed[i];
+        }
+    }
     EmitCount n{0, 0};
     // (m == 0: nothing was heard -- with no enabled receiver at all the sweep did not even run and `seg` is stale)
     if (m > 0 && max_bucket <= kBucketSortMax) {

@@ -45,7 +45,8 @@ cudaError_t launch_gather_records(const NodeArrays &nd, int rx_base, int n_tx, c
 constexpr size_t kPeerFlagBytes = 256;       // flags[kMaxPeers] at the start of a gather buffer, records follow
 struct PeerPush { char *peer[kMaxPeers]; int world, rank; size_t rec_off; unsigned epoch; unsigned *done; };
 cudaError_t launch_peer_push(const rmb_tx_record *local, int slots, const PeerPush &pp, cudaStream_t st);
-cudaError_t launch_peer_barrier(const PeerPush &pp, Counters *ctr, cudaStream_t st);   // pp.epoch = barrier epoch, second flag row
+cudaError_t launch_peer_barrier(const PeerPush &pp, Counters *ctr, cudaStream_t st);
+cudaError_t launch_peer_wait(const unsigned *flags, int world, unsigned epoch, Counters *ctr, cudaStream_t st);   // all ranks' records of `epoch` have landed   // pp.epoch = barrier epoch, second flag row
 struct TxStage { float4 *f; float *theta; int *gid; };
 // one cooperative launch: peer wait, counter zeroing, per-tx constants, tx-failure rule, stable bucketing
 int prepare_grid(int n_tx);
@@ -156,7 +157,31 @@ struct PairArrays {
     void *cub_tmp; size_t cub_tmp_bytes;
     // outputs
     int *o_tx, *o_rx; float *o_rssi, *o_sinr; uint8_t *o_outcome; double *o_rssi64, *o_sinr64;
+    // finish.cu only: all columns in ONE buffer, packed for the tick's actual row count (slab_layout), so that the
+    // lists travel to the host in a single copy; slab == nullptr: the separate arrays above
+    char *slab; int slab_flags;
 };
+// Where the columns of a tick with m rows and n_tx packets sit in the slab (16-byte aligned); the same arithmetic on
+// the device (finish kernel, m from the counters) and on the host (download).  flags: rmb_flags of the handle.
+struct SlabLayout { long long rx, rssi, tx, sinr, rssi64, sinr64, outcome, first, failed, total; };
+__host__ __device__ inline SlabLayout slab_layout(long long m, int n_tx, int flags)
+{
+    auto up = [](long long v) { return (v + 15) / 16 * 16; };
+    const bool f64 = (flags & RMB_FLAG_F64_VALUES) != 0, compact = (flags & RMB_FLAG_COMPACT) != 0;
+    SlabLayout L{};
+    long long o = 0;
+    L.rx = o; o += up(4 * m);
+    L.rssi = o; o += up(4 * m);
+    L.tx = L.sinr = -1;
+    if (!compact) { L.tx = o; o += up(4 * m); L.sinr = o; o += up(4 * m); }
+    L.rssi64 = L.sinr64 = -1;
+    if (f64) { L.rssi64 = o; o += up(8 * m); L.sinr64 = o; o += up(8 * m); }
+    L.outcome = o; o += up(m);
+    L.first = o; o += up(4ll * (n_tx + 1));
+    L.failed = o; o += up(n_tx);
+    L.total = o;
+    return L;
+}
 // exclusive scan of int32 (n elements) using tmp (>= n/1024+2 ints); total written to *total_out (device)
 cudaError_t launch_exclusive_scan(const int *in, int *out, int n, int *tmp, int *total_out, cudaStream_t st);
 // SINR medium: pair records -> (packet arrival, node index) order.

@@ -257,6 +257,18 @@ __global__ void peer_barrier_kernel(PeerPush pp, Counters *ctr)
     if (p < pp.world && !peer_wait(reinterpret_cast<const unsigned *>(pp.peer[pp.rank] + 64) + p, pp.epoch)) ctr->peer_timeout = 1;
 }
 
+// the reference media's tick has no preparation kernel to wait for the peers' records in: a one-warp kernel does it
+__global__ void peer_wait_kernel(const unsigned *flags, int world, unsigned epoch, Counters *ctr)
+{
+    if ((int)threadIdx.x < world && !peer_wait(flags + threadIdx.x, epoch)) ctr->peer_timeout = 1;
+}
+
+cudaError_t launch_peer_wait(const unsigned *flags, int world, unsigned epoch, Counters *ctr, cudaStream_t st)
+{
+    peer_wait_kernel<<<1, 32, 0, st>>>(flags, world, epoch, ctr);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_peer_barrier(const PeerPush &pp, Counters *ctr, cudaStream_t st)
 {
     peer_barrier_kernel<<<1, 32, 0, st>>>(pp, ctr);
