@@ -7,6 +7,8 @@
 // one box ... the compacted delivery lists are gathered back to the host".
 #include "../../include/radiomedium_b200.h"
 #include <algorithm>
+#include <atomic>
+#include <chrono>
 #include <condition_variable>
 #include <cstring>
 #include <functional>
@@ -29,7 +31,7 @@ struct rmb_group {
     // worker threads: run `job(r)` on every shard, wait for all
     std::vector<std::thread> workers;
     std::mutex wmu; std::condition_variable wcv, dcv;
-    std::function<int(int)> job; unsigned long long generation = 0; int remaining = 0; bool quit = false;
+    std::function<int(int)> job; std::atomic<unsigned long long> generation{0}; std::atomic<int> remaining{0}; bool quit = false;
     std::vector<int> rc;
 
     // per tick scratch
@@ -49,23 +51,30 @@ int owner_of(const rmb_group *g, int node)
     return r;
 }
 
+// Ticks come in quick succession, and a condition-variable wake-up costs tens of microseconds on each side of a
+// 0.4 ms tick: a worker that has just finished a job spins on the generation counter for a short while (kSpinUs)
+// before it goes to sleep, and the caller spins on the completion count the same way.
+constexpr int kSpinUs = 300;
+
 void worker_main(rmb_group *g, int r)
 {
     unsigned long long seen = 0;
     for (;;) {
+        const auto t0 = std::chrono::steady_clock::now();
+        while (g->generation.load(std::memory_order_acquire) == seen &&
+               std::chrono::steady_clock::now() - t0 < std::chrono::microseconds(kSpinUs)) { }
         std::function<int(int)> job;
         {
             std::unique_lock<std::mutex> lk(g->wmu);
-            g->wcv.wait(lk, [&] { return g->quit || g->generation != seen; });
+            g->wcv.wait(lk, [&] { return g->quit || g->generation.load() != seen; });
             if (g->quit) return;
-            seen = g->generation;
+            seen = g->generation.load();
             job = g->job;
         }
-        const int rc = job(r);
-        {
+        g->rc[r] = job(r);
+        if (g->remaining.fetch_sub(1, std::memory_order_acq_rel) == 1) {
             std::lock_guard<std::mutex> lk(g->wmu);
-            g->rc[r] = rc;
-            if (--g->remaining == 0) g->dcv.notify_all();
+            g->dcv.notify_all();
         }
     }
 }
@@ -76,13 +85,17 @@ int run_all(rmb_group *g, std::function<int(int)> job)
     if (g->world == 1) { const int rc = job(0); if (rc) g->err = rmb_last_error(g->h[0]); return rc; }
     {
         std::lock_guard<std::mutex> lk(g->wmu);
-        g->job = std::move(job); g->remaining = g->world; ++g->generation;
+        g->job = std::move(job); g->remaining.store(g->world);
         std::fill(g->rc.begin(), g->rc.end(), 0);
+        g->generation.fetch_add(1, std::memory_order_release);
     }
     g->wcv.notify_all();
-    {
+    const auto t0 = std::chrono::steady_clock::now();
+    while (g->remaining.load(std::memory_order_acquire) != 0 &&
+           std::chrono::steady_clock::now() - t0 < std::chrono::milliseconds(20)) { }
+    if (g->remaining.load(std::memory_order_acquire) != 0) {
         std::unique_lock<std::mutex> lk(g->wmu);
-        g->dcv.wait(lk, [&] { return g->remaining == 0; });
+        g->dcv.wait(lk, [&] { return g->remaining.load() == 0; });
     }
     for (int r = 0; r < g->world; ++r)
         if (g->rc[r]) { g->err = std::string("shard ") + std::to_string(r) + ": " + rmb_last_error(g->h[r]); return g->rc[r]; }
