@@ -125,3 +125,16 @@ def test_group_reference_media_and_errors(rsb, orc):
         with pytest.raises(rsb.MediumError) as e:
             g.tick(np.arange(40, dtype=np.int32))
         assert e.value.code == A.ERR_CAPACITY
+
+
+def test_group_with_fewer_nodes_than_devices(rsb, orc):
+    """Three nodes on four handles: one shard owns nobody, another a single node; the lists still merge to the oracle's."""
+    x, y = np.array([0.0, 20.0, 45.0]), np.zeros(3)
+    for model, omodel in (("udgm", 1), ("sinr", 4)):
+        with rsb.Group(model, devices=(0, 0, 0, 0), max_tx_per_tick=8, compact=True) as g:
+            g.set_nodes(x, y)
+            m = g.tick(np.array([0, 2], dtype=np.int32)).merged()
+            rssi, recv = g.node_info_f64()
+        ref = orc.tick(orc.params(omodel), orc.NodeSet(x, y), orc.make_packets(np.array([0, 2]), 0.0, 26))
+        assert np.array_equal(m["tx"], ref["pairs"]["tx"]) and np.array_equal(m["rx"], ref["pairs"]["rx"])
+        assert np.array_equal(m["outcome"], ref["pairs"]["outcome"]) and len(rssi) == 3
