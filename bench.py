@@ -620,6 +620,42 @@ def run_c5(args):
             sweep_ms.append(tm["ms_sweep"]); launches += tm["kernel_launches"]
         return times, dec, pairs, sweep_ms, launches
 
+    def pipelined(steps, sets=4):
+        """The same host-lists-in / host-lists-out tick, K ticks timed as a whole, with the asynchronous forms of the
+        C-ABI: tick k is enqueued, the positions of tick k+1 are uploaded beside it (rmb_update_positions_async), then
+        tick k's lists are fetched.  Positions and transmitters cycle through `sets` pre-drawn consecutive ticks held
+        in pinned host memory (drawing 2 M uniforms per tick on the host would dwarf the tick)."""
+        pxs = [torch.empty(hi - lo, dtype=torch.float64).pin_memory().numpy() for _ in range(sets)]
+        pys = [torch.empty(hi - lo, dtype=torch.float64).pin_memory().numpy() for _ in range(sets)]
+        srcs, plans = [], []
+        for j in range(sets):
+            src, plan = next_tick()
+            pxs[j][:], pys[j][:] = px[lo:hi], py[lo:hi]
+            srcs.append(src); plans.append(plan)
+        walls = []
+        for phase_steps in (min(8, steps), steps):                   # warm-up pass, timed pass
+            med.update_positions(pxs[0], pys[0])
+            torch.cuda.synchronize()
+            if G > 1:
+                med.peer_barrier_enqueue()
+                torch.cuda.synchronize()
+            pairs = 0
+            t0 = time.perf_counter()
+            for k in range(phase_steps):
+                j = k % sets
+                if G == 1:
+                    med.build_tx_records(srcs[j], rec_local.data_ptr())
+                    med.tick_enqueue(T, rec_local.data_ptr())
+                else:
+                    med.peer_push(plans[j].local_src[rank])
+                    med.tick_peers_enqueue()
+                med.update_positions_async(pxs[(j + 1) % sets], pys[(j + 1) % sets])
+                med.tick_finish()
+                pairs += med.fetch(copy=False).n_pairs
+            torch.cuda.synchronize()
+            walls.append((time.perf_counter() - t0) / phase_steps)
+        return walls[-1], pairs
+
     sampler = ClockSampler(local, period=0.0003)        # the timed windows are ~0.3 ms
     sampler.start()
     timed("resident", args.warmup)
@@ -631,8 +667,13 @@ def run_c5(args):
     med.set_tuning(0, 0)
     timed("e2e", max(1, args.warmup // 2))
     e_times, e_dec, e_pairs, _, _ = timed("e2e", args.steps)
+    p_wall, _ = pipelined(min(args.steps, 200))
     sampler.stop_flag = True
     sampler.join(timeout=2)
+    ptot = torch.tensor([p_wall], dtype=torch.float64, device=dev)
+    if G > 1:
+        dist.all_reduce(ptot, op=dist.ReduceOp.MAX)
+    p_wall = float(ptot[0])
     tot = torch.tensor([sum(times), sum(e_times)], dtype=torch.float64, device=dev)
     cnt = torch.tensor([float(dec), float(e_dec), float(e_pairs)], dtype=torch.float64, device=dev)
     if G > 1:
@@ -654,7 +695,11 @@ def run_c5(args):
                 "clocks": clocks,
                 "e2e": {"value": float(cnt[1]) / float(tot[1]), "unit": UNIT, "ms_per_step": 1e3 * float(tot[1]) / args.steps,
                         "h2d_bytes_per_step": int(16 * (hi - lo) + 4 * T / G), "d2h_bytes_per_step": int(9 * float(cnt[2]) / args.steps / G + 5 * T),
-                        "heard_pairs_per_tick": float(cnt[2]) / args.steps},
+                        "heard_pairs_per_tick": float(cnt[2]) / args.steps,
+                        "pipelined": {"ms_per_step": 1e3 * p_wall, "value": float(cnt[1]) / args.steps / p_wall, "unit": UNIT,
+                                      "what": "the same host-lists-in / host-lists-out tick through the asynchronous C-ABI forms, K ticks "
+                                              "timed as a whole: tick k enqueued, positions of tick k+1 uploaded beside it "
+                                              "(rmb_update_positions_async), tick k's lists fetched; max over ranks"}},
                 "gpu_launches": int(launches),
                 "roofline": {"bound": "sfu", "kernel": "sweep_kernel", "achieved": achieved / 1e9, "peak": peak / 1e9,
                              "unit": "G MUFU-op/s (1 rsqrt per decision; peak = 148 SM x 16 lanes x sm_max_mhz)",

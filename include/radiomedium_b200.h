@@ -170,6 +170,14 @@ int rmb_set_matrix(rmb_handle *h, int32_t n, const double *matrix);
  * idx==NULL => dense replace of all `count`==n nodes; z==NULL => z=0 (Position.set(x,y)). */
 int rmb_update_positions(rmb_handle *h, int32_t count, const int32_t *idx,
                          const double *x, const double *y, const double *z);
+/* The dense form without the wait: the next positions of ALL nodes are uploaded on a copy stream into a second set of
+ * arrays and become the node table at the next call that settles the handle (a tick, an update, rmb_build_tx_records,
+ * rmb_fetch ...; rmb_tick_finish alone does not).
+ * It does NOT wait for an enqueued tick (rmb_tick_enqueue / rmb_tick_peers_enqueue): the upload of tick k+1's
+ * positions runs beside tick k on the GPU -- per-tick mobility of every node (BASELINE configs[4]) costs one PCIe
+ * transfer that hides behind the previous tick.  The caller's arrays must stay untouched until that next settling
+ * call returns (pinned memory makes the copy asynchronous; pageable memory is staged by the driver inside the call). */
+int rmb_update_positions_async(rmb_handle *h, int32_t count, const double *x, const double *y, const double *z);
 /* node-config-set rf-power / wireless-channel / rx-loss / tx-loss / radio-state
  * (net/SimulatorJSONHandler.java:123-143).  NULL field arrays are left unchanged. */
 int rmb_update_radio(rmb_handle *h, int32_t count, const int32_t *idx, const double *txpower_dbm,

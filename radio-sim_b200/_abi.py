@@ -20,7 +20,7 @@ FLAG_COMPACT = 2
 
 # every symbol include/radiomedium_b200.h declares
 SYMBOLS = ("rmb_version", "rmb_config_default", "rmb_create", "rmb_destroy", "rmb_last_error",
-           "rmb_set_nodes", "rmb_set_matrix", "rmb_update_positions", "rmb_update_radio", "rmb_tick",
+           "rmb_set_nodes", "rmb_set_matrix", "rmb_update_positions", "rmb_update_positions_async", "rmb_update_radio", "rmb_tick",
            "rmb_build_tx_records", "rmb_tick_records", "rmb_tick_resident", "rmb_fetch",
            "rmb_node_info", "rmb_node_info_f64", "rmb_last_timing", "rmb_set_tuning", "rmb_get_stream", "rmb_set_stream",
            "rmb_peer_export", "rmb_peer_open", "rmb_peer_push", "rmb_peer_push_records", "rmb_tick_peers",
@@ -91,6 +91,7 @@ def load():
     L.rmb_set_nodes.argtypes = [H, C.c_int32, pd, pd, pd, pd, pi, pu8, pd, pd, pi]
     L.rmb_set_matrix.argtypes = [H, C.c_int32, pd]
     L.rmb_update_positions.argtypes = [H, C.c_int32, pi, pd, pd, pd]
+    L.rmb_update_positions_async.argtypes = [H, C.c_int32, pd, pd, pd]
     L.rmb_update_radio.argtypes = [H, C.c_int32, pi, pd, pi, pu8, pd, pd]
     L.rmb_tick.argtypes = [H, C.c_int32, pi, pd, pi, pd, C.c_size_t, C.POINTER(Result)]
     L.rmb_build_tx_records.argtypes = [H, C.c_int32, pi, pd, pi, C.c_void_p]

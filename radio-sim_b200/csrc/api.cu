@@ -70,6 +70,10 @@ struct rmb_handle {
     bool maybe_draws = false;
     bool planar = true; double planar_z = 0.0;      // all nodes share one z (2-D sweep) and which
     cudaEvent_t ev_h2d = nullptr;                   // "the caller's arrays have been read" (dense position updates)
+    // rmb_update_positions_async: the next positions of ALL nodes, uploaded on a copy stream into a second set of
+    // arrays while a tick may still be running on the first; swapped in by the next call that settles the handle
+    DevBuf<double> x2, y2, z2; cudaStream_t st_copy = nullptr; cudaEvent_t ev_staged = nullptr;
+    bool staged = false; int staged_n = 0, staged_planar = 1; double staged_z = 0.0; bool staged_has_z = false;
 
     // device state
     DevBuf<double> x, y, z, txpower, rxprob, txprob, matrix;
@@ -155,7 +159,8 @@ struct rmb_handle {
 #define RMB_CK(h, expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) return (h)->cuda_fail(e__, #expr); } while (0)
 // an enqueued tick (rmb_tick_enqueue) is settled before anything else touches the handle
 static int finish_pending(rmb_handle *h);
-#define RMB_SETTLE(h) do { int rc__ = finish_pending(h); if (rc__) return rc__; } while (0)
+static int apply_staged(rmb_handle *h);
+#define RMB_SETTLE(h) do { int rc__ = finish_pending(h); if (rc__) return rc__; rc__ = apply_staged(h); if (rc__) return rc__; } while (0)
 
 namespace {
 
@@ -310,6 +315,11 @@ static int refresh_geometry(rmb_handle *h, bool reorder, int planar_known = -1)
     Geom g{};
     if (planar_known < 0) RMB_CK(h, cudaMemcpyAsync(&g, h->geom.p, sizeof(Geom), cudaMemcpyDeviceToHost, h->st));
     if (reorder) {
+        // the last tick's per-receiver results are in the OLD work order: turn them into per-node values before it goes
+        if (h->node_info_dirty && h->n_work > 0 && h->node_rssi.p) {
+            RMB_CK(h, launch_node_info(work_arrays(h), slot_arrays(h), h->node_rssi.p, h->node_rssi64.p, h->node_recv.p, h->st));
+            h->node_info_dirty = false;
+        }
         ReorderScratch sc{h->ro_key.p, h->ro_key_alt.p, h->ro_val.p, h->ro_val_alt.p, h->ro_tmp.p, h->ro_tmp.cap};
         RMB_CK(h, launch_reorder(nd, h->gid.p, h->geom.p, h->groups, h->n_work, sc, h->perm.p, h->st));
     }
@@ -387,6 +397,8 @@ int rmb_create(const rmb_config *cfg, rmb_handle **out)
     if ((e = cudaStreamCreateWithFlags(&h->st2, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
     for (auto &ev : h->ev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) return bail(e, "cudaEventCreate");
     if ((e = cudaEventCreateWithFlags(&h->ev_h2d, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
+    if ((e = cudaEventCreateWithFlags(&h->ev_staged, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
+    if ((e = cudaStreamCreateWithFlags(&h->st_copy, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
     if ((e = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming)) != cudaSuccess ||
         (e = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
     if ((e = h->dp.ensure(1)) != cudaSuccess || (e = h->geom.ensure(1)) != cudaSuccess ||
@@ -436,6 +448,9 @@ int rmb_destroy(rmb_handle *h)
     for (auto &ev : h->ev) if (ev) cudaEventDestroy(ev);
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     if (h->ev_h2d) cudaEventDestroy(h->ev_h2d);
+    if (h->ev_staged) cudaEventDestroy(h->ev_staged);
+    if (h->st_copy) { cudaStreamSynchronize(h->st_copy); cudaStreamDestroy(h->st_copy); }
+    h->x2.release(); h->y2.release(); h->z2.release();
     if (h->ev_join) cudaEventDestroy(h->ev_join);
     for (int r = 0; r < kMaxPeers; ++r) if (h->peer.ipc[r] && h->peer.peer[r]) cudaIpcCloseMemHandle(h->peer.peer[r]);
     if (h->peer.buf) cudaFree(h->peer.buf);
@@ -556,6 +571,50 @@ extern "C" int rmb_update_positions(rmb_handle *h, int32_t count, const int32_t 
     // the caller may reuse its arrays on return: wait for the upload (not for the kernels queued behind it)
     if (!idx) RMB_CK(h, cudaEventSynchronize(h->ev_h2d));
     else if (planar_known >= 0) RMB_CK(h, cudaStreamSynchronize(h->st));           // staged copies of idx / x / y / z
+    return RMB_OK;
+}
+
+// positions staged by rmb_update_positions_async become the node table's: the handle's stream waits for the upload,
+// the two sets of arrays trade places, the work-order copy is rebuilt -- all enqueued, nothing waits on the host
+static int apply_staged(rmb_handle *h)
+{
+    if (!h->staged) return RMB_OK;
+    h->staged = false;
+    if (h->staged_n != h->n || !h->have_nodes) return RMB_OK;           // the node table changed meanwhile: the staged set is void
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    RMB_CK(h, cudaStreamWaitEvent(h->st, h->ev_staged, 0));
+    std::swap(h->x.p, h->x2.p); std::swap(h->x.cap, h->x2.cap);
+    std::swap(h->y.p, h->y2.p); std::swap(h->y.cap, h->y2.cap);
+    if (h->staged_has_z) { std::swap(h->z.p, h->z2.p); std::swap(h->z.cap, h->z2.cap); }
+    else RMB_CK(h, cudaMemsetAsync(h->z.p, 0, (size_t)h->n * sizeof(double), h->st));      // Position.set(x, y) zeroes z
+    h->planar_z = h->staged_z;
+    constexpr int kReorderEvery = 8;
+    const bool reorder = (h->dense_updates++ % kReorderEvery) == 0;
+    return refresh_geometry(h, reorder, h->staged_planar);
+}
+
+extern "C" int rmb_update_positions_async(rmb_handle *h, int32_t count, const double *x, const double *y, const double *z)
+{
+    if (!h) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    // (no settling here: the point is to run beside an enqueued tick)
+    if (!h->have_nodes) return h->fail(RMB_ERR_STATE, "rmb_update_positions_async before rmb_set_nodes");
+    if (count != h->n || (count > 0 && (!x || !y))) return h->fail(RMB_ERR_INVALID, "rmb_update_positions_async: dense updates only (count == n, x and y given)");
+    if (count == 0) return RMB_OK;
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    if (h->staged) RMB_CK(h, cudaStreamSynchronize(h->st_copy));        // a staged set nobody consumed is overwritten
+    const size_t b = (size_t)count * sizeof(double);
+    RMB_CK(h, h->x2.ensure(count)); RMB_CK(h, h->y2.ensure(count));
+    if (z) RMB_CK(h, h->z2.ensure(count));
+    // the staging arrays were the node table before the last swap: the tick that read them must be done before they
+    // are overwritten -- it is: a swap only happens when the handle is settled, i.e. after that tick's results were taken
+    RMB_CK(h, cudaMemcpyAsync(h->x2.p, x, b, cudaMemcpyHostToDevice, h->st_copy));
+    RMB_CK(h, cudaMemcpyAsync(h->y2.p, y, b, cudaMemcpyHostToDevice, h->st_copy));
+    if (z) RMB_CK(h, cudaMemcpyAsync(h->z2.p, z, b, cudaMemcpyHostToDevice, h->st_copy));
+    RMB_CK(h, cudaEventRecord(h->ev_staged, h->st_copy));
+    h->staged_planar = 1; h->staged_z = z ? z[0] : 0.0; h->staged_has_z = z != nullptr;
+    if (z) for (int i = 1; i < count; ++i) if (z[i] != z[0]) { h->staged_planar = 0; break; }
+    h->staged = true; h->staged_n = count;
     return RMB_OK;
 }
 

@@ -142,6 +142,14 @@ class Medium:
         self._ck(self._lib.rmb_update_positions(self._h, c, _ptr(idx, C.c_int32), _ptr(x, C.c_double),
                                                 _ptr(y, C.c_double), _ptr(z, C.c_double)))
 
+    def update_positions_async(self, x, y, z=None):
+        """Dense update that does not wait for an enqueued tick: uploaded beside it, swapped in by the next settling call.
+        The arrays are used as they are (no copy): keep them untouched until that call returns."""
+        if x.dtype != np.float64 or y.dtype != np.float64 or not x.flags.c_contiguous or not y.flags.c_contiguous:
+            raise ValueError("update_positions_async takes contiguous float64 arrays (they are read asynchronously)")
+        self._ck(self._lib.rmb_update_positions_async(self._h, x.shape[0], _ptr(x, C.c_double), _ptr(y, C.c_double),
+                                                      None if z is None else _ptr(z, C.c_double)))
+
     def update_radio(self, idx=None, txpower_dbm=None, channel=None, enabled=None, rxprob=None, txprob=None):
         fields = [f for f in (txpower_dbm, channel, enabled, rxprob, txprob) if f is not None]
         c = len(idx) if idx is not None else (len(fields[0]) if fields else 0)

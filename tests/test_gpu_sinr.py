@@ -342,3 +342,43 @@ def test_limits_are_errors_not_wrong_results(rsb):
             r["txprob"][3] = 1.0
             recs.copy_(torch.from_numpy(np.frombuffer(r.tobytes(), dtype=np.uint8).copy()))
             assert m.tick_records(4, recs.data_ptr()).n_tx == 4
+
+
+def test_positions_uploaded_beside_the_running_tick(rsb, orc):
+    """rmb_update_positions_async: tick k is enqueued, the positions of tick k+1 are uploaded while it runs and swapped
+    in when the handle is next settled; every tick must see exactly its own positions (per-tick mobility, C5)."""
+    import torch
+    x, y, z, ch = random_deployment(81, 30_000, 1500.0, channels=4)
+    rng = np.random.default_rng(82)
+    n, t = len(x), 300
+    px = [torch.empty(n, dtype=torch.float64).pin_memory().numpy() for _ in range(2)]
+    py = [torch.empty(n, dtype=torch.float64).pin_memory().numpy() for _ in range(2)]
+    px[0][:], py[0][:] = x, y
+    rec = torch.zeros(t * 48, dtype=torch.uint8, device="cuda")
+    with rsb.Medium("sinr", f64_values=True) as m:
+        m.set_nodes(x, y, z, channel=ch)
+        for k in range(12):
+            cur, nxt = k % 2, (k + 1) % 2
+            src = rng.permutation(n)[:t].astype(np.int32)
+            m.build_tx_records(src, rec.data_ptr())                  # settles: positions of tick k are the node table now
+            m.tick_enqueue(t, rec.data_ptr())
+            px[nxt][:] = np.clip(px[cur] + rng.uniform(-0.5, 0.5, n), 0, 1500.0)
+            py[nxt][:] = np.clip(py[cur] + rng.uniform(-0.5, 0.5, n), 0, 1500.0)
+            m.update_positions_async(px[nxt], py[nxt])               # beside the running tick
+            cnt = m.tick_finish()
+            r = m.fetch()
+            if k == 5:
+                rssi, _ = m.node_info_f64()                          # of tick 5, although tick 6's positions are in already
+            ref = orc.tick(orc.params(orc.MODEL_SINR), orc.NodeSet(px[cur].copy(), py[cur].copy(), z, channel=ch),
+                           orc.make_packets(src, 0.0, ch[src]), threads=8, want_total=True)
+            assert cnt.n_pairs == ref["n_pairs"]
+            compare(r, ref)
+            if k == 5:
+                assert np.abs(rssi - ref["total_dbm"]).max() < SINR_TOL_DB
+        # a staged set that nobody consumed before the node table changes is void
+        m.update_positions_async(px[0], py[0])
+        m.set_nodes(x[:1000], y[:1000], channel=ch[:1000])
+        r = m.tick(np.arange(20, dtype=np.int32))
+        ref = orc.tick(orc.params(orc.MODEL_SINR), orc.NodeSet(x[:1000], y[:1000], channel=ch[:1000]),
+                       orc.make_packets(np.arange(20), 0.0, ch[:20]))
+        compare(r, ref)
