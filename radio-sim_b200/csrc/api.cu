@@ -114,6 +114,11 @@ struct rmb_handle {
     PinBuf<int> ho_tx, ho_rx, ho_first; DevBuf<int> o_first; PinBuf<float> ho_rssi, ho_sinr; PinBuf<uint8_t> ho_outcome, ho_failed;
     PinBuf<double> ho_rssi64, ho_sinr64;
     DevBuf<char> o_slab; PinBuf<char> ho_slab; bool slab_ready = false;     // finish.cu path: all columns packed, one copy (kernels.h slab_layout)
+    // The synchronous calls (rmb_tick, rmb_tick_records, rmb_tick_peers) copy the slab home BEHIND the finish kernel,
+    // before the host knows the row count: as many bytes as the previous tick's lists took plus 1/64.  If that
+    // covers this tick's lists -- it does whenever consecutive ticks are alike -- the counters and the lists arrive
+    // with ONE stream synchronisation instead of two (wait, look at the count, copy, wait again).
+    bool want_download = false; size_t slab_pred = 0, slab_copied = 0;
 
     // multi-GPU exchange over peer memory (rmb_peer_*)
     struct Peer {
@@ -842,6 +847,8 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
 {
     int rc;
     int launches = 0, sweeps = 0;
+    const bool lists_wanted = h->want_download;
+    h->want_download = false; h->slab_copied = 0;
     if (h->cfg.half_duplex) ++h->hd_epoch;            // every evaluation stamps its own sources (a redo stamps them again)
     const NodeArrays nd = node_arrays(h);
     const WorkArrays wk = work_arrays(h);
@@ -981,6 +988,14 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
                 if (!draws) { RMB_CK(h, launch_emit_sinr(nd, h->dp.p, d_rec, n_tx, pr, h->val.p, pa, -1, false, h->ctr.p, nullptr, h->st)); launches += 1; }
             }
             RMB_CK(h, cudaEventRecord(h->ev[4], h->st));
+            h->slab_copied = 0;
+            static const bool guess_off = getenv("RMB_SLAB_GUESS") && atoi(getenv("RMB_SLAB_GUESS")) == 0;    // A/B knob
+            if (dev_publish && lists_wanted && !guess_off && !h->async_mode && !draws && h->slab_pred > 0 && n_tx > 0) {
+                const size_t guess = std::min(h->slab_pred, h->o_slab.cap);
+                RMB_CK(h, h->ho_slab.ensure(guess));
+                RMB_CK(h, cudaMemcpyAsync(h->ho_slab.p, h->o_slab.p, guess, cudaMemcpyDeviceToHost, h->st));
+                h->slab_copied = guess;
+            }
             if (h->async_mode && attempt == 0 && !draws) {
                 // enqueue only: the counters travel to the host behind the tick, finish_pending looks at them
                 if (!dev_publish) RMB_CK(h, cudaMemcpyAsync(h->h_ctr.p, h->ctr.p, sizeof(Counters), cudaMemcpyDeviceToHost, h->st));
@@ -1091,9 +1106,15 @@ static int download(rmb_handle *h, rmb_result *out)
     if (h->slab_ready) {
         // the finish kernel packed every column for exactly m rows: ONE copy, then pointers into the pinned slab
         const SlabLayout L = slab_layout(m, nt, h->cfg.flags);
-        RMB_CK(h, h->ho_slab.ensure((size_t)L.total));
-        RMB_CK(h, cudaMemcpyAsync(h->ho_slab.p, h->o_slab.p, (size_t)L.total, cudaMemcpyDeviceToHost, h->st));
-        RMB_CK(h, cudaStreamSynchronize(h->st));
+        if (h->slab_copied < (size_t)L.total) {          // no guess, or this tick's lists are longer than the guess: the rest
+            size_t have = h->slab_copied;
+            if (h->ho_slab.cap < (size_t)L.total) have = 0;                 // the pinned buffer moves: everything again
+            RMB_CK(h, h->ho_slab.ensure((size_t)L.total));
+            RMB_CK(h, cudaMemcpyAsync(h->ho_slab.p + have, h->o_slab.p + have, (size_t)L.total - have, cudaMemcpyDeviceToHost, h->st));
+            RMB_CK(h, cudaStreamSynchronize(h->st));
+        }
+        h->slab_copied = 0;
+        h->slab_pred = (size_t)L.total + (size_t)L.total / 64 + 4096;       // every byte of the guess is PCIe time
         char *b = h->ho_slab.p;
         rmb_result &r = h->last;
         r.rx = (const int32_t *)(b + L.rx); r.rssi_dbm = (const float *)(b + L.rssi); r.outcome = (const uint8_t *)(b + L.outcome);
@@ -1170,6 +1191,7 @@ int rmb_tick(rmb_handle *h, int32_t n_tx, const int32_t *src, const double *powe
     RMB_CK(h, h->rec.ensure(std::max(n_tx, 1)));
     int rc = stage_records(h, n_tx, src, power_dbm, channel, h->rec.p, true);
     if (rc) return rc;
+    h->want_download = true;
     rc = compute(h, n_tx, h->rec.p, uniforms, n_uniforms);
     if (rc && rc != RMB_ERR_UNIFORMS) return rc;
     int rc2 = download(h, out);
@@ -1200,6 +1222,7 @@ int rmb_tick_records(rmb_handle *h, int32_t n_tx, const void *d_records, const d
     if (!h->have_nodes) return h->fail(RMB_ERR_STATE, "rmb_tick_records before rmb_set_nodes");
     if (n_tx < 0 || (n_tx > 0 && !d_records) || !out) return h->fail(RMB_ERR_INVALID, "rmb_tick_records: bad arguments");
     RMB_CK(h, cudaSetDevice(h->cfg.device));
+    h->want_download = true;
     int rc = compute(h, n_tx, (const rmb_tx_record *)d_records, uniforms, n_uniforms);
     if (rc && rc != RMB_ERR_UNIFORMS) return rc;
     int rc2 = download(h, out);
@@ -1422,6 +1445,7 @@ int rmb_tick_peers(rmb_handle *h, const double *uniforms, size_t n_uniforms, rmb
     std::lock_guard<std::mutex> lk(h->mu);
     RMB_SETTLE(h);
     RMB_CK(h, cudaSetDevice(h->cfg.device));
+    h->want_download = true;
     int rc = tick_peers_locked(h, uniforms, n_uniforms);
     if (rc && rc != RMB_ERR_UNIFORMS) return rc;
     int rc2 = download(h, out);

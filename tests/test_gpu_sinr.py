@@ -382,3 +382,26 @@ def test_positions_uploaded_beside_the_running_tick(rsb, orc):
         ref = orc.tick(orc.params(orc.MODEL_SINR), orc.NodeSet(x[:1000], y[:1000], channel=ch[:1000]),
                        orc.make_packets(np.arange(20), 0.0, ch[:20]))
         compare(r, ref)
+
+
+@pytest.mark.parametrize("compact", [False, True])
+def test_lists_copied_behind_the_tick_on_a_guessed_length(rsb, orc, compact):
+    """The synchronous calls copy the result slab home behind the finish kernel on the previous tick's length (+ 1/8):
+    ticks that grow, shrink, repeat and go empty must all come back whole (a short guess is topped up by a second copy)."""
+    x, y, z, ch = random_deployment(91, 6000, 500.0)
+    nodes = orc.NodeSet(x, y, z, channel=ch)
+    p = orc.params(orc.MODEL_SINR)
+    with rsb.Medium("sinr", f64_values=not compact, compact=compact) as m:
+        m.set_nodes(x, y, z, channel=ch)
+        for k, n_tx in enumerate([3, 3, 200, 200, 1, 0, 40, 45, 600, 2]):
+            src = pick_sources(1000 + k, 6000, n_tx) if n_tx else np.zeros(0, dtype=np.int32)
+            r = m.tick(src)
+            ref = orc.tick(p, nodes, orc.make_packets(src, 0.0, ch[src]), threads=8)
+            assert r.n_pairs == ref["n_pairs"]
+            if compact:
+                assert np.array_equal(r.tx_column(), ref["pairs"]["tx"]) and np.array_equal(r.rx, ref["pairs"]["rx"])
+                assert np.array_equal(r.outcome, ref["pairs"]["outcome"])
+                assert r.tx_first[-1] == ref["n_pairs"] and len(r.tx_first) == n_tx + 1
+                assert np.array_equal(r.tx_failed, ref["tx_failed"])
+            else:
+                compare(r, ref)

@@ -299,3 +299,19 @@ def test_adapter_host_logic_without_a_gpu(monkeypatch):
     sim.step_time(5000, 11)
     step = [m for m in emu.sent if m.get("command") == "time-step"][-1]
     assert [ni["rssi"] for ni in step["parameters"]["node-info"]] == [-90.0, -90.0, -90.0]
+
+
+def test_link_quality_is_accepted_and_changes_nothing(oracle_factory):
+    """`link-quality` is a logged TODO in the reference (net/SimulatorJSONHandler.java:155-168): the command gets the
+    plain OK reply and no medium ever sees it -- the same tick delivers the same frames before and after."""
+    def run(with_command):
+        s = Session(oracle_factory)
+        s.cmd(s.ctrl, "configuration-set", parameters={"propagation-option": "udgm"})
+        grid10(s)
+        emu = s.emus[0]
+        if with_command:
+            rid = s.cmd(emu, "link-quality", link={"src": 1, "dst": 2, "quality": 0}, **{"wireless-channel": 26})
+            assert [m for m in emu.sent if m.get("id") == rid][0]["reply"] == "OK"
+        s.step_to(1000, [(emu, i + 1, 0, "0102030405", {}) for i in range(10)])
+        return sorted((int(m["node-id"]), m["time-start"], m["packet-data"]) for m in s.received())
+    assert run(True) == run(False) and len(run(False)) > 0

@@ -38,7 +38,7 @@ for i in range(reps):
     tm = med.timing()
     rows.append((e0.elapsed_time(e1) * 1e3, wall * 1e6, tm["ms_prepare"] * 1e3, tm["ms_sweep"] * 1e3, tm["ms_resolve"] * 1e3,
                  tm["ms_emit"] * 1e3, tm["ms_total"] * 1e3))
-rows = np.array(rows[3:])
+rows = np.array(rows[min(3, reps - 1):])
 print("G", G, "tuning", hex(tuning), "pairs", r.n_pairs, "decisions", r.n_decisions, "launches", tm["kernel_launches"])
 print("median us: events %.1f wall %.1f | prepare %.1f sweep %.1f resolve %.1f emit %.1f total %.1f" % tuple(np.median(rows, axis=0)))
 med.close()
