@@ -98,8 +98,9 @@ typedef struct rmb_config {
  *   - N2N needs the source's integer id, which a tx record does not carry: RMB_MODEL_N2N with n_shards > 1 is
  *     rejected by rmb_create (RMB_ERR_UNSUPPORTED);
  *   - stochastic reception (any rx/tx probability strictly between 0 and 1) on sharded receivers needs the
- *     rmb_tick_draws_begin/_end pair; any other tick entry point returns RMB_ERR_UNSUPPORTED for such a tick,
- *     also when the probability arrives in a record built by another shard;
+ *     rmb_tick_draws_begin/_end pair (SINR medium; rmb_group_tick goes through it by itself); any other per-handle
+ *     tick entry point returns RMB_ERR_UNSUPPORTED for such a tick, also when the probability arrives in a record
+ *     built by another shard;
  *   - at most 16 handles exchange records with rmb_peer_* (RMB_ERR_INVALID). */
 
 /* One active transmission as the device sees it (RadioPacket.java:46-52 plus the
@@ -293,9 +294,12 @@ int rmb_node_info_f64(rmb_handle *h, double *rssi_dbm, uint8_t *receiving);
  *                      p = r * slots + i is packet packet_of[p] of the caller's list (-1 = padding).  Shards own
  *                      increasing node blocks, so packet t's rows in the reference's order are shard 0's rows of t,
  *                      then shard 1's, ...  (*slots_out, packet_of[n_devices * max_tx_per_tick] may be NULL for
- *                      n_devices == 1, where position == packet).  uniforms: as for rmb_tick, used by a group of ONE
- *                      device (RMB_ERR_UNIFORMS tells how many a tick needs); on several devices stochastic reception
- *                      needs the draws API of the handles (rmb_group_shard) and returns RMB_ERR_UNSUPPORTED here. */
+ *                      n_devices == 1, where position == packet).  uniforms: as for rmb_tick (RMB_ERR_UNIFORMS tells
+ *                      how many a tick needs).  On several devices stochastic reception goes through the handles'
+ *                      rmb_tick_peers_draws_begin / rmb_tick_draws_end with the per-packet draw counts gathered in
+ *                      between, in the caller's packet order: the same draws as one device makes; every results[r]
+ *                      then carries the GLOBAL n_uniforms_used.  (SINR medium; the reference media with draws on
+ *                      several devices return RMB_ERR_UNSUPPORTED.) */
 typedef struct rmb_group rmb_group;
 int         rmb_group_create(const rmb_config *cfg, int32_t n_devices, const int32_t *devices, int32_t max_tx_per_tick, rmb_group **out);
 int         rmb_group_destroy(rmb_group *g);
@@ -314,6 +318,11 @@ int rmb_group_node_info_f64(rmb_group *g, double *rssi_dbm, uint8_t *receiving);
 /* Moves a shard: the global index of the handle's first node (rmb_config.rx_base) for the node table that the next
  * rmb_set_nodes uploads.  What rmb_group_set_nodes uses when the node count, and with it the partition, changes. */
 int rmb_set_shard_base(rmb_handle *h, int32_t rx_base);
+/* 1 when a tick on this handle may draw from the uniform stream -- some node of its table has an rx or tx probability
+ * below 1, or the model draws by itself (N2N; UDGM with success_ratio_rx < 1: UDGMRadioMedium.java:104-111) -- else 0.
+ * When ANY shard of a partition says 1, every shard has to evaluate its ticks through rmb_tick_draws_begin/_end (a
+ * packet's source may sit on another shard); rmb_group_tick asks this. */
+int32_t rmb_may_draw(rmb_handle *h);
 
 int rmb_last_timing(const rmb_handle *h, rmb_timing *out);
 /* CUDA stream the handle's kernels and copies run on (a cudaStream_t passed as void*).

@@ -510,6 +510,13 @@ int rmb_set_shard_base(rmb_handle *h, int32_t rx_base)
     return RMB_OK;
 }
 
+int32_t rmb_may_draw(rmb_handle *h)
+{
+    if (!h) return 0;
+    std::lock_guard<std::mutex> lk(h->mu);
+    return h->maybe_draws ? 1 : 0;
+}
+
 int rmb_set_matrix(rmb_handle *h, int32_t n, const double *matrix)
 {
     if (!h) return RMB_ERR_INVALID;

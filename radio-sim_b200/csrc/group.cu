@@ -6,6 +6,7 @@
 // and their device-to-host copies -- run side by side.  north_star: "receivers are partitioned across the 8 B200s of
 // one box ... the compacted delivery lists are gathered back to the host".
 #include "../../include/radiomedium_b200.h"
+#include <cuda_runtime.h>
 #include <algorithm>
 #include <atomic>
 #include <chrono>
@@ -38,6 +39,13 @@ struct rmb_group {
     // per tick scratch
     std::vector<std::vector<int32_t>> l_src, l_chan; std::vector<std::vector<double>> l_power;
     std::vector<std::vector<int32_t>> l_packet;  // slot -> original packet index
+
+    // stochastic reception on several devices (tick_with_draws): per-shard device scratch for the draw counts of the
+    // shard [positions], of all shards [world][positions] and the packets' positions in arrival order; host copies
+    int model = 0;
+    std::vector<int32_t *> d_counts, d_all, d_order; std::vector<size_t> scratch_positions;
+    std::vector<int32_t> h_counts, h_order;
+    std::vector<std::string> shard_err;          // a failure of the group's own CUDA calls on shard r
 };
 
 namespace {
@@ -101,8 +109,75 @@ int run_all(rmb_group *g, std::function<int(int)> job)
         g->dcv.wait(lk, [&] { return g->remaining.load() == 0; });
     }
     for (int r = 0; r < g->world; ++r)
-        if (g->rc[r]) { g->err = std::string("shard ") + std::to_string(r) + ": " + rmb_last_error(g->h[r]); return g->rc[r]; }
+        if (g->rc[r]) {
+            g->err = std::string("shard ") + std::to_string(r) + ": " + (g->shard_err[r].empty() ? rmb_last_error(g->h[r]) : g->shard_err[r].c_str());
+            g->shard_err[r].clear();
+            return g->rc[r];
+        }
     return RMB_OK;
+}
+
+int cuda_failed(rmb_group *g, int r, cudaError_t e, const char *what)
+{
+    g->shard_err[r] = std::string(what) + ": " + cudaGetErrorString(e);
+    return RMB_ERR_CUDA;
+}
+#define GRP_CK(g, r, call, what) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return cuda_failed(g, r, e_, what); } while (0)
+
+// device scratch of shard r for a tick of `positions` gathered record positions (on the shard's worker thread)
+int ensure_draw_scratch(rmb_group *g, int r, size_t positions)
+{
+    GRP_CK(g, r, cudaSetDevice(g->device[r]), "cudaSetDevice");
+    if (positions <= g->scratch_positions[r]) return RMB_OK;
+    cudaFree(g->d_counts[r]); cudaFree(g->d_all[r]); cudaFree(g->d_order[r]);
+    g->d_counts[r] = g->d_all[r] = g->d_order[r] = nullptr; g->scratch_positions[r] = 0;
+    const size_t cap = positions + positions / 2 + 64;
+    GRP_CK(g, r, cudaMalloc((void **)&g->d_counts[r], cap * sizeof(int32_t)), "draw counts");
+    GRP_CK(g, r, cudaMalloc((void **)&g->d_all[r], cap * (size_t)g->world * sizeof(int32_t)), "draw counts of all shards");
+    GRP_CK(g, r, cudaMalloc((void **)&g->d_order[r], cap * sizeof(int32_t)), "arrival order");
+    g->scratch_positions[r] = cap;
+    return RMB_OK;
+}
+
+// Stochastic reception with the receivers on several devices.  The reference draws from ONE java.util.Random: per
+// packet, in arrival order, the tx draw and then one draw per receiver that needs it, in node order
+// (UDGMRadioMedium.java:85-92,104-111).  Every shard evaluates the tick up to its draw flags and counts its draws per
+// packet; the counts of all shards meet on the host; every shard then walks the one uniform stream knowing where its
+// receivers' draws sit (rmb_tick_draws_begin / _end in the header).  Two rounds over the worker threads.
+int tick_with_draws(rmb_group *g, int n_tx, int slots, const double *power_dbm, const int32_t *channel,
+                    const double *uniforms, size_t n_uniforms, rmb_result *results)
+{
+    const int world = g->world;
+    const size_t positions = (size_t)world * (size_t)slots;
+    g->h_counts.assign((size_t)world * positions, 0);
+    g->h_order.assign((size_t)std::max(n_tx, 1), 0);
+    for (int r = 0; r < world; ++r)
+        for (size_t i = 0; i < g->l_packet[r].size(); ++i) g->h_order[g->l_packet[r][i]] = (int32_t)((size_t)r * slots + i);
+    int rc = run_all(g, [=](int r) -> int {
+        int rc = rmb_peer_push(g->h[r], slots, g->l_src[r].data(), power_dbm ? g->l_power[r].data() : nullptr,
+                               channel ? g->l_chan[r].data() : nullptr);
+        if (rc) return rc;
+        if ((rc = ensure_draw_scratch(g, r, positions))) return rc;
+        if ((rc = rmb_tick_peers_draws_begin(g->h[r], g->d_counts[r]))) return rc;
+        void *st = nullptr;
+        if ((rc = rmb_get_stream(g->h[r], &st))) return rc;
+        GRP_CK(g, r, cudaMemcpyAsync(g->h_counts.data() + (size_t)r * positions, g->d_counts[r], positions * sizeof(int32_t),
+                                     cudaMemcpyDeviceToHost, (cudaStream_t)st), "draw counts to the host");
+        GRP_CK(g, r, cudaStreamSynchronize((cudaStream_t)st), "draw counts to the host");
+        return RMB_OK;
+    });
+    if (rc) return rc;
+    return run_all(g, [=](int r) -> int {
+        void *st = nullptr;
+        int rc = rmb_get_stream(g->h[r], &st);
+        if (rc) return rc;
+        GRP_CK(g, r, cudaSetDevice(g->device[r]), "cudaSetDevice");
+        GRP_CK(g, r, cudaMemcpyAsync(g->d_all[r], g->h_counts.data(), (size_t)world * positions * sizeof(int32_t),
+                                     cudaMemcpyHostToDevice, (cudaStream_t)st), "draw counts of all shards");
+        GRP_CK(g, r, cudaMemcpyAsync(g->d_order[r], g->h_order.data(), (size_t)std::max(n_tx, 1) * sizeof(int32_t),
+                                     cudaMemcpyHostToDevice, (cudaStream_t)st), "arrival order");
+        return rmb_tick_draws_end(g->h[r], g->d_all[r], world, r, g->d_order[r], n_tx, uniforms, n_uniforms, &results[r]);
+    });
 }
 
 int open_peers(rmb_group *g, int max_slots)
@@ -134,7 +209,10 @@ int rmb_group_create(const rmb_config *cfg, int32_t n_devices, const int32_t *de
     rmb_group *g = new rmb_group();
     g->world = n_devices;
     g->h.assign(n_devices, nullptr); g->lo.assign(n_devices, 0); g->hi.assign(n_devices, 0); g->device.resize(n_devices);
-    g->rc.assign(n_devices, 0);
+    g->rc.assign(n_devices, 0); g->shard_err.assign(n_devices, std::string());
+    g->model = cfg->model;
+    g->d_counts.assign(n_devices, nullptr); g->d_all.assign(n_devices, nullptr); g->d_order.assign(n_devices, nullptr);
+    g->scratch_positions.assign(n_devices, 0);
     g->l_src.resize(n_devices); g->l_chan.resize(n_devices); g->l_power.resize(n_devices); g->l_packet.resize(n_devices);
     for (int r = 0; r < n_devices; ++r) {
         rmb_config c = *cfg;
@@ -164,6 +242,11 @@ int rmb_group_destroy(rmb_group *g)
     }
     g->wcv.notify_all();
     for (auto &t : g->workers) t.join();
+    for (int r = 0; r < g->world; ++r)
+        if (g->d_counts[r] || g->d_all[r] || g->d_order[r]) {
+            cudaSetDevice(g->device[r]);
+            cudaFree(g->d_counts[r]); cudaFree(g->d_all[r]); cudaFree(g->d_order[r]);
+        }
     for (auto *h : g->h) if (h) rmb_destroy(h);
     delete g;
     return RMB_OK;
@@ -298,6 +381,11 @@ int rmb_group_tick(rmb_group *g, int32_t n_tx, const int32_t *src, const double 
         for (int r = 0; r < g->world; ++r)
             for (size_t i = 0; i < g->l_packet[r].size(); ++i) packet_of[(size_t)r * slots + i] = g->l_packet[r][i];
     }
+    // one shard that may draw puts every shard on the draws path (a packet's source may sit on another shard)
+    bool draws = false;
+    if (g->model == RMB_MODEL_SINR)
+        for (int r = 0; r < g->world; ++r) draws = draws || rmb_may_draw(g->h[r]) != 0;
+    if (draws) return tick_with_draws(g, n_tx, slots, power_dbm, channel, uniforms, n_uniforms, results);
     return run_all(g, [=](int r) {
         int rc = rmb_peer_push(g->h[r], slots, g->l_src[r].data(), power_dbm ? g->l_power[r].data() : nullptr,
                                channel ? g->l_chan[r].data() : nullptr);

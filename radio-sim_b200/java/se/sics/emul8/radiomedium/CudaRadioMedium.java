@@ -286,7 +286,8 @@ public class CudaRadioMedium extends AbstractRadioMedium {
             MemorySegment res = tick.allocate(RES_SIZE * world, 8);                 /* rmb_result[world] */
             MemorySegment slotsOut = tick.allocate(JAVA_INT), packetOf = tick.allocate(JAVA_INT, (long) world * Math.max(options.maxTxPerTick, t));
 
-            /* deterministic tick: one call.  With draws (one device only: the draw order is global): the first call (no
+            /* deterministic tick: one call.  With draws (on several devices the library gathers the shards' draw counts and
+             * every shard walks the one stream: each rmb_result then carries the global count): the first call (no
              * uniforms; missing draws read as 0.0 = "success", which maximises the number of later draws) tells how
              * many uniforms the tick can consume at most; a copy of the simulator's generator supplies that many, and
              * the real generator is advanced by the number actually consumed -- the sequence the reference's media

@@ -226,6 +226,10 @@ class Medium:
         """Exchange + tick in one step (the preparation kernel pushes the records itself); asynchronous."""
         self._ck(self._lib.rmb_peer_exchange_tick_enqueue(self._h, slots, C.c_void_p(d_records)))
 
+    def may_draw(self):
+        """True when a tick on this handle may consume uniforms (some rx / tx probability below 1, or the model draws)."""
+        return bool(self._lib.rmb_may_draw(self._h))
+
     def peer_barrier_enqueue(self):
         """Device-side rendezvous of all ranks' streams (no host synchronisation)."""
         self._ck(self._lib.rmb_peer_barrier_enqueue(self._h))
@@ -317,6 +321,15 @@ class GroupResult:
         self.n_pairs = sum(p.n_pairs for p in parts)
         self.n_decisions = sum(p.n_decisions for p in parts)
         self.n_delivered = sum(p.n_delivered for p in parts)
+
+    def tx_failed(self):
+        """Per packet of the caller's list: the transmission itself failed (tx-loss draw).  Every shard walks the same
+        tx draws, so shard 0's column says it for all."""
+        p0 = np.asarray(self.parts[0].tx_failed)
+        valid = np.flatnonzero(self.packet_of >= 0)
+        out = np.zeros(len(valid), dtype=np.uint8)
+        out[self.packet_of[valid]] = p0[valid]
+        return out
 
     def merged(self):
         """-> dict(tx, rx, outcome, rssi_dbm): tx = index into the caller's packet list.  (The adapter does not need
@@ -429,7 +442,7 @@ class Group:
         parts = [TickResult(res[r], self._f64, copy) for r in range(self.world)]
         out = GroupResult(parts, slots.value, packet_of[:self.world * slots.value])
         out.status = rc
-        out.n_uniforms_used = sum(p.n_uniforms_used for p in parts)
+        out.n_uniforms_used = max(p.n_uniforms_used for p in parts)      # several shards: each carries the global count
         return out
 
     def node_info_f64(self):

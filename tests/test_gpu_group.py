@@ -138,3 +138,45 @@ def test_group_with_fewer_nodes_than_devices(rsb, orc):
         ref = orc.tick(orc.params(omodel), orc.NodeSet(x, y), orc.make_packets(np.array([0, 2]), 0.0, 26))
         assert np.array_equal(m["tx"], ref["pairs"]["tx"]) and np.array_equal(m["rx"], ref["pairs"]["rx"])
         assert np.array_equal(m["outcome"], ref["pairs"]["outcome"]) and len(rssi) == 3
+
+
+@pytest.mark.parametrize("compact", [False, True])
+def test_group_stochastic_reception_on_several_shards(rsb, orc, compact):
+    """rx-loss / tx-loss < 1 with the receivers of ONE group on three handles: rmb_group_tick gathers the shards' draw
+    counts itself and every shard walks the one java.util.Random stream -- same lists, same tx failures and the same
+    number of uniforms consumed as the oracle's unsharded tick, through the adapter's two calls (the first, without
+    uniforms, tells how many the tick can consume at most)."""
+    from radio_sim_b200 import _abi as A
+    from radio_sim_b200.javarandom import JavaRandom
+    n, t = 2400, 140
+    x, y, z, ch = random_deployment(61, n, 650.0)
+    rng = np.random.default_rng(61)
+    rxprob = np.where(rng.uniform(size=n) < 0.5, 0.9, 1.0); rxprob[::50] = 0.0
+    txprob = np.where(rng.uniform(size=n) < 0.3, 0.8, 1.0); txprob[::97] = 0.0
+    rxprob[:n // 3] = 1.0; txprob[:n // 3] = 1.0        # shard 0 alone is deterministic: it has to follow the others
+    nodes = orc.NodeSet(x, y, z, channel=ch, rxprob=rxprob, txprob=txprob)
+    rnd, rnd_ref = JavaRandom(42), JavaRandom(42)
+    with rsb.Group("sinr", devices=(0, 0, 0), max_tx_per_tick=256, compact=compact, f64_values=not compact) as g:
+        g.set_nodes(x, y, z, channel=ch, rxprob=rxprob, txprob=txprob)
+        for tick in range(3):
+            src = pick_sources(61 + tick, n, t) if tick < 2 else np.zeros(0, dtype=np.int32)
+            probe = g.tick(src, allow_short_uniforms=True)
+            if len(src):
+                assert probe.status == A.ERR_UNIFORMS and probe.n_uniforms_used > 50
+            r = g.tick(src, uniforms=rnd.peek_doubles(probe.n_uniforms_used))
+            rnd.skip_doubles(r.n_uniforms_used)
+            u = rnd_ref.peek_doubles(100000)
+            ref = orc.tick(orc.params(orc.MODEL_SINR), nodes, orc.make_packets(src, 0.0, 26), uniforms=u)
+            rnd_ref.skip_doubles(ref["n_uniforms_used"])
+            assert r.status == 0 and r.n_uniforms_used == ref["n_uniforms_used"] <= probe.n_uniforms_used
+            m = r.merged()
+            assert np.array_equal(m["tx"], ref["pairs"]["tx"]) and np.array_equal(m["rx"], ref["pairs"]["rx"])
+            assert np.array_equal(m["outcome"], ref["pairs"]["outcome"])
+            assert np.array_equal(r.tx_failed(), ref["tx_failed"])
+            if len(src):
+                assert ref["tx_failed"].sum() > 0 and (ref["pairs"]["outcome"] == 1).sum() > 0
+        # back to deterministic nodes: the group leaves the draws path (and consumes nothing)
+        g.set_nodes(x, y, z, channel=ch)
+        r = g.tick(pick_sources(61, n, t))
+        ref = orc.tick(orc.params(orc.MODEL_SINR), orc.NodeSet(x, y, z, channel=ch), orc.make_packets(pick_sources(61, n, t), 0.0, 26))
+        assert r.status == 0 and r.n_uniforms_used == 0 and np.array_equal(r.merged()["rx"], ref["pairs"]["rx"])

@@ -405,3 +405,18 @@ def test_lists_copied_behind_the_tick_on_a_guessed_length(rsb, orc, compact):
                 assert np.array_equal(r.tx_failed, ref["tx_failed"])
             else:
                 compare(r, ref)
+
+
+def test_more_packets_than_the_finish_kernel_scans(rsb, orc):
+    """Above 16 383 packets per tick the per-packet segment offsets are scanned in the sweep's epilogue instead of the
+    finish kernel's shared memory (finish.cu finish_scans): 20 000 of 30 000 nodes transmit at once."""
+    x, y, z, ch = random_deployment(123, 30000, 3000.0)
+    ch[:] = 26
+    src = pick_sources(123, 30000, 20000)
+    r, ref = run_case(rsb, orc, x, y, z, ch, src)
+    assert r.n_tx == 20000 and ref["n_pairs"] > 100000
+    with rsb.Medium("sinr", compact=True) as m:
+        m.set_nodes(x, y, z, channel=ch)
+        c = m.tick(src)
+        assert np.array_equal(c.tx_column(), ref["pairs"]["tx"]) and np.array_equal(c.rx, ref["pairs"]["rx"])
+        assert np.array_equal(c.outcome, ref["pairs"]["outcome"])
