@@ -98,7 +98,7 @@ typedef struct rmb_config {
  *   - N2N needs the source's integer id, which a tx record does not carry: RMB_MODEL_N2N with n_shards > 1 is
  *     rejected by rmb_create (RMB_ERR_UNSUPPORTED);
  *   - stochastic reception (any rx/tx probability strictly between 0 and 1) on sharded receivers needs the
- *     rmb_tick_draws_begin/_end pair (SINR medium; rmb_group_tick goes through it by itself); any other per-handle
+ *     rmb_tick_draws_begin/_end pair (rmb_group_tick goes through it by itself); any other per-handle
  *     tick entry point returns RMB_ERR_UNSUPPORTED for such a tick, also when the probability arrives in a record
  *     built by another shard;
  *   - at most 16 handles exchange records with rmb_peer_* (RMB_ERR_INVALID). */
@@ -218,7 +218,8 @@ int rmb_fetch(rmb_handle *h, rmb_result *out);
  *                         n_uniforms_used is the global count.  d_order (DEVICE int32[n_order], may be NULL =
  *                         as stored): the record positions in the tick's original packet arrival order -- an
  *                         exchanged record list is grouped by owner rank, the reference draws in arrival order.
- * Works on an unsharded handle too (world = 1).  SINR medium only. */
+ * Works on an unsharded handle too (world = 1).  SINR and UDGM media (the other media draw nothing, or -- N2N --
+ * cannot be sharded). */
 int rmb_tick_draws_begin(rmb_handle *h, int32_t n_tx, const void *d_records, int32_t *d_counts_out);
 int rmb_tick_draws_end(rmb_handle *h, const int32_t *d_all_counts, int32_t world, int32_t rank,
                        const int32_t *d_order, int32_t n_order,
@@ -298,8 +299,7 @@ int rmb_node_info_f64(rmb_handle *h, double *rssi_dbm, uint8_t *receiving);
  *                      how many a tick needs).  On several devices stochastic reception goes through the handles'
  *                      rmb_tick_peers_draws_begin / rmb_tick_draws_end with the per-packet draw counts gathered in
  *                      between, in the caller's packet order: the same draws as one device makes; every results[r]
- *                      then carries the GLOBAL n_uniforms_used.  (SINR medium; the reference media with draws on
- *                      several devices return RMB_ERR_UNSUPPORTED.) */
+ *                      then carries the GLOBAL n_uniforms_used. */
 typedef struct rmb_group rmb_group;
 int         rmb_group_create(const rmb_config *cfg, int32_t n_devices, const int32_t *devices, int32_t max_tx_per_tick, rmb_group **out);
 int         rmb_group_destroy(rmb_group *g);

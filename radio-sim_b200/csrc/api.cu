@@ -865,8 +865,9 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
     if (draws && h->cfg.n_shards > 1 && !h->split_counts)
         return h->fail(RMB_ERR_UNSUPPORTED, "stochastic reception (rx/tx probability < 1) on sharded receivers needs "
                                             "rmb_tick_draws_begin / rmb_tick_draws_end (the draw order is global)");
-    if (h->split_counts && h->cfg.model != RMB_MODEL_SINR)
-        return h->fail(RMB_ERR_UNSUPPORTED, "rmb_tick_draws_begin exists for the SINR medium only");
+    if (h->split_counts && h->cfg.model != RMB_MODEL_SINR && h->cfg.model != RMB_MODEL_UDGM)
+        return h->fail(RMB_ERR_UNSUPPORTED, "rmb_tick_draws_begin exists for the SINR and UDGM media (the other media draw nothing "
+                                            "or cannot be sharded)");
     h->split.active = false;
     h->slab_ready = false;
     RMB_CK(h, h->seg.ensure((size_t)n_tx + 2)); RMB_CK(h, h->tx_base.ensure((size_t)n_tx + 1));
@@ -1093,6 +1094,14 @@ static int compute(rmb_handle *h, int n_tx, const rmb_tx_record *d_rec, const do
             ++launches;
         }
     }
+    if (h->cfg.model != RMB_MODEL_SINR && h->split_counts) {
+        // sharded receivers with draws: the first half of the draw stage only (flags, scan, per-packet counts)
+        RMB_CK(h, launch_emit_draw_prepare(n_tx, pair_arrays(h), m, h->split_counts, h->st));
+        h->split.active = true; h->split.n_tx = n_tx; h->split.m = m; h->split.rec = d_rec;
+        h->split.launches = launches + 6; h->split.sweeps = sweeps;
+        if (h->st == h->own_st) RMB_CK(h, cudaStreamSynchronize(h->st));
+        return RMB_OK;
+    }
     if (h->cfg.model != RMB_MODEL_SINR) {
         RMB_CK(h, launch_emit(h->dp.p, d_rec, n_tx, pair_arrays(h), m, draws, h->uniforms.p, nu, h->ctr.p, h->st));
         launches += draws ? 7 : 2;
@@ -1292,7 +1301,7 @@ int rmb_tick_draws_end(rmb_handle *h, const int32_t *d_all_counts, int32_t world
         nu = (long long)n_uniforms;
     }
     PairArrays pa = pair_arrays(h);
-    pa.key = h->key_alt.p;
+    if (h->cfg.model == RMB_MODEL_SINR) pa.key = h->key_alt.p;      // the ordering stage left the sorted keys there
     RMB_CK(h, launch_emit_draw_finish(h->dp.p, h->split.rec, h->split.n_tx, pa, h->split.m, h->uniforms.p, nu, h->ctr.p,
                                       d_all_counts, world, rank, d_order, n_order, h->st));
     RMB_CK(h, cudaEventRecord(h->ev[4], h->st));

@@ -383,7 +383,7 @@ int rmb_group_tick(rmb_group *g, int32_t n_tx, const int32_t *src, const double 
     }
     // one shard that may draw puts every shard on the draws path (a packet's source may sit on another shard)
     bool draws = false;
-    if (g->model == RMB_MODEL_SINR)
+    if (g->model == RMB_MODEL_SINR || g->model == RMB_MODEL_UDGM)
         for (int r = 0; r < g->world; ++r) draws = draws || rmb_may_draw(g->h[r]) != 0;
     if (draws) return tick_with_draws(g, n_tx, slots, power_dbm, channel, uniforms, n_uniforms, results);
     return run_all(g, [=](int r) {

@@ -104,20 +104,20 @@ def test_group_reference_media_and_errors(rsb, orc):
         m = g.tick(src).merged()
     ref = orc.tick(orc.params(orc.MODEL_UDGM), orc.NodeSet(x, y, z, channel=ch), orc.make_packets(src, 0.0, ch[src]))
     assert np.array_equal(m["tx"], ref["pairs"]["tx"]) and np.array_equal(m["rx"], ref["pairs"]["rx"])
-    # stochastic reception on several shards is refused (the draw order is global), on one shard it draws
+    # stochastic reception: one shard draws by itself, several shards follow the one global draw order
     rxp = np.full(3000, 0.5)
-    with rsb.Group("udgm", devices=(0, 0), max_tx_per_tick=64) as g:
-        g.set_nodes(x, y, z, channel=ch, rxprob=rxp)
-        with pytest.raises(rsb.MediumError) as e:
-            g.tick(src)
-        assert e.value.code == A.ERR_UNSUPPORTED
     u = orc.jrandom_doubles(5, 20000)
-    with rsb.Group("udgm", devices=(0,), max_tx_per_tick=64) as g:
-        g.set_nodes(x, y, z, channel=ch, rxprob=rxp)
-        r = g.tick(src, uniforms=u)
     ref = orc.tick(orc.params(orc.MODEL_UDGM), orc.NodeSet(x, y, z, channel=ch, rxprob=rxp), orc.make_packets(src, 0.0, ch[src]), uniforms=u)
-    m = r.merged()
-    assert np.array_equal(m["outcome"], ref["pairs"]["outcome"]) and r.n_uniforms_used == ref["n_uniforms_used"]
+    for devices in ((0,), (0, 0), (0, 0, 0)):
+        with rsb.Group("udgm", devices=devices, max_tx_per_tick=64) as g:
+            g.set_nodes(x, y, z, channel=ch, rxprob=rxp)
+            with pytest.raises(rsb.MediumError) as e:
+                g.tick(src)                                # no uniforms: told how many the tick can consume
+            assert e.value.code == A.ERR_UNIFORMS
+            r = g.tick(src, uniforms=u)
+        m = r.merged()
+        assert np.array_equal(m["tx"], ref["pairs"]["tx"]) and np.array_equal(m["rx"], ref["pairs"]["rx"])
+        assert np.array_equal(m["outcome"], ref["pairs"]["outcome"]) and r.n_uniforms_used == ref["n_uniforms_used"] > 100
     # more packets from one shard than the exchange buffers were sized for
     with rsb.Group("sinr", devices=(0, 0), max_tx_per_tick=8) as g:
         g.set_nodes(x, y, z, channel=ch)
@@ -138,6 +138,36 @@ def test_group_with_fewer_nodes_than_devices(rsb, orc):
         ref = orc.tick(orc.params(omodel), orc.NodeSet(x, y), orc.make_packets(np.array([0, 2]), 0.0, 26))
         assert np.array_equal(m["tx"], ref["pairs"]["tx"]) and np.array_equal(m["rx"], ref["pairs"]["rx"])
         assert np.array_equal(m["outcome"], ref["pairs"]["outcome"]) and len(rssi) == 3
+
+
+def test_group_udgm_success_ratio_and_tx_loss_on_several_shards(rsb, orc):
+    """The reference's own stochastic medium sharded: UDGM with SUCCESS_RATIO_RX < 1 (which the reference applies to the
+    transmission, UDGMRadioMedium.java:63-65) and per-node rx/tx probabilities, three handles, two ticks out of one
+    java.util.Random stream."""
+    from radio_sim_b200.javarandom import JavaRandom
+    n, t = 3000, 90
+    x, y, z, ch = random_deployment(88, n, 420.0, channels=2)
+    rng = np.random.default_rng(88)
+    rxprob = np.where(rng.uniform(size=n) < 0.4, 0.7, 1.0); rxprob[::41] = 0.0
+    txprob = np.where(rng.uniform(size=n) < 0.4, 0.85, 1.0); txprob[::53] = 0.0
+    nodes = orc.NodeSet(x, y, z, channel=ch, rxprob=rxprob, txprob=txprob)
+    p = orc.params(orc.MODEL_UDGM, success_ratio_rx=0.9)
+    rnd, rnd_ref = JavaRandom(7), JavaRandom(7)
+    with rsb.Group("udgm", devices=(0, 0, 0), max_tx_per_tick=128, success_ratio_rx=0.9) as g:
+        g.set_nodes(x, y, z, channel=ch, rxprob=rxprob, txprob=txprob)
+        for tick in range(2):
+            src = pick_sources(88 + tick, n, t)
+            probe = g.tick(src, allow_short_uniforms=True)
+            r = g.tick(src, uniforms=rnd.peek_doubles(probe.n_uniforms_used))
+            rnd.skip_doubles(r.n_uniforms_used)
+            ref = orc.tick(p, nodes, orc.make_packets(src, 0.0, ch[src]), uniforms=rnd_ref.peek_doubles(100000))
+            rnd_ref.skip_doubles(ref["n_uniforms_used"])
+            m = r.merged()
+            assert r.status == 0 and r.n_uniforms_used == ref["n_uniforms_used"] > 50
+            assert np.array_equal(m["tx"], ref["pairs"]["tx"]) and np.array_equal(m["rx"], ref["pairs"]["rx"])
+            assert np.array_equal(m["outcome"], ref["pairs"]["outcome"])
+            assert np.array_equal(r.tx_failed(), ref["tx_failed"]) and ref["tx_failed"].sum() > 0
+        assert rnd.seed == rnd_ref.seed
 
 
 @pytest.mark.parametrize("compact", [False, True])

@@ -112,15 +112,16 @@ def test_stochastic_replay_draws_from_the_simulators_random(orc, option, hook):
     assert ginfo["seed"] == winfo["seed"]                        # the generator is left exactly where the reference leaves it
 
 
-def test_stochastic_replay_with_the_receivers_on_two_handles(orc):
-    """The same script on a group of two handles (SINR medium): rmb_group_tick gathers the shards' draw counts, the
-    messages and the generator's final state are those of the oracle medium driven by the same java.util.Random."""
+@pytest.mark.parametrize("option", ["sinr-b200", "udgm"])
+def test_stochastic_replay_with_the_receivers_on_two_handles(orc, option):
+    """The same script on a group of two handles: rmb_group_tick gathers the shards' draw counts, the messages and
+    the generator's final state are those of the oracle medium driven by the same java.util.Random."""
     import radio_sim_b200
     from radio_sim_b200.simulator import CudaRadioMedium
     radio_sim_b200.load()
     winfo, ginfo = {}, {}
-    want = _run(lambda o, p: OracleRadioMedium(MODEL_OF[o]), "sinr-b200", _stochastic_script, keep=winfo)
-    got = _run(lambda o, p: CudaRadioMedium(MODEL_OF[o], devices=(0, 0)), "sinr-b200", _stochastic_script, keep=ginfo)
+    want = _run(lambda o, p: OracleRadioMedium(MODEL_OF[o]), option, _stochastic_script, keep=winfo)
+    got = _run(lambda o, p: CudaRadioMedium(MODEL_OF[o], devices=(0, 0)), option, _stochastic_script, keep=ginfo)
     assert len([m for m in want[0] + want[1] if m.get("command") == "receive"]) > 3
     assert got == want and ginfo["seed"] == winfo["seed"]
 
