@@ -28,31 +28,55 @@ def _arr(a, dt, n=None):
     return a
 
 
+_from_memory = C.pythonapi.PyMemoryView_FromMemory
+_from_memory.restype, _from_memory.argtypes = C.py_object, [C.c_void_p, C.c_ssize_t, C.c_int]
+_PyBUF_WRITE = 0x200
+
+
+def _column(p, dt, m, copy):
+    """numpy view (or copy) of m elements at the ctypes pointer p.  (np.ctypeslib.as_array builds a new ctypes array
+    type for every new length -- 45 us a column when the pair count changes from tick to tick.)"""
+    if not p or m == 0:
+        return np.zeros(0, dtype=dt)
+    v = np.frombuffer(_from_memory(C.addressof(p.contents), m * dt.itemsize, _PyBUF_WRITE), dtype=dt)
+    return v.copy() if copy else v
+
+
 class TickResult:
     """Heard (tx, rx) pairs of one tick in generateReceptionEvents call order
-    (packets in arrival order, receivers in node-array order; Simulator.java:321-335)."""
+    (packets in arrival order, receivers in node-array order; Simulator.java:321-335).
+    copy=False: the columns are views of the handle's pinned host memory (valid until the handle's next call), made
+    when first touched; copy=True: copies, made here."""
+
+    # column -> (rmb_result field, dtype, length attribute, offset added to the length)
+    _COLUMNS = {"tx": ("tx", np.dtype(np.int32), "n_pairs", 0), "rx": ("rx", np.dtype(np.int32), "n_pairs", 0),
+                "rssi_dbm": ("rssi_dbm", np.dtype(np.float32), "n_pairs", 0), "sinr_db": ("sinr_db", np.dtype(np.float32), "n_pairs", 0),
+                "outcome": ("outcome", np.dtype(np.uint8), "n_pairs", 0),
+                "rssi_dbm_f64": ("rssi_dbm_f64", np.dtype(np.float64), "n_pairs", 0),
+                "sinr_db_f64": ("sinr_db_f64", np.dtype(np.float64), "n_pairs", 0),
+                "tx_failed": ("tx_failed", np.dtype(np.uint8), "n_tx", 0), "tx_first": ("tx_first", np.dtype(np.int32), "n_tx", 1)}
 
     def __init__(self, r, f64, copy=True):
-        n = int(r.n_pairs)
-        self.n_pairs, self.n_delivered, self.n_interfered = n, int(r.n_delivered), int(r.n_interfered)
+        self.n_pairs, self.n_delivered, self.n_interfered = int(r.n_pairs), int(r.n_delivered), int(r.n_interfered)
         self.n_decisions, self.n_uniforms_used = int(r.n_decisions), int(r.n_uniforms_used)
         self.n_recheck, self.n_tx, self.near_slots = int(r.n_recheck), int(r.n_tx), int(r.near_slots)
+        self._r, self._f64, self._copy = r, f64, copy
+        if copy:
+            for name in self._COLUMNS:
+                getattr(self, name)
 
-        def view(p, dt, m):
-            if not p or m == 0:
-                return np.zeros(0, dtype=dt)
-            v = np.ctypeslib.as_array(p, shape=(m,))
-            return v.copy() if copy else v
-        self.tx = view(r.tx, np.int32, n)
-        self.rx = view(r.rx, np.int32, n)
-        self.rssi_dbm = view(r.rssi_dbm, np.float32, n)
-        self.sinr_db = view(r.sinr_db, np.float32, n)
-        self.outcome = view(r.outcome, np.uint8, n)
-        self.rssi_dbm_f64 = view(r.rssi_dbm_f64, np.float64, n) if f64 else None
-        self.sinr_db_f64 = view(r.sinr_db_f64, np.float64, n) if f64 else None
-        self.tx_failed = view(r.tx_failed, np.uint8, self.n_tx)
-        # compact form (RMB_FLAG_COMPACT): no tx / sinr columns, rows of packet t are tx_first[t] .. tx_first[t+1]
-        self.tx_first = view(r.tx_first, np.int32, self.n_tx + 1) if r.tx_first else None
+    def __getattr__(self, name):                     # reached only for a column not made yet
+        spec = TickResult._COLUMNS.get(name)
+        if spec is None:
+            raise AttributeError(name)
+        field, dt, length, extra = spec
+        p = getattr(self._r, field)
+        if (name.endswith("_f64") and not self._f64) or (name == "tx_first" and not p):
+            v = None        # compact form (RMB_FLAG_COMPACT) has tx_first and no tx / sinr columns; f64 columns on request
+        else:
+            v = _column(p, dt, getattr(self, length) + extra, self._copy)
+        setattr(self, name, v)
+        return v
 
     def tx_column(self):
         """The tx column, rebuilt from tx_first when the result is in the compact form."""
