@@ -341,6 +341,37 @@ int rmb_set_stream(rmb_handle *h, void *stream);
  * Results do not depend on any of these. */
 int rmb_set_tuning(rmb_handle *h, int32_t sweep_variant, int32_t near_slots);
 
+/* NO COUNTERPART IN THE REFERENCE.  One tick of the UDGM medium with every
+ * probability at 1 (the rule of UDGMRadioMedium.java:67-81,100-102 without its draws: heard <=> node != source,
+ * enabled, on the packet's channel, d*d / (R*R) <= 1; heard == delivered; RSSI = the packet's tx power) for callers
+ * that cannot allocate -- code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc.
+ * No handle; the call allocates NOTHING (no cudaMalloc / cudaFree / allocating library routine): inputs and outputs
+ * are the caller's DEVICE buffers, and the one piece of scratch the computation needs -- a count per (packet, block
+ * of 256 nodes), scanned in place -- lives in a file-scope __device__ array of RMB_STATIC_MAX_CELLS ints (2 MiB per
+ * GPU that loads the library, held until exit).
+ *   limit      n_tx * ceil(n / 256) <= RMB_STATIC_MAX_CELLS (e.g. 100 000 nodes x 1 000 packets); beyond it the call
+ *              returns RMB_ERR_CAPACITY and says so in error_text.  rmb_tick has no such limit.
+ *   sharing    every call on a device uses the same array, which keeps the last call's contents; nothing in it has to
+ *              start at zero (each call writes every cell it reads).  Calls that OVERLAP on one GPU (two streams, two
+ *              threads) race on it: order them on one stream.
+ *   inputs     device: node-array order as for rmb_set_nodes (d_z, d_enabled may be NULL = 0 / all on); n_tx packets
+ *              by source node index (outside 0..n-1, e.g. -1: heard by nobody), power in dBm, channel (d_pkt_channel
+ *              NULL = the source's channel).  stream: a cudaStream_t (NULL = the default stream); the call only
+ *              enqueues (three kernels) and does not synchronise.
+ *   outputs    rows in the reference's call order (packets in arrival order, receivers in node-array order), as
+ *              rmb_tick returns them: d_tx (may be NULL), d_rx, d_rssi_dbm, d_outcome hold `capacity` rows each;
+ *              d_tx_first[n_tx + 1] = first row of every packet; *d_n_pairs = rows the tick has -- when that exceeds
+ *              capacity, rows beyond capacity were not written.
+ *   set-up     the first call on a device looks the array's device address up (cudaGetSymbolAddress): make one call
+ *              (n_tx = 0 will do) before starting a graph capture on that device.
+ *   error_text (may be NULL) receives the reason for a non-zero return. */
+#define RMB_STATIC_MAX_CELLS (1 << 19)
+int rmb_udgm_tick_static(int32_t device, void *stream, int32_t n, const double *d_x, const double *d_y, const double *d_z,
+                         const int32_t *d_channel, const uint8_t *d_enabled, int32_t n_tx, const int32_t *d_src,
+                         const double *d_power_dbm, const int32_t *d_pkt_channel, double transmission_range,
+                         int64_t capacity, int32_t *d_tx, int32_t *d_rx, float *d_rssi_dbm, uint8_t *d_outcome,
+                         int32_t *d_tx_first, int64_t *d_n_pairs, char *error_text, size_t error_text_bytes);
+
 #ifdef __cplusplus
 }
 #endif

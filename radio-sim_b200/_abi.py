@@ -28,7 +28,7 @@ SYMBOLS = ("rmb_version", "rmb_config_default", "rmb_create", "rmb_destroy", "rm
            "rmb_tick_peers_draws_begin", "rmb_set_shard_base", "rmb_may_draw",
            "rmb_group_create", "rmb_group_destroy", "rmb_group_last_error", "rmb_group_size", "rmb_group_shard",
            "rmb_group_set_nodes", "rmb_group_update_positions", "rmb_group_update_radio", "rmb_group_tick",
-           "rmb_group_node_info_f64")
+           "rmb_group_node_info_f64", "rmb_udgm_tick_static")
 
 
 class Config(C.Structure):
@@ -119,6 +119,9 @@ def load():
     L.rmb_set_shard_base.argtypes = [H, C.c_int32]
     L.rmb_may_draw.argtypes = [H]
     L.rmb_may_draw.restype = C.c_int32
+    L.rmb_udgm_tick_static.argtypes = [C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                       C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_int64, C.c_void_p, C.c_void_p,
+                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_char_p, C.c_size_t]
     L.rmb_group_create.argtypes = [C.POINTER(Config), C.c_int32, pi, C.c_int32, C.POINTER(H)]
     L.rmb_group_destroy.argtypes = [H]
     L.rmb_group_last_error.argtypes = [H]
