@@ -354,8 +354,7 @@ def run_static(args):
         if G == 1:
             return med.tick(lists[k], uniforms=uniforms, copy=False)
         if p2p:
-            med.peer_push(p.local_src[rank])
-            return med.tick_peers(copy=False)
+            return med.peer_tick(p.local_src[rank], copy=False)
         med.build_tx_records(p.local_src[rank], rec_local[k].data_ptr())
         dist.all_gather_into_tensor(rec_all[:G * p.tpad * 48], rec_local[k][:p.tpad * 48])
         return med.tick_records(p.n_records, rec_all.data_ptr(), copy=False)
@@ -381,14 +380,20 @@ def run_static(args):
                 line_up()
                 torch.cuda.synchronize()
             t0 = time.perf_counter()
-            e0.record(stream)
-            res = fn(k)
-            e1.record(stream)
-            torch.cuda.synchronize()
-            walls.append(time.perf_counter() - t0)
-            if res is None:
-                res = med.tick_finish()
-            times.append(e0.elapsed_time(e1) * 1e-3)
+            if device_timed:
+                e0.record(stream)
+                res = fn(k)
+                e1.record(stream)
+                torch.cuda.synchronize()
+                walls.append(time.perf_counter() - t0)
+                if res is None:
+                    res = med.tick_finish()
+                times.append(e0.elapsed_time(e1) * 1e-3)
+            else:
+                # the call is synchronous: when it returns the lists are in host memory -- that is the end of the step
+                res = fn(k)
+                walls.append(time.perf_counter() - t0)
+                times.append(walls[-1])
             if sampler:
                 sampler.active = False
             tm = med.timing()
@@ -561,8 +566,7 @@ def run_c5(args):
         med.update_positions(px[lo:hi], py[lo:hi])
         if G == 1:
             return med.tick(src, copy=False)
-        med.peer_push(plan.local_src[rank])
-        return med.tick_peers(copy=False)
+        return med.peer_tick(plan.local_src[rank], copy=False)
 
     # ticks 1..3 against the oracle's digests (tests/golden/fullsize_hashes.json)
     verified = None
@@ -596,18 +600,19 @@ def run_c5(args):
             if kind == "e2e":
                 torch.cuda.synchronize()
             t0 = time.perf_counter()
-            e0.record(stream)
             if kind != "e2e":
+                e0.record(stream)
                 if G == 1:
                     med.tick_enqueue(T, rec_local.data_ptr())
                 else:
                     med.peer_exchange_tick_enqueue(plan.tpad, rec_local.data_ptr())
                 res = None
+                e1.record(stream)
+                torch.cuda.synchronize()
+                wall = time.perf_counter() - t0
             else:
-                res = tick_e2e(src, plan)
-            e1.record(stream)
-            torch.cuda.synchronize()
-            wall = time.perf_counter() - t0
+                res = tick_e2e(src, plan)       # synchronous: the lists are in host memory when it returns
+                wall = time.perf_counter() - t0
             if sampler:
                 sampler.active = False
             if res is None:

@@ -248,6 +248,12 @@ int rmb_tick_finish(rmb_handle *h, rmb_result *out);
  *   rmb_tick_peers         waits ON THE DEVICE for all ranks' flags (no host synchronisation, no
  *                          collective) and evaluates the world*slots gathered records exactly like
  *                          rmb_tick_records; arrival index of a record = rank*slots + slot.
+ *   rmb_peer_tick          rmb_peer_push + rmb_tick_peers in ONE call, host packet list in, host lists out.  On the
+ *                          SINR medium without draws, every handle on a device of its own, the exchange is part of
+ *                          the tick's first kernel (no separate push launch); otherwise the two steps run back to
+ *                          back.  A handle's records leave when its tick starts, so every rank has to be inside
+ *                          this call at the same time -- one thread or process per handle; calling the handles one
+ *                          after another from one thread runs into the time-out.
  * Pushes and ticks must alternate, in step on all ranks (buffers are double-buffered by tick parity).
  * A rank that never pushes makes the others fail with RMB_ERR_PEER after ~20 s instead of hanging. */
 #define RMB_PEER_HANDLE_BYTES 128
@@ -256,6 +262,7 @@ int rmb_peer_open(rmb_handle *h, const void *blobs /* world * RMB_PEER_HANDLE_BY
 int rmb_peer_push(rmb_handle *h, int32_t slots, const int32_t *src, const double *power_dbm, const int32_t *channel);
 int rmb_peer_push_records(rmb_handle *h, int32_t slots, const void *d_records);
 int rmb_tick_peers(rmb_handle *h, const double *uniforms, size_t n_uniforms, rmb_result *out);
+int rmb_peer_tick(rmb_handle *h, int32_t slots, const int32_t *src, const double *power_dbm, const int32_t *channel, rmb_result *out);
 int rmb_tick_peers_resident(rmb_handle *h, rmb_result *out);   /* results stay on the device, see rmb_fetch */
 int rmb_tick_peers_enqueue(rmb_handle *h);                     /* asynchronous, settled by rmb_tick_finish */
 int rmb_tick_peers_draws_begin(rmb_handle *h, int32_t *d_counts_out);   /* rmb_tick_draws_begin on the gathered records */

@@ -23,7 +23,7 @@ SYMBOLS = ("rmb_version", "rmb_config_default", "rmb_create", "rmb_destroy", "rm
            "rmb_set_nodes", "rmb_set_matrix", "rmb_update_positions", "rmb_update_positions_async", "rmb_update_radio", "rmb_tick",
            "rmb_build_tx_records", "rmb_tick_records", "rmb_tick_resident", "rmb_fetch",
            "rmb_node_info", "rmb_node_info_f64", "rmb_last_timing", "rmb_set_tuning", "rmb_get_stream", "rmb_set_stream",
-           "rmb_peer_export", "rmb_peer_open", "rmb_peer_push", "rmb_peer_push_records", "rmb_tick_peers",
+           "rmb_peer_export", "rmb_peer_open", "rmb_peer_push", "rmb_peer_push_records", "rmb_tick_peers", "rmb_peer_tick",
            "rmb_tick_peers_resident", "rmb_tick_enqueue", "rmb_tick_finish", "rmb_tick_peers_enqueue", "rmb_peer_exchange_tick_enqueue", "rmb_peer_barrier_enqueue", "rmb_tick_draws_begin", "rmb_tick_draws_end",
            "rmb_tick_peers_draws_begin", "rmb_set_shard_base", "rmb_may_draw",
            "rmb_group_create", "rmb_group_destroy", "rmb_group_last_error", "rmb_group_size", "rmb_group_shard",
@@ -117,6 +117,7 @@ def load():
     L.rmb_tick_draws_end.argtypes = [H, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int32, pd, C.c_size_t, C.POINTER(Result)]
     L.rmb_tick_peers_draws_begin.argtypes = [H, C.c_void_p]
     L.rmb_set_shard_base.argtypes = [H, C.c_int32]
+    L.rmb_peer_tick.argtypes = [H, C.c_int32, pi, pd, pi, C.POINTER(Result)]
     L.rmb_may_draw.argtypes = [H]
     L.rmb_may_draw.restype = C.c_int32
     L.rmb_udgm_tick_static.argtypes = [C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,

@@ -126,6 +126,7 @@ struct rmb_handle {
         unsigned epoch = 0;               // ticks pushed so far (flags carry this value)
         unsigned barrier_epoch = 0;       // rmb_peer_barrier_enqueue calls so far (second flag row)
         bool pushed = false;              // a push is waiting for its tick
+        bool shares_device = false;       // some peer sits on this handle's device (development on a one-GPU box)
         char *buf = nullptr;              // this handle's gather buffer: flags, then 2 x world x max_slots records
         char *peer[kMaxPeers] = {};       // every rank's buffer as mapped here (peer[rank] == buf)
         bool ipc[kMaxPeers] = {};         // mapped with cudaIpcOpenMemHandle (must be closed)
@@ -1381,12 +1382,14 @@ int rmb_peer_open(rmb_handle *h, const void *blobs)
     if (!P.buf) return h->fail(RMB_ERR_STATE, "rmb_peer_open before rmb_peer_export");
     if (!blobs) return h->fail(RMB_ERR_INVALID, "rmb_peer_open: null blobs");
     RMB_CK(h, cudaSetDevice(h->cfg.device));
+    P.shares_device = false;
     for (int r = 0; r < P.world; ++r) {
         PeerBlob b;
         memcpy(&b, (const char *)blobs + (size_t)r * RMB_PEER_HANDLE_BYTES, sizeof(b));
         if (b.magic != kPeerMagic || b.world != P.world || b.rank != r || b.max_slots != P.max_slots)
             return h->fail(RMB_ERR_INVALID, "rmb_peer_open: blob does not match (world / rank order / max_slots)");
         if (r == P.rank) { P.peer[r] = P.buf; continue; }
+        if (b.device == h->cfg.device) P.shares_device = true;
         if (b.pid == (int64_t)getpid()) {
             // a peer handle in this very process: use its pointer (peer access between the two devices)
             if (b.device != h->cfg.device) {
@@ -1466,6 +1469,38 @@ int rmb_tick_peers(rmb_handle *h, const double *uniforms, size_t n_uniforms, rmb
     if (rc && rc != RMB_ERR_UNIFORMS) return rc;
     int rc2 = download(h, out);
     return rc2 ? rc2 : rc;
+}
+
+int rmb_peer_tick(rmb_handle *h, int32_t slots, const int32_t *src, const double *power_dbm, const int32_t *channel, rmb_result *out)
+{
+    if (!h || !out) return RMB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    RMB_SETTLE(h);
+    auto &P = h->peer;
+    if (!h->have_nodes) return h->fail(RMB_ERR_STATE, "rmb_peer_tick before rmb_set_nodes");
+    if (slots < 0 || slots > P.max_slots || (slots > 0 && !src)) return h->fail(RMB_ERR_INVALID, "rmb_peer_tick: bad arguments (slots <= max_slots)");
+    if (P.world < 1) return h->fail(RMB_ERR_STATE, "rmb_peer_tick before rmb_peer_export");
+    for (int r = 0; r < P.world; ++r) if (!P.peer[r]) return h->fail(RMB_ERR_STATE, "rmb_peer_tick before rmb_peer_open");
+    if (P.pushed) return h->fail(RMB_ERR_STATE, "a pushed tick is still waiting for rmb_tick_peers");
+    RMB_CK(h, cudaSetDevice(h->cfg.device));
+    RMB_CK(h, h->rec.ensure(std::max(slots, 1)));
+    int rc = stage_records(h, slots, src, power_dbm, channel, h->rec.p, false);
+    if (rc) return rc;
+    h->want_download = true;
+    if (h->cfg.model == RMB_MODEL_SINR && !h->maybe_draws && !P.shares_device) {
+        // the preparation kernel stores this rank's records into every peer's buffer and raises the flags itself
+        // (two handles on ONE device take the separate push: their preparation kernels are cooperative launches
+        // that wait for each other's records, and nothing says both are resident at once)
+        P.slots = slots; ++P.epoch; P.pushed = true;
+        h->fused_push = h->rec.p;
+        rc = tick_peers_locked(h, nullptr, 0);
+        h->fused_push = nullptr;
+    } else {
+        if ((rc = peer_push_locked(h, slots, h->rec.p))) return rc;
+        rc = tick_peers_locked(h, nullptr, 0);
+    }
+    if (rc) return rc;
+    return download(h, out);
 }
 
 int rmb_tick_peers_enqueue(rmb_handle *h)

@@ -386,11 +386,10 @@ int rmb_group_tick(rmb_group *g, int32_t n_tx, const int32_t *src, const double 
     if (g->model == RMB_MODEL_SINR || g->model == RMB_MODEL_UDGM)
         for (int r = 0; r < g->world; ++r) draws = draws || rmb_may_draw(g->h[r]) != 0;
     if (draws) return tick_with_draws(g, n_tx, slots, power_dbm, channel, uniforms, n_uniforms, results);
+    // the shards' calls run side by side on the worker threads: the exchange rides in each tick's first kernel
     return run_all(g, [=](int r) {
-        int rc = rmb_peer_push(g->h[r], slots, g->l_src[r].data(), power_dbm ? g->l_power[r].data() : nullptr,
-                               channel ? g->l_chan[r].data() : nullptr);
-        if (rc) return rc;
-        return rmb_tick_peers(g->h[r], nullptr, 0, &results[r]);
+        return rmb_peer_tick(g->h[r], slots, g->l_src[r].data(), power_dbm ? g->l_power[r].data() : nullptr,
+                             channel ? g->l_chan[r].data() : nullptr, &results[r]);
     });
 }
 

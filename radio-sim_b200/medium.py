@@ -298,6 +298,16 @@ class Medium:
         self._ck(self._lib.rmb_tick_peers(self._h, _ptr(uniforms, C.c_double), 0 if uniforms is None else uniforms.shape[0], C.byref(r)))
         return TickResult(r, self._f64, copy)
 
+    def peer_tick(self, src, power_dbm=None, channel=None, copy=True):
+        """peer_push + tick_peers in one call (the exchange inside the tick's first kernel where the medium allows).
+        Every rank has to be in this call at the same time: one thread or process per handle."""
+        src = _arr(src, np.int32)
+        t = src.shape[0]
+        power_dbm, channel = _arr(power_dbm, np.float64, t), _arr(channel, np.int32, t)
+        r = A.Result()
+        self._ck(self._lib.rmb_peer_tick(self._h, t, _ptr(src, C.c_int32), _ptr(power_dbm, C.c_double), _ptr(channel, C.c_int32), C.byref(r)))
+        return TickResult(r, self._f64, copy)
+
     def tick_peers_resident(self):
         r = A.Result()
         self._ck(self._lib.rmb_tick_peers_resident(self._h, C.byref(r)))

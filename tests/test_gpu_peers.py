@@ -167,3 +167,74 @@ def test_stochastic_reception_on_sharded_receivers_follows_the_global_draw_order
     finally:
         for m in meds:
             m.close()
+
+
+@pytest.mark.parametrize("model", ["sinr", "udgm"])
+def test_peer_tick_one_call_per_rank_from_concurrent_threads(rsb, orc, model):
+    """rmb_peer_tick: push + tick in one call, every rank inside it at the same time (one host thread per handle, as
+    rmb_group_* runs them).  Handles that share a device take the separate push inside the call; mixed with the
+    two-call form in between, pushes and ticks stay in step."""
+    import threading
+    from radio_sim_b200.sharding import shard_bounds, TickPlan, merge_results
+    n, world = 3000, 3
+    x, y, z, ch = random_deployment(43, n, 500.0, channels=2)
+    bounds = shard_bounds(n, world)
+    meds = []
+    for r, (lo, hi) in enumerate(bounds):
+        m = rsb.Medium(model, f64_values=True, rx_base=lo, n_shards=world)
+        m.set_nodes(x[lo:hi], y[lo:hi], z[lo:hi], channel=ch[lo:hi])
+        meds.append(m)
+    blobs = [m.peer_export(world, r, 128) for r, m in enumerate(meds)]
+    for m in meds:
+        m.peer_open(blobs)
+    omodel = orc.MODEL_SINR if model == "sinr" else orc.MODEL_UDGM
+    try:
+        for tick in range(5):
+            t = [90, 40, 0, 120, 7][tick]
+            src = pick_sources(43 + tick, n, t)
+            plan = TickPlan(src, bounds)
+            parts, errors = [None] * world, []
+            if tick == 3:                                   # the two-call form between one-call ticks
+                for r, m in enumerate(meds):
+                    m.peer_push(plan.local_src[r])
+                for r, m in enumerate(meds):
+                    parts[r] = m.tick_peers()
+            else:
+                def run(r):
+                    try:
+                        parts[r] = meds[r].peer_tick(plan.local_src[r])
+                    except Exception as e:                  # noqa: BLE001 - reported below
+                        errors.append((r, e))
+                threads = [threading.Thread(target=run, args=(r,)) for r in range(world)]
+                for th in threads:
+                    th.start()
+                for th in threads:
+                    th.join()
+                assert not errors, errors
+            merged = merge_results(plan, [dict(tx=p.tx, rx=p.rx, outcome=p.outcome, rssi=p.rssi_dbm_f64) for p in parts])
+            full = orc.tick(orc.params(omodel), orc.NodeSet(x, y, z, channel=ch), orc.make_packets(src, 0.0, ch[src]))["pairs"]
+            assert np.array_equal(merged["tx"], full["tx"]) and np.array_equal(merged["rx"], full["rx"])
+            assert np.array_equal(merged["outcome"], full["outcome"]) and np.array_equal(merged["rssi"], full["rssi_dbm"])
+    finally:
+        for m in meds:
+            m.close()
+
+
+def test_peer_tick_fused_form_with_a_world_of_one(rsb, orc):
+    """rmb_peer_tick takes the fused form (records pushed by the tick's first kernel) only when no peer shares the
+    handle's device, so on a one-GPU box it is exercised with a world of one rank, like the enqueued form above; with
+    one GPU per rank it is what bench.py --gpus N times and verifies (digest of the merged lists)."""
+    n = 3000
+    x, y, z, ch = random_deployment(44, n, 500.0)
+    with rsb.Medium("sinr", f64_values=True) as m:
+        m.set_nodes(x, y, z, channel=ch)
+        m.peer_open([m.peer_export(1, 0, 128)])
+        for tick in range(4):
+            src = pick_sources(60 + tick, n, [70, 5, 0, 110][tick])
+            padded = np.concatenate([src[:3], [-1, -1], src[3:]]).astype(np.int32)
+            res = m.peer_tick(padded)
+            full = orc.tick(orc.params(orc.MODEL_SINR), orc.NodeSet(x, y, z, channel=ch), orc.make_packets(src, 0.0, 26))["pairs"]
+            slot_of = np.flatnonzero(padded >= 0)
+            assert res.n_pairs == len(full["tx"])
+            assert np.array_equal(res.tx, slot_of[full["tx"]]) and np.array_equal(res.rx, full["rx"])
+            assert np.array_equal(res.outcome, full["outcome"]) and np.array_equal(res.rssi_dbm_f64, full["rssi_dbm"])
