@@ -67,7 +67,7 @@ def test_static_tick_equals_rmb_tick_on_two_calls_in_a_row():
     from radio_sim_b200 import _abi as A
     lib = A.load()
     # call 1: 5 000 nodes x 300 packets, two channels, some radios off, mixed power, per-packet channel override,
-    # a duplicate source and an out-of-range one (heard by nobody)
+    # a node that sends twice
     n1 = 5000
     x1, y1, z1, ch1 = random_deployment(301, n1, 700.0, channels=2, z_spread=20.0)
     en1 = np.ones(n1, dtype=np.uint8); en1[::17] = 0
